@@ -1,0 +1,515 @@
+// fattn.cu -- (a10-a12) FLASH_ATTN_EXT over an f16 or q8_0 KV cache: split-K flash-decode with online softmax.
+//
+// Replaces flash_attn_vec_ext_f16/f32 + flash_attn_combine_results and (for now also) the wmma prefill kernel of
+// the reference (/root/reference/ggml/src/ggml-cuda/fattn-vec-f16.cuh:8-299, fattn-common.cuh:519-708,
+// fattn-wmma-f16.cuh:13-506).  Semantics follow ggml_compute_forward_flash_attn_ext_f16 (ggml/src/ggml.c:15667-15877).
+//
+// B200 design (HBM-bound at decode: every K/V byte must be read exactly once and >= 40 KB kept in flight per SM):
+//   * grid = (split, kv-head, column tile).  One CTA serves ALL q-heads of a kv-head (GQA) and up to 8 query
+//     columns at once, so K/V rows are fetched once per kv-head instead of once per q-head;
+//   * the KV range of a CTA is walked in 16-row tiles, round-robin over its 4 warps; each warp owns a private
+//     3-deep ring of (K tile, V tile) buffers filled with cp.async (16-byte LDGSTS for f16 rows, 8-byte for the
+//     136-byte q8_0 rows): no CTA-wide barrier inside the KV loop, two tiles always in flight per warp;
+//   * lane (r, j) holds 8 head dims (chunk j) of row-class r; per tile the 16 partial K.Q sums are reduced with a
+//     transposing butterfly (8 shuffles instead of 64); q8_0 K uses int8 Q (quantised like the CPU reference,
+//     quantize_row_q8_0) and dp4a; softmax state and the V accumulator stay in fp32 registers;
+//   * the number of splits is chosen so that #CTAs is a near-multiple of 2 x SM count; the last CTA to finish a
+//     (kv-head, column tile) merges the splits itself (ticket counter), so there is no combine launch.
+#include "b200_common.cuh"
+
+namespace b200 {
+
+constexpr int FA_NW    = 4;   // warps per CTA
+constexpr int FA_NBUF  = 3;   // tiles in the per-warp ring
+constexpr int FA_TP    = 16;  // KV rows per tile
+constexpr int FA_MAXC  = 8;   // query columns per CTA
+constexpr int FA_MAX_SPLITS = 32;
+
+struct FaParams {
+    const unsigned char *q, *k, *v, *mask;
+    float *dst;
+    float *part;       // [pair][split][col][D + 2]
+    int   *tickets;    // [pair]
+    int    D, N, n_head, n_head_kv, n_kv, gqa;
+    int    n_cols;     // N * gqa query columns per kv-head
+    int    n_splits, tiles_per_split;
+    size_t q_nb1, q_nb2, k_nb1, k_nb2, v_nb1, v_nb2, mask_nb1;
+    float  scale, max_bias, softcap, m0, m1;
+    int    n_head_log2;
+};
+
+template <int TYPE, int D>
+struct KvGeo {
+    static constexpr int ROW_BYTES  = TYPE == B200_TYPE_F16 ? D * 2 : D / 32 * Q8_0_BYTES;
+    static constexpr int ROW_STRIDE = TYPE == B200_TYPE_F16 ? ROW_BYTES : (ROW_BYTES + 15) / 16 * 16 + 8;  // q8_0: 8-byte aligned rows, staggered banks
+    static constexpr int TILE_BYTES = (FA_TP * ROW_STRIDE + 16 + 127) / 128 * 128;
+};
+
+// copy a tile of rows [row0, row0+16) of one head into shared memory; rows >= n_kv are zero-filled
+template <int TYPE, int D>
+__device__ __forceinline__ void load_tile(unsigned char *dst, const unsigned char *base, size_t nb1, int row0, int n_kv, int lane) {
+    using G = KvGeo<TYPE, D>;
+    if constexpr (TYPE == B200_TYPE_F16) {
+        constexpr int CPR = G::ROW_BYTES / 16;  // 16-byte chunks per row
+#pragma unroll
+        for (int i = lane; i < FA_TP * CPR; i += 32) {
+            const int r = i / CPR, c = i % CPR;
+            unsigned char *d = dst + r * G::ROW_STRIDE + c * 16;
+            if (row0 + r < n_kv) cp_async16(d, base + (size_t)(row0 + r) * nb1 + c * 16);
+            else *reinterpret_cast<uint4 *>(d) = make_uint4(0, 0, 0, 0);
+        }
+    } else {
+        constexpr int CPR = G::ROW_BYTES / 8;  // 8-byte chunks per row (136 = 17 * 8)
+        for (int i = lane; i < FA_TP * CPR; i += 32) {
+            const int r = i / CPR, c = i % CPR;
+            unsigned char *d = dst + r * G::ROW_STRIDE + c * 8;
+            if (row0 + r < n_kv) cp_async8(d, base + (size_t)(row0 + r) * nb1 + c * 8);
+            else *reinterpret_cast<uint2 *>(d) = make_uint2(0, 0);
+        }
+    }
+}
+
+__device__ __forceinline__ void unpack8(const uint4 &u, float f[8]) {
+    const __half2 *h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const float2 t = __half22float2(h[i]);
+        f[2 * i] = t.x;
+        f[2 * i + 1] = t.y;
+    }
+}
+
+// transposing butterfly: every lane of an LPR-lane group enters with NV = LPR/2 partial sums (one per tile row of
+// its row class) and leaves with the complete sum of row (j >> 1), duplicated in lanes j and j^1.
+template <int LPR>
+__device__ __forceinline__ float butterfly(float (&v)[LPR / 2], int lane) {
+#pragma unroll
+    for (int o = LPR / 2, n = LPR / 2; n >= 2; o >>= 1, n >>= 1) {
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int i = 0; i < n / 2; i++) {
+            const float send = up ? v[i] : v[i + n / 2];
+            const float keep = up ? v[i + n / 2] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+template <int TYPE, int D, int C>
+__global__ void __launch_bounds__(FA_NW * 32, 2) fattn_kernel(const __grid_constant__ FaParams p) {
+    using G = KvGeo<TYPE, D>;
+    constexpr int LPR = D / 8;        // lanes per row (each lane: 8 dims)
+    constexpr int RPW = 32 / LPR;     // rows per warp wave
+    constexpr int NV  = FA_TP / RPW;  // rows per lane per tile == LPR / 2
+    static_assert(NV == LPR / 2, "tile geometry");
+
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = lane % LPR, rsel = lane / LPR;
+    const int split = blockIdx.x, hk = blockIdx.y, ct = blockIdx.z;
+    const int col0 = ct * C;
+    const int ncol = min(C, p.n_cols - col0);
+
+    unsigned char *my_tiles = smem + (size_t)warp * FA_NBUF * 2 * G::TILE_BYTES;
+
+    const int n_tiles = (p.n_kv + FA_TP - 1) / FA_TP;
+    const int t_begin = split * p.tiles_per_split;
+    const int t_end   = min(n_tiles, t_begin + p.tiles_per_split);
+    const unsigned char *kbase = p.k + (size_t)hk * p.k_nb2;
+    const unsigned char *vbase = p.v + (size_t)hk * p.v_nb2;
+
+    // K/V do not depend on the producer kernel in a decode graph only if the cache rows were written earlier;
+    // the current token's row is written by the immediately preceding kernels, so wait first.
+    pdl_wait();
+    pdl_trigger();
+
+    // ---- prologue: start the first tiles
+    int t_issue = t_begin + warp;
+    int ibuf = 0;
+    auto issue = [&]() {
+        if (t_issue < t_end) {
+            unsigned char *kb = my_tiles + (size_t)ibuf * 2 * G::TILE_BYTES;
+            load_tile<TYPE, D>(kb, kbase, p.k_nb1, t_issue * FA_TP, p.n_kv, lane);
+            load_tile<TYPE, D>(kb + G::TILE_BYTES, vbase, p.v_nb1, t_issue * FA_TP, p.n_kv, lane);
+        }
+        cp_async_commit();  // always commit (possibly empty) so the group accounting stays uniform
+        t_issue += FA_NW;
+        ibuf = ibuf + 1 == FA_NBUF ? 0 : ibuf + 1;
+    };
+#pragma unroll
+    for (int s = 0; s < FA_NBUF - 1; s++) issue();
+
+    // ---- Q for this lane: 8 dims x C columns (f16 path: f32 pre-scaled; q8_0 path: int8 + per-32 scale)
+    float qf[C][8];
+    int   qi[C][2];
+    float qd[C];
+    float slope[C];
+    int   col_n[C];
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        const int col = col0 + (c < ncol ? c : 0);
+        const int n = col / p.gqa, g = col % p.gqa;
+        const int h = hk * p.gqa + g;
+        col_n[c] = n;
+        slope[c] = 1.0f;
+        if (p.max_bias > 0.0f) {  // ALiBi, ggml.c:15743-15766
+            slope[c] = h < p.n_head_log2 ? powf(p.m0, (float)(h + 1)) : powf(p.m1, (float)(2 * (h - p.n_head_log2) + 1));
+        }
+        const float *qrow = reinterpret_cast<const float *>(p.q + (size_t)n * p.q_nb1 + (size_t)h * p.q_nb2) + 8 * j;
+        const float4 a = *reinterpret_cast<const float4 *>(qrow), b = *reinterpret_cast<const float4 *>(qrow + 4);
+        const float x[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        if constexpr (TYPE == B200_TYPE_F16) {
+            // the CPU reference rounds Q to f16 before the dot (ggml.c:15788, vec_dot_type of an f16 K is f16)
+#pragma unroll
+            for (int i = 0; i < 8; i++) qf[c][i] = __half2float(__float2half_rn(x[i]));
+        } else {
+            // quantize_row_q8_0_ref on the 32-dim block this lane belongs to (4 lanes per block)
+            float amax = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; i++) amax = fmaxf(amax, fabsf(x[i]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+            const float d  = __fdiv_rn(amax, 127.0f);
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            int q[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) q[i] = (int)roundf(__fmul_rn(x[i], id)) & 0xff;
+            qi[c][0] = q[0] | (q[1] << 8) | (q[2] << 16) | (q[3] << 24);
+            qi[c][1] = q[4] | (q[5] << 8) | (q[6] << 16) | (q[7] << 24);
+            qd[c] = __half2float(__float2half_rn(d));
+        }
+    }
+    float scale = p.scale;
+    if (p.softcap != 0.0f) scale /= p.softcap;
+
+    float m[C], l[C], acc[C][8];
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        m[c] = -INFINITY;
+        l[c] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; i++) acc[c][i] = 0.f;
+    }
+
+    // ---- main loop over this warp's tiles
+    int cbuf = 0;
+    for (int t = t_begin + warp; t < t_end; t += FA_NW) {
+        issue();
+        cp_async_wait<FA_NBUF - 1>();
+        __syncwarp();
+        const unsigned char *kt = my_tiles + (size_t)cbuf * 2 * G::TILE_BYTES;
+        const unsigned char *vt = kt + G::TILE_BYTES;
+
+        // scores: partial sums for this lane's NV rows
+        float s[C][NV];
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            const int r = i * RPW + rsel;
+            if constexpr (TYPE == B200_TYPE_F16) {
+                float kf[8];
+                unpack8(*reinterpret_cast<const uint4 *>(kt + r * G::ROW_STRIDE + 16 * j), kf);
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    float a = 0.f;
+#pragma unroll
+                    for (int e = 0; e < 8; e++) a = fmaf(kf[e], qf[c][e], a);
+                    s[c][i] = a;
+                }
+            } else {
+                const unsigned char *blk = kt + r * G::ROW_STRIDE + (j >> 2) * Q8_0_BYTES;
+                const float dk = h2f(*reinterpret_cast<const unsigned short *>(blk));
+                const unsigned *w2 = reinterpret_cast<const unsigned *>(blk + 2 + 8 * (j & 3) - ((j >> 2) & 1 ? 0 : 2));
+                // blk + 2 + 8*(j&3) is 4-byte aligned for odd blocks, 2 mod 4 for even blocks (rows are 8-byte aligned)
+                unsigned w0, w1;
+                if ((j >> 2) & 1) { w0 = w2[0]; w1 = w2[1]; }
+                else { w0 = __funnelshift_r(w2[0], w2[1], 16); w1 = __funnelshift_r(w2[1], w2[2], 16); }
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    const int si = dp4a((int)w1, qi[c][1], dp4a((int)w0, qi[c][0], 0));
+                    s[c][i] = (float)si * (dk * qd[c]);
+                }
+            }
+        }
+        const int my_row = t * FA_TP + (j >> 1) * RPW + rsel;  // the row whose full score this lane ends up with
+        float pr[C];
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+            float sc = butterfly<LPR>(s[c], lane) * scale;
+            if (p.softcap != 0.0f) sc = p.softcap * tanhf(sc);
+            float mv = 0.f;
+            if (p.mask != nullptr && my_row < p.n_kv) {
+                mv = slope[c] * __half2float(*reinterpret_cast<const __half *>(p.mask + (size_t)col_n[c] * p.mask_nb1 + 2 * (size_t)my_row));
+            }
+            sc = my_row < p.n_kv ? sc + mv : -INFINITY;
+            const float tmax = warp_max(sc);
+            const float mn = fmaxf(m[c], tmax);
+            const float alpha = mn == -INFINITY ? 1.0f : __expf(m[c] - mn);
+            const float pv = mn == -INFINITY ? 0.0f : __expf(sc - mn);
+            const float psum = warp_sum((j & 1) ? 0.f : pv);  // every row score is held by two lanes
+            l[c] = l[c] * alpha + psum;
+            m[c] = mn;
+            pr[c] = pv;
+#pragma unroll
+            for (int e = 0; e < 8; e++) acc[c][e] *= alpha;
+        }
+        // P.V: lane accumulates its 8 dims over its NV rows
+#pragma unroll
+        for (int i = 0; i < NV; i++) {
+            const int r = i * RPW + rsel;
+            float vf[8];
+            if constexpr (TYPE == B200_TYPE_F16) {
+                unpack8(*reinterpret_cast<const uint4 *>(vt + r * G::ROW_STRIDE + 16 * j), vf);
+            } else {
+                const unsigned char *blk = vt + r * G::ROW_STRIDE + (j >> 2) * Q8_0_BYTES;
+                const float dv = h2f(*reinterpret_cast<const unsigned short *>(blk));
+                const unsigned *w2 = reinterpret_cast<const unsigned *>(blk + 2 + 8 * (j & 3) - ((j >> 2) & 1 ? 0 : 2));
+                unsigned w0, w1;
+                if ((j >> 2) & 1) { w0 = w2[0]; w1 = w2[1]; }
+                else { w0 = __funnelshift_r(w2[0], w2[1], 16); w1 = __funnelshift_r(w2[1], w2[2], 16); }
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    vf[e]     = dv * (float)(signed char)((w0 >> (8 * e)) & 0xff);
+                    vf[4 + e] = dv * (float)(signed char)((w1 >> (8 * e)) & 0xff);
+                }
+            }
+#pragma unroll
+            for (int c = 0; c < C; c++) {
+                const float pw = __shfl_sync(0xffffffffu, pr[c], rsel * LPR + 2 * i);
+#pragma unroll
+                for (int e = 0; e < 8; e++) acc[c][e] = fmaf(pw, vf[e], acc[c][e]);
+            }
+        }
+        __syncwarp();  // all lanes are done with this buffer before it is refilled two iterations from now
+        cbuf = cbuf + 1 == FA_NBUF ? 0 : cbuf + 1;
+    }
+    cp_async_wait<0>();
+
+    // ---- merge the row classes inside the warp (lanes with equal j hold disjoint rows)
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+#pragma unroll
+        for (int o = LPR; o < 32; o <<= 1) {
+#pragma unroll
+            for (int e = 0; e < 8; e++) acc[c][e] += __shfl_xor_sync(0xffffffffu, acc[c][e], o);
+        }
+    }
+    // ---- merge the warps of the CTA through shared memory (reuse the tile ring)
+    __syncthreads();
+    float *red = reinterpret_cast<float *>(smem);  // [warp][c][D + 2]
+    constexpr int RS = D + 2;
+    if (rsel == 0) {
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+            float *o = red + ((size_t)warp * C + c) * RS;
+#pragma unroll
+            for (int e = 0; e < 8; e++) o[8 * j + e] = acc[c][e];
+            if (j == 0) { o[D] = m[c]; o[D + 1] = l[c]; }
+        }
+    }
+    __syncthreads();
+    const int pair = (ct * p.n_head_kv + hk);
+    float *part = p.part + ((size_t)pair * p.n_splits + split) * C * RS;
+    for (int idx = threadIdx.x; idx < C * D; idx += FA_NW * 32) {
+        const int c = idx / D, d = idx % D;
+        float M = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < FA_NW; w++) M = fmaxf(M, red[((size_t)w * C + c) * RS + D]);
+        float a = 0.f, L = 0.f;
+#pragma unroll
+        for (int w = 0; w < FA_NW; w++) {
+            const float *o = red + ((size_t)w * C + c) * RS;
+            const float f = o[D] == -INFINITY ? 0.f : __expf(o[D] - M);
+            a += f * o[d];
+            L += f * o[D + 1];
+        }
+        if (p.n_splits == 1) {
+            if (c < ncol) {
+                const int col = col0 + c, n = col / p.gqa, h = hk * p.gqa + col % p.gqa;
+                p.dst[((size_t)n * p.n_head + h) * D + d] = a / L;
+            }
+        } else {
+            part[(size_t)c * RS + d] = a;
+            if (d == 0) { part[(size_t)c * RS + D] = M; part[(size_t)c * RS + D + 1] = L; }
+        }
+    }
+    if (p.n_splits == 1) return;
+
+    // ---- split-K merge by the last CTA of this (kv-head, column tile)
+    __shared__ int is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const int tk = atomicAdd(&p.tickets[pair], 1);
+        is_last = tk == p.n_splits - 1;
+        if (is_last) p.tickets[pair] = 0;  // leave the counter ready for the next launch
+    }
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    const float *all = p.part + (size_t)pair * p.n_splits * C * RS;
+    for (int idx = threadIdx.x; idx < ncol * D; idx += FA_NW * 32) {
+        const int c = idx / D, d = idx % D;
+        float M = -INFINITY;
+        for (int s2 = 0; s2 < p.n_splits; s2++) M = fmaxf(M, __ldcg(all + ((size_t)s2 * C + c) * RS + D));
+        float a = 0.f, L = 0.f;
+        for (int s2 = 0; s2 < p.n_splits; s2++) {
+            const float *o = all + ((size_t)s2 * C + c) * RS;
+            const float ms = __ldcg(o + D);
+            const float f = ms == -INFINITY ? 0.f : __expf(ms - M);
+            a += f * __ldcg(o + d);
+            L += f * __ldcg(o + D + 1);
+        }
+        const int col = col0 + c, n = col / p.gqa, h = hk * p.gqa + col % p.gqa;
+        p.dst[((size_t)n * p.n_head + h) * D + d] = a / L;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+struct FaPlan {
+    int C, n_ct, n_splits, tiles_per_split;
+    size_t part_bytes, ticket_bytes;
+};
+
+static int fa_sm_count() {
+    static int sm = 0;
+    if (!sm) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+            cudaGetLastError();
+            sm = 148;
+        }
+    }
+    return sm;
+}
+
+static FaPlan fa_plan(const b200_fattn_args *a) {
+    FaPlan pl;
+    const int64_t n_cols = a->N * (a->n_head / a->n_head_kv);
+    pl.C = n_cols >= 8 ? 8 : n_cols >= 4 ? 4 : n_cols >= 2 ? 2 : 1;
+    if (n_cols == 3) pl.C = 4;
+    if (n_cols > 4 && n_cols < 8) pl.C = 8;
+    pl.n_ct = (int)((n_cols + pl.C - 1) / pl.C);
+    const int n_tiles = (int)((a->n_kv + FA_TP - 1) / FA_TP);
+    const int64_t pairs = (int64_t)pl.n_ct * a->n_head_kv;
+    const int slots = 2 * fa_sm_count();
+    // choose the split count that minimises (waves x tiles per split), i.e. the length of the critical path;
+    // every warp should still see >= 2 tiles; ties go to fewer splits (less merge traffic)
+    int best = 1;
+    int64_t best_cost = -1;
+    for (int s = 1; s <= FA_MAX_SPLITS; s++) {
+        const int tps = (n_tiles + s - 1) / s;
+        if (s > 1 && tps < 2 * FA_NW) break;
+        if ((int64_t)(s - 1) * tps >= n_tiles) continue;  // would leave an empty split
+        const int64_t ctas = pairs * s;
+        const int64_t waves = (ctas + slots - 1) / slots;
+        const int64_t cost = waves * tps;
+        if (best_cost < 0 || cost * 100 < best_cost * 97) { best = s; best_cost = cost; }
+    }
+    pl.n_splits = best;
+    pl.tiles_per_split = (n_tiles + best - 1) / best;
+    pl.ticket_bytes = ((size_t)pairs * sizeof(int) + 255) / 256 * 256;
+    pl.part_bytes = best > 1 ? (size_t)pairs * best * pl.C * (a->D + 2) * sizeof(float) : 0;
+    return pl;
+}
+
+template <int TYPE, int D, int C>
+static int fa_launch(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
+    using G = KvGeo<TYPE, D>;
+    size_t smem = (size_t)FA_NW * FA_NBUF * 2 * G::TILE_BYTES;
+    const size_t red = (size_t)FA_NW * C * (D + 2) * sizeof(float);
+    if (red > smem) smem = red;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_kernel<TYPE, D, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl.n_splits, (unsigned)p.n_head_kv, (unsigned)pl.n_ct);
+    cfg.blockDim = dim3(FA_NW * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fattn_kernel<TYPE, D, C>, p));
+    return B200_OK;
+}
+
+template <int TYPE, int D>
+static int fa_dispatch_c(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
+    switch (pl.C) {
+        case 1: return fa_launch<TYPE, D, 1>(p, pl, st, pdl);
+        case 2: return fa_launch<TYPE, D, 2>(p, pl, st, pdl);
+        case 4: return fa_launch<TYPE, D, 4>(p, pl, st, pdl);
+        case 8: return fa_launch<TYPE, D, 8>(p, pl, st, pdl);
+    }
+    return B200_ERR_INVALID;
+}
+
+extern bool g_mmvq_pdl;
+
+static int fa_check(const b200_fattn_args *a) {
+    if (!a || !a->q || !a->k || !a->v || !a->dst) { set_error("b200_flash_attn_ext: NULL argument"); return B200_ERR_INVALID; }
+    if (a->D != 64 && a->D != 128) { set_error("b200_flash_attn_ext: head size %lld not supported (64, 128)", (long long)a->D); return B200_ERR_UNSUPPORTED; }
+    if (a->type_k != a->type_v || (a->type_k != B200_TYPE_F16 && a->type_k != B200_TYPE_Q8_0)) {
+        set_error("b200_flash_attn_ext: K/V types (%d, %d) not supported (f16/f16, q8_0/q8_0)", a->type_k, a->type_v);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (a->n_head_kv <= 0 || a->n_head % a->n_head_kv || a->N <= 0 || a->n_kv <= 0) { set_error("b200_flash_attn_ext: bad shape"); return B200_ERR_INVALID; }
+    const int align = a->type_k == B200_TYPE_F16 ? 16 : 8;
+    if (((uintptr_t)a->k | (uintptr_t)a->v | a->k_nb1 | a->k_nb2 | a->v_nb1 | a->v_nb2) & (align - 1)) {
+        set_error("b200_flash_attn_ext: K/V pointers and strides must be %d-byte aligned", align);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (((uintptr_t)a->q | a->q_nb1 | a->q_nb2) & 15) { set_error("b200_flash_attn_ext: Q must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
+    if (a->n_head_kv > 65535 || a->N * (a->n_head / a->n_head_kv) > 8 * 65535) { set_error("b200_flash_attn_ext: grid too large"); return B200_ERR_UNSUPPORTED; }
+    return B200_OK;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" size_t b200_flash_attn_workspace_bytes(const b200_fattn_args *a) {
+    if (fa_check(a) != B200_OK) return 0;
+    const FaPlan pl = fa_plan(a);
+    return pl.ticket_bytes + pl.part_bytes;
+}
+
+// The first ticket_bytes of the workspace are split-K arrival counters: they must be zero on entry and are left
+// zero on exit (the backend zeroes its workspace once, at allocation).
+extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, size_t workspace_bytes, b200_stream_t stream) {
+    int rc = fa_check(a);
+    if (rc) return rc;
+    const FaPlan pl = fa_plan(a);
+    if (pl.n_splits > 1 && (!workspace || workspace_bytes < pl.ticket_bytes + pl.part_bytes)) {
+        set_error("b200_flash_attn_ext: workspace too small (%zu < %zu)", workspace_bytes, pl.ticket_bytes + pl.part_bytes);
+        return B200_ERR_INVALID;
+    }
+    FaParams p = {};
+    p.q = (const unsigned char *)a->q; p.k = (const unsigned char *)a->k; p.v = (const unsigned char *)a->v;
+    p.mask = (const unsigned char *)a->mask;
+    p.dst = a->dst;
+    p.tickets = (int *)workspace;
+    p.part = workspace ? (float *)((unsigned char *)workspace + pl.ticket_bytes) : nullptr;
+    p.D = (int)a->D; p.N = (int)a->N; p.n_head = (int)a->n_head; p.n_head_kv = (int)a->n_head_kv; p.n_kv = (int)a->n_kv;
+    p.gqa = (int)(a->n_head / a->n_head_kv);
+    p.n_cols = p.N * p.gqa;
+    p.n_splits = pl.n_splits; p.tiles_per_split = pl.tiles_per_split;
+    p.q_nb1 = a->q_nb1; p.q_nb2 = a->q_nb2; p.k_nb1 = a->k_nb1; p.k_nb2 = a->k_nb2; p.v_nb1 = a->v_nb1; p.v_nb2 = a->v_nb2;
+    p.mask_nb1 = a->mask_nb1;
+    p.scale = a->scale; p.max_bias = a->max_bias; p.softcap = a->logit_softcap;
+    p.n_head_log2 = 1;
+    while (p.n_head_log2 * 2 <= p.n_head) p.n_head_log2 *= 2;
+    p.m0 = powf(2.0f, -(a->max_bias) / p.n_head_log2);
+    p.m1 = powf(2.0f, -(a->max_bias / 2.0f) / p.n_head_log2);
+    const cudaStream_t st = (cudaStream_t)stream;
+    const bool pdl = g_mmvq_pdl;
+    if (a->type_k == B200_TYPE_F16) {
+        return a->D == 128 ? fa_dispatch_c<B200_TYPE_F16, 128>(p, pl, st, pdl) : fa_dispatch_c<B200_TYPE_F16, 64>(p, pl, st, pdl);
+    }
+    return a->D == 128 ? fa_dispatch_c<B200_TYPE_Q8_0, 128>(p, pl, st, pdl) : fa_dispatch_c<B200_TYPE_Q8_0, 64>(p, pl, st, pdl);
+}

@@ -1,0 +1,682 @@
+// mmvq.cu -- (a6, a9) decode GEMV over GGUF block formats: dst[n][m] = W[m][:] . X[n][:], N <= 8,
+// plus the expert-indexed (MUL_MAT_ID) and multi-matrix (fused Q/K/V, gate/up) forms.
+//
+// Replaces the reference's quantize_q8_1 + mul_mat_vec_q<type,ncols_y> pair
+// (/root/reference/ggml/src/ggml-cuda/quantize.cu:4-38, mmvq.cu:50-202, vecdotq.cuh:23-787) and, for MUL_MAT_ID,
+// the host round trip in ggml_cuda_mul_mat_id (ggml-cuda.cu:2003-2139).
+//
+// B200 design (HBM-bound: the job is to keep >= ~40 KB of weight bytes in flight per SM and never touch a byte twice):
+//   * one persistent CTA per SM; CTA c owns a contiguous, byte-balanced range of the (concatenated) weight rows;
+//   * every warp streams whole rows through its OWN ring of shared-memory stages filled by the TMA engine with
+//     1-D bulk copies (cp.async.bulk ... mbarrier::complete_tx, SASS UBLKCP): the raw 144/176/210/34/18-byte blocks
+//     land in shared memory untouched, so no lane ever issues a misaligned or sub-32-bit global load, and no
+//     registers or LSU slots are spent on in-flight data.  Stage reuse is warp-private: no CTA barrier in the loop;
+//   * the f32 activation row(s) are quantised to q8_1 by the CTA itself while the first weight stages are in flight
+//     (same arithmetic as quantize_row_q8_1_ref) and kept in shared memory in a lane-major layout so every
+//     activation read is a conflict-free LDS.128;
+//   * a lane handles one 128-weight slice per step: K-quant 6-bit scales/mins are unpacked in registers, nibbles are
+//     split with two LOP3s per word and contracted with dp4a against the int8 activations; the q4_K/q5_K "min"
+//     term and the q4_0 "-8" offset use the q8_1 block sums, the q6_K "-32" offset uses 16-wide integer sums;
+//   * weight streaming starts BEFORE griddepcontrol.wait, so under programmatic dependent launch the ramp-up of
+//     this kernel overlaps the tail of its producer.
+#include "b200_common.cuh"
+
+#include <cstdio>
+
+namespace b200 {
+
+constexpr int MMVQ_NW        = 16;                 // warps per CTA
+constexpr int MMVQ_THREADS   = MMVQ_NW * 32;
+constexpr int MMVQ_MAX_STAGE = 8;
+constexpr int MMVQ_BAR_BYTES = 128 * ((MMVQ_NW * MMVQ_MAX_STAGE * 8 + 127) / 128);
+
+struct MmvqParams {
+    b200_gemv_job  jobs[B200_GEMV_MAX_JOBS];
+    int            n_jobs;
+    int            n_stage;
+    int            n_it;          // ceil(K / 4096): steps per row
+    int            n_expert;
+    int64_t        K;
+    int64_t        total_rows;
+    size_t         w_row_bytes;   // row stride
+    unsigned       row_bytes;     // payload bytes of one row
+    int64_t        x_stride, dst_stride;
+    const int32_t *ids;
+    size_t         expert_bytes;
+};
+
+template <int TYPE>
+struct Geo {
+    static constexpr int SLICE_BYTES = type_slice_bytes(TYPE);          // 128 weights
+    static constexpr int SEG_BYTES   = SLICE_BYTES * 32;               // 4096 weights: one warp step
+    static constexpr int STAGE_BYTES = ((SEG_BYTES + 32 + 15) / 16) * 16;  // head misalignment (<16) + word over-read slack
+};
+
+// per-column activation storage for n_it steps: qs [it][8][32] int4, d [it][32] float4, s [it][32] float4, g [it][32] int4
+__host__ __device__ constexpr int act_col_bytes(int n_it) { return n_it * (4096 + 3 * 512); }
+
+struct ActView {
+    const int4   *q;
+    const float4 *d, *s;
+    const int4   *g;
+};
+__device__ __forceinline__ ActView act_view(unsigned char *base, int n_it, int col) {
+    unsigned char *p = base + (size_t)col * act_col_bytes(n_it);
+    ActView v;
+    v.q = (const int4 *)p;
+    v.d = (const float4 *)(p + (size_t)n_it * 4096);
+    v.s = (const float4 *)(p + (size_t)n_it * (4096 + 512));
+    v.g = (const int4 *)(p + (size_t)n_it * (4096 + 1024));
+    return v;
+}
+
+// Quantise X[n][0..K) (f32, global) into the CTA's shared activation store.  All threads of the CTA call this.
+template <int NCOLS>
+__device__ void load_activations(unsigned char *act_base, const float *__restrict__ X, int64_t x_stride, int64_t K, int n_it) {
+    const int n4 = (int)(K / 4);
+    for (int n = 0; n < NCOLS; n++) {
+        unsigned char *p = act_base + (size_t)n * act_col_bytes(n_it);
+        int   *aq = (int *)p;
+        float *ad = (float *)(p + (size_t)n_it * 4096);
+        float *as = (float *)(p + (size_t)n_it * (4096 + 512));
+        int   *ag = (int *)(p + (size_t)n_it * (4096 + 1024));
+        const float *x = X + (int64_t)n * x_stride;
+        for (int base = 0; base < n4; base += MMVQ_THREADS) {
+            const int i4 = base + threadIdx.x;
+            const bool active = i4 < n4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (active) v = __ldg(reinterpret_cast<const float4 *>(x) + i4);
+            float d, s;
+            int sum4;
+            const int packed = quantize_q8_1_group8(v, d, s, sum4);
+            const int hi4 = __shfl_xor_sync(0xffffffffu, sum4, 4);
+            if (active) {
+                const int blk = i4 >> 3, part = i4 & 7;
+                const int slice = blk >> 2, b = blk & 3;
+                const int it = slice >> 5, lane = slice & 31;
+                const int j = b * 2 + (part >> 2);
+                aq[(((it * 8 + j) * 32 + lane) << 2) + (part & 3)] = packed;
+                if (part == 0) {
+                    const int o = ((it * 32 + lane) << 2) + b;
+                    ad[o] = d;
+                    as[o] = s;
+                    ag[o] = (sum4 & 0xffff) | (hi4 << 16);  // 16-wide integer sums (q6_K offset term)
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ per-type slice dot
+// Each returns, for every column, the contribution of this lane's 128-weight slice.
+template <int TYPE, int NCOLS>
+struct SliceDot;
+
+// ---- Q4_K: half a super-block per lane.  block: half d, half dmin, u8 scales[12], u8 qs[128]  (ggml-common.h:286-298)
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q4_K, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * Q4_K_BYTES;
+        const int h = lane & 1;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(b);
+        const float d = h2f((unsigned short)(hdr.x & 0xffff)), dmin = h2f((unsigned short)(hdr.x >> 16));
+        unsigned scw, mnw;  // 4 scales / 4 mins of sub-blocks 4h..4h+3, one per byte (get_scale_min_k4)
+        if (h == 0) {
+            scw = hdr.y & 0x3f3f3f3fu;
+            mnw = hdr.z & 0x3f3f3f3fu;
+        } else {
+            scw = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+            mnw = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+        }
+        const uint4 *qp = reinterpret_cast<const uint4 *>(b + 16 + 64 * h);
+        unsigned v[16];
+        *reinterpret_cast<uint4 *>(v + 0)  = qp[0];
+        *reinterpret_cast<uint4 *>(v + 4)  = qp[1];
+        *reinterpret_cast<uint4 *>(v + 8)  = qp[2];
+        *reinterpret_cast<uint4 *>(v + 12) = qp[3];
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            int sumi[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int cc = 0; cc < 2; cc++) {       // 64-value chunk: low nibbles -> sub-block 2cc, high -> 2cc+1
+#pragma unroll
+                for (int hq = 0; hq < 2; hq++) {   // which 16 bytes of the chunk
+                    const int4 ulo = a.q[((it * 8 + (2 * cc) * 2 + hq) * 32) + lane];
+                    const int4 uhi = a.q[((it * 8 + (2 * cc + 1) * 2 + hq) * 32) + lane];
+                    const unsigned *w = v + 8 * cc + 4 * hq;
+                    sumi[2 * cc]     = dp4a((int)(w[0] & 0x0f0f0f0fu), ulo.x, sumi[2 * cc]);
+                    sumi[2 * cc]     = dp4a((int)(w[1] & 0x0f0f0f0fu), ulo.y, sumi[2 * cc]);
+                    sumi[2 * cc]     = dp4a((int)(w[2] & 0x0f0f0f0fu), ulo.z, sumi[2 * cc]);
+                    sumi[2 * cc]     = dp4a((int)(w[3] & 0x0f0f0f0fu), ulo.w, sumi[2 * cc]);
+                    sumi[2 * cc + 1] = dp4a((int)((w[0] >> 4) & 0x0f0f0f0fu), uhi.x, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a((int)((w[1] >> 4) & 0x0f0f0f0fu), uhi.y, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a((int)((w[2] >> 4) & 0x0f0f0f0fu), uhi.z, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a((int)((w[3] >> 4) & 0x0f0f0f0fu), uhi.w, sumi[2 * cc + 1]);
+                }
+            }
+            const float4 d8 = a.d[it * 32 + lane], s8 = a.s[it * 32 + lane];
+            const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
+                             d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
+            const float sm = s8.x * (float)(mnw & 0xff) + s8.y * (float)((mnw >> 8) & 0xff) + s8.z * (float)((mnw >> 16) & 0xff) +
+                             s8.w * (float)(mnw >> 24);
+            acc[n] += d * sd - dmin * sm;
+        }
+    }
+};
+
+// ---- Q5_K: half d, half dmin, u8 scales[12], u8 qh[32], u8 qs[128]  (ggml-common.h:303-316)
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q5_K, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * Q5_K_BYTES;
+        const int h = lane & 1;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(b);
+        const float d = h2f((unsigned short)(hdr.x & 0xffff)), dmin = h2f((unsigned short)(hdr.x >> 16));
+        unsigned scw, mnw;
+        if (h == 0) {
+            scw = hdr.y & 0x3f3f3f3fu;
+            mnw = hdr.z & 0x3f3f3f3fu;
+        } else {
+            scw = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+            mnw = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+        }
+        unsigned qh[8], v[16];
+        *reinterpret_cast<uint4 *>(qh + 0) = *reinterpret_cast<const uint4 *>(b + 16);
+        *reinterpret_cast<uint4 *>(qh + 4) = *reinterpret_cast<const uint4 *>(b + 32);
+        const uint4 *qp = reinterpret_cast<const uint4 *>(b + 48 + 64 * h);
+        *reinterpret_cast<uint4 *>(v + 0)  = qp[0];
+        *reinterpret_cast<uint4 *>(v + 4)  = qp[1];
+        *reinterpret_cast<uint4 *>(v + 8)  = qp[2];
+        *reinterpret_cast<uint4 *>(v + 12) = qp[3];
+        // 5-bit values: sub-block sb = 4h + 2cc + {0: low nibble, 1: high nibble}; fifth bit = bit sb of qh[l] (ggml-quants.c:2783-2786)
+        unsigned q5[4][8];
+#pragma unroll
+        for (int cc = 0; cc < 2; cc++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const unsigned w = v[8 * cc + i], hb = qh[i] >> (4 * h + 2 * cc);
+                q5[2 * cc][i]     = (w & 0x0f0f0f0fu) | ((hb << 4) & 0x10101010u);
+                q5[2 * cc + 1][i] = ((w >> 4) & 0x0f0f0f0fu) | ((hb << 3) & 0x10101010u);
+            }
+        }
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            int sumi[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int sb = 0; sb < 4; sb++) {
+#pragma unroll
+                for (int hq = 0; hq < 2; hq++) {
+                    const int4 u = a.q[((it * 8 + sb * 2 + hq) * 32) + lane];
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 0], u.x, sumi[sb]);
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 1], u.y, sumi[sb]);
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 2], u.z, sumi[sb]);
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 3], u.w, sumi[sb]);
+                }
+            }
+            const float4 d8 = a.d[it * 32 + lane], s8 = a.s[it * 32 + lane];
+            const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
+                             d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
+            const float sm = s8.x * (float)(mnw & 0xff) + s8.y * (float)((mnw >> 8) & 0xff) + s8.z * (float)((mnw >> 16) & 0xff) +
+                             s8.w * (float)(mnw >> 24);
+            acc[n] += d * sd - dmin * sm;
+        }
+    }
+};
+
+// consecutive 32-bit words from a shared-memory byte run that is only 2-byte aligned
+template <int NW>
+__device__ __forceinline__ void lds_words(const unsigned char *p, unsigned (&out)[NW]) {
+    const unsigned *w = reinterpret_cast<const unsigned *>((uintptr_t)p & ~(uintptr_t)3);
+    const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
+    unsigned prev = w[0];
+#pragma unroll
+    for (int i = 0; i < NW; i++) {
+        const unsigned nxt = w[i + 1];  // one word of over-read at most: stages carry 16 bytes of slack
+        out[i] = __funnelshift_r(prev, nxt, sh);
+        prev = nxt;
+    }
+}
+
+// ---- Q6_K: u8 ql[128], u8 qh[64], i8 scales[16], half d  (ggml-common.h:321-327); 210 bytes => 2-byte aligned
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q6_K, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * Q6_K_BYTES;
+        const int h = lane & 1;
+        unsigned ql[16], qh[8], scw[2];
+        lds_words<16>(b + 64 * h, ql);
+        lds_words<8>(b + 128 + 32 * h, qh);
+        lds_words<2>(b + 192 + 8 * h, scw);
+        const float d = h2f(*reinterpret_cast<const unsigned short *>(b + 208));
+        // q[r][i]: 4 values of row-group r (= q8_1 block r of this slice), word i (ggml-quants.c:2990-2999)
+        unsigned q[4][8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const unsigned l0 = ql[i], l1 = ql[8 + i], hb = qh[i];
+            q[0][i] = (l0 & 0x0f0f0f0fu) | ((hb << 4) & 0x30303030u);
+            q[1][i] = (l1 & 0x0f0f0f0fu) | ((hb << 2) & 0x30303030u);
+            q[2][i] = ((l0 >> 4) & 0x0f0f0f0fu) | (hb & 0x30303030u);
+            q[3][i] = ((l1 >> 4) & 0x0f0f0f0fu) | ((hb >> 2) & 0x30303030u);
+        }
+        const signed char *sc = reinterpret_cast<const signed char *>(scw);
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            const float4 d8 = a.d[it * 32 + lane];
+            const int4 g = a.g[it * 32 + lane];
+            const float d8v[4] = {d8.x, d8.y, d8.z, d8.w};
+            const int gv[4] = {g.x, g.y, g.z, g.w};
+            float sd = 0.f;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int4 u0 = a.q[((it * 8 + r * 2 + 0) * 32) + lane];
+                const int4 u1 = a.q[((it * 8 + r * 2 + 1) * 32) + lane];
+                int s0 = dp4a((int)q[r][0], u0.x, 0);
+                s0 = dp4a((int)q[r][1], u0.y, s0);
+                s0 = dp4a((int)q[r][2], u0.z, s0);
+                s0 = dp4a((int)q[r][3], u0.w, s0);
+                int s1 = dp4a((int)q[r][4], u1.x, 0);
+                s1 = dp4a((int)q[r][5], u1.y, s1);
+                s1 = dp4a((int)q[r][6], u1.z, s1);
+                s1 = dp4a((int)q[r][7], u1.w, s1);
+                // stored values are q+32: subtract 32 * (sum of the 16 activations of the group)
+                s0 -= 32 * (int)(short)(gv[r] & 0xffff);
+                s1 -= 32 * (gv[r] >> 16);
+                sd += d8v[r] * (float)(s0 * (int)sc[2 * r] + s1 * (int)sc[2 * r + 1]);
+            }
+            acc[n] += d * sd;
+        }
+    }
+};
+
+// ---- Q8_0: half d, i8 qs[32] (ggml-common.h:186-191); 4 blocks (136 bytes) per lane
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q8_0, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int nblk, float acc[NCOLS]) {
+        const unsigned char *b = seg + lane * (4 * Q8_0_BYTES);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+                const unsigned char *bk = b + k * Q8_0_BYTES;
+                const float d = h2f(*reinterpret_cast<const unsigned short *>(bk));
+                unsigned w[8];
+                lds_words<8>(bk + 2, w);
+#pragma unroll
+                for (int n = 0; n < NCOLS; n++) {
+                    const ActView a = act_view(act_base, n_it, n);
+                    const int4 u0 = a.q[((it * 8 + k * 2 + 0) * 32) + lane];
+                    const int4 u1 = a.q[((it * 8 + k * 2 + 1) * 32) + lane];
+                    int s = dp4a((int)w[0], u0.x, 0);
+                    s = dp4a((int)w[1], u0.y, s);
+                    s = dp4a((int)w[2], u0.z, s);
+                    s = dp4a((int)w[3], u0.w, s);
+                    s = dp4a((int)w[4], u1.x, s);
+                    s = dp4a((int)w[5], u1.y, s);
+                    s = dp4a((int)w[6], u1.z, s);
+                    s = dp4a((int)w[7], u1.w, s);
+                    const float d8 = reinterpret_cast<const float *>(a.d)[((it * 32 + lane) << 2) + k];
+                    acc[n] += d * d8 * (float)s;
+                }
+            }
+        }
+    }
+};
+
+// ---- Q4_0: half d, u8 qs[16] (ggml-common.h:144-149); values 0..15 in low nibbles, 16..31 in high nibbles; 4 blocks (72 B) per lane
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int nblk, float acc[NCOLS]) {
+        const unsigned char *b = seg + lane * (4 * Q4_0_BYTES);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+                const unsigned char *bk = b + k * Q4_0_BYTES;
+                const float d = h2f(*reinterpret_cast<const unsigned short *>(bk));
+                unsigned w[4];
+                lds_words<4>(bk + 2, w);
+#pragma unroll
+                for (int n = 0; n < NCOLS; n++) {
+                    const ActView a = act_view(act_base, n_it, n);
+                    const int4 u0 = a.q[((it * 8 + k * 2 + 0) * 32) + lane];
+                    const int4 u1 = a.q[((it * 8 + k * 2 + 1) * 32) + lane];
+                    int s = dp4a((int)(w[0] & 0x0f0f0f0fu), u0.x, 0);
+                    s = dp4a((int)(w[1] & 0x0f0f0f0fu), u0.y, s);
+                    s = dp4a((int)(w[2] & 0x0f0f0f0fu), u0.z, s);
+                    s = dp4a((int)(w[3] & 0x0f0f0f0fu), u0.w, s);
+                    s = dp4a((int)((w[0] >> 4) & 0x0f0f0f0fu), u1.x, s);
+                    s = dp4a((int)((w[1] >> 4) & 0x0f0f0f0fu), u1.y, s);
+                    s = dp4a((int)((w[2] >> 4) & 0x0f0f0f0fu), u1.z, s);
+                    s = dp4a((int)((w[3] >> 4) & 0x0f0f0f0fu), u1.w, s);
+                    const int o = ((it * 32 + lane) << 2) + k;
+                    const float d8 = reinterpret_cast<const float *>(a.d)[o], s8 = reinterpret_cast<const float *>(a.s)[o];
+                    acc[n] += d * (d8 * (float)s - 8.0f * s8);  // sum (v-8)*u*d8 = d8*sum(v*u) - 8*s8  (vecdotq.cuh:23-42)
+                }
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------ the kernel
+// Per-CTA view of the jobs: job j's rows that fall inside this CTA's range are [seg_a[j], seg_b[j]) (global row
+// numbering over the concatenated jobs); warp w owns rows seg_a[j] + w, + NW, ... of each segment.
+struct SegTable {
+    int64_t a[B200_GEMV_MAX_JOBS], b[B200_GEMV_MAX_JOBS], base[B200_GEMV_MAX_JOBS];
+    const unsigned char *w[B200_GEMV_MAX_JOBS];
+};
+
+struct UnitCursor {
+    int     job;  // n_jobs = exhausted
+    int     it;   // 4096-weight step within the row
+    int64_t row;
+};
+__device__ __forceinline__ void cursor_settle(UnitCursor &c, const SegTable &t, int n_jobs, int warp) {
+    while (c.job < n_jobs && c.row >= t.b[c.job]) {
+        c.job++;
+        if (c.job < n_jobs) c.row = t.a[c.job] + warp;
+    }
+}
+__device__ __forceinline__ void cursor_init(UnitCursor &c, const SegTable &t, int n_jobs, int warp) {
+    c.job = 0; c.it = 0; c.row = t.a[0] + warp;
+    cursor_settle(c, t, n_jobs, warp);
+}
+__device__ __forceinline__ void cursor_next(UnitCursor &c, const SegTable &t, int n_jobs, int n_it, int warp) {
+    if (++c.it < n_it) return;
+    c.it = 0;
+    c.row += MMVQ_NW;
+    cursor_settle(c, t, n_jobs, warp);
+}
+
+template <int TYPE, int NCOLS>
+__global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_constant__ MmvqParams p) {
+    using G = Geo<TYPE>;
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ SegTable tab;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_stage = p.n_stage, n_jobs = p.n_jobs, n_it = p.n_it;
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem);  // [NW][MAX_STAGE]
+    unsigned char *act_base  = smem + MMVQ_BAR_BYTES;
+    unsigned char *ring      = act_base + ((size_t)NCOLS * act_col_bytes(n_it) + 127) / 128 * 128;
+    unsigned char *my_ring   = ring + (size_t)warp * n_stage * G::STAGE_BYTES;
+    unsigned long long *my_bars = bars + warp * MMVQ_MAX_STAGE;
+
+    // CTA row range: contiguous, balanced to one row
+    const int64_t r0 = p.total_rows * blockIdx.x / gridDim.x;
+    const int64_t r1 = p.total_rows * (blockIdx.x + 1) / gridDim.x;
+
+    if (lane == 0) {
+        for (int s = 0; s < n_stage; s++) mbar_init(&my_bars[s], 1);
+        mbar_fence_init();
+    }
+    const bool by_id = p.ids != nullptr;
+    if (by_id) pdl_wait();  // expert ids are written by the producer kernel
+    if (threadIdx.x == 0) {
+        int64_t base = 0;
+        for (int j = 0; j < n_jobs; j++) {
+            const int64_t end = base + p.jobs[j].M;
+            tab.base[j] = base;
+            tab.a[j] = r0 > base ? r0 : base;
+            tab.b[j] = r1 < end ? r1 : end;
+            const unsigned char *w = (const unsigned char *)p.jobs[j].W;
+            if (by_id && p.jobs[j].id_index >= 0) {
+                const int e = p.ids[p.jobs[j].id_index];
+                w = (e >= 0 && e < p.n_expert) ? w + (size_t)e * p.expert_bytes : nullptr;
+            }
+            tab.w[j] = w;
+            base = end;
+        }
+    }
+    __syncthreads();
+    pdl_trigger();  // dependents may start their own (independent) prologue as our CTAs retire
+
+    // ---- producer side of the warp-private ring: lane 0 issues, every lane tracks the cursor
+    UnitCursor ic, cc;
+    cursor_init(ic, tab, n_jobs, warp);
+    cc = ic;
+    int istage = 0;
+    auto issue = [&]() {
+        if (lane == 0) {
+            const unsigned char *wj = tab.w[ic.job];
+            const unsigned seg_off = (unsigned)ic.it * G::SEG_BYTES;
+            const unsigned left = p.row_bytes - seg_off;
+            const unsigned bytes = left < (unsigned)G::SEG_BYTES ? left : (unsigned)G::SEG_BYTES;
+            if (wj != nullptr) {
+                // aligned-down source, length rounded up to 16: the slack lands in the stage's head/tail padding
+                const unsigned char *src = wj + (size_t)(ic.row - tab.base[ic.job]) * p.w_row_bytes + seg_off;
+                const unsigned mis = (unsigned)((uintptr_t)src & 15);
+                const unsigned len = (mis + bytes + 15u) & ~15u;
+                mbar_expect_tx(&my_bars[istage], len);
+                bulk_g2s(my_ring + (size_t)istage * G::STAGE_BYTES, src - mis, len, &my_bars[istage]);
+            } else {
+                // invalid expert id: nothing to copy; complete the phase so the consumer does not hang
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&my_bars[istage])) : "memory");
+            }
+        }
+        istage = istage + 1 == n_stage ? 0 : istage + 1;
+        cursor_next(ic, tab, n_jobs, n_it, warp);
+    };
+    for (int s = 0; s < n_stage && ic.job < n_jobs; s++) issue();
+
+    // ---- everything above is independent of the producer kernel's output
+    if (!by_id) pdl_wait();
+
+    int cstage = 0;
+    unsigned cphase = 0;
+    const float *loaded_x = nullptr;
+    float acc[NCOLS];
+#pragma unroll
+    for (int n = 0; n < NCOLS; n++) acc[n] = 0.f;
+
+    for (int job = 0; job < n_jobs; job++) {
+        if (tab.a[job] >= tab.b[job]) continue;  // CTA-uniform
+        if (loaded_x != p.jobs[job].X) {
+            if (loaded_x != nullptr) __syncthreads();  // everyone is done with the previous activations
+            load_activations<NCOLS>(act_base, p.jobs[job].X, p.x_stride, p.K, n_it);
+            __syncthreads();
+            loaded_x = p.jobs[job].X;
+        }
+        const unsigned char *wj = tab.w[job];
+        const int64_t jbase = tab.base[job];
+        while (cc.job == job) {
+            const int64_t row = cc.row;
+            const int it = cc.it;
+            mbar_wait(&my_bars[cstage], cphase);
+            const int64_t slice = (int64_t)it * 32 + lane;
+            const int64_t blocks_left = p.K / 32 - slice * 4;  // q8_1 blocks from this slice to the end of the row
+            if (wj != nullptr && blocks_left > 0) {
+                const uintptr_t src = (uintptr_t)wj + (size_t)(row - jbase) * p.w_row_bytes + (size_t)it * G::SEG_BYTES;
+                const unsigned char *seg = my_ring + (size_t)cstage * G::STAGE_BYTES + (src & 15);
+                SliceDot<TYPE, NCOLS>::run(seg, lane, it, act_base, n_it, blocks_left < 4 ? (int)blocks_left : 4, acc);
+            }
+            __syncwarp();
+            if (lane == 0) fence_proxy_async_smem();  // our generic reads of the stage precede the next bulk write to it
+            cstage = cstage + 1 == n_stage ? 0 : cstage + 1;
+            cphase ^= (cstage == 0);
+            if (ic.job < n_jobs) issue();
+            if (it + 1 == n_it) {
+                float *dst = p.jobs[job].dst + (row - jbase);
+#pragma unroll
+                for (int n = 0; n < NCOLS; n++) {
+                    float v = warp_sum(acc[n]);
+                    if (wj == nullptr) v = __int_as_float(0x7fc00000);
+                    if (lane == 0) dst[(int64_t)n * p.dst_stride] = v;
+                    acc[n] = 0.f;
+                }
+            }
+            cursor_next(cc, tab, n_jobs, n_it, warp);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+static int g_sm_count = 0;
+static size_t g_smem_optin = 0;
+
+static int device_props() {
+    if (g_sm_count) return B200_OK;
+    int dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&dev));
+    int sm = 0, smem = 0;
+    B200_CUDA_TRY(cudaDeviceGetAttribute(&sm, cudaDevAttrMultiProcessorCount, dev));
+    B200_CUDA_TRY(cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+    g_sm_count = sm;
+    g_smem_optin = (size_t)smem;
+    return B200_OK;
+}
+
+template <int TYPE, int NCOLS>
+static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
+    using G = Geo<TYPE>;
+    int rc = device_props();
+    if (rc) return rc;
+    const size_t bar_bytes = MMVQ_BAR_BYTES;
+    const size_t act_bytes = ((size_t)NCOLS * act_col_bytes(p.n_it) + 127) / 128 * 128;
+    const size_t budget = g_smem_optin - sizeof(SegTable) - 256;  // static smem (segment table) + slack
+    if (bar_bytes + act_bytes + 2 * (size_t)MMVQ_NW * G::STAGE_BYTES > budget) {
+        set_error("b200_mul_mat_vec_q: K=%lld x N=%d activations do not fit in shared memory", (long long)p.K, NCOLS);
+        return B200_ERR_UNSUPPORTED;
+    }
+    size_t ns = (budget - bar_bytes - act_bytes) / ((size_t)MMVQ_NW * G::STAGE_BYTES);
+    // no point in more stages than a warp has steps: rows per warp ~ total_rows / (SMs * NW)
+    const int64_t steps = ((p.total_rows + g_sm_count - 1) / g_sm_count + MMVQ_NW - 1) / MMVQ_NW * p.n_it;
+    if ((int64_t)ns > steps) ns = (size_t)(steps < 2 ? 2 : steps);
+    if (ns > (size_t)MMVQ_MAX_STAGE) ns = MMVQ_MAX_STAGE;
+    p.n_stage = (int)ns;
+    const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * G::STAGE_BYTES;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmvq_kernel<TYPE, NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+        attr_set = true;
+    }
+    const int64_t grid = p.total_rows < g_sm_count ? p.total_rows : g_sm_count;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(MMVQ_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, mmvq_kernel<TYPE, NCOLS>, p));
+    return B200_OK;
+}
+
+template <int TYPE>
+static int dispatch_cols(MmvqParams &p, int N, cudaStream_t st, bool pdl) {
+    switch (N) {
+        case 1: return launch_mmvq<TYPE, 1>(p, st, pdl);
+        case 2: return launch_mmvq<TYPE, 2>(p, st, pdl);
+        case 3: return launch_mmvq<TYPE, 3>(p, st, pdl);
+        case 4: return launch_mmvq<TYPE, 4>(p, st, pdl);
+        case 5: return launch_mmvq<TYPE, 5>(p, st, pdl);
+        case 6: return launch_mmvq<TYPE, 6>(p, st, pdl);
+        case 7: return launch_mmvq<TYPE, 7>(p, st, pdl);
+        case 8: return launch_mmvq<TYPE, 8>(p, st, pdl);
+    }
+    set_error("b200_mul_mat_vec_q: N=%d out of range 1..8", N);
+    return B200_ERR_INVALID;
+}
+
+bool g_mmvq_pdl = false;  // set by the backend when it launches chains of dependent kernels
+
+int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride, int64_t dst_stride,
+                int64_t K, int64_t N, const int32_t *ids, size_t expert_bytes, int32_t n_expert, cudaStream_t st) {
+    if (!jobs || n_jobs < 1 || n_jobs > B200_GEMV_MAX_JOBS) { set_error("b200_mul_mat_vec_q: n_jobs=%d out of range", n_jobs); return B200_ERR_INVALID; }
+    const int bv = type_block_values(type);
+    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
+        set_error("b200_mul_mat_vec_q: unsupported weight type %d", type);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (K <= 0 || K % bv) { set_error("b200_mul_mat_vec_q: K=%lld must be a positive multiple of %d", (long long)K, bv); return B200_ERR_INVALID; }
+    if (N < 1 || N > 8) { set_error("b200_mul_mat_vec_q: N=%lld out of range 1..8", (long long)N); return B200_ERR_INVALID; }
+    const size_t row_bytes = (size_t)(K / bv) * type_block_bytes(type);
+    if (w_row_bytes < row_bytes) { set_error("b200_mul_mat_vec_q: row stride %zu < row size %zu", w_row_bytes, row_bytes); return B200_ERR_INVALID; }
+    MmvqParams p = {};
+    p.n_jobs = n_jobs;
+    p.K = K;
+    p.n_it = (int)((K + 4095) / 4096);
+    p.w_row_bytes = w_row_bytes;
+    p.row_bytes = (unsigned)row_bytes;
+    p.x_stride = x_stride;
+    p.dst_stride = dst_stride;
+    p.ids = ids;
+    p.expert_bytes = expert_bytes;
+    p.n_expert = n_expert;
+    int64_t total = 0;
+    const bool need16 = (type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K);
+    for (int j = 0; j < n_jobs; j++) {
+        p.jobs[j] = jobs[j];
+        if (!jobs[j].W || !jobs[j].X || !jobs[j].dst || jobs[j].M < 0) { set_error("b200_mul_mat_vec_q: job %d has a NULL pointer", j); return B200_ERR_INVALID; }
+        if (((uintptr_t)jobs[j].W & (need16 ? 15 : 1)) || (need16 && ((w_row_bytes & 15) || (expert_bytes & 15)))) {
+            set_error("b200_mul_mat_vec_q: weight pointer/stride alignment (need %d bytes)", need16 ? 16 : 2);
+            return B200_ERR_UNSUPPORTED;
+        }
+        if (((uintptr_t)jobs[j].X & 15) || (x_stride & 3)) { set_error("b200_mul_mat_vec_q: X must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
+        total += jobs[j].M;
+    }
+    if ((w_row_bytes & 1) || (expert_bytes & 1)) { set_error("b200_mul_mat_vec_q: odd strides"); return B200_ERR_UNSUPPORTED; }
+    p.total_rows = total;
+    if (total == 0) return B200_OK;
+    const bool pdl = g_mmvq_pdl;
+    switch (type) {
+        case B200_TYPE_Q4_0: return dispatch_cols<B200_TYPE_Q4_0>(p, (int)N, st, pdl);
+        case B200_TYPE_Q8_0: return dispatch_cols<B200_TYPE_Q8_0>(p, (int)N, st, pdl);
+        case B200_TYPE_Q4_K: return dispatch_cols<B200_TYPE_Q4_K>(p, (int)N, st, pdl);
+        case B200_TYPE_Q5_K: return dispatch_cols<B200_TYPE_Q5_K>(p, (int)N, st, pdl);
+        case B200_TYPE_Q6_K: return dispatch_cols<B200_TYPE_Q6_K>(p, (int)N, st, pdl);
+    }
+    return B200_ERR_UNSUPPORTED;
+}
+
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" int b200_mul_mat_vec_q(int type, const void *W, size_t w_row_bytes, const float *X, int64_t x_stride, float *dst,
+                                  int64_t dst_stride, int64_t K, int64_t M, int64_t N, b200_stream_t stream) {
+    b200_gemv_job job = {W, X, dst, M, -1, 0};
+    return mmvq_launch(type, &job, 1, w_row_bytes, x_stride, dst_stride, K, N, nullptr, 0, 0, (cudaStream_t)stream);
+}
+
+extern "C" int b200_mul_mat_vec_q_multi(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride,
+                                        int64_t dst_stride, int64_t K, int64_t N, const int32_t *ids, size_t expert_bytes,
+                                        int32_t n_expert, b200_stream_t stream) {
+    return mmvq_launch(type, jobs, n_jobs, w_row_bytes, x_stride, dst_stride, K, N, ids, expert_bytes, n_expert, (cudaStream_t)stream);
+}
+
+extern "C" int b200_mul_mat_id_vec_q(int type, const void *as, size_t w_row_bytes, size_t expert_bytes, int32_t n_expert,
+                                     const int32_t *ids, int64_t ids_stride, const float *b, int64_t b_stride_row,
+                                     int64_t b_stride_tok, float *dst, int64_t dst_stride_row, int64_t dst_stride_tok, int64_t K,
+                                     int64_t M, int64_t n_used, int64_t n_b_rows, int64_t T, b200_stream_t stream) {
+    if (!as || !ids || !b || !dst) { set_error("b200_mul_mat_id_vec_q: NULL argument"); return B200_ERR_INVALID; }
+    if (T < 0 || n_used < 1 || n_b_rows < 1) { set_error("b200_mul_mat_id_vec_q: bad shape"); return B200_ERR_INVALID; }
+    if (T * n_used > B200_GEMV_MAX_JOBS) {
+        set_error("b200_mul_mat_id_vec_q: T*n_used=%lld exceeds %d (decode regime only)", (long long)(T * n_used), B200_GEMV_MAX_JOBS);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (ids_stride * (T - 1) + n_used > 0x7fffffff) { set_error("b200_mul_mat_id_vec_q: ids too large"); return B200_ERR_UNSUPPORTED; }
+    b200_gemv_job jobs[B200_GEMV_MAX_JOBS];
+    int nj = 0;
+    for (int64_t t = 0; t < T; t++) {
+        for (int64_t e = 0; e < n_used; e++) {
+            jobs[nj].W = as;
+            jobs[nj].X = b + t * b_stride_tok + (e % n_b_rows) * b_stride_row;
+            jobs[nj].dst = dst + t * dst_stride_tok + e * dst_stride_row;
+            jobs[nj].M = M;
+            jobs[nj].id_index = (int32_t)(t * ids_stride + e);
+            jobs[nj]._pad = 0;
+            nj++;
+        }
+    }
+    if (nj == 0) return B200_OK;
+    return mmvq_launch(type, jobs, nj, w_row_bytes, 0, 0, K, 1, ids, expert_bytes, n_expert, (cudaStream_t)stream);
+}

@@ -1,0 +1,101 @@
+"""ctypes loader for libkcpp_b200.so (include/b200_ggml.h)."""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+LIB_PATH = PKG / "libkcpp_b200.so"
+
+# enum ggml_type values (reference ggml/include/ggml.h:361-398)
+F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, I32 = 0, 1, 2, 8, 9, 12, 13, 14, 26
+BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q8_0: (32, 34), Q8_1: (32, 36), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), I32: (1, 4)}
+TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", I32: "i32"}
+
+
+def row_size(t: int, ne: int) -> int:
+    bs, by = BLOCK[t]
+    assert ne % bs == 0, (t, ne)
+    return ne // bs * by
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+class GemvJob(C.Structure):
+    _fields_ = [("W", C.c_void_p), ("X", C.c_void_p), ("dst", C.c_void_p), ("M", C.c_int64), ("id_index", C.c_int32), ("_pad", C.c_int32)]
+
+
+class FattnArgs(C.Structure):
+    _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("mask", C.c_void_p), ("dst", C.c_void_p),
+                ("D", C.c_int64), ("N", C.c_int64), ("n_head", C.c_int64), ("n_head_kv", C.c_int64), ("n_kv", C.c_int64),
+                ("type_k", C.c_int32), ("type_v", C.c_int32),
+                ("q_nb1", C.c_size_t), ("q_nb2", C.c_size_t), ("k_nb1", C.c_size_t), ("k_nb2", C.c_size_t),
+                ("v_nb1", C.c_size_t), ("v_nb2", C.c_size_t), ("mask_nb1", C.c_size_t),
+                ("scale", C.c_float), ("max_bias", C.c_float), ("logit_softcap", C.c_float)]
+
+
+_SIGS = {
+    # name: (restype, argtypes)
+    "b200_last_error": (C.c_char_p, []),
+    "b200_version": (C.c_char_p, []),
+    "b200_device_count": (C.c_int, []),
+    "b200_set_device": (C.c_int, [C.c_int]),
+    "b200_device_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b200_malloc": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "b200_free": (C.c_int, [C.c_void_p]),
+    "b200_malloc_host": (C.c_int, [C.POINTER(C.c_void_p), C.c_size_t]),
+    "b200_free_host": (C.c_int, [C.c_void_p]),
+    "b200_memcpy_h2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200_memcpy_d2h": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200_memcpy_d2d": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200_memset": (C.c_int, [C.c_void_p, C.c_int, C.c_size_t, C.c_void_p]),
+    "b200_stream_create": (C.c_int, [C.POINTER(C.c_void_p)]),
+    "b200_stream_destroy": (C.c_int, [C.c_void_p]),
+    "b200_stream_synchronize": (C.c_int, [C.c_void_p]),
+    "b200_device_synchronize": (C.c_int, []),
+    "b200_event_create": (C.c_int, [C.POINTER(C.c_void_p)]),
+    "b200_event_destroy": (C.c_int, [C.c_void_p]),
+    "b200_event_record": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b200_event_elapsed_ms": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]),
+    "b200_dequantize": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p]),
+    "b200_quantize_q8_1": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
+    "b200_mul_mat_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "b200_mul_mat_vec_q_multi": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p]),
+    "b200_mul_mat_id_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
+                                        C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "b200_mul_mat_q_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int64, C.c_int64, C.c_int64]),
+    "b200_mul_mat_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200_flash_attn_workspace_bytes": (C.c_size_t, [C.POINTER(FattnArgs)]),
+    "b200_flash_attn_ext": (C.c_int, [C.POINTER(FattnArgs), C.c_void_p, C.c_size_t, C.c_void_p]),
+}
+
+_lib = None
+
+
+def load(path: Path | None = None):
+    """Load the shared library and declare every symbol of include/b200_ggml.h.  Raises if it is missing:
+    the product has no fallback path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise B200Error(f"{p} not found: build it with `python -m koboldcpp_b200.build` (nvcc, sm_100a)")
+    L = C.CDLL(str(p))
+    for name, (res, args) in _SIGS.items():
+        f = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+        f.restype = res
+        f.argtypes = args
+    _lib = L
+    return L
+
+
+def lib():
+    return load()
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        raise B200Error(f"{what or 'b200 call'} failed with status {rc}: {lib().b200_last_error().decode()}")
