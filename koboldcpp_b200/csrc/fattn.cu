@@ -58,13 +58,21 @@ __device__ __forceinline__ void load_tile(unsigned char *dst, const unsigned cha
             if (row0 + r < n_kv) cp_async16(d, base + (size_t)(row0 + r) * nb1 + c * 16);
             else *reinterpret_cast<uint4 *>(d) = make_uint4(0, 0, 0, 0);
         }
-    } else {
-        constexpr int CPR = G::ROW_BYTES / 8;  // 8-byte chunks per row (136 = 17 * 8)
+    } else if constexpr (G::ROW_BYTES % 8 == 0) {
+        constexpr int CPR = G::ROW_BYTES / 8;  // 8-byte chunks per row (D=128: 136 = 17 * 8)
         for (int i = lane; i < FA_TP * CPR; i += 32) {
             const int r = i / CPR, c = i % CPR;
             unsigned char *d = dst + r * G::ROW_STRIDE + c * 8;
             if (row0 + r < n_kv) cp_async8(d, base + (size_t)(row0 + r) * nb1 + c * 8);
             else *reinterpret_cast<uint2 *>(d) = make_uint2(0, 0);
+        }
+    } else {
+        constexpr int CPR = G::ROW_BYTES / 4;  // 4-byte chunks per row (D=64: 68 = 17 * 4)
+        for (int i = lane; i < FA_TP * CPR; i += 32) {
+            const int r = i / CPR, c = i % CPR;
+            unsigned char *d = dst + r * G::ROW_STRIDE + c * 4;
+            if (row0 + r < n_kv) cp_async4(d, base + (size_t)(row0 + r) * nb1 + c * 4);
+            else *reinterpret_cast<unsigned *>(d) = 0u;
         }
     }
 }
@@ -459,7 +467,7 @@ static int fa_check(const b200_fattn_args *a) {
         return B200_ERR_UNSUPPORTED;
     }
     if (a->n_head_kv <= 0 || a->n_head % a->n_head_kv || a->N <= 0 || a->n_kv <= 0) { set_error("b200_flash_attn_ext: bad shape"); return B200_ERR_INVALID; }
-    const int align = a->type_k == B200_TYPE_F16 ? 16 : 8;
+    const int align = a->type_k == B200_TYPE_F16 ? 16 : (a->D % 128 == 0 ? 8 : 4);
     if (((uintptr_t)a->k | (uintptr_t)a->v | a->k_nb1 | a->k_nb2 | a->v_nb1 | a->v_nb2) & (align - 1)) {
         set_error("b200_flash_attn_ext: K/V pointers and strides must be %d-byte aligned", align);
         return B200_ERR_UNSUPPORTED;

@@ -20,7 +20,8 @@ NAME = R.TYPE_NAMES
 # tolerances (measured headroom: see DESIGN.md "Parity")
 TOL_Q81 = 3e-5     # |gpu - exact q8_1 contraction| / max|ref|: only fp32 summation order differs
 TOL_CPU_NMSE = 2e-2  # ||gpu - cpu|| / ||cpu||: q8_1 (32-wide) vs q8_0/q8_K (CPU) activation rounding
-TOL_FA = 2.5e-3    # max abs error of attention outputs vs fp64 (outputs are O(0.3))
+TOL_FA = {1: 2.5e-3, 8: 5e-3}  # max abs error of attention outputs vs fp64 (outputs are O(0.3)); q8_0 KV also rounds Q to int8
+                                # (the CPU reference itself is 2.7e-3 / 1.3e-3 away from fp64 on the golden case)
 
 
 @pytest.fixture(scope="module")
@@ -32,6 +33,13 @@ def H():
 
 def bits(a):
     return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def same_f32(a, b):
+    """Bit-identical, except that NaNs only have to be NaNs (x86 propagates NaN payloads, the GPU canonicalises them)."""
+    a, b = np.ascontiguousarray(a, dtype=np.float32), np.ascontiguousarray(b, dtype=np.float32)
+    na, nb = np.isnan(a), np.isnan(b)
+    return np.array_equal(na, nb) and np.array_equal(bits(a)[~na], bits(b)[~nb])
 
 
 def quantize_weights(t, x):
@@ -66,7 +74,7 @@ def random_blocks(t, M, K, rng):
 def test_dequantize_bit_exact(H, golden, t):
     blocks, want = golden[f"w_{NAME[t]}_blocks"], golden[f"w_{NAME[t]}_dequant"]
     got = H.dequantize(t, blocks, want.size).reshape(want.shape)
-    assert np.array_equal(bits(got), bits(want))
+    assert same_f32(got, want)
     rng = np.random.default_rng(5 + t)
     K = 4096
     w = quantize_weights(t, (rng.standard_normal((16, K)) * 0.1).astype(np.float32))
@@ -74,7 +82,7 @@ def test_dequantize_bit_exact(H, golden, t):
     for blk in (w, raw):
         want = np.stack([O.dequantize(t, r, K) for r in blk])
         got = H.dequantize(t, blk, want.size).reshape(want.shape)
-        assert np.array_equal(bits(got), bits(want))
+        assert same_f32(got, want)
         got16 = H.dequantize(t, blk, want.size, dst_type=1).reshape(want.shape)
         with np.errstate(over="ignore", invalid="ignore"):
             want16 = want.astype(np.float16)
@@ -108,10 +116,15 @@ def check_gemv(H, t, K, M, N, rng, w=None):
     x = rng.standard_normal((N, K)).astype(np.float32)
     got = H.mul_mat_vec_q(t, w, x, K, M)
     exact = O.mul_mat_q8_1(t, w, x, K, M)
-    scale = np.abs(exact).max() + 1e-30
+    # fp32 summation error is relative to sum|terms| ~ ||x|| ||w||, not to the (possibly cancelling) result
+    wn = max(np.linalg.norm(O.dequantize(t, w[i], K)) for i in range(0, M, max(1, M // 8)))
+    scale = np.abs(exact).max() + 0.03 * wn * np.linalg.norm(x, axis=1).max() + 1e-30
     assert np.abs(got - exact).max() <= TOL_Q81 * scale, (NAME[t], K, M, N, np.abs(got - exact).max() / scale)
     cpu = O.mul_mat(t, w, x, K, M)
-    nmse = np.linalg.norm(got - cpu) / (np.linalg.norm(cpu) + 1e-30)
+    # few outputs: a single cancelling dot product makes a relative norm meaningless, so floor the denominator with
+    # the typical output magnitude ||x|| ||w|| / sqrt(K)
+    floor = wn * np.linalg.norm(x, axis=1).max() / np.sqrt(K) * np.sqrt(M * N)
+    nmse = np.linalg.norm(got - cpu) / max(np.linalg.norm(cpu), floor)
     assert nmse <= TOL_CPU_NMSE, (NAME[t], K, M, N, nmse)
     return got
 
@@ -224,8 +237,8 @@ def test_flash_attn_golden(H, golden, tkv, N):
     got = H.flash_attn_ext(q, k, v, mask, tkv, 1.0 / np.sqrt(D))
     cpu = golden[f"fa_out_{NAME[tkv]}_N{N}"]
     f64 = O.flash_attn_f64(q, k, v, mask, tkv, 1.0 / np.sqrt(D))
-    assert np.abs(got - f64).max() <= TOL_FA
-    assert np.abs(got - cpu).max() <= 2 * TOL_FA
+    assert np.abs(got - f64).max() <= TOL_FA[tkv]
+    assert np.abs(got - cpu).max() <= 2 * TOL_FA[tkv]
     assert np.abs(got - f64).max() <= np.abs(cpu - f64).max() * 1.5 + 1e-4  # at least as accurate as the CPU path
 
 
@@ -233,7 +246,7 @@ def test_flash_attn_golden(H, golden, tkv, N):
 def test_flash_attn_softcap_alibi_golden(H, golden, N):
     q, mask = golden[f"fa_q_N{N}"], golden[f"fa_mask_N{N}"]
     got = H.flash_attn_ext(q, golden["fa_k_f16"], golden["fa_v_f16"], mask, R.F16, 1.0 / np.sqrt(q.shape[2]), 8.0, 30.0)
-    assert np.abs(got - golden[f"fa_out_f16_N{N}_softcap_alibi"]).max() <= 2 * TOL_FA
+    assert np.abs(got - golden[f"fa_out_f16_N{N}_softcap_alibi"]).max() <= 2 * TOL_FA[R.F16]
 
 
 @pytest.mark.parametrize("cfg", [
@@ -260,10 +273,15 @@ def test_flash_attn_shapes(H, tkv, cfg):
         mask[i, cut:] = -np.inf
     got = H.flash_attn_ext(q, k, v, mask, tkv, 1.0 / np.sqrt(D))
     f64 = O.flash_attn_f64(q, k, v, mask, tkv, 1.0 / np.sqrt(D))
-    assert np.abs(got - f64).max() <= TOL_FA, np.abs(got - f64).max()
+    err = np.abs(got - f64).max()
     if nh * N * nkv <= 40 * 16 * 512:
         cpu = O.flash_attn_ext(q, k, v, mask, tkv, 1.0 / np.sqrt(D))
-        assert np.abs(got - cpu).max() <= 2 * TOL_FA
+        err_cpu = np.abs(cpu - f64).max()
+        # few keys = little averaging of the int8-Q / f16-V rounding noise: the bar is the CPU path's own distance to fp64
+        assert err <= max(TOL_FA[tkv], 1.5 * err_cpu + 1e-4), (err, err_cpu)
+        assert np.abs(got - cpu).max() <= 2 * max(TOL_FA[tkv], err_cpu)
+    else:
+        assert err <= TOL_FA[tkv], err
 
 
 def test_flash_attn_no_mask_and_fully_masked_prefix(H):
@@ -272,11 +290,11 @@ def test_flash_attn_no_mask_and_fully_masked_prefix(H):
     q = rng.standard_normal((nh, 1, D)).astype(np.float32)
     k = O.pack_kv(R.F16, rng.standard_normal((nhkv, nkv, D))); v = O.pack_kv(R.F16, rng.standard_normal((nhkv, nkv, D)))
     got = H.flash_attn_ext(q, k, v, None, R.F16, 0.1)
-    assert np.abs(got - O.flash_attn_f64(q, k, v, None, R.F16, 0.1)).max() <= TOL_FA
+    assert np.abs(got - O.flash_attn_f64(q, k, v, None, R.F16, 0.1)).max() <= TOL_FA[R.F16]
     mask = np.zeros((32, nkv), dtype=np.float16)
     mask[:, :200] = -np.inf  # whole leading tiles masked: the running max starts at -inf
     got = H.flash_attn_ext(q, k, v, mask, R.F16, 0.1)
-    assert np.abs(got - O.flash_attn_f64(q, k, v, mask, R.F16, 0.1)).max() <= TOL_FA
+    assert np.abs(got - O.flash_attn_f64(q, k, v, mask, R.F16, 0.1)).max() <= TOL_FA[R.F16]
 
 
 def test_flash_attn_long_context_split_invariance(H):
@@ -290,7 +308,7 @@ def test_flash_attn_long_context_split_invariance(H):
     k, v = O.pack_kv(R.Q8_0, kf), O.pack_kv(R.Q8_0, vf)
     got = H.flash_attn_ext(q, k, v, None, R.Q8_0, 1.0 / np.sqrt(D))
     f64 = O.flash_attn_f64(q, k, v, None, R.Q8_0, 1.0 / np.sqrt(D))
-    assert np.abs(got - f64).max() <= TOL_FA
+    assert np.abs(got - f64).max() <= TOL_FA[R.Q8_0]
     # repeatability: the ticket counters must be left clean, and results must not depend on CTA arrival order by more than fp32 noise
     again = H.flash_attn_ext(q, k, v, None, R.Q8_0, 1.0 / np.sqrt(D))
     assert np.abs(got - again).max() <= 1e-6
