@@ -57,6 +57,9 @@ enum b200_type {
 
 B200_API const char *b200_last_error(void);
 B200_API const char *b200_version(void);
+/* Launch the kernels with the programmatic-dependent-launch attribute (griddepcontrol): a kernel's weight
+ * prefetch then overlaps the tail of its producer.  Off by default; the ggml backend turns it on for its graphs. */
+B200_API void b200_set_pdl(int enabled);
 
 /* ---- device plumbing (so ctypes / cgo / JNI hosts need no CUDA binding of their own) ------------
  * replaces: ggml_backend_cuda_get_device_count / cudaMalloc / cudaMemcpyAsync call sites in

@@ -7,6 +7,7 @@
 
 namespace b200 {
 
+extern bool g_mmvq_pdl;
 static thread_local char g_err[512] = "";
 
 void set_error(const char *fmt, ...) {
@@ -29,6 +30,7 @@ extern "C" {
 
 const char *b200_last_error(void) { return g_err; }
 const char *b200_version(void) { return "koboldcpp_b200 0.1 (sm_100a)"; }
+void b200_set_pdl(int enabled) { g_mmvq_pdl = enabled != 0; }
 
 int b200_device_count(void) {
     int n = 0;

@@ -36,6 +36,7 @@ struct MmvqParams {
     int            n_stage;
     int            n_it;          // ceil(K / 4096): steps per row
     int            n_expert;
+    int            rows_q, rows_rem;   // rows per CTA = rows_q (+1 for the first rows_rem CTAs)
     int64_t        K;
     int64_t        total_rows;
     size_t         w_row_bytes;   // row stride
@@ -81,26 +82,36 @@ __device__ void load_activations(unsigned char *act_base, const float *__restric
         float *as = (float *)(p + (size_t)n_it * (4096 + 512));
         int   *ag = (int *)(p + (size_t)n_it * (4096 + 1024));
         const float *x = X + (int64_t)n * x_stride;
-        for (int base = 0; base < n4; base += MMVQ_THREADS) {
-            const int i4 = base + threadIdx.x;
-            const bool active = i4 < n4;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (active) v = __ldg(reinterpret_cast<const float4 *>(x) + i4);
-            float d, s;
-            int sum4;
-            const int packed = quantize_q8_1_group8(v, d, s, sum4);
-            const int hi4 = __shfl_xor_sync(0xffffffffu, sum4, 4);
-            if (active) {
-                const int blk = i4 >> 3, part = i4 & 7;
-                const int slice = blk >> 2, b = blk & 3;
-                const int it = slice >> 5, lane = slice & 31;
-                const int j = b * 2 + (part >> 2);
-                aq[(((it * 8 + j) * 32 + lane) << 2) + (part & 3)] = packed;
-                if (part == 0) {
-                    const int o = ((it * 32 + lane) << 2) + b;
-                    ad[o] = d;
-                    as[o] = s;
-                    ag[o] = (sum4 & 0xffff) | (hi4 << 16);  // 16-wide integer sums (q6_K offset term)
+        // 4 independent 16-byte loads per thread are issued before any of them is consumed (one L2 round trip per
+        // 8192 activations instead of one per 2048)
+        for (int base = 0; base < n4; base += 4 * MMVQ_THREADS) {
+            float4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i4 = base + u * MMVQ_THREADS + threadIdx.x;
+                v[u] = i4 < n4 ? __ldg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int i4 = base + u * MMVQ_THREADS + threadIdx.x;
+                if (base + u * MMVQ_THREADS >= n4) break;  // warp-uniform: the whole batch is past the end
+                const bool active = i4 < n4;
+                float d, s;
+                int sum4;
+                const int packed = quantize_q8_1_group8(v[u], d, s, sum4);
+                const int hi4 = __shfl_xor_sync(0xffffffffu, sum4, 4);
+                if (active) {
+                    const int blk = i4 >> 3, part = i4 & 7;
+                    const int slice = blk >> 2, b = blk & 3;
+                    const int it = slice >> 5, lane = slice & 31;
+                    const int j = b * 2 + (part >> 2);
+                    aq[(((it * 8 + j) * 32 + lane) << 2) + (part & 3)] = packed;
+                    if (part == 0) {
+                        const int o = ((it * 32 + lane) << 2) + b;
+                        ad[o] = d;
+                        as[o] = s;
+                        ag[o] = (sum4 & 0xffff) | (hi4 << 16);  // 16-wide integer sums (q6_K offset term)
+                    }
                 }
             }
         }
@@ -150,12 +161,15 @@ struct SliceDot<B200_TYPE_Q4_K, NCOLS> {
                     sumi[2 * cc]     = dp4a((int)(w[1] & 0x0f0f0f0fu), ulo.y, sumi[2 * cc]);
                     sumi[2 * cc]     = dp4a((int)(w[2] & 0x0f0f0f0fu), ulo.z, sumi[2 * cc]);
                     sumi[2 * cc]     = dp4a((int)(w[3] & 0x0f0f0f0fu), ulo.w, sumi[2 * cc]);
-                    sumi[2 * cc + 1] = dp4a((int)((w[0] >> 4) & 0x0f0f0f0fu), uhi.x, sumi[2 * cc + 1]);
-                    sumi[2 * cc + 1] = dp4a((int)((w[1] >> 4) & 0x0f0f0f0fu), uhi.y, sumi[2 * cc + 1]);
-                    sumi[2 * cc + 1] = dp4a((int)((w[2] >> 4) & 0x0f0f0f0fu), uhi.z, sumi[2 * cc + 1]);
-                    sumi[2 * cc + 1] = dp4a((int)((w[3] >> 4) & 0x0f0f0f0fu), uhi.w, sumi[2 * cc + 1]);
+                    // high nibbles stay in place (value * 16, unsigned byte): exact >> 4 after the accumulation
+                    sumi[2 * cc + 1] = dp4a_u(w[0] & 0xf0f0f0f0u, uhi.x, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a_u(w[1] & 0xf0f0f0f0u, uhi.y, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a_u(w[2] & 0xf0f0f0f0u, uhi.z, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a_u(w[3] & 0xf0f0f0f0u, uhi.w, sumi[2 * cc + 1]);
                 }
             }
+            sumi[1] >>= 4;
+            sumi[3] >>= 4;
             const float4 d8 = a.d[it * 32 + lane], s8 = a.s[it * 32 + lane];
             const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
                              d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
@@ -350,10 +364,11 @@ struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
                     s = dp4a((int)(w[1] & 0x0f0f0f0fu), u0.y, s);
                     s = dp4a((int)(w[2] & 0x0f0f0f0fu), u0.z, s);
                     s = dp4a((int)(w[3] & 0x0f0f0f0fu), u0.w, s);
-                    s = dp4a((int)((w[0] >> 4) & 0x0f0f0f0fu), u1.x, s);
-                    s = dp4a((int)((w[1] >> 4) & 0x0f0f0f0fu), u1.y, s);
-                    s = dp4a((int)((w[2] >> 4) & 0x0f0f0f0fu), u1.z, s);
-                    s = dp4a((int)((w[3] >> 4) & 0x0f0f0f0fu), u1.w, s);
+                    int sh = dp4a_u(w[0] & 0xf0f0f0f0u, u1.x, 0);
+                    sh = dp4a_u(w[1] & 0xf0f0f0f0u, u1.y, sh);
+                    sh = dp4a_u(w[2] & 0xf0f0f0f0u, u1.z, sh);
+                    sh = dp4a_u(w[3] & 0xf0f0f0f0u, u1.w, sh);
+                    s += sh >> 4;
                     const int o = ((it * 32 + lane) << 2) + k;
                     const float d8 = reinterpret_cast<const float *>(a.d)[o], s8 = reinterpret_cast<const float *>(a.s)[o];
                     acc[n] += d * (d8 * (float)s - 8.0f * s8);  // sum (v-8)*u*d8 = d8*sum(v*u) - 8*s8  (vecdotq.cuh:23-42)
@@ -364,93 +379,88 @@ struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
 };
 
 // ------------------------------------------------------------------------------------------------ the kernel
-// Per-CTA view of the jobs: job j's rows that fall inside this CTA's range are [seg_a[j], seg_b[j]) (global row
-// numbering over the concatenated jobs); warp w owns rows seg_a[j] + w, + NW, ... of each segment.
-struct SegTable {
-    int64_t a[B200_GEMV_MAX_JOBS], b[B200_GEMV_MAX_JOBS], base[B200_GEMV_MAX_JOBS];
-    const unsigned char *w[B200_GEMV_MAX_JOBS];
-};
+// CTA c owns the contiguous row range [r0, r1) of the concatenated jobs; warp w owns local rows w, w+NW, ...
+// A row is consumed in n_it steps of 4096 weights; step u of a warp lives in ring stage u % n_stage.
+//
+// MULTI (several jobs, or expert ids): a per-CTA row table in shared memory (source pointer, destination pointer,
+// job) replaces index arithmetic, so the streaming loop is identical and prefetch runs across job boundaries.
+constexpr int MMVQ_MAX_TAB = 1024;  // rows per CTA in MULTI mode (17 bytes each)
 
-struct UnitCursor {
-    int     job;  // n_jobs = exhausted
-    int     it;   // 4096-weight step within the row
-    int64_t row;
-};
-__device__ __forceinline__ void cursor_settle(UnitCursor &c, const SegTable &t, int n_jobs, int warp) {
-    while (c.job < n_jobs && c.row >= t.b[c.job]) {
-        c.job++;
-        if (c.job < n_jobs) c.row = t.a[c.job] + warp;
-    }
-}
-__device__ __forceinline__ void cursor_init(UnitCursor &c, const SegTable &t, int n_jobs, int warp) {
-    c.job = 0; c.it = 0; c.row = t.a[0] + warp;
-    cursor_settle(c, t, n_jobs, warp);
-}
-__device__ __forceinline__ void cursor_next(UnitCursor &c, const SegTable &t, int n_jobs, int n_it, int warp) {
-    if (++c.it < n_it) return;
-    c.it = 0;
-    c.row += MMVQ_NW;
-    cursor_settle(c, t, n_jobs, warp);
-}
+#ifdef B200_MMVQ_TRACE
+__device__ unsigned long long g_mmvq_trace[148 * 8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TRACE(i) do { if (threadIdx.x == 0 && blockIdx.x < 148) g_mmvq_trace[blockIdx.x * 8 + (i)] = gtime(); } while (0)
+#else
+#define TRACE(i) do {} while (0)
+#endif
 
-template <int TYPE, int NCOLS>
+template <int TYPE, int NCOLS, bool MULTI>
 __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_constant__ MmvqParams p) {
     using G = Geo<TYPE>;
+    TRACE(0);
+    constexpr bool ALIGNED16 = (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K);  // host guarantees 16-byte rows
     extern __shared__ __align__(128) unsigned char smem[];
-    __shared__ SegTable tab;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_stage = p.n_stage, n_jobs = p.n_jobs, n_it = p.n_it;
+    const int n_stage = p.n_stage, n_it = p.n_it;
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(smem);  // [NW][MAX_STAGE]
     unsigned char *act_base  = smem + MMVQ_BAR_BYTES;
     unsigned char *ring      = act_base + ((size_t)NCOLS * act_col_bytes(n_it) + 127) / 128 * 128;
     unsigned char *my_ring   = ring + (size_t)warp * n_stage * G::STAGE_BYTES;
     unsigned long long *my_bars = bars + warp * MMVQ_MAX_STAGE;
+    // MULTI row table lives behind the ring
+    unsigned char *tab_base = ring + (size_t)MMVQ_NW * n_stage * G::STAGE_BYTES;
+    const unsigned char **rsrc = reinterpret_cast<const unsigned char **>(tab_base);
+    float **rdst = reinterpret_cast<float **>(tab_base + 8 * MMVQ_MAX_TAB);
+    signed char *rjob = reinterpret_cast<signed char *>(tab_base + 16 * MMVQ_MAX_TAB);
 
-    // CTA row range: contiguous, balanced to one row
-    const int64_t r0 = p.total_rows * blockIdx.x / gridDim.x;
-    const int64_t r1 = p.total_rows * (blockIdx.x + 1) / gridDim.x;
+    // contiguous row range, balanced to one row: the first rows_rem CTAs take rows_q + 1 rows
+    const int bid = blockIdx.x;
+    const int r0 = bid * p.rows_q + (bid < p.rows_rem ? bid : p.rows_rem);
+    const int nrows = p.rows_q + (bid < p.rows_rem ? 1 : 0);
+    const int nmy = warp < nrows ? (nrows - warp + MMVQ_NW - 1) / MMVQ_NW : 0;  // rows of this warp
 
     if (lane == 0) {
         for (int s = 0; s < n_stage; s++) mbar_init(&my_bars[s], 1);
         mbar_fence_init();
     }
-    const bool by_id = p.ids != nullptr;
-    if (by_id) pdl_wait();  // expert ids are written by the producer kernel
-    if (threadIdx.x == 0) {
-        int64_t base = 0;
-        for (int j = 0; j < n_jobs; j++) {
-            const int64_t end = base + p.jobs[j].M;
-            tab.base[j] = base;
-            tab.a[j] = r0 > base ? r0 : base;
-            tab.b[j] = r1 < end ? r1 : end;
+    int jfirst = 0, jlast = 0;
+    if constexpr (MULTI) {
+        if (p.ids != nullptr) pdl_wait();  // expert ids are written by the producer kernel
+        // row table: every thread resolves a few rows (<= 16 jobs: linear scan)
+        for (int lr = threadIdx.x; lr < nrows; lr += MMVQ_THREADS) {
+            int64_t row = r0 + lr;
+            int j = 0;
+            while (row >= p.jobs[j].M) { row -= p.jobs[j].M; j++; }
             const unsigned char *w = (const unsigned char *)p.jobs[j].W;
-            if (by_id && p.jobs[j].id_index >= 0) {
+            if (p.ids != nullptr && p.jobs[j].id_index >= 0) {
                 const int e = p.ids[p.jobs[j].id_index];
                 w = (e >= 0 && e < p.n_expert) ? w + (size_t)e * p.expert_bytes : nullptr;
             }
-            tab.w[j] = w;
-            base = end;
+            rsrc[lr] = w ? w + (size_t)row * p.w_row_bytes : nullptr;
+            rdst[lr] = p.jobs[j].dst + row;
+            rjob[lr] = (signed char)j;
         }
+        __syncthreads();
+        if (nrows > 0) { jfirst = rjob[0]; jlast = rjob[nrows - 1]; }
     }
-    __syncthreads();
     pdl_trigger();  // dependents may start their own (independent) prologue as our CTAs retire
 
-    // ---- producer side of the warp-private ring: lane 0 issues, every lane tracks the cursor
-    UnitCursor ic, cc;
-    cursor_init(ic, tab, n_jobs, warp);
-    cc = ic;
-    int istage = 0;
+    // ---- producer side of the warp-private ring (lane 0 issues)
+    const unsigned char *w0 = (const unsigned char *)p.jobs[0].W;
+    const unsigned tail_bytes = p.row_bytes - (unsigned)(n_it - 1) * G::SEG_BYTES;
+    int ik = 0, iit = 0, istage = 0;  // next unit to issue: row counter, step, stage
     auto issue = [&]() {
         if (lane == 0) {
-            const unsigned char *wj = tab.w[ic.job];
-            const unsigned seg_off = (unsigned)ic.it * G::SEG_BYTES;
-            const unsigned left = p.row_bytes - seg_off;
-            const unsigned bytes = left < (unsigned)G::SEG_BYTES ? left : (unsigned)G::SEG_BYTES;
-            if (wj != nullptr) {
+            const int lr = warp + ik * MMVQ_NW;
+            const unsigned char *src;
+            if constexpr (MULTI) src = rsrc[lr];
+            else src = w0 + (size_t)(r0 + lr) * p.w_row_bytes;
+            const unsigned bytes = iit == n_it - 1 ? tail_bytes : (unsigned)G::SEG_BYTES;
+            if (!MULTI || src != nullptr) {
+                src += (size_t)iit * G::SEG_BYTES;
                 // aligned-down source, length rounded up to 16: the slack lands in the stage's head/tail padding
-                const unsigned char *src = wj + (size_t)(ic.row - tab.base[ic.job]) * p.w_row_bytes + seg_off;
-                const unsigned mis = (unsigned)((uintptr_t)src & 15);
+                const unsigned mis = ALIGNED16 ? 0u : (unsigned)((uintptr_t)src & 15);
                 const unsigned len = (mis + bytes + 15u) & ~15u;
                 mbar_expect_tx(&my_bars[istage], len);
                 bulk_g2s(my_ring + (size_t)istage * G::STAGE_BYTES, src - mis, len, &my_bars[istage]);
@@ -460,12 +470,19 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
             }
         }
         istage = istage + 1 == n_stage ? 0 : istage + 1;
-        cursor_next(ic, tab, n_jobs, n_it, warp);
+        if (++iit == n_it) { iit = 0; ik++; }
     };
-    for (int s = 0; s < n_stage && ic.job < n_jobs; s++) issue();
+    TRACE(1);
+    for (int s = 0; s < n_stage && ik < nmy; s++) issue();
+    TRACE(2);
 
     // ---- everything above is independent of the producer kernel's output
-    if (!by_id) pdl_wait();
+    if (!MULTI || p.ids == nullptr) pdl_wait();
+    TRACE(3);
+
+    // lanes past the end of the row in the last step (and, for q4_0/q8_0, a partial last slice)
+    int last_nblk = (int)(p.K / 32) - 4 * ((n_it - 1) * 32 + lane);
+    last_nblk = last_nblk < 0 ? 0 : (last_nblk > 4 ? 4 : last_nblk);
 
     int cstage = 0;
     unsigned cphase = 0;
@@ -474,45 +491,54 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
 #pragma unroll
     for (int n = 0; n < NCOLS; n++) acc[n] = 0.f;
 
-    for (int job = 0; job < n_jobs; job++) {
-        if (tab.a[job] >= tab.b[job]) continue;  // CTA-uniform
-        if (loaded_x != p.jobs[job].X) {
+    int k = 0;
+    for (int job = jfirst; job <= jlast; job++) {
+        const float *xj = p.jobs[job].X;
+        if (loaded_x != xj && nrows > 0) {
             if (loaded_x != nullptr) __syncthreads();  // everyone is done with the previous activations
-            load_activations<NCOLS>(act_base, p.jobs[job].X, p.x_stride, p.K, n_it);
+            load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it);
             __syncthreads();
-            loaded_x = p.jobs[job].X;
+            loaded_x = xj;
+            TRACE(4);
         }
-        const unsigned char *wj = tab.w[job];
-        const int64_t jbase = tab.base[job];
-        while (cc.job == job) {
-            const int64_t row = cc.row;
-            const int it = cc.it;
-            mbar_wait(&my_bars[cstage], cphase);
-            const int64_t slice = (int64_t)it * 32 + lane;
-            const int64_t blocks_left = p.K / 32 - slice * 4;  // q8_1 blocks from this slice to the end of the row
-            if (wj != nullptr && blocks_left > 0) {
-                const uintptr_t src = (uintptr_t)wj + (size_t)(row - jbase) * p.w_row_bytes + (size_t)it * G::SEG_BYTES;
-                const unsigned char *seg = my_ring + (size_t)cstage * G::STAGE_BYTES + (src & 15);
-                SliceDot<TYPE, NCOLS>::run(seg, lane, it, act_base, n_it, blocks_left < 4 ? (int)blocks_left : 4, acc);
+        for (; k < nmy; k++) {
+            const int lr = warp + k * MMVQ_NW;
+            uintptr_t src;
+            float *dst;
+            if constexpr (MULTI) {
+                if (rjob[lr] != job) break;
+                src = (uintptr_t)rsrc[lr];
+                dst = rdst[lr];
+            } else {
+                src = (uintptr_t)w0 + (size_t)(r0 + lr) * p.w_row_bytes;
+                dst = p.jobs[0].dst + (r0 + lr);
             }
-            __syncwarp();
-            if (lane == 0) fence_proxy_async_smem();  // our generic reads of the stage precede the next bulk write to it
-            cstage = cstage + 1 == n_stage ? 0 : cstage + 1;
-            cphase ^= (cstage == 0);
-            if (ic.job < n_jobs) issue();
-            if (it + 1 == n_it) {
-                float *dst = p.jobs[job].dst + (row - jbase);
-#pragma unroll
-                for (int n = 0; n < NCOLS; n++) {
-                    float v = warp_sum(acc[n]);
-                    if (wj == nullptr) v = __int_as_float(0x7fc00000);
-                    if (lane == 0) dst[(int64_t)n * p.dst_stride] = v;
-                    acc[n] = 0.f;
+            for (int it = 0; it < n_it; it++) {
+                mbar_wait(&my_bars[cstage], cphase);
+                if (k == 0 && it == 0) TRACE(5);
+                const int nblk = it == n_it - 1 ? last_nblk : 4;
+                if ((!MULTI || src != 0) && nblk > 0) {
+                    const unsigned mis = ALIGNED16 ? 0u : (unsigned)((src + (size_t)it * G::SEG_BYTES) & 15);
+                    SliceDot<TYPE, NCOLS>::run(my_ring + (size_t)cstage * G::STAGE_BYTES + mis, lane, it, act_base, n_it, nblk, acc);
                 }
+                __syncwarp();
+                if (lane == 0) fence_proxy_async_smem();  // our generic reads of the stage precede the next bulk write to it
+                cstage = cstage + 1 == n_stage ? 0 : cstage + 1;
+                cphase ^= (cstage == 0);
+                if (ik < nmy) issue();
             }
-            cursor_next(cc, tab, n_jobs, n_it, warp);
+#pragma unroll
+            for (int n = 0; n < NCOLS; n++) {
+                float v = warp_sum(acc[n]);
+                if (MULTI && src == 0) v = __int_as_float(0x7fc00000);
+                if (lane == 0) dst[(int64_t)n * p.dst_stride] = v;
+                acc[n] = 0.f;
+            }
+            if (k == 0) TRACE(6);
         }
     }
+    __syncthreads();
+    TRACE(7);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -531,14 +557,15 @@ static int device_props() {
     return B200_OK;
 }
 
-template <int TYPE, int NCOLS>
+template <int TYPE, int NCOLS, bool MULTI>
 static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     using G = Geo<TYPE>;
     int rc = device_props();
     if (rc) return rc;
     const size_t bar_bytes = MMVQ_BAR_BYTES;
     const size_t act_bytes = ((size_t)NCOLS * act_col_bytes(p.n_it) + 127) / 128 * 128;
-    const size_t budget = g_smem_optin - sizeof(SegTable) - 256;  // static smem (segment table) + slack
+    const size_t tab_bytes = MULTI ? (size_t)17 * MMVQ_MAX_TAB + 64 : 0;
+    const size_t budget = g_smem_optin - 256 - tab_bytes;
     if (bar_bytes + act_bytes + 2 * (size_t)MMVQ_NW * G::STAGE_BYTES > budget) {
         set_error("b200_mul_mat_vec_q: K=%lld x N=%d activations do not fit in shared memory", (long long)p.K, NCOLS);
         return B200_ERR_UNSUPPORTED;
@@ -549,13 +576,20 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     if ((int64_t)ns > steps) ns = (size_t)(steps < 2 ? 2 : steps);
     if (ns > (size_t)MMVQ_MAX_STAGE) ns = MMVQ_MAX_STAGE;
     p.n_stage = (int)ns;
-    const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * G::STAGE_BYTES;
+    const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * G::STAGE_BYTES + tab_bytes;
     static bool attr_set = false;
     if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(mmvq_kernel<TYPE, NCOLS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)budget));
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmvq_kernel<TYPE, NCOLS, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)(g_smem_optin - 256)));
         attr_set = true;
     }
     const int64_t grid = p.total_rows < g_sm_count ? p.total_rows : g_sm_count;
+    p.rows_q = (int)(p.total_rows / grid);
+    p.rows_rem = (int)(p.total_rows % grid);
+    if (MULTI && (p.total_rows + grid - 1) / grid > MMVQ_MAX_TAB) {
+        set_error("b200_mul_mat_vec_q_multi: %lld rows exceed the per-CTA row table", (long long)p.total_rows);
+        return B200_ERR_UNSUPPORTED;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(MMVQ_THREADS);
@@ -566,21 +600,32 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, mmvq_kernel<TYPE, NCOLS>, p));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, mmvq_kernel<TYPE, NCOLS, MULTI>, p));
     return B200_OK;
 }
 
 template <int TYPE>
 static int dispatch_cols(MmvqParams &p, int N, cudaStream_t st, bool pdl) {
+    const bool multi = p.n_jobs > 1 || p.ids != nullptr;
+    if (multi) {  // fused / expert launches are decode-only: 1..4 columns
+        switch (N) {
+            case 1: return launch_mmvq<TYPE, 1, true>(p, st, pdl);
+            case 2: return launch_mmvq<TYPE, 2, true>(p, st, pdl);
+            case 3: return launch_mmvq<TYPE, 3, true>(p, st, pdl);
+            case 4: return launch_mmvq<TYPE, 4, true>(p, st, pdl);
+        }
+        set_error("b200_mul_mat_vec_q_multi: N=%d out of range 1..4", N);
+        return B200_ERR_UNSUPPORTED;
+    }
     switch (N) {
-        case 1: return launch_mmvq<TYPE, 1>(p, st, pdl);
-        case 2: return launch_mmvq<TYPE, 2>(p, st, pdl);
-        case 3: return launch_mmvq<TYPE, 3>(p, st, pdl);
-        case 4: return launch_mmvq<TYPE, 4>(p, st, pdl);
-        case 5: return launch_mmvq<TYPE, 5>(p, st, pdl);
-        case 6: return launch_mmvq<TYPE, 6>(p, st, pdl);
-        case 7: return launch_mmvq<TYPE, 7>(p, st, pdl);
-        case 8: return launch_mmvq<TYPE, 8>(p, st, pdl);
+        case 1: return launch_mmvq<TYPE, 1, false>(p, st, pdl);
+        case 2: return launch_mmvq<TYPE, 2, false>(p, st, pdl);
+        case 3: return launch_mmvq<TYPE, 3, false>(p, st, pdl);
+        case 4: return launch_mmvq<TYPE, 4, false>(p, st, pdl);
+        case 5: return launch_mmvq<TYPE, 5, false>(p, st, pdl);
+        case 6: return launch_mmvq<TYPE, 6, false>(p, st, pdl);
+        case 7: return launch_mmvq<TYPE, 7, false>(p, st, pdl);
+        case 8: return launch_mmvq<TYPE, 8, false>(p, st, pdl);
     }
     set_error("b200_mul_mat_vec_q: N=%d out of range 1..8", N);
     return B200_ERR_INVALID;
@@ -626,6 +671,7 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
     if ((w_row_bytes & 1) || (expert_bytes & 1)) { set_error("b200_mul_mat_vec_q: odd strides"); return B200_ERR_UNSUPPORTED; }
     p.total_rows = total;
     if (total == 0) return B200_OK;
+    if (total > 0x7fffffff) { set_error("b200_mul_mat_vec_q: too many rows"); return B200_ERR_UNSUPPORTED; }
     const bool pdl = g_mmvq_pdl;
     switch (type) {
         case B200_TYPE_Q4_0: return dispatch_cols<B200_TYPE_Q4_0>(p, (int)N, st, pdl);
@@ -640,6 +686,13 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
 }  // namespace b200
 
 using namespace b200;
+
+#ifdef B200_MMVQ_TRACE
+extern "C" __attribute__((visibility("default"))) int b200_mmvq_trace(unsigned long long *out) {
+    B200_CUDA_TRY(cudaMemcpyFromSymbol(out, g_mmvq_trace, sizeof(unsigned long long) * 148 * 8));
+    return B200_OK;
+}
+#endif
 
 extern "C" int b200_mul_mat_vec_q(int type, const void *W, size_t w_row_bytes, const float *X, int64_t x_stride, float *dst,
                                   int64_t dst_stride, int64_t K, int64_t M, int64_t N, b200_stream_t stream) {

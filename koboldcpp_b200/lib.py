@@ -40,6 +40,7 @@ _SIGS = {
     # name: (restype, argtypes)
     "b200_last_error": (C.c_char_p, []),
     "b200_version": (C.c_char_p, []),
+    "b200_set_pdl": (None, [C.c_int]),
     "b200_device_count": (C.c_int, []),
     "b200_set_device": (C.c_int, [C.c_int]),
     "b200_device_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
