@@ -32,6 +32,13 @@ enum b200_unary_op {
  * x, dst: f32, rows contiguous (nb[0] == 4).  w: f32 [ne0] or NULL. */
 B200_API int b200_op_rms_norm(const b200_tensor *x, const float *w, const b200_tensor *dst, float eps, b200_stream_t stream);
 
+/* Fused RMS_NORM -> MUL(weight) pair as llama graphs emit it (src/llama.cpp:9130-9160 llm_build_norm): dst = norm(x) * w;
+ * norm_out (optional, contiguous rows) also receives norm(x), the intermediate node's value. */
+B200_API int b200_op_rms_norm_mul(const b200_tensor *x, const float *w, float *norm_out, const b200_tensor *dst, float eps, b200_stream_t stream);
+/* Fused UNARY(SILU) -> MUL pair of the gated FFN (src/llama.cpp:9416-9515 llm_build_ffn, LLM_FFN_SILU + LLM_FFN_PAR):
+ * dst = silu(gate) * up over n contiguous floats; act_out (optional) also receives silu(gate). */
+B200_API int b200_op_silu_mul(const float *gate, const float *up, float *act_out, float *dst, int64_t n, b200_stream_t stream);
+
 /* ADD / SUB / MUL / DIV with ggml broadcasting of src1 over src0 (ggml_can_repeat): f32 only.
  * replaces k_bin_bcast, ggml-cuda/binbcast.cu:26-120; semantics ggml_compute_forward_{add,sub,mul,div}_f32, ggml.c:10241-10900 */
 B200_API int b200_op_binary(int op, const b200_tensor *a, const b200_tensor *b, const b200_tensor *dst, b200_stream_t stream);
@@ -53,6 +60,10 @@ B200_API int b200_op_rope(const b200_tensor *x, const int32_t *pos, const float 
  * store; quantize_row_q8_0_ref arithmetic, ggml-quants.c:849-872).  For q8_0 destinations src rows must be contiguous.
  * replaces ggml-cuda/cpy.cu:34-440 */
 B200_API int b200_op_cpy(const b200_tensor *src, const b200_tensor *dst, b200_stream_t stream);
+/* Same, but the destination base pointer is read on the device from *dst_slot when the kernel runs (dst->data is ignored
+ * when dst_slot != NULL).  Used for the KV-cache store inside a replayed CUDA graph: the write position moves every token
+ * (reference: cudaGraphExecKernelNodeSetParams patching of the cpy nodes, ggml-cuda.cu:2593-2650). */
+B200_API int b200_op_cpy_indirect(const b200_tensor *src, const b200_tensor *dst, void *const *dst_slot, b200_stream_t stream);
 
 /* GET_ROWS: dst[i] = dequantise(src row ids[i]); src f32 / f16 / q4_0 / q8_0 / q4_K / q5_K / q6_K (K-quant token embeddings
  * stay on the device -- the reference falls back to the CPU for them, ggml-cuda.cu:3033-3047).

@@ -1,0 +1,334 @@
+// backend_graph.cu -- graph_compute of the B200 ggml backend: plan -> fuse -> (capture once) -> replay.
+//
+// Replaces ggml_backend_cuda_graph_compute (ggml-cuda.cu:2508-2823).  The reference walks the node list and launches one
+// kernel chain per node (plus a quantize_q8_1 launch per matmul), and patches the KV-store cpy nodes of its CUDA graph with
+// cudaGraphExecKernelNodeSetParams every token (:2593-2650).  Here:
+//   * plan:   the node list is lowered to a list of Steps.  Adjacent RMS_NORM -> MUL and SILU -> MUL pairs become one kernel;
+//             decode-regime MUL_MATs that read the same activation (Q/K/V, gate/up) are hoisted into one multi-job GEMV launch
+//             when no node in between touches the hoisted node's output bytes.
+//   * capture: the Step list is captured into one CUDA graph keyed by a hash over everything that is baked into kernel
+//             parameters (ops, shapes, strides, op_params, data pointers) EXCEPT the destination of CPY nodes: those read
+//             their base pointer from a device slot table that is refreshed by one small H2D copy before each replay, so the
+//             moving KV-cache write position does not invalidate the graph.
+//   * replay: cudaGraphLaunch.
+// There is no CPU fallback: a node supports_op said no to never reaches this file, and anything else aborts like the reference.
+#include <unordered_map>
+
+#include "backend_exec.h"
+
+namespace b200 {
+
+enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV_MULTI };
+
+struct Step {
+    int kind;
+    const ggml_tensor *n;               // the node (STEP_NODE), or the first node of the fused group
+    const ggml_tensor *n2;              // second node of a fused pair
+    std::vector<const ggml_tensor *> group;  // STEP_GEMV_MULTI members
+    int slot;                           // CPY nodes: index into the slot table, else -1
+};
+
+struct CachedGraph {
+    cudaGraphExec_t exec = nullptr;
+    int64_t launches = 0;  // kernels inside one replay
+    int n_slots = 0;
+    uint64_t last_used = 0;
+};
+
+struct GraphExec {
+    int device;
+    cudaStream_t stream;
+    void *scratch = nullptr;  size_t scratch_bytes = 0;
+    void *fa_ws = nullptr;    size_t fa_ws_bytes = 0;
+    void **slots_dev = nullptr;  int slots_cap = 0;
+    std::vector<void *> slots_host;
+    std::unordered_map<uint64_t, CachedGraph> cache;
+    uint64_t tick = 0;
+    std::vector<Step> steps;  // plan of the graph being computed (reused storage)
+};
+
+GraphExec *graph_exec_new(int device) {
+    GraphExec *g = new GraphExec();
+    g->device = device;
+    B200_CHECK_CUDA(cudaSetDevice(device));
+    B200_CHECK_CUDA(cudaStreamCreateWithFlags(&g->stream, cudaStreamNonBlocking));
+    return g;
+}
+
+static void drop_cache(GraphExec *g) {
+    for (auto &kv : g->cache) if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    g->cache.clear();
+}
+
+void graph_exec_free(GraphExec *g) {
+    if (!g) return;
+    cudaSetDevice(g->device);
+    cudaStreamSynchronize(g->stream);
+    drop_cache(g);
+    if (g->scratch) cudaFree(g->scratch);
+    if (g->fa_ws) cudaFree(g->fa_ws);
+    if (g->slots_dev) cudaFree(g->slots_dev);
+    cudaStreamDestroy(g->stream);
+    delete g;
+}
+
+cudaStream_t graph_exec_stream(GraphExec *g) { return g->stream; }
+
+// ------------------------------------------------------------------------------------------------ planning
+static bool is_view_op(int op) {
+    return op == GGML_OP_NONE || op == GGML_OP_RESHAPE || op == GGML_OP_VIEW || op == GGML_OP_PERMUTE || op == GGML_OP_TRANSPOSE;
+}
+static bool is_cpy_op(int op) { return op == GGML_OP_CPY || op == GGML_OP_DUP || op == GGML_OP_CONT; }
+
+static bool ranges_overlap(const void *a, size_t na, const void *b, size_t nb_) {
+    const char *pa = (const char *)a, *pb = (const char *)b;
+    return pa < pb + nb_ && pb < pa + na;
+}
+// does node `m` read or write any byte of [p, p+len)?
+static bool node_touches(const ggml_tensor *m, const void *p, size_t len) {
+    if (m->data && ranges_overlap(m->data, nbytes(m), p, len)) return true;
+    for (int i = 0; i < GGML_MAX_SRC; i++) {
+        const ggml_tensor *s = m->src[i];
+        if (s && s->data && ranges_overlap(s->data, nbytes(s), p, len)) return true;
+    }
+    return false;
+}
+
+static bool rms_mul_pair(const ggml_tensor *a, const ggml_tensor *b) {
+    if (a->op != GGML_OP_RMS_NORM || b->op != GGML_OP_MUL) return false;
+    const ggml_tensor *w = b->src[0] == a ? b->src[1] : (b->src[1] == a ? b->src[0] : nullptr);
+    if (!w || w->type != GGML_TYPE_F32 || !is_contiguous(w)) return false;
+    if (w->ne[0] != a->ne[0] || w->ne[1] != 1 || w->ne[2] != 1 || w->ne[3] != 1) return false;
+    return same_shape(a, b) && is_contiguous(a) && b->type == GGML_TYPE_F32 && b->nb[0] == 4 && a->src[0]->nb[0] == 4;
+}
+static bool silu_mul_pair(const ggml_tensor *a, const ggml_tensor *b) {
+    if (a->op != GGML_OP_UNARY || a->op_params[0] != GGML_UNARY_OP_SILU || b->op != GGML_OP_MUL) return false;
+    const ggml_tensor *u = b->src[0] == a ? b->src[1] : (b->src[1] == a ? b->src[0] : nullptr);
+    if (!u || u->type != GGML_TYPE_F32) return false;
+    return same_shape(a, b) && same_shape(a, u) && is_contiguous(a) && is_contiguous(b) && is_contiguous(u) && is_contiguous(a->src[0]);
+}
+
+// Lower cgraph -> Steps.  `done[i]` marks nodes already absorbed by an earlier fused step.
+static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
+    std::vector<Step> &steps = g->steps;
+    steps.clear();
+    const int n = cg->n_nodes;
+    std::vector<char> done((size_t)n, 0);
+    int n_slots = 0;
+    for (int i = 0; i < n; i++) {
+        if (done[i]) continue;
+        const ggml_tensor *a = cg->nodes[i];
+        if (is_view_op(a->op) || nelements(a) == 0) continue;
+        Step s;
+        s.kind = STEP_NODE; s.n = a; s.n2 = nullptr; s.slot = -1;
+        if (is_cpy_op(a->op)) {
+            s.slot = n_slots++;
+            steps.push_back(s);
+            continue;
+        }
+        if (g_use_fusion) {
+            // the partner of a pair is the next non-view node
+            int j = i + 1;
+            while (j < n && (done[j] || is_view_op(cg->nodes[j]->op))) j++;
+            if (j < n && rms_mul_pair(a, cg->nodes[j])) { s.kind = STEP_RMS_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
+            if (j < n && silu_mul_pair(a, cg->nodes[j])) { s.kind = STEP_SILU_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
+            if (mul_mat_fusable(a)) {
+                // siblings: later MUL_MATs with the same activation tensor, weight type and row stride; hoisting node j to
+                // position i is legal when no node in (i, j) reads or writes node j's output bytes (ggml-alloc reuses memory)
+                s.group.push_back(a);
+                const int horizon = i + 48 < n ? i + 48 : n;
+                for (int j2 = i + 1; j2 < horizon && s.group.size() < B200_GEMV_MAX_JOBS; j2++) {
+                    const ggml_tensor *b = cg->nodes[j2];
+                    if (done[j2] || !mul_mat_fusable(b)) continue;
+                    if (b->src[1] != a->src[1] || b->src[0]->type != a->src[0]->type || b->src[0]->nb[1] != a->src[0]->nb[1] || (a->ne[1] > 1 && b->nb[1] != a->nb[1])) continue;
+                    bool ok = true;
+                    const size_t len = nbytes(b);
+                    for (int m = i; m < j2 && ok; m++) ok = !node_touches(cg->nodes[m], b->data, len);
+                    if (!ok) continue;
+                    s.group.push_back(b);
+                    done[j2] = 1;
+                }
+                if (s.group.size() > 1) { s.kind = STEP_GEMV_MULTI; steps.push_back(s); continue; }
+                s.group.clear();
+            }
+        }
+        steps.push_back(s);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ graph key
+static inline void mix(uint64_t &h, uint64_t v) {
+    h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
+    h *= 0xff51afd7ed558ccdull;
+    h ^= h >> 32;
+}
+static void hash_tensor(uint64_t &h, const ggml_tensor *t, bool with_data) {
+    mix(h, (uint64_t)t->type | ((uint64_t)t->op << 32));
+    for (int i = 0; i < 4; i++) { mix(h, (uint64_t)t->ne[i]); mix(h, (uint64_t)t->nb[i]); }
+    if (with_data) mix(h, (uint64_t)(uintptr_t)t->data);
+}
+static uint64_t graph_key(const ggml_cgraph *cg) {
+    uint64_t h = 0x243f6a8885a308d3ull;
+    mix(h, (uint64_t)cg->n_nodes);
+    mix(h, (uint64_t)g_use_fusion);
+    for (int i = 0; i < cg->n_nodes; i++) {
+        const ggml_tensor *t = cg->nodes[i];
+        if (is_view_op(t->op)) continue;  // views matter only through the tensors that consume them (hashed as srcs)
+        const bool cpy = is_cpy_op(t->op);
+        hash_tensor(h, t, !cpy);
+        const uint64_t *op = (const uint64_t *)t->op_params;
+        for (int k = 0; k < GGML_MAX_OP_PARAMS / 8; k++) mix(h, op[k]);
+        for (int k = 0; k < GGML_MAX_SRC; k++) {
+            const ggml_tensor *s = t->src[k];
+            if (!s) { mix(h, 0); continue; }
+            // CPY(a, b): src[1] is the destination view, its address moves with the KV head and goes through the slot table
+            hash_tensor(h, s, !(cpy && k == 1));
+        }
+    }
+    return h;
+}
+
+// ------------------------------------------------------------------------------------------------ execution
+static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
+    switch (s.kind) {
+        case STEP_NODE:
+            run_node(x, s.n, s.slot >= 0 ? (void *const *)(g->slots_dev + s.slot) : nullptr);
+            return;
+        case STEP_RMS_MUL: {
+            const ggml_tensor *a = s.n, *b = s.n2;
+            const ggml_tensor *w = b->src[0] == a ? b->src[1] : b->src[0];
+            float eps;
+            memcpy(&eps, a->op_params, 4);
+            b200_tensor tx = as_b200(a->src[0]), td = as_b200(b);
+            // the RMS_NORM node's own value is still written: another node may read it, and ggml-alloc may have aliased it
+            // with the MUL output (in-place), in which case norm_out == dst and the kernel writes dst last
+            float *norm_out = a->data == b->data ? nullptr : (float *)a->data;
+            B200_CHECK_RC(b200_op_rms_norm_mul(&tx, (const float *)w->data, norm_out, &td, eps, x.stream));
+            x.launches++;
+            return;
+        }
+        case STEP_SILU_MUL: {
+            const ggml_tensor *a = s.n, *b = s.n2;
+            const ggml_tensor *u = b->src[0] == a ? b->src[1] : b->src[0];
+            float *act_out = a->data == b->data ? nullptr : (float *)a->data;
+            B200_CHECK_RC(b200_op_silu_mul((const float *)a->src[0]->data, (const float *)u->data, act_out, (float *)b->data, nelements(b), x.stream));
+            x.launches++;
+            return;
+        }
+        case STEP_GEMV_MULTI: {
+            b200_gemv_job jobs[B200_GEMV_MAX_JOBS];
+            const ggml_tensor *a = s.group[0];
+            const ggml_tensor *act = a->src[1];
+            int nj = 0;
+            for (const ggml_tensor *m : s.group) {
+                jobs[nj].W = m->src[0]->data; jobs[nj].X = (const float *)act->data; jobs[nj].dst = (float *)m->data;
+                jobs[nj].M = m->src[0]->ne[1]; jobs[nj].id_index = -1; jobs[nj]._pad = 0;
+                nj++;
+            }
+            B200_CHECK_RC(b200_mul_mat_vec_q_multi(a->src[0]->type, jobs, nj, a->src[0]->nb[1], (int64_t)(act->nb[1] / 4), (int64_t)(a->nb[1] / 4),
+                                                   a->src[0]->ne[0], act->ne[1], nullptr, 0, 0, x.stream));
+            x.launches++;
+            return;
+        }
+    }
+}
+
+static void ensure_workspaces(GraphExec *g, const ggml_cgraph *cg, int n_slots) {
+    size_t fa = 0, sc = 0;
+    for (int i = 0; i < cg->n_nodes; i++) {
+        const ggml_tensor *t = cg->nodes[i];
+        if (t->op == GGML_OP_FLASH_ATTN_EXT) { const size_t b = node_fa_workspace(t); if (b > fa) fa = b; }
+        if (t->op == GGML_OP_MUL_MAT) { const size_t b = node_scratch_bytes(t); if (b > sc) sc = b; }
+    }
+    // growing a workspace moves it: every captured graph has the old pointer baked in
+    if (fa > g->fa_ws_bytes) {
+        B200_CHECK_CUDA(cudaStreamSynchronize(g->stream));
+        drop_cache(g);
+        if (g->fa_ws) B200_CHECK_CUDA(cudaFree(g->fa_ws));
+        fa += fa / 4;
+        B200_CHECK_CUDA(cudaMalloc(&g->fa_ws, fa));
+        B200_CHECK_CUDA(cudaMemsetAsync(g->fa_ws, 0, fa, g->stream));
+        g->fa_ws_bytes = fa;
+    }
+    if (sc > g->scratch_bytes) {
+        B200_CHECK_CUDA(cudaStreamSynchronize(g->stream));
+        drop_cache(g);
+        if (g->scratch) B200_CHECK_CUDA(cudaFree(g->scratch));
+        B200_CHECK_CUDA(cudaMalloc(&g->scratch, sc));
+        g->scratch_bytes = sc;
+    }
+    if (n_slots > g->slots_cap) {
+        B200_CHECK_CUDA(cudaStreamSynchronize(g->stream));
+        drop_cache(g);
+        if (g->slots_dev) B200_CHECK_CUDA(cudaFree(g->slots_dev));
+        g->slots_cap = n_slots + 64;
+        B200_CHECK_CUDA(cudaMalloc((void **)&g->slots_dev, sizeof(void *) * (size_t)g->slots_cap));
+    }
+}
+
+static int count_cpy(const ggml_cgraph *cg) {
+    int c = 0;
+    for (int i = 0; i < cg->n_nodes; i++) if (is_cpy_op(cg->nodes[i]->op) && nelements(cg->nodes[i]) != 0) c++;
+    return c;
+}
+
+// refresh the CPY destination slots (pageable source: the runtime stages it before returning, so the vector is reusable)
+static void upload_slots(GraphExec *g, const ggml_cgraph *cg, int n_slots) {
+    if (n_slots == 0) return;
+    g->slots_host.resize((size_t)n_slots);
+    int k = 0;
+    for (int i = 0; i < cg->n_nodes; i++) {
+        const ggml_tensor *t = cg->nodes[i];
+        if (is_cpy_op(t->op) && nelements(t) != 0) g->slots_host[(size_t)k++] = t->data;
+    }
+    B200_CHECK_CUDA(cudaMemcpyAsync(g->slots_dev, g->slots_host.data(), sizeof(void *) * (size_t)n_slots, cudaMemcpyHostToDevice, g->stream));
+}
+
+enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cg) {
+    if (cg->n_nodes == 0) return GGML_STATUS_SUCCESS;
+    const int n_slots = count_cpy(cg);
+    ensure_workspaces(g, cg, n_slots);
+    upload_slots(g, cg, n_slots);
+    ExecCtx x;
+    x.stream = g->stream; x.scratch = g->scratch; x.scratch_bytes = g->scratch_bytes; x.fa_ws = g->fa_ws; x.fa_ws_bytes = g->fa_ws_bytes; x.launches = 0;
+
+    // graphs with a handful of nodes (op tests, K-shift) are not worth an instantiate
+    const bool use_graph = g_use_graphs && cg->n_nodes >= 16;
+    if (!use_graph) {
+        plan_steps(g, cg);
+        for (const Step &s : g->steps) run_step(g, x, s);
+        g_stat_launches += x.launches;
+        return GGML_STATUS_SUCCESS;
+    }
+    const uint64_t key = graph_key(cg);
+    g->tick++;
+    auto it = g->cache.find(key);
+    if (it == g->cache.end()) {
+        if (g->cache.size() >= 24) {  // prefill with ever-changing batch sizes must not leak executables: evict the oldest
+            auto old = g->cache.begin();
+            for (auto c = g->cache.begin(); c != g->cache.end(); ++c) if (c->second.last_used < old->second.last_used) old = c;
+            B200_CHECK_CUDA(cudaStreamSynchronize(g->stream));
+            cudaGraphExecDestroy(old->second.exec);
+            g->cache.erase(old);
+        }
+        plan_steps(g, cg);
+        cudaGraph_t graph = nullptr;
+        B200_CHECK_CUDA(cudaStreamBeginCapture(g->stream, cudaStreamCaptureModeThreadLocal));
+        for (const Step &s : g->steps) run_step(g, x, s);
+        B200_CHECK_CUDA(cudaStreamEndCapture(g->stream, &graph));
+        CachedGraph c;
+        B200_CHECK_CUDA(cudaGraphInstantiate(&c.exec, graph, 0));
+        B200_CHECK_CUDA(cudaGraphDestroy(graph));
+        c.launches = x.launches;
+        c.n_slots = n_slots;
+        it = g->cache.emplace(key, c).first;
+        g_stat_captures++;
+    }
+    it->second.last_used = g->tick;
+    B200_CHECK_CUDA(cudaGraphLaunch(it->second.exec, g->stream));
+    g_stat_replays++;
+    g_stat_launches += it->second.launches;
+    return GGML_STATUS_SUCCESS;
+}
+
+}  // namespace b200

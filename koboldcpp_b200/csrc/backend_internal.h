@@ -1,0 +1,137 @@
+// backend_internal.h -- shared declarations of the ggml_backend glue (buffers, device/reg, graph executor).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b200_ggml_backend.h"
+#include "../../include/b200_ggml_ops.h"
+
+namespace b200 {
+
+// ---- the type traits the backend needs (ggml.c:740-1080 type_traits[]: blck_size, type_size) without linking ggml
+struct TypeTraits { int blck; int size; };
+inline TypeTraits type_traits(int t) {
+    switch (t) {
+        case GGML_TYPE_F32: return {1, 4};
+        case GGML_TYPE_F16: return {1, 2};
+        case GGML_TYPE_BF16: return {1, 2};
+        case GGML_TYPE_Q4_0: return {32, 18};
+        case GGML_TYPE_Q4_1: return {32, 20};
+        case GGML_TYPE_Q5_0: return {32, 22};
+        case GGML_TYPE_Q5_1: return {32, 24};
+        case GGML_TYPE_Q8_0: return {32, 34};
+        case GGML_TYPE_Q8_1: return {32, 36};
+        case GGML_TYPE_Q2_K: return {256, 84};
+        case GGML_TYPE_Q3_K: return {256, 110};
+        case GGML_TYPE_Q4_K: return {256, 144};
+        case GGML_TYPE_Q5_K: return {256, 176};
+        case GGML_TYPE_Q6_K: return {256, 210};
+        case GGML_TYPE_Q8_K: return {256, 292};
+        case GGML_TYPE_I8: return {1, 1};
+        case GGML_TYPE_I16: return {1, 2};
+        case GGML_TYPE_I32: return {1, 4};
+        case GGML_TYPE_I64: return {1, 8};
+        case GGML_TYPE_F64: return {1, 8};
+        default: return {0, 0};
+    }
+}
+inline bool is_quantized(int t) { return type_traits(t).blck > 1; }
+inline int64_t nelements(const ggml_tensor *t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
+inline int64_t nrows(const ggml_tensor *t) { return t->ne[1] * t->ne[2] * t->ne[3]; }
+inline size_t row_size(int type, int64_t ne) { const TypeTraits tt = type_traits(type); return tt.blck ? (size_t)(ne / tt.blck) * tt.size : 0; }
+// ggml_nbytes, ggml.c:3544-3564
+inline size_t nbytes(const ggml_tensor *t) {
+    const TypeTraits tt = type_traits(t->type);
+    if (!tt.blck) return 0;
+    size_t n;
+    if (tt.blck == 1) {
+        n = tt.size;
+        for (int i = 0; i < GGML_MAX_DIMS; i++) n += (size_t)(t->ne[i] - 1) * t->nb[i];
+    } else {
+        n = (size_t)t->ne[0] * t->nb[0] / tt.blck;
+        for (int i = 1; i < GGML_MAX_DIMS; i++) n += (size_t)(t->ne[i] - 1) * t->nb[i];
+    }
+    return n;
+}
+inline bool is_contiguous(const ggml_tensor *t) {
+    const TypeTraits tt = type_traits(t->type);
+    if (!tt.blck) return false;
+    return t->nb[0] == (size_t)tt.size && t->nb[1] == t->nb[0] * (size_t)(t->ne[0] / tt.blck) && t->nb[2] == t->nb[1] * (size_t)t->ne[1] &&
+           t->nb[3] == t->nb[2] * (size_t)t->ne[2];
+}
+inline bool same_shape(const ggml_tensor *a, const ggml_tensor *b) {
+    return a->ne[0] == b->ne[0] && a->ne[1] == b->ne[1] && a->ne[2] == b->ne[2] && a->ne[3] == b->ne[3];
+}
+inline b200_tensor as_b200(const ggml_tensor *t) {
+    b200_tensor d;
+    d.data = t->data;
+    d.type = (int32_t)t->type;
+    d._pad = 0;
+    for (int i = 0; i < 4; i++) { d.ne[i] = t->ne[i]; d.nb[i] = t->nb[i]; }
+    return d;
+}
+
+// error convention of the reference backend: a CUDA failure is fatal (ggml_cuda_error -> GGML_ABORT, ggml-cuda.cu:63-73)
+[[noreturn]] void backend_abort(const char *what, const char *detail);
+#define B200_CHECK_CUDA(call)                                                          \
+    do {                                                                               \
+        cudaError_t e__ = (call);                                                      \
+        if (e__ != cudaSuccess) ::b200::backend_abort(#call, cudaGetErrorString(e__)); \
+    } while (0)
+#define B200_CHECK_RC(call)                                                  \
+    do {                                                                     \
+        int rc__ = (call);                                                   \
+        if (rc__ != 0) ::b200::backend_abort(#call, b200_last_error());      \
+    } while (0)
+
+// ---- contexts hanging off the vtable objects
+struct DeviceCtx {
+    int device;
+    std::string name, description;
+};
+struct BuftCtx {
+    int device;
+    std::string name;
+};
+struct BufferCtx {
+    int   device;
+    void *base;
+    size_t size;
+};
+struct SplitBuftCtx {
+    float split[GGML_B200_MAX_DEVICES + 1];  // cumulative fractions, split[n_dev] = 1
+    int   n_dev;
+};
+// tensor->extra of a tensor living in a split buffer: one row slice per device
+struct SplitTensorExtra {
+    void   *data[GGML_B200_MAX_DEVICES];
+    int64_t row_low[GGML_B200_MAX_DEVICES], row_high[GGML_B200_MAX_DEVICES];
+};
+
+int device_count();
+ggml_backend_dev_t device_get(int i);
+bool buft_is_b200_device(ggml_backend_buffer_type_t buft);
+bool buft_is_b200_split(ggml_backend_buffer_type_t buft);
+bool buft_is_b200_host(ggml_backend_buffer_type_t buft);
+bool buffer_is_b200_device(ggml_backend_buffer_t buf);
+
+// graph executor (backend_graph.cu)
+struct GraphExec;
+GraphExec *graph_exec_new(int device);
+void graph_exec_free(GraphExec *g);
+cudaStream_t graph_exec_stream(GraphExec *g);
+enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cgraph);
+bool op_supported(int device, const ggml_tensor *op);
+
+extern bool g_use_graphs, g_use_fusion;
+extern int64_t g_stat_launches, g_stat_replays, g_stat_captures;
+
+}  // namespace b200

@@ -1,0 +1,265 @@
+// backend_ops.cu -- per-node dispatch of the B200 ggml backend: supports_op (exact: graph_compute aborts on anything it
+// said yes to and cannot run, like the reference, ggml-cuda.cu:2671-2675) and the node -> C-ABI kernel mapping.
+// Replaces ggml_cuda_compute_forward / ggml_backend_cuda_device_supports_op (ggml-cuda.cu:2145-2340, 2959-3185).
+#include "backend_exec.h"
+
+namespace b200 {
+
+static bool is_hot_weight_type(int t) {
+    return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q5_K || t == GGML_TYPE_Q6_K;
+}
+static bool rows_contiguous_f32(const ggml_tensor *t) { return t->type == GGML_TYPE_F32 && t->nb[0] == 4; }
+static bool in_split_buffer(const ggml_tensor *t) { return t->buffer && buft_is_b200_split(t->buffer->buft); }
+
+// MUL_MAT with quantised weights: plain 2-D weight, activations [K, N] with contiguous 16-byte aligned rows
+static bool mul_mat_q_ok(const ggml_tensor *w, const ggml_tensor *x, const ggml_tensor *dst) {
+    if (!is_hot_weight_type(w->type) || x->type != GGML_TYPE_F32 || dst->type != GGML_TYPE_F32) return false;
+    if (w->ne[2] != 1 || w->ne[3] != 1 || x->ne[2] != 1 || x->ne[3] != 1) return false;
+    if (x->nb[0] != 4 || dst->nb[0] != 4 || (x->nb[1] & 15) || (dst->nb[1] & 3)) return false;
+    if (w->nb[0] != (size_t)type_traits(w->type).size || w->nb[1] < row_size(w->type, w->ne[0])) return false;
+    if ((w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q5_K) && (w->nb[1] & 15)) return false;
+    return w->ne[0] == x->ne[0] && dst->ne[0] == w->ne[1] && dst->ne[1] == x->ne[1];
+}
+
+bool op_supported(int /*device*/, const ggml_tensor *op) {
+    const ggml_tensor *s0 = op->src[0], *s1 = op->src[1];
+    for (int i = 0; i < GGML_MAX_SRC; i++) {
+        // split tensors can only be the weight of a MUL_MAT
+        if (op->src[i] && in_split_buffer(op->src[i]) && !(op->op == GGML_OP_MUL_MAT && i == 0)) return false;
+    }
+    switch (op->op) {
+        case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT:
+            if (!s0 || !s1) return false;
+            if (is_quantized(s0->type)) return mul_mat_q_ok(s0, s1, op);
+            return (s0->type == GGML_TYPE_F32 || s0->type == GGML_TYPE_F16) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
+                   s0->nb[0] == (size_t)type_traits(s0->type).size && s1->nb[0] == 4 && !in_split_buffer(s0);
+        case GGML_OP_MUL_MAT_ID: {
+            const ggml_tensor *ids = op->src[2];
+            if (!s0 || !s1 || !ids) return false;
+            if (!is_hot_weight_type(s0->type) || s1->type != GGML_TYPE_F32 || ids->type != GGML_TYPE_I32 || op->type != GGML_TYPE_F32) return false;
+            if (s1->nb[0] != 4 || ((s1->nb[1] | s1->nb[2]) & 15) || op->nb[0] != 4 || ids->nb[0] != 4 || (ids->nb[1] & 3)) return false;
+            if (s0->ne[3] != 1 || s1->ne[3] != 1) return false;
+            if ((s0->type == GGML_TYPE_Q4_K || s0->type == GGML_TYPE_Q5_K) && ((s0->nb[1] | s0->nb[2]) & 15)) return false;
+            return ids->ne[0] * ids->ne[1] <= B200_GEMV_MAX_JOBS;  // decode regime (T * n_used <= 16)
+        }
+        case GGML_OP_FLASH_ATTN_EXT: {
+            const ggml_tensor *k = op->src[1], *v = op->src[2], *m = op->src[3];
+            if (!s0 || !k || !v) return false;
+            if (s0->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || s0->nb[0] != 4) return false;
+            if (k->type != v->type || (k->type != GGML_TYPE_F16 && k->type != GGML_TYPE_Q8_0)) return false;
+            if (s0->ne[0] != 64 && s0->ne[0] != 128) return false;
+            if (s0->ne[3] != 1 || k->ne[3] != 1 || v->ne[3] != 1 || k->ne[2] == 0 || s0->ne[2] % k->ne[2]) return false;
+            if (m && (m->type != GGML_TYPE_F16 || m->nb[0] != 2)) return false;
+            const size_t al = k->type == GGML_TYPE_F16 ? 15 : (s0->ne[0] == 128 ? 7 : 3);
+            if ((k->nb[1] | k->nb[2] | v->nb[1] | v->nb[2]) & al) return false;
+            return ((s0->nb[1] | s0->nb[2]) & 15) == 0 && is_contiguous(op);
+        }
+        case GGML_OP_RMS_NORM:
+            return s0 && rows_contiguous_f32(s0) && rows_contiguous_f32(op);
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV:
+            return s0 && s1 && s0->type == GGML_TYPE_F32 && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32;
+        case GGML_OP_SQR: case GGML_OP_SCALE: case GGML_OP_CLAMP:
+            return s0 && s0->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && is_contiguous(s0) && is_contiguous(op);
+        case GGML_OP_UNARY: {
+            if (!s0 || s0->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || !is_contiguous(s0) || !is_contiguous(op)) return false;
+            switch (op->op_params[0]) {
+                case GGML_UNARY_OP_SILU: case GGML_UNARY_OP_GELU: case GGML_UNARY_OP_GELU_QUICK: case GGML_UNARY_OP_RELU:
+                case GGML_UNARY_OP_TANH: case GGML_UNARY_OP_SIGMOID: return true;
+                default: return false;
+            }
+        }
+        case GGML_OP_ROPE:
+            return s0 && s1 && rows_contiguous_f32(s0) && rows_contiguous_f32(op) && s1->type == GGML_TYPE_I32 && (op->op_params[2] & ~GGML_ROPE_TYPE_NEOX) == 0 &&
+                   (!op->src[2] || op->src[2]->type == GGML_TYPE_F32);
+        case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
+            if (!s0) return false;
+            const int a = s0->type, b = op->type;
+            if (a == GGML_TYPE_F32 && b == GGML_TYPE_Q8_0) return s0->nb[0] == 4 && s0->ne[0] % 32 == 0 && op->ne[0] % 32 == 0 && ((s0->nb[1] | s0->nb[2] | s0->nb[3]) & 15) == 0;
+            if ((a == GGML_TYPE_F32 || a == GGML_TYPE_F16) && (b == GGML_TYPE_F32 || b == GGML_TYPE_F16)) return true;
+            if (a == GGML_TYPE_I32 && b == GGML_TYPE_I32) return true;
+            return a == b && is_contiguous(s0) && is_contiguous(op);
+        }
+        case GGML_OP_GET_ROWS:
+            return s0 && s1 && s1->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 &&
+                   (s0->type == GGML_TYPE_F32 || s0->type == GGML_TYPE_F16 || is_hot_weight_type(s0->type));
+        case GGML_OP_SOFT_MAX:
+            return s0 && rows_contiguous_f32(s0) && rows_contiguous_f32(op) && s0->ne[0] <= 50 * 1024 &&
+                   (!s1 || s1->type == GGML_TYPE_F16 || s1->type == GGML_TYPE_F32);
+        case GGML_OP_ARGSORT:
+            return s0 && s0->type == GGML_TYPE_F32 && is_contiguous(s0) && s0->ne[0] <= 1024;
+        case GGML_OP_SUM_ROWS:
+            return s0 && rows_contiguous_f32(s0);
+        default:
+            return false;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ single-node execution
+static void run_mul_mat(ExecCtx &x, const ggml_tensor *n) {
+    const ggml_tensor *w = n->src[0], *a = n->src[1];
+    if (!is_quantized(w->type)) {
+        b200_tensor tw = as_b200(w), ta = as_b200(a), td = as_b200(n);
+        B200_CHECK_RC(b200_op_mul_mat_float(&tw, &ta, &td, x.stream));
+        x.launches++;
+        return;
+    }
+    const int64_t K = w->ne[0], M = w->ne[1], N = a->ne[1];
+    const int64_t xs = (int64_t)(a->nb[1] / 4), ds = (int64_t)(n->nb[1] / 4);
+    // N <= 8: the HBM-bound GEMV.  Larger batches: tensor-core GEMM when built, else the GEMV over column groups of 8
+    // (every group re-streams the weights; correct, and only the stop-gap for prefill until b200_mul_mat_q lands)
+    if (N > 8) {
+        const size_t ws = b200_mul_mat_q_workspace_bytes(w->type, K, M, N);
+        if (ws <= x.scratch_bytes) {
+            const int rc = b200_mul_mat_q(w->type, w->data, w->nb[1], (const float *)a->data, xs, (float *)n->data, ds, K, M, N, x.scratch, x.scratch_bytes, x.stream);
+            if (rc == B200_OK) { x.launches++; return; }
+            if (rc != B200_ERR_UNSUPPORTED) backend_abort("b200_mul_mat_q", b200_last_error());
+        }
+    }
+    for (int64_t c0 = 0; c0 < N; c0 += 8) {
+        const int64_t nc = N - c0 < 8 ? N - c0 : 8;
+        B200_CHECK_RC(b200_mul_mat_vec_q(w->type, w->data, w->nb[1], (const float *)a->data + c0 * xs, xs, (float *)n->data + c0 * ds, ds, K, M, nc, x.stream));
+        x.launches++;
+    }
+}
+
+static void run_mul_mat_id(ExecCtx &x, const ggml_tensor *n) {
+    const ggml_tensor *as = n->src[0], *b = n->src[1], *ids = n->src[2];
+    // as [K, M, n_expert]; b [K, n_b_rows, T]; ids [n_used, T]; dst [M, n_used, T]   (ggml.c:5693-5729)
+    B200_CHECK_RC(b200_mul_mat_id_vec_q(as->type, as->data, as->nb[1], as->nb[2], (int32_t)as->ne[2], (const int32_t *)ids->data, (int64_t)(ids->nb[1] / 4),
+                                        (const float *)b->data, (int64_t)(b->nb[1] / 4), (int64_t)(b->nb[2] / 4), (float *)n->data, (int64_t)(n->nb[1] / 4),
+                                        (int64_t)(n->nb[2] / 4), as->ne[0], as->ne[1], ids->ne[0], b->ne[1], ids->ne[1], x.stream));
+    x.launches++;
+}
+
+static void run_flash_attn(ExecCtx &x, const ggml_tensor *n) {
+    const ggml_tensor *q = n->src[0], *k = n->src[1], *v = n->src[2], *m = n->src[3];
+    b200_fattn_args a;
+    memset(&a, 0, sizeof(a));
+    a.q = q->data; a.k = k->data; a.v = v->data; a.mask = m ? m->data : nullptr; a.dst = (float *)n->data;
+    a.D = q->ne[0]; a.N = q->ne[1]; a.n_head = q->ne[2]; a.n_head_kv = k->ne[2]; a.n_kv = k->ne[1];
+    a.type_k = k->type; a.type_v = v->type;
+    a.q_nb1 = q->nb[1]; a.q_nb2 = q->nb[2]; a.k_nb1 = k->nb[1]; a.k_nb2 = k->nb[2]; a.v_nb1 = v->nb[1]; a.v_nb2 = v->nb[2];
+    a.mask_nb1 = m ? m->nb[1] : 0;
+    memcpy(&a.scale, (const float *)n->op_params + 0, 4);
+    memcpy(&a.max_bias, (const float *)n->op_params + 1, 4);
+    memcpy(&a.logit_softcap, (const float *)n->op_params + 2, 4);
+    const size_t need = b200_flash_attn_workspace_bytes(&a);
+    if (need > x.fa_ws_bytes) backend_abort("flash_attn workspace", "workspace smaller than planned");
+    B200_CHECK_RC(b200_flash_attn_ext(&a, x.fa_ws, x.fa_ws_bytes, x.stream));
+    x.launches++;
+}
+
+size_t node_fa_workspace(const ggml_tensor *n) {
+    if (n->op != GGML_OP_FLASH_ATTN_EXT) return 0;
+    const ggml_tensor *q = n->src[0], *k = n->src[1], *v = n->src[2];
+    b200_fattn_args a;
+    memset(&a, 0, sizeof(a));
+    a.q = q->data; a.k = k->data; a.v = v->data; a.dst = (float *)n->data;
+    a.D = q->ne[0]; a.N = q->ne[1]; a.n_head = q->ne[2]; a.n_head_kv = k->ne[2]; a.n_kv = k->ne[1];
+    a.type_k = k->type; a.type_v = v->type;
+    a.q_nb1 = q->nb[1]; a.q_nb2 = q->nb[2]; a.k_nb1 = k->nb[1]; a.k_nb2 = k->nb[2]; a.v_nb1 = v->nb[1]; a.v_nb2 = v->nb[2];
+    return b200_flash_attn_workspace_bytes(&a);
+}
+
+size_t node_scratch_bytes(const ggml_tensor *n) {
+    if (n->op != GGML_OP_MUL_MAT || !n->src[0] || !n->src[1] || !is_quantized(n->src[0]->type) || n->src[1]->ne[1] <= 8) return 0;
+    return b200_mul_mat_q_workspace_bytes(n->src[0]->type, n->src[0]->ne[0], n->src[0]->ne[1], n->src[1]->ne[1]);
+}
+
+static int unary_code(int ggml_unary) {
+    switch (ggml_unary) {
+        case GGML_UNARY_OP_SILU: return B200_UN_SILU;
+        case GGML_UNARY_OP_GELU: return B200_UN_GELU;
+        case GGML_UNARY_OP_GELU_QUICK: return B200_UN_GELU_QUICK;
+        case GGML_UNARY_OP_RELU: return B200_UN_RELU;
+        case GGML_UNARY_OP_TANH: return B200_UN_TANH;
+        case GGML_UNARY_OP_SIGMOID: return B200_UN_SIGMOID;
+    }
+    return -1;
+}
+
+void run_node(ExecCtx &x, const ggml_tensor *n, void *const *dst_slot) {
+    const ggml_tensor *s0 = n->src[0], *s1 = n->src[1];
+    switch (n->op) {
+        case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
+            return;
+        case GGML_OP_MUL_MAT: run_mul_mat(x, n); return;
+        case GGML_OP_MUL_MAT_ID: run_mul_mat_id(x, n); return;
+        case GGML_OP_FLASH_ATTN_EXT: run_flash_attn(x, n); return;
+        case GGML_OP_RMS_NORM: {
+            float eps;
+            memcpy(&eps, n->op_params, 4);
+            b200_tensor a = as_b200(s0), d = as_b200(n);
+            B200_CHECK_RC(b200_op_rms_norm(&a, nullptr, &d, eps, x.stream));
+            break;
+        }
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV: {
+            const int op = n->op == GGML_OP_ADD ? B200_BIN_ADD : n->op == GGML_OP_SUB ? B200_BIN_SUB : n->op == GGML_OP_MUL ? B200_BIN_MUL : B200_BIN_DIV;
+            b200_tensor a = as_b200(s0), b = as_b200(s1), d = as_b200(n);
+            B200_CHECK_RC(b200_op_binary(op, &a, &b, &d, x.stream));
+            break;
+        }
+        case GGML_OP_SQR: case GGML_OP_SCALE: case GGML_OP_CLAMP: case GGML_OP_UNARY: {
+            float p0 = 0, p1 = 0;
+            int op;
+            if (n->op == GGML_OP_SQR) op = B200_UN_SQR;
+            else if (n->op == GGML_OP_SCALE) { op = B200_UN_SCALE; memcpy(&p0, n->op_params, 4); }
+            else if (n->op == GGML_OP_CLAMP) { op = B200_UN_CLAMP; memcpy(&p0, n->op_params, 4); memcpy(&p1, (const float *)n->op_params + 1, 4); }
+            else op = unary_code(n->op_params[0]);
+            b200_tensor a = as_b200(s0), d = as_b200(n);
+            B200_CHECK_RC(b200_op_unary(op, &a, &d, p0, p1, x.stream));
+            break;
+        }
+        case GGML_OP_ROPE: {
+            b200_rope_params rp;
+            rp.n_dims = n->op_params[1]; rp.mode = n->op_params[2]; rp.n_ctx_orig = n->op_params[4];
+            memcpy(&rp.freq_base, n->op_params + 5, 4); memcpy(&rp.freq_scale, n->op_params + 6, 4); memcpy(&rp.ext_factor, n->op_params + 7, 4);
+            memcpy(&rp.attn_factor, n->op_params + 8, 4); memcpy(&rp.beta_fast, n->op_params + 9, 4); memcpy(&rp.beta_slow, n->op_params + 10, 4);
+            b200_tensor a = as_b200(s0), d = as_b200(n);
+            B200_CHECK_RC(b200_op_rope(&a, (const int32_t *)s1->data, n->src[2] ? (const float *)n->src[2]->data : nullptr, &d, &rp, x.stream));
+            break;
+        }
+        case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
+            // CPY(a, b): the result aliases b (ggml.c:5982-6005): node->data == src[1]->data
+            b200_tensor a = as_b200(s0), d = as_b200(n);
+            B200_CHECK_RC(b200_op_cpy_indirect(&a, &d, dst_slot, x.stream));
+            break;
+        }
+        case GGML_OP_GET_ROWS: {
+            b200_tensor a = as_b200(s0), i = as_b200(s1), d = as_b200(n);
+            B200_CHECK_RC(b200_op_get_rows(&a, &i, &d, x.stream));
+            break;
+        }
+        case GGML_OP_SOFT_MAX: {
+            float scale = 1.0f, max_bias = 0.0f;
+            memcpy(&scale, n->op_params, 4);
+            memcpy(&max_bias, (const float *)n->op_params + 1, 4);
+            b200_tensor a = as_b200(s0), d = as_b200(n), m;
+            if (s1) m = as_b200(s1);
+            B200_CHECK_RC(b200_op_soft_max(&a, s1 ? &m : nullptr, &d, scale, max_bias, x.stream));
+            break;
+        }
+        case GGML_OP_ARGSORT: {
+            b200_tensor a = as_b200(s0), d = as_b200(n);
+            B200_CHECK_RC(b200_op_argsort(&a, &d, n->op_params[0], x.stream));
+            break;
+        }
+        case GGML_OP_SUM_ROWS: {
+            b200_tensor a = as_b200(s0), d = as_b200(n);
+            B200_CHECK_RC(b200_op_sum_rows(&a, &d, x.stream));
+            break;
+        }
+        default:
+            backend_abort("graph_compute", "op not supported by the B200 backend (supports_op must have said so)");
+    }
+    x.launches++;
+}
+
+bool mul_mat_fusable(const ggml_tensor *n) {
+    return n->op == GGML_OP_MUL_MAT && n->src[0] && n->src[1] && is_quantized(n->src[0]->type) && mul_mat_q_ok(n->src[0], n->src[1], n) &&
+           n->src[1]->ne[1] <= 4 && !in_split_buffer(n->src[0]);
+}
+
+}  // namespace b200

@@ -58,15 +58,16 @@ __device__ __forceinline__ float block_max(float v, float *sh) {
 }
 
 // ------------------------------------------------------------------------------------------------ RMS_NORM (+MUL)
-__global__ void rms_norm_kernel(TD x, const float *__restrict__ w, TD dst, float eps) {
+__global__ void rms_norm_kernel(TD x, const float *__restrict__ w, TD dst, float eps, float *__restrict__ norm_out) {
     __shared__ float sh[32];
     const int64_t r = blockIdx.x;
     const int64_t i1 = r % x.ne[1], i2 = (r / x.ne[1]) % x.ne[2], i3 = r / (x.ne[1] * x.ne[2]);
     const float *xr = (const float *)(x.data + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
     float *yr = (float *)(dst.data + i1 * dst.nb[1] + i2 * dst.nb[2] + i3 * dst.nb[3]);
     const int n = (int)x.ne[0];
+    float *nr = norm_out ? norm_out + r * n : nullptr;  // contiguous rows
     float s = 0.f;
-    const bool vec = (n & 3) == 0 && (((uintptr_t)xr | (uintptr_t)yr) & 15) == 0;
+    const bool vec = (n & 3) == 0 && (((uintptr_t)xr | (uintptr_t)yr | (uintptr_t)nr) & 15) == 0;
     if (vec) {
         for (int i = threadIdx.x; i < n / 4; i += blockDim.x) {
             const float4 v = reinterpret_cast<const float4 *>(xr)[i];
@@ -81,6 +82,7 @@ __global__ void rms_norm_kernel(TD x, const float *__restrict__ w, TD dst, float
         for (int i = threadIdx.x; i < n / 4; i += blockDim.x) {
             float4 v = reinterpret_cast<const float4 *>(xr)[i];
             v.x *= scale; v.y *= scale; v.z *= scale; v.w *= scale;
+            if (nr) reinterpret_cast<float4 *>(nr)[i] = v;
             if (w) {
                 const float4 ww = reinterpret_cast<const float4 *>(w)[i];
                 v.x *= ww.x; v.y *= ww.y; v.z *= ww.z; v.w *= ww.w;
@@ -88,8 +90,22 @@ __global__ void rms_norm_kernel(TD x, const float *__restrict__ w, TD dst, float
             reinterpret_cast<float4 *>(yr)[i] = v;
         }
     } else {
-        for (int i = threadIdx.x; i < n; i += blockDim.x) yr[i] = xr[i] * scale * (w ? w[i] : 1.0f);
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const float v = xr[i] * scale;
+            if (nr) nr[i] = v;
+            yr[i] = w ? v * w[i] : v;
+        }
     }
+}
+
+// fused SILU(gate) * up; optionally also stores SILU(gate) (the intermediate ggml node)
+__global__ void silu_mul_kernel(const float *__restrict__ g, const float *__restrict__ u, float *__restrict__ act, float *__restrict__ dst, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float x = g[i];
+    const float a = x / (1.0f + expf(-x));
+    if (act) act[i] = a;
+    dst[i] = a * u[i];
 }
 
 // ------------------------------------------------------------------------------------------------ binary with broadcast
@@ -196,10 +212,13 @@ template <> __device__ __forceinline__ float  cvt<__half, float>(__half v) { ret
 template <> __device__ __forceinline__ __half cvt<__half, __half>(__half v) { return v; }
 template <> __device__ __forceinline__ int    cvt<int, int>(int v) { return v; }
 
+// `ind` (optional): device slot holding the destination base pointer, read at run time -- lets a captured CUDA graph
+// follow a KV-cache write position that moves every token without being re-captured or patched.
 template <typename S, typename D>
-__global__ void cpy_kernel(TD src, TD dst, int64_t n) {
+__global__ void cpy_kernel(TD src, TD dst, int64_t n, char *const *ind) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (ind) dst.data = *ind;
     // same linear element order, possibly different shapes (ggml_cpy only requires equal element counts)
     const int64_t s0 = i % src.ne[0], s1 = (i / src.ne[0]) % src.ne[1], s2 = (i / (src.ne[0] * src.ne[1])) % src.ne[2],
                   s3 = i / (src.ne[0] * src.ne[1] * src.ne[2]);
@@ -210,7 +229,8 @@ __global__ void cpy_kernel(TD src, TD dst, int64_t n) {
 }
 
 // f32 -> q8_0 (KV-cache store): 8 lanes per 32-value block; quantize_row_q8_0_ref arithmetic (ggml-quants.c:849-872)
-__global__ void cpy_f32_q8_0_kernel(TD src, TD dst, int64_t nblocks) {
+__global__ void cpy_f32_q8_0_kernel(TD src, TD dst, int64_t nblocks, char *const *ind) {
+    if (ind) dst.data = *ind;
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t blk = t >> 3;
     const int part = (int)(t & 7);
@@ -403,7 +423,27 @@ extern "C" int b200_op_rms_norm(const b200_tensor *x, const float *w, const b200
     const int64_t rows = nrows(x);
     if (rows == 0 || x->ne[0] == 0) return B200_OK;
     const int block = x->ne[0] >= 4096 ? 512 : (x->ne[0] >= 1024 ? 256 : 128);
-    rms_norm_kernel<<<(unsigned)rows, block, 0, (cudaStream_t)stream>>>(td(x), w, td(dst), eps);
+    rms_norm_kernel<<<(unsigned)rows, block, 0, (cudaStream_t)stream>>>(td(x), w, td(dst), eps, nullptr);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_op_rms_norm_mul(const b200_tensor *x, const float *w, float *norm_out, const b200_tensor *dst, float eps, b200_stream_t stream) {
+    REQUIRE(x && dst && w && x->data && dst->data, B200_ERR_INVALID, "b200_op_rms_norm_mul: NULL argument");
+    REQUIRE(x->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && x->nb[0] == 4 && dst->nb[0] == 4 && same_shape(x, dst), B200_ERR_UNSUPPORTED,
+            "b200_op_rms_norm_mul: f32 rows only");
+    const int64_t rows = nrows(x);
+    if (rows == 0 || x->ne[0] == 0) return B200_OK;
+    const int block = x->ne[0] >= 4096 ? 512 : (x->ne[0] >= 1024 ? 256 : 128);
+    rms_norm_kernel<<<(unsigned)rows, block, 0, (cudaStream_t)stream>>>(td(x), w, td(dst), eps, norm_out);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_op_silu_mul(const float *gate, const float *up, float *act_out, float *dst, int64_t n, b200_stream_t stream) {
+    REQUIRE(gate && up && dst && n >= 0, B200_ERR_INVALID, "b200_op_silu_mul: NULL argument");
+    if (n == 0) return B200_OK;
+    silu_mul_kernel<<<grid1d(n, 256), 256, 0, (cudaStream_t)stream>>>(gate, up, act_out, dst, n);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }
@@ -482,28 +522,33 @@ extern "C" int b200_op_rope(const b200_tensor *x, const int32_t *pos, const floa
 }
 
 extern "C" int b200_op_cpy(const b200_tensor *src, const b200_tensor *dst, b200_stream_t stream) {
-    REQUIRE(src && dst && src->data && dst->data, B200_ERR_INVALID, "b200_op_cpy: NULL argument");
+    return b200_op_cpy_indirect(src, dst, nullptr, stream);
+}
+
+extern "C" int b200_op_cpy_indirect(const b200_tensor *src, const b200_tensor *dst, void *const *dst_slot, b200_stream_t stream) {
+    REQUIRE(src && dst && src->data && (dst->data || dst_slot), B200_ERR_INVALID, "b200_op_cpy: NULL argument");
+    char *const *ind = (char *const *)dst_slot;
     const int64_t n = nelements(src);
     REQUIRE(n == nelements(dst), B200_ERR_INVALID, "b200_op_cpy: element counts differ");
     if (n == 0) return B200_OK;
     const cudaStream_t st = (cudaStream_t)stream;
     const int s = src->type, d = dst->type;
-    if (s == d && contiguous(src) && contiguous(dst)) {
+    if (s == d && contiguous(src) && contiguous(dst) && !ind) {
         const size_t bytes = (size_t)(n / type_block_values(s)) * type_block_bytes(s);
         B200_CUDA_TRY(cudaMemcpyAsync(dst->data, src->data, bytes, cudaMemcpyDeviceToDevice, st));
         return B200_OK;
     }
     const unsigned g = grid1d(n, 256);
-    if (s == B200_TYPE_F32 && d == B200_TYPE_F32) cpy_kernel<float, float><<<g, 256, 0, st>>>(td(src), td(dst), n);
-    else if (s == B200_TYPE_F32 && d == B200_TYPE_F16) cpy_kernel<float, __half><<<g, 256, 0, st>>>(td(src), td(dst), n);
-    else if (s == B200_TYPE_F16 && d == B200_TYPE_F32) cpy_kernel<__half, float><<<g, 256, 0, st>>>(td(src), td(dst), n);
-    else if (s == B200_TYPE_F16 && d == B200_TYPE_F16) cpy_kernel<__half, __half><<<g, 256, 0, st>>>(td(src), td(dst), n);
-    else if (s == B200_TYPE_I32 && d == B200_TYPE_I32) cpy_kernel<int, int><<<g, 256, 0, st>>>(td(src), td(dst), n);
+    if (s == B200_TYPE_F32 && d == B200_TYPE_F32) cpy_kernel<float, float><<<g, 256, 0, st>>>(td(src), td(dst), n, ind);
+    else if (s == B200_TYPE_F32 && d == B200_TYPE_F16) cpy_kernel<float, __half><<<g, 256, 0, st>>>(td(src), td(dst), n, ind);
+    else if (s == B200_TYPE_F16 && d == B200_TYPE_F32) cpy_kernel<__half, float><<<g, 256, 0, st>>>(td(src), td(dst), n, ind);
+    else if (s == B200_TYPE_F16 && d == B200_TYPE_F16) cpy_kernel<__half, __half><<<g, 256, 0, st>>>(td(src), td(dst), n, ind);
+    else if (s == B200_TYPE_I32 && d == B200_TYPE_I32) cpy_kernel<int, int><<<g, 256, 0, st>>>(td(src), td(dst), n, ind);
     else if (s == B200_TYPE_F32 && d == B200_TYPE_Q8_0) {
         REQUIRE(src->nb[0] == 4 && src->ne[0] % 32 == 0 && dst->ne[0] % 32 == 0 && dst->nb[0] == Q8_0_BYTES && (((uintptr_t)src->data | src->nb[1] | src->nb[2] | src->nb[3]) & 15) == 0,
                 B200_ERR_UNSUPPORTED, "b200_op_cpy: f32->q8_0 needs contiguous 16-byte aligned source rows of a multiple of 32 values");
         const int64_t nblk = n / 32;
-        cpy_f32_q8_0_kernel<<<grid1d(nblk * 8, 256), 256, 0, st>>>(td(src), td(dst), nblk);
+        cpy_f32_q8_0_kernel<<<grid1d(nblk * 8, 256), 256, 0, st>>>(td(src), td(dst), nblk, ind);
     } else {
         REQUIRE(false, B200_ERR_UNSUPPORTED, "b200_op_cpy: type pair (%d -> %d) not supported", s, d);
     }
