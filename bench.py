@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""Round benchmark: batch-1 decode of a Llama-2-7B-shaped Q4_K_M model at 4k context on B200 (BASELINE.json configs[1]).
+
+One "step" = one decoded token = one pass of the hot path (all MUL_MATs as decode GEMVs + FLASH_ATTN_EXT over the f16 KV
+cache + the small ops of the graph) through the ggml_backend boundary of libkcpp_b200.so.
+
+Legs (all printed in ONE JSON line by rank 0):
+  value      tokens/s with everything resident in HBM: graph_compute replayed K times, CUDA events on the backend stream.
+  e2e        tokens/s through the public call b200_llama_decode with HOST buffers: per step host token id -> H2D (token,
+             position, KQ mask), graph_compute, D2H of the logits (pinned), host argmax feeds the next token (greedy).
+  roofline   the decode GEMV family: the token's GEMV launch sequence (same types, shapes and order, rotating weight sets
+             larger than L2) timed alone with CUDA events; achieved = algorithmic bytes / time against the measured HBM peak.
+  cpu_baseline  the reference's own CPU backend (oracle/_ref) timed on this box's host cores on a bounded sample.
+`--impl reference` prints the CPU arm only.   N > 1: one replica per rank (weak scaling, no data-path collective yet; the
+row-split tensor-parallel path is DESIGN.md section "multi-GPU").
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOAD = "llama2-7b-q4_k_m"
+N_CTX = 4096
+N_PREFILLED = 3968  # tg128 at 4k context: cells [0, 3968) pre-filled, positions 3968..4095 decoded (n_kv = 4096 throughout)
+METRIC = "decode_tokens_per_s"
+UNIT = "tok/s"
+
+
+def peaks() -> tuple[float, str]:
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.rows: list[list[str]] = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                continue
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def reference_arm(args, rank: int) -> int:
+    """The reference's own CPU implementation of the path on this box's host cores (see tests/cpu_baseline.py)."""
+    if rank != 0:
+        return 0
+    sys.path.insert(0, str(ROOT / "tests"))
+    import cpu_baseline as B
+    from koboldcpp_b200.llama import SHAPES
+    shape = SHAPES[WORKLOAD]
+    budget = min(150.0, max(10.0, 1.0 * (args.steps + args.warmup)))
+    r = B.time_decode(shape, N_CTX, budget_s=budget)
+    line = {"impl": "reference", "metric": METRIC, "value": r["tok_s"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": r["ms_per_token"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 dot / f32 accumulate",
+            "data": "synthetic", "config": config_dict(shape),
+            "cpu_baseline": {"value": r["tok_s"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"]},
+            "e2e": {"value": r["tok_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+def config_dict(shape) -> dict:
+    return {"workload": f"{shape.name} random-init GGUF-shaped model, batch-1 greedy decode (tg128) at n_kv={N_CTX} (KV pre-filled to {N_PREFILLED}), f16 KV, flash attention",
+            "n_embd": shape.n_embd, "n_layer": shape.n_layer, "n_head": shape.n_head, "n_ff": shape.n_ff, "n_vocab": shape.n_vocab,
+            "l2_policy": "inputs larger than L2: 4.0 GB of weights + 2.1 GB of KV streamed per step vs 126 MB L2"}
+
+
+# ------------------------------------------------------------------------------------------------ GEMV roofline leg
+def gemv_launch_plan(shape):
+    """The decode GEMV launches of one token as graph_compute issues them (backend_graph.cu: siblings reading the same
+    activation and sharing a weight type are one multi-job launch).  Returns per layer a list of (type, K, [M, ...])."""
+    from koboldcpp_b200.llama import tensor_shape, tensor_types
+    types = tensor_types(shape)
+    layers = []
+    for il in range(shape.n_layer):
+        p = f"blk.{il}."
+        launches = []
+        for group in (["attn_q.weight", "attn_k.weight", "attn_v.weight"], ["attn_output.weight"], ["ffn_gate.weight", "ffn_up.weight"], ["ffn_down.weight"]):
+            by_type: dict[int, list[int]] = {}
+            order = []
+            for leaf in group:
+                ty = types[p + leaf]
+                if ty not in by_type:
+                    order.append(ty)
+                by_type.setdefault(ty, []).append(tensor_shape(shape, p + leaf)[1])
+            K = tensor_shape(shape, p + group[0])[0]
+            for ty in order:
+                launches.append((ty, K, by_type[ty]))
+        layers.append(launches)
+    head = (types["output.weight"], shape.n_embd, [shape.n_vocab])
+    return layers, head
+
+
+def gemv_leg(shape, steps: int, warmup: int) -> dict:
+    """Time the token's GEMV sequence alone: weights rotate through 4 layer-sized sets (> L2 between reuses)."""
+    import koboldcpp_b200.host as H
+    from koboldcpp_b200.lib import GemvJob, check, lib, row_size
+    L = lib()
+    layers, head = gemv_launch_plan(shape)
+    n_sets = 4
+    rng = np.random.default_rng(0)
+    kinds = sorted({(ty, K, tuple(Ms)) for lay in layers for (ty, K, Ms) in lay} | {(head[0], head[1], tuple(head[2]))})
+    pool = {}
+    for (ty, K, Ms) in kinds:
+        rs = row_size(ty, K)
+        sets = []
+        for _ in range(1 if (ty, K, list(Ms)) == (head[0], head[1], list(head[2])) else n_sets):
+            sets.append([H.DeviceBuffer.from_numpy(rng.integers(0, 256, size=rs * M, dtype=np.uint8), pad=256) for M in Ms])
+        pool[(ty, K, Ms)] = sets
+    kmax = max(k for _, k, _ in kinds)
+    mmax = max(sum(Ms) for _, _, Ms in kinds)
+    x = H.DeviceBuffer.from_numpy(rng.standard_normal(kmax).astype(np.float32))
+    y = H.DeviceBuffer(4 * mmax + 256)
+    st = C.c_void_p()
+    check(L.b200_stream_create(C.byref(st)))
+    L.b200_set_pdl(1)
+    alg_bytes = 0
+    n_launch = 0
+
+    def issue():
+        nonlocal alg_bytes, n_launch
+        alg_bytes = 0
+        n_launch = 0
+        seq = [(il, l) for il, lay in enumerate(layers) for l in lay] + [(0, head)]
+        for il, (ty, K, Ms) in seq:
+            sets = pool[(ty, K, tuple(Ms))]
+            bufs = sets[il % len(sets)]
+            rs = row_size(ty, K)
+            if len(Ms) == 1:
+                check(L.b200_mul_mat_vec_q(ty, bufs[0].ptr, rs, x.ptr, K, y.ptr, Ms[0], K, Ms[0], 1, st))
+            else:
+                jobs = (GemvJob * len(Ms))()
+                off = 0
+                for j, M in enumerate(Ms):
+                    jobs[j].W = bufs[j].ptr; jobs[j].X = x.ptr; jobs[j].dst = y.ptr + 4 * off; jobs[j].M = M; jobs[j].id_index = -1
+                    off += M
+                check(L.b200_mul_mat_vec_q_multi(ty, jobs, len(Ms), rs, K, sum(Ms), K, 1, None, 0, 0, st))
+            alg_bytes += sum(rs * M + 4 * M for M in Ms) + 4 * K
+            n_launch += 1
+
+    check(L.b200_graph_begin_capture(st))
+    issue()
+    g = C.c_void_p()
+    check(L.b200_graph_end_capture(st, C.byref(g)))
+    for _ in range(max(3, warmup)):
+        check(L.b200_graph_launch(g, st))
+    check(L.b200_stream_synchronize(st))
+    e0, e1 = C.c_void_p(), C.c_void_p()
+    check(L.b200_event_create(C.byref(e0))); check(L.b200_event_create(C.byref(e1)))
+    check(L.b200_event_record(e0, st))
+    for _ in range(steps):
+        check(L.b200_graph_launch(g, st))
+    check(L.b200_event_record(e1, st))
+    ms = C.c_float()
+    check(L.b200_event_elapsed_ms(e0, e1, C.byref(ms)))
+    L.b200_graph_destroy(g)
+    L.b200_set_pdl(0)
+    per_token_ms = ms.value / steps
+    for sets in pool.values():
+        for bufs in sets:
+            for b in bufs:
+                b.free()
+    x.free(); y.free()
+    L.b200_stream_destroy(st)
+    return {"ms_per_token": per_token_ms, "launches_per_token": n_launch, "alg_bytes_per_token": alg_bytes,
+            "avg_launch_us": per_token_ms * 1e3 / n_launch, "gbs": alg_bytes / per_token_ms / 1e6}
+
+
+# ------------------------------------------------------------------------------------------------ product arm
+def product_arm(args, rank: int, world: int, local_rank: int) -> int:
+    import koboldcpp_b200.llama as LL
+    from koboldcpp_b200.lib import F16, check, lib
+    L = lib()
+    if L.b200_device_count() <= 0:
+        print("bench.py: no CUDA device and the product has no CPU path", file=sys.stderr)
+        return 2
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist_
+        torch.cuda.set_device(local_rank)
+        dist_.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = dist_
+    check(L.b200_set_device(local_rank), "set_device")
+    shape = LL.SHAPES[WORKLOAD]
+    steps, warmup = args.steps, max(3, args.warmup)
+    t_setup = time.time()
+    m = LL.LlamaModel(shape, N_CTX, F16, main_device=local_rank)
+    m.init_random(seed=1234 + rank)
+    m.finalize(max_batch=1)
+    m.kv_fill_random(N_PREFILLED, seed=7 + rank)
+    setup_s = time.time() - t_setup
+    span = N_CTX - N_PREFILLED  # positions cycle inside [3968, 4096): n_kv stays 4096 for any K
+
+    def pos(i):
+        return N_PREFILLED + (i % span)
+
+    ev = [C.c_void_p() for _ in range(4)]
+    for e in ev:
+        check(L.b200_event_create(C.byref(e)))
+    stream = m.stream
+
+    def barrier():
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier()
+        m.synchronize()
+
+    # ---- e2e leg: the public call with host buffers, greedy token feedback
+    tok = 1
+    for i in range(warmup):
+        tok = int(np.argmax(m.decode([tok], pos(i))[0]))
+    barrier()
+    clocks = ClockSampler(local_rank)
+    check(L.b200_event_record(ev[0], stream))
+    t0 = time.perf_counter()
+    for i in range(steps):
+        tok = int(np.argmax(m.decode([tok], pos(warmup + i))[0]))
+    check(L.b200_event_record(ev[1], stream))
+    ms = C.c_float()
+    check(L.b200_event_elapsed_ms(ev[0], ev[1], C.byref(ms)))
+    e2e_wall_ms = (time.perf_counter() - t0) * 1e3
+    e2e_ms = max(ms.value, e2e_wall_ms)  # host-synchronous loop: the wall clock bounds the device span from above
+    st = m.stats()
+    barrier()
+
+    # ---- resident leg: graph_compute replayed with inputs in HBM
+    for _ in range(warmup):
+        m.replay()
+    barrier()
+    check(L.b200_event_record(ev[2], stream))
+    for _ in range(steps):
+        m.replay()
+    check(L.b200_event_record(ev[3], stream))
+    check(L.b200_event_elapsed_ms(ev[2], ev[3], C.byref(ms)))
+    res_ms = ms.value
+    clk = clocks.stop()
+    barrier()
+
+    if dist is not None:
+        import torch
+        t = torch.tensor([res_ms, e2e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res_ms, e2e_ms = float(t[0]), float(t[1])
+    m.close()
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        g = gemv_leg(shape, steps, warmup)
+        wbytes = LL.weight_bytes_per_token(shape)
+        kvbytes = LL.kv_bytes_per_token(shape, N_CTX, F16)
+        tok_s = world * steps / (res_ms / 1e3)
+        e2e_tok_s = world * steps / (e2e_ms / 1e3)
+        mask_bytes = 4 * N_CTX * 32
+        line = {
+            "metric": METRIC, "value": tok_s, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": res_ms / steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 dot (dp4a) / f32 accumulate; f16 KV",
+            "data": "synthetic", "config": config_dict(shape),
+            "e2e": {"value": e2e_tok_s, "unit": UNIT, "h2d_bytes_per_step": 4 + 4 + mask_bytes, "d2h_bytes_per_step": 4 * shape.n_vocab,
+                    "ms_per_step": e2e_ms / steps},
+            "gpu_launches": int(st["n_kernels"]) * steps * 2,
+            "launches_per_step": int(st["n_kernels"]), "graph_nodes_per_step": int(st["n_nodes"]),
+            "roofline": {"bound": "hbm", "kernel": "decode GEMV family (gemv_stream_kernel), the token's launch sequence timed alone",
+                         "achieved": g["gbs"], "peak": peak, "unit": "GB/s", "frac": g["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                         "alg_bytes_per_launch": g["alg_bytes_per_token"] / g["launches_per_token"], "avg_launch_us": g["avg_launch_us"],
+                         "launches_per_step": g["launches_per_token"], "share_of_step": g["ms_per_token"] / (res_ms / steps)},
+            "step_roofline": {"alg_bytes_per_step": wbytes + kvbytes, "achieved": (wbytes + kvbytes) / (res_ms / steps) / 1e6, "peak": peak, "unit": "GB/s",
+                              "frac": (wbytes + kvbytes) / (res_ms / steps) / 1e6 / peak, "frac_of_8TBs_nominal": (wbytes + kvbytes) / (res_ms / steps) / 1e6 / 8000.0},
+            "clocks": clk, "setup_s": setup_s,
+        }
+        if world == 1 and not args.no_cpu:
+            try:
+                sys.path.insert(0, str(ROOT / "tests"))
+                import cpu_baseline as B
+                r = B.time_decode(shape, N_CTX, budget_s=args.cpu_budget)
+                line["cpu_baseline"] = {"value": r["tok_s"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"]}
+            except Exception as ex:  # the checker library is prebuilt in oracle/_ref; its absence must not hide the GPU numbers
+                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=125)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--cpu-budget", type=float, default=18.0)
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return reference_arm(args, rank)
+    return product_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -85,6 +85,12 @@ B200_API int b200_event_create(void **event);
 B200_API int b200_event_destroy(void *event);
 B200_API int b200_event_record(void *event, b200_stream_t stream);
 B200_API int b200_event_elapsed_ms(void *start, void *stop, float *ms); /* synchronises on `stop` */
+/* Capture the launches issued on `stream` (a stream from b200_stream_create, not NULL) into an executable CUDA graph and
+ * replay it: what ggml_backend_cuda_graph_compute does with cudaStreamBeginCapture / cudaGraphLaunch, ggml-cuda.cu:2700-2800 */
+B200_API int b200_graph_begin_capture(b200_stream_t stream);
+B200_API int b200_graph_end_capture(b200_stream_t stream, void **graph_exec);
+B200_API int b200_graph_launch(void *graph_exec, b200_stream_t stream);
+B200_API int b200_graph_destroy(void *graph_exec);
 
 /* ---- (a2) block dequantisation ------------------------------------------------------------------
  * replaces: dequantize_block_* / to_fp32_cuda / to_fp16_cuda, ggml/src/ggml-cuda/convert.cu:7-445, 460-540

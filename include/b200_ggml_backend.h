@@ -48,6 +48,8 @@ B200_API void ggml_backend_b200_set_fusion(int enabled);  /* node fusion in grap
 /* counters for tests / bench: kernels launched (or replayed) by graph_compute since the last reset */
 B200_API void ggml_backend_b200_get_stats(int64_t *n_kernel_launches, int64_t *n_graph_replays, int64_t *n_graph_captures);
 B200_API void ggml_backend_b200_reset_stats(void);
+/* the backend's CUDA stream (cudaStream_t), for CUDA-event timing around graph_compute */
+B200_API void *ggml_backend_b200_get_stream(ggml_backend_t backend);
 
 #ifdef __cplusplus
 }

@@ -117,4 +117,22 @@ int b200_event_elapsed_ms(void *start, void *stop, float *ms) {
     return B200_OK;
 }
 
+// stream capture -> executable graph, so a host in any language can replay a launch sequence without per-launch overhead
+int b200_graph_begin_capture(b200_stream_t stream) {
+    B200_CUDA_TRY(cudaStreamBeginCapture((cudaStream_t)stream, cudaStreamCaptureModeThreadLocal));
+    return B200_OK;
+}
+int b200_graph_end_capture(b200_stream_t stream, void **graph_exec) {
+    cudaGraph_t g = nullptr;
+    B200_CUDA_TRY(cudaStreamEndCapture((cudaStream_t)stream, &g));
+    cudaGraphExec_t e = nullptr;
+    const cudaError_t err = cudaGraphInstantiate(&e, g, 0);
+    cudaGraphDestroy(g);
+    B200_CUDA_TRY(err);
+    *graph_exec = e;
+    return B200_OK;
+}
+int b200_graph_launch(void *graph_exec, b200_stream_t stream) { B200_CUDA_TRY(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)stream)); return B200_OK; }
+int b200_graph_destroy(void *graph_exec) { B200_CUDA_TRY(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec)); return B200_OK; }
+
 }  // extern "C"

@@ -211,6 +211,7 @@ void ggml_backend_b200_get_stats(int64_t *launches, int64_t *replays, int64_t *c
     if (replays) *replays = g_stat_replays;
     if (captures) *captures = g_stat_captures;
 }
+void *ggml_backend_b200_get_stream(ggml_backend_t b) { return ggml_backend_is_b200(b) ? (void *)graph_exec_stream(((BackendCtx *)b->context)->exec) : nullptr; }
 void ggml_backend_b200_reset_stats(void) { g_stat_launches = g_stat_replays = g_stat_captures = 0; }
 
 // ---- Route 1: the public symbols of ggml/include/ggml-cuda.h:22-44 under their reference names, so the library can be

@@ -60,6 +60,10 @@ _SIGS = {
     "b200_event_destroy": (C.c_int, [C.c_void_p]),
     "b200_event_record": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200_event_elapsed_ms": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]),
+    "b200_graph_begin_capture": (C.c_int, [C.c_void_p]),
+    "b200_graph_end_capture": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "b200_graph_launch": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b200_graph_destroy": (C.c_int, [C.c_void_p]),
     "b200_dequantize": (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p]),
     "b200_quantize_q8_1": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),

@@ -19,6 +19,36 @@ def test_library_exports_every_declared_symbol():
     assert syms <= set(L._SIGS), syms - set(L._SIGS)  # the Python mirror binds all of them
 
 
+def test_library_exports_backend_ops_and_decoder_symbols():
+    """Every B200_API symbol of the other public headers (ggml_backend boundary, graph ops, decoder) is exported too."""
+    import koboldcpp_b200.lib as L
+    lib = L.load()
+    n = 0
+    for h in ("b200_ggml_backend.h", "b200_ggml_ops.h", "b200_llama.h"):
+        txt = (ROOT / "include" / h).read_text()
+        for s in set(re.findall(r"B200_API\s+[\w\s\*]+?\b((?:b200|ggml_backend_b200)_\w+)\s*\(", txt)):
+            assert hasattr(lib, s), f"{s} declared in {h} but not exported"
+            n += 1
+    assert n >= 35, n
+    # Route 1: the reference's public CUDA-backend symbol set (ggml/include/ggml-cuda.h:22-44)
+    for s in ("ggml_cuda_set_mul_mat_q", "ggml_backend_cuda_init", "ggml_backend_is_cuda", "ggml_backend_cuda_buffer_type",
+              "ggml_backend_cuda_split_buffer_type", "ggml_backend_cuda_host_buffer_type", "ggml_backend_cuda_get_device_count",
+              "ggml_backend_cuda_get_device_description", "ggml_backend_cuda_get_device_memory", "ggml_backend_cuda_register_host_buffer",
+              "ggml_backend_cuda_unregister_host_buffer", "ggml_backend_cuda_reg"):
+        assert hasattr(lib, s), s
+
+
+def test_decoder_refuses_to_run_without_a_gpu():
+    import pytest
+
+    import koboldcpp_b200.lib as L
+    from koboldcpp_b200.llama import SHAPES, LlamaModel
+    if L.lib().b200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(L.B200Error):
+        LlamaModel(SHAPES["test-dense"], 256)
+
+
 def test_no_gpu_means_loud_failure_not_fallback():
     import numpy as np
     import pytest

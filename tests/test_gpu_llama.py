@@ -1,0 +1,119 @@
+"""GPU parity of whole-token decode through the ggml_backend boundary (b200_llama_* -> graph_compute) against the fp64
+restatement in llama_ref.py.  Tolerances: matmuls run on q8_1-quantised activations (like the reference CUDA path), which
+puts ~1e-2 relative noise on each matmul; logits of a 2-3 layer model must agree to 4e-2 of their
+RMS and the executor variants (graphs / fusion on or off) must agree with each other far tighter than that."""
+from __future__ import annotations
+
+import numpy as np
+import pytest
+
+from koboldcpp_b200.lib import F16, F32, Q8_0
+from koboldcpp_b200.llama import SHAPES, LlamaModel, _l, random_blocks, tensor_shape, tensor_types
+
+pytestmark = pytest.mark.gpu
+
+
+def make_tensors(shape, seed):
+    rng = np.random.default_rng(seed)
+    out = {}
+    for name, ty in tensor_types(shape).items():
+        ne = tensor_shape(shape, name)
+        if name.endswith("norm.weight"):
+            out[name] = (F32, (1.0 + 0.1 * rng.standard_normal(ne[0])).astype(np.float32).view(np.uint8))
+        else:
+            out[name] = (ty, random_blocks(rng, ty, ne[1] * ne[2], ne[0]).reshape(-1))
+    # a wider spread on the embeddings and the router so that tokens / experts differ visibly
+    return out
+
+
+def build(shape, tensors, n_ctx, type_kv, max_batch=8):
+    m = LlamaModel(shape, n_ctx, type_kv)
+    for name, (ty, raw) in tensors.items():
+        m.set_tensor(name, ty, tensor_shape(shape, name), raw)
+    m.finalize(max_batch)
+    return m
+
+
+def rel_rms(a, b):
+    return float(np.sqrt(((a - b) ** 2).mean()) / (np.sqrt((b ** 2).mean()) + 1e-30))
+
+
+@pytest.mark.parametrize("cfg,type_kv", [("test-dense", F16), ("test-dense", Q8_0), ("test-moe", F16)])
+def test_decode_matches_fp64_reference(cfg, type_kv):
+    from llama_ref import RefModel
+    shape = SHAPES[cfg]
+    tensors = make_tensors(shape, 11)
+    ref = RefModel(shape, tensors, 512, type_kv)
+    m = build(shape, tensors, 512, type_kv)
+    try:
+        prompt = [(i * 7919 + 3) % shape.n_vocab for i in range(5)]
+        got = m.decode(prompt, 0, logits_all=True).copy()
+        exp = ref.decode(prompt, 0)
+        assert np.isfinite(got).all()
+        assert rel_rms(got, exp) < 4e-2, rel_rms(got, exp)
+        n_past = len(prompt)
+        tok = int(np.argmax(exp[-1]))
+        for _ in range(6):
+            got = m.decode([tok], n_past).copy()
+            exp = ref.decode([tok], n_past)
+            assert rel_rms(got[0], exp[0]) < 4e-2, rel_rms(got[0], exp[0])
+            n_past += 1
+            tok = int(np.argmax(exp[0]))
+        # the cache rows written by the CPY nodes: f16 rounding of nearly equal values
+        if type_kv == F16:
+            k = m.kv_read(0, 0, 0, n_past).view(np.float16).astype(np.float64)
+            assert rel_rms(k, ref.k[0, :n_past]) < 2e-2
+    finally:
+        m.close()
+
+
+def test_executor_variants_agree():
+    """CUDA-graph replay and node fusion must not change results: graphs on/off bit-identical, fusion on/off within
+    float reassociation (the fused kernels do the same arithmetic per element)."""
+    shape = SHAPES["test-dense"]
+    tensors = make_tensors(shape, 5)
+    outs = {}
+    L = _l()
+    try:
+        for graphs in (1, 0):
+            for fusion in (1, 0):
+                L.ggml_backend_b200_set_graphs(graphs)
+                L.ggml_backend_b200_set_fusion(fusion)
+                m = build(shape, tensors, 256, F16)
+                try:
+                    seq = []
+                    n_past = 0
+                    for t in range(20):
+                        seq.append(m.decode([(t * 31 + 1) % shape.n_vocab], n_past).copy())
+                        n_past += 1
+                    outs[(graphs, fusion)] = np.concatenate(seq)
+                    if graphs and fusion:
+                        st = m.stats()
+                        assert st["n_kernels"] < st["n_nodes"], st  # fusion + view elision: fewer launches than nodes
+                finally:
+                    m.close()
+    finally:
+        L.ggml_backend_b200_set_graphs(1)
+        L.ggml_backend_b200_set_fusion(1)
+    assert np.array_equal(outs[(1, 1)], outs[(0, 1)])
+    assert np.array_equal(outs[(1, 0)], outs[(0, 0)])
+    assert rel_rms(outs[(1, 1)], outs[(1, 0)]) < 1e-5
+
+
+def test_graph_replay_counts():
+    """After the first token of a steady-state decode every token is one cudaGraphLaunch (the KV write position moves
+    through the CPY slot table, not through a re-capture)."""
+    import ctypes as C
+    shape = SHAPES["test-dense"]
+    m = build(shape, make_tensors(shape, 3), 512, F16)
+    L = _l()
+    try:
+        m.decode([1], 0)
+        L.ggml_backend_b200_reset_stats()
+        for t in range(1, 40):
+            m.decode([t], t)
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        L.ggml_backend_b200_get_stats(C.byref(a), C.byref(b), C.byref(c))
+        assert b.value == 39 and c.value == 0, (a.value, b.value, c.value)
+    finally:
+        m.close()
