@@ -134,6 +134,20 @@ B200_API int b200_mul_mat_vec_q_multi(int type, const b200_gemv_job *jobs, int n
                                       int64_t x_stride, int64_t dst_stride, int64_t K, int64_t N,
                                       const int32_t *ids, size_t expert_bytes, int32_t n_expert, b200_stream_t stream);
 
+/* The same launch with the neighbouring graph nodes folded in (what llm_build_norm + llm_build_lora_mm + ggml_add emit around
+ * every matmul of a layer, src/llama.cpp:9254-9287, 10479-10560):
+ *   norm_weight != NULL: X is replaced by RMS_NORM(X, norm_eps) * norm_weight while it is quantised (X rows of K floats; the
+ *                        normalised activations are never written to memory);
+ *   residual[j] != NULL: dst_j = W_j . X + residual[j]   (same layout as dst_j; may alias it). */
+typedef struct {
+    const float *norm_weight; /* f32 [K], 16-byte aligned, or NULL */
+    float        norm_eps;
+    int32_t      _pad;
+    const float *residual[B200_GEMV_MAX_JOBS];
+} b200_gemv_fuse;
+B200_API int b200_mul_mat_vec_q_fused(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride,
+                                      int64_t dst_stride, int64_t K, int64_t N, const b200_gemv_fuse *fuse, b200_stream_t stream);
+
 /* ---- (a9) MUL_MAT_ID (expert GEMV), ids read on the device ------------------------------------------
  * replaces: ggml_cuda_mul_mat_id incl. its cudaMemcpyAsync(ids)+cudaStreamSynchronize and the
  * k_copy_src1_to_contiguous / k_copy_dst_from_contiguous gather-scatter, ggml/src/ggml-cuda.cu:1954-2139

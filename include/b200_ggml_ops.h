@@ -65,6 +65,14 @@ B200_API int b200_op_cpy(const b200_tensor *src, const b200_tensor *dst, b200_st
  * (reference: cudaGraphExecKernelNodeSetParams patching of the cpy nodes, ggml-cuda.cu:2593-2650). */
 B200_API int b200_op_cpy_indirect(const b200_tensor *src, const b200_tensor *dst, void *const *dst_slot, b200_stream_t stream);
 
+/* The four nodes llm_build_kv emits per layer in one launch (src/llama.cpp:9161-9203, 10504-10523): q_dst = ROPE(q),
+ * k_dst = ROPE(k), cache_k[new rows] = CPY(k_dst), cache_v[new rows] = CPY(v).  q [D, n_head, T], k [D, n_head_kv, T],
+ * v [D*n_head_kv, T]: contiguous f32.  kv_type: F16 or Q8_0; the T new cache rows are contiguous at k_cache / v_cache, or at
+ * *k_slot / *v_slot read on the device (CUDA-graph replay with a moving write position).  NORM rope ordering only. */
+B200_API int b200_op_rope_kv_store(const b200_tensor *q, const b200_tensor *q_dst, const b200_tensor *k, const b200_tensor *k_dst,
+                                   const b200_tensor *v, const int32_t *pos, const float *freq_factors, const b200_rope_params *rp,
+                                   int kv_type, void *k_cache, void *v_cache, void *const *k_slot, void *const *v_slot, b200_stream_t stream);
+
 /* GET_ROWS: dst[i] = dequantise(src row ids[i]); src f32 / f16 / q4_0 / q8_0 / q4_K / q5_K / q6_K (K-quant token embeddings
  * stay on the device -- the reference falls back to the CPU for them, ggml-cuda.cu:3033-3047).
  * replaces k_get_rows / k_get_rows_float, ggml-cuda/getrows.cu:5-120 */

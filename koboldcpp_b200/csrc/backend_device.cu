@@ -16,6 +16,8 @@ int device_count() {
         n = c > GGML_B200_MAX_DEVICES ? GGML_B200_MAX_DEVICES : c;
         if (getenv("B200_NO_GRAPHS")) g_use_graphs = false;
         if (getenv("B200_NO_FUSION")) g_use_fusion = false;
+        // programmatic dependent launch: a GEMV's weight prefetch overlaps the tail of its producer (b200_ggml.h)
+        b200_set_pdl(getenv("B200_NO_PDL") ? 0 : 1);
     }
     return n;
 }

@@ -18,14 +18,16 @@
 
 namespace b200 {
 
-enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV_MULTI };
+enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV };
 
 struct Step {
     int kind;
     const ggml_tensor *n;               // the node (STEP_NODE), or the first node of the fused group
     const ggml_tensor *n2;              // second node of a fused pair
-    std::vector<const ggml_tensor *> group;  // STEP_GEMV_MULTI members
-    int slot;                           // CPY nodes: index into the slot table, else -1
+    std::vector<const ggml_tensor *> group;  // STEP_GEMV members; STEP_ROPE_KV: {CPY K, CPY V}
+    std::vector<const ggml_tensor *> adds;   // STEP_GEMV: per member the ADD node folded into its epilogue (or NULL)
+    int slot = -1, slot2 = -1;          // CPY nodes: index into the slot table, else -1
+    Step() : kind(STEP_NODE), n(nullptr), n2(nullptr) {}
 };
 
 struct CachedGraph {
@@ -108,49 +110,210 @@ static bool silu_mul_pair(const ggml_tensor *a, const ggml_tensor *b) {
     return same_shape(a, b) && same_shape(a, u) && is_contiguous(a) && is_contiguous(b) && is_contiguous(u) && is_contiguous(a->src[0]);
 }
 
-// Lower cgraph -> Steps.  `done[i]` marks nodes already absorbed by an earlier fused step.
+// ---- graph facts the fusion rules need
+struct GraphInfo {
+    const ggml_cgraph *cg;
+    std::unordered_map<const ggml_tensor *, int> index;     // node -> position
+    std::unordered_map<const ggml_tensor *, int> n_uses;    // tensor -> number of nodes that have it as a src
+    std::unordered_map<const ggml_tensor *, const ggml_tensor *> last_user;
+    explicit GraphInfo(const ggml_cgraph *g) : cg(g) {
+        for (int i = 0; i < g->n_nodes; i++) {
+            const ggml_tensor *t = g->nodes[i];
+            index[t] = i;
+            for (int k = 0; k < GGML_MAX_SRC; k++) {
+                if (t->src[k]) { n_uses[t->src[k]]++; last_user[t->src[k]] = t; }
+            }
+        }
+    }
+    int pos(const ggml_tensor *t) const { auto it = index.find(t); return it == index.end() ? -1 : it->second; }
+    int uses(const ggml_tensor *t) const { auto it = n_uses.find(t); return it == n_uses.end() ? 0 : it->second; }
+    // t is read by exactly one node, and nothing outside the graph can want it (outputs are flagged or named result*)
+    const ggml_tensor *sole_user(const ggml_tensor *t) const {
+        if (uses(t) != 1 || (t->flags & GGML_TENSOR_FLAG_OUTPUT) || strncmp(t->name, "result", 6) == 0) return nullptr;
+        if (pos(t) == cg->n_nodes - 1) return nullptr;
+        return last_user.find(t)->second;
+    }
+};
+
+static bool same_op_params(const ggml_tensor *a, const ggml_tensor *b) { return memcmp(a->op_params, b->op_params, sizeof(a->op_params)) == 0; }
+
+// May the nodes `members` (positions ascending) all execute at position `at` (>= first member, <= last member)?
+//   * a member moved LATER (pos < at): no outside node in (pos, at] reads or writes its output, or writes one of its inputs;
+//   * a member moved EARLIER (pos > at): its inputs exist at `at` (checked by the caller), and no outside node in [at, pos)
+//     reads or writes its output bytes.
+static bool can_gather(const GraphInfo &gi, const std::vector<int> &members, int at, const std::vector<char> &done) {
+    auto is_member = [&](int i) { for (int m : members) if (m == i) return true; return false; };
+    for (int m : members) {
+        const ggml_tensor *t = gi.cg->nodes[m];
+        const size_t len = nbytes(t);
+        const int lo = m < at ? m + 1 : at, hi = m < at ? at : m - 1;
+        for (int i = lo; i <= hi; i++) {
+            if (is_member(i) || (done[i] && i != at)) continue;
+            const ggml_tensor *o = gi.cg->nodes[i];
+            if (is_view_op(o->op)) continue;
+            if (node_touches(o, t->data, len)) return false;
+            if (m < at && o->data) {
+                for (int k = 0; k < GGML_MAX_SRC; k++) {
+                    const ggml_tensor *sk = t->src[k];
+                    if (sk && sk->data && ranges_overlap(o->data, nbytes(o), sk->data, nbytes(sk))) return false;
+                }
+            }
+        }
+    }
+    return true;
+}
+
+// ROPE(Q) at position i: find ROPE(K), CPY(K -> cache), CPY(V -> cache) behind it (llm_build_kv order) -> one launch at the last one
+static bool match_rope_kv(const GraphInfo &gi, int i, const std::vector<char> &done, int out[4]) {
+    const ggml_cgraph *cg = gi.cg;
+    const ggml_tensor *rq = cg->nodes[i];
+    if (rq->op != GGML_OP_ROPE || (rq->op_params[2] & GGML_ROPE_TYPE_NEOX) || rq->type != GGML_TYPE_F32) return false;
+    if (!is_contiguous(rq) || !is_contiguous(rq->src[0]) || rq->ne[3] != 1 || rq->ne[0] % 32) return false;
+    int rk = -1, ck = -1, cv = -1;
+    const int horizon = i + 24 < cg->n_nodes ? i + 24 : cg->n_nodes;
+    for (int j = i + 1; j < horizon; j++) {
+        const ggml_tensor *t = cg->nodes[j];
+        if (done[j]) continue;
+        if (rk < 0) {
+            if (t->op == GGML_OP_ROPE && t->src[1] == rq->src[1] && t->src[2] == rq->src[2] && same_op_params(t, rq) && t->ne[0] == rq->ne[0] &&
+                t->ne[2] == rq->ne[2] && t->ne[3] == 1 && t->type == GGML_TYPE_F32 && is_contiguous(t) && is_contiguous(t->src[0])) rk = j;
+            else if (t->op == GGML_OP_ROPE || t->op == GGML_OP_FLASH_ATTN_EXT) return false;
+            continue;
+        }
+        if (t->op != GGML_OP_CPY) { if (t->op == GGML_OP_FLASH_ATTN_EXT || t->op == GGML_OP_ROPE) break; continue; }
+        const ggml_tensor *src = t->src[0];
+        if (t->type != GGML_TYPE_F16 && t->type != GGML_TYPE_Q8_0) continue;
+        if (!is_contiguous(t) || src->type != GGML_TYPE_F32 || !is_contiguous(src)) continue;
+        if (nelements(t) != nelements(cg->nodes[rk])) continue;
+        if (ck < 0 && src == cg->nodes[rk]) { ck = j; continue; }
+        if (ck >= 0 && cv < 0 && t->type == cg->nodes[ck]->type && gi.pos(src) < j) { cv = j; break; }
+    }
+    if (rk < 0 || ck < 0 || cv < 0) return false;
+    out[0] = i; out[1] = rk; out[2] = ck; out[3] = cv;
+    return true;
+}
+
+// Lower cgraph -> Steps.  `done[i]` marks nodes absorbed by a fused step.
 static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
     std::vector<Step> &steps = g->steps;
     steps.clear();
     const int n = cg->n_nodes;
     std::vector<char> done((size_t)n, 0);
+    std::vector<int> slot_of((size_t)n, -1);
     int n_slots = 0;
+    for (int i = 0; i < n; i++) if (is_cpy_op(cg->nodes[i]->op) && nelements(cg->nodes[i]) != 0) slot_of[(size_t)i] = n_slots++;
+    if (!g_use_fusion) {
+        for (int i = 0; i < n; i++) {
+            const ggml_tensor *a = cg->nodes[i];
+            if (is_view_op(a->op) || nelements(a) == 0) continue;
+            Step s;
+            s.kind = STEP_NODE; s.n = a; s.slot = slot_of[(size_t)i];
+            steps.push_back(s);
+        }
+        return;
+    }
+    const GraphInfo gi(cg);
+    // fused attributes discovered ahead of the matmuls they apply to
+    std::unordered_map<const ggml_tensor *, const ggml_tensor *> norm_mul_of;  // activation tensor (MUL node) -> its RMS_NORM node
+    std::unordered_map<const ggml_tensor *, const ggml_tensor *> add_of;       // MUL_MAT node -> the ADD node folded into it
+    std::unordered_map<int, Step> deferred;                                    // position -> step to emit there
+
     for (int i = 0; i < n; i++) {
+        auto df = deferred.find(i);
+        if (df != deferred.end()) { steps.push_back(df->second); continue; }
         if (done[i]) continue;
         const ggml_tensor *a = cg->nodes[i];
         if (is_view_op(a->op) || nelements(a) == 0) continue;
         Step s;
-        s.kind = STEP_NODE; s.n = a; s.n2 = nullptr; s.slot = -1;
-        if (is_cpy_op(a->op)) {
-            s.slot = n_slots++;
-            steps.push_back(s);
+        s.kind = STEP_NODE; s.n = a; s.slot = slot_of[(size_t)i];
+        if (is_cpy_op(a->op)) { steps.push_back(s); continue; }
+
+        // the partner of a pair is the next node that is neither a view nor already absorbed
+        int j = i + 1;
+        while (j < n && (done[j] || is_view_op(cg->nodes[j]->op))) j++;
+
+        if (j < n && rms_mul_pair(a, cg->nodes[j])) {
+            const ggml_tensor *b = cg->nodes[j];
+            // R1: every reader of the normalised activation is a decode GEMV -> the norm moves into their prologue
+            bool all_gemv = gi.sole_user(a) == b && gi.uses(b) > 0 && !(b->flags & GGML_TENSOR_FLAG_OUTPUT) && strncmp(b->name, "result", 6) != 0 &&
+                            is_contiguous(a->src[0]) && (((uintptr_t)a->src[0]->data) & 15) == 0;
+            const ggml_tensor *w = b->src[0] == a ? b->src[1] : b->src[0];
+            all_gemv = all_gemv && (((uintptr_t)w->data) & 15) == 0;
+            int readers = 0;
+            for (int k = j + 1; k < n && all_gemv; k++) {
+                const ggml_tensor *t = cg->nodes[k];
+                // the un-normalised input must stay intact until the last GEMV that re-derives the norm from it has run
+                if (!is_view_op(t->op) && t->data && ranges_overlap(t->data, nbytes(t), a->src[0]->data, nbytes(a->src[0]))) all_gemv = false;
+                for (int q = 0; q < GGML_MAX_SRC; q++) {
+                    if (t->src[q] != b) continue;
+                    if (q == 1 && mul_mat_fusable(t)) readers++;
+                    else all_gemv = false;
+                }
+                if (readers == gi.uses(b)) break;
+            }
+            if (all_gemv && readers == gi.uses(b)) {
+                norm_mul_of[b] = a;
+                done[j] = 1;
+                continue;  // no step: RMS_NORM and MUL are computed inside the GEMVs
+            }
+            s.kind = STEP_RMS_MUL; s.n2 = b; done[j] = 1; steps.push_back(s);
             continue;
         }
-        if (g_use_fusion) {
-            // the partner of a pair is the next non-view node
-            int j = i + 1;
-            while (j < n && (done[j] || is_view_op(cg->nodes[j]->op))) j++;
-            if (j < n && rms_mul_pair(a, cg->nodes[j])) { s.kind = STEP_RMS_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
-            if (j < n && silu_mul_pair(a, cg->nodes[j])) { s.kind = STEP_SILU_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
-            if (mul_mat_fusable(a)) {
-                // siblings: later MUL_MATs with the same activation tensor, weight type and row stride; hoisting node j to
-                // position i is legal when no node in (i, j) reads or writes node j's output bytes (ggml-alloc reuses memory)
-                s.group.push_back(a);
-                const int horizon = i + 48 < n ? i + 48 : n;
-                for (int j2 = i + 1; j2 < horizon && s.group.size() < B200_GEMV_MAX_JOBS; j2++) {
-                    const ggml_tensor *b = cg->nodes[j2];
-                    if (done[j2] || !mul_mat_fusable(b)) continue;
-                    if (b->src[1] != a->src[1] || b->src[0]->type != a->src[0]->type || b->src[0]->nb[1] != a->src[0]->nb[1] || (a->ne[1] > 1 && b->nb[1] != a->nb[1])) continue;
-                    bool ok = true;
-                    const size_t len = nbytes(b);
-                    for (int m = i; m < j2 && ok; m++) ok = !node_touches(cg->nodes[m], b->data, len);
-                    if (!ok) continue;
-                    s.group.push_back(b);
-                    done[j2] = 1;
+        if (j < n && silu_mul_pair(a, cg->nodes[j])) { s.kind = STEP_SILU_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
+
+        if (a->op == GGML_OP_ROPE) {
+            int m[4];
+            if (match_rope_kv(gi, i, done, m)) {
+                std::vector<int> members(m, m + 4);
+                if (can_gather(gi, members, m[3], done)) {
+                    Step f;
+                    f.kind = STEP_ROPE_KV; f.n = a; f.n2 = cg->nodes[m[1]];
+                    f.group = {cg->nodes[m[2]], cg->nodes[m[3]]};
+                    f.slot = slot_of[(size_t)m[2]]; f.slot2 = slot_of[(size_t)m[3]];
+                    for (int q = 0; q < 4; q++) done[m[q]] = 1;
+                    deferred[m[3]] = f;
+                    continue;
                 }
-                if (s.group.size() > 1) { s.kind = STEP_GEMV_MULTI; steps.push_back(s); continue; }
-                s.group.clear();
             }
+        }
+
+        if (mul_mat_fusable(a)) {
+            // siblings: later MUL_MATs with the same activation tensor, weight type and row stride, hoisted to this position
+            s.group.push_back(a);
+            const int horizon = i + 48 < n ? i + 48 : n;
+            for (int j2 = i + 1; j2 < horizon && s.group.size() < B200_GEMV_MAX_JOBS; j2++) {
+                const ggml_tensor *b = cg->nodes[j2];
+                if (done[j2] || !mul_mat_fusable(b)) continue;
+                if (b->src[1] != a->src[1] || b->src[0]->type != a->src[0]->type || b->src[0]->nb[1] != a->src[0]->nb[1] || (a->ne[1] > 1 && b->nb[1] != a->nb[1])) continue;
+                std::vector<int> mem = {i, j2};
+                if (!can_gather(gi, mem, i, done)) continue;
+                s.group.push_back(b);
+                done[j2] = 1;
+            }
+            // R2: a GEMV whose only reader is ADD(mm, r) with r already computed -> residual epilogue, the ADD node disappears
+            for (const ggml_tensor *mm : s.group) {
+                const ggml_tensor *d = gi.sole_user(mm);
+                if (!d || d->op != GGML_OP_ADD || d->type != GGML_TYPE_F32) continue;
+                const ggml_tensor *r = d->src[0] == mm ? d->src[1] : d->src[0];
+                if (!r || r == mm || r->type != GGML_TYPE_F32 || !same_shape(r, mm) || !same_shape(d, mm)) continue;
+                if (!is_contiguous(r) || !is_contiguous(d) || !is_contiguous(mm)) continue;
+                const int pr = gi.pos(r), pd = gi.pos(d), pm = gi.pos(mm);
+                if (pr >= i || pd < 0 || done[pd]) continue;  // r must exist before the GEMV runs (leafs have pos -1)
+                std::vector<int> mem = {pm, pd};
+                if (pm != i) mem = {pd};  // a hoisted sibling: only the ADD moves (up to i)
+                if (!can_gather(gi, mem, i, done)) continue;
+                add_of[mm] = d;
+                done[pd] = 1;
+            }
+            s.kind = STEP_GEMV;
+            auto nm = norm_mul_of.find(a->src[1]);
+            s.n2 = nm == norm_mul_of.end() ? nullptr : nm->second;  // RMS_NORM node folded into the prologue
+            for (const ggml_tensor *mm : s.group) {
+                auto ad = add_of.find(mm);
+                s.adds.push_back(ad == add_of.end() ? nullptr : ad->second);
+            }
+            steps.push_back(s);
+            continue;
         }
         steps.push_back(s);
     }
@@ -215,18 +378,49 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
             x.launches++;
             return;
         }
-        case STEP_GEMV_MULTI: {
+        case STEP_GEMV: {
             b200_gemv_job jobs[B200_GEMV_MAX_JOBS];
+            b200_gemv_fuse fuse;
+            memset(&fuse, 0, sizeof(fuse));
             const ggml_tensor *a = s.group[0];
             const ggml_tensor *act = a->src[1];
+            const float *X = (const float *)act->data;
+            int64_t x_stride = (int64_t)(act->nb[1] / 4);
+            if (s.n2) {  // RMS_NORM -> MUL folded into the prologue: read the un-normalised rows
+                const ggml_tensor *rn = s.n2, *mul = act;
+                const ggml_tensor *w = mul->src[0] == rn ? mul->src[1] : mul->src[0];
+                X = (const float *)rn->src[0]->data;
+                x_stride = (int64_t)(rn->src[0]->nb[1] / 4);
+                fuse.norm_weight = (const float *)w->data;
+                memcpy(&fuse.norm_eps, rn->op_params, 4);
+            }
             int nj = 0;
-            for (const ggml_tensor *m : s.group) {
-                jobs[nj].W = m->src[0]->data; jobs[nj].X = (const float *)act->data; jobs[nj].dst = (float *)m->data;
-                jobs[nj].M = m->src[0]->ne[1]; jobs[nj].id_index = -1; jobs[nj]._pad = 0;
+            for (size_t q = 0; q < s.group.size(); q++) {
+                const ggml_tensor *m = s.group[q], *add = s.adds[q];
+                jobs[nj].W = m->src[0]->data; jobs[nj].X = X; jobs[nj].M = m->src[0]->ne[1]; jobs[nj].id_index = -1; jobs[nj]._pad = 0;
+                if (add) {
+                    const ggml_tensor *r = add->src[0] == m ? add->src[1] : add->src[0];
+                    jobs[nj].dst = (float *)add->data;
+                    fuse.residual[nj] = (const float *)r->data;
+                } else {
+                    jobs[nj].dst = (float *)m->data;
+                }
                 nj++;
             }
-            B200_CHECK_RC(b200_mul_mat_vec_q_multi(a->src[0]->type, jobs, nj, a->src[0]->nb[1], (int64_t)(act->nb[1] / 4), (int64_t)(a->nb[1] / 4),
-                                                   a->src[0]->ne[0], act->ne[1], nullptr, 0, 0, x.stream));
+            B200_CHECK_RC(b200_mul_mat_vec_q_fused(a->src[0]->type, jobs, nj, a->src[0]->nb[1], x_stride, (int64_t)(a->nb[1] / 4), a->src[0]->ne[0], act->ne[1],
+                                                   &fuse, x.stream));
+            x.launches++;
+            return;
+        }
+        case STEP_ROPE_KV: {
+            const ggml_tensor *rq = s.n, *rk = s.n2, *ck = s.group[0], *cv = s.group[1];
+            b200_rope_params rp;
+            rp.n_dims = rq->op_params[1]; rp.mode = rq->op_params[2]; rp.n_ctx_orig = rq->op_params[4];
+            memcpy(&rp.freq_base, rq->op_params + 5, 4); memcpy(&rp.freq_scale, rq->op_params + 6, 4); memcpy(&rp.ext_factor, rq->op_params + 7, 4);
+            memcpy(&rp.attn_factor, rq->op_params + 8, 4); memcpy(&rp.beta_fast, rq->op_params + 9, 4); memcpy(&rp.beta_slow, rq->op_params + 10, 4);
+            b200_tensor q = as_b200(rq->src[0]), qd = as_b200(rq), k = as_b200(rk->src[0]), kd = as_b200(rk), v = as_b200(cv->src[0]);
+            B200_CHECK_RC(b200_op_rope_kv_store(&q, &qd, &k, &kd, &v, (const int32_t *)rq->src[1]->data, rq->src[2] ? (const float *)rq->src[2]->data : nullptr, &rp,
+                                                ck->type, nullptr, nullptr, (void *const *)(g->slots_dev + s.slot), (void *const *)(g->slots_dev + s.slot2), x.stream));
             x.launches++;
             return;
         }

@@ -44,6 +44,11 @@ struct MmvqParams {
     int64_t        x_stride, dst_stride;
     const int32_t *ids;
     size_t         expert_bytes;
+    // fused prologue / epilogue (b200_mul_mat_vec_q_fused): X is RMS-normalised and scaled by norm_w while it is quantised;
+    // residual[j] (same layout as jobs[j].dst) is added to the result of job j
+    const float   *norm_w;
+    float          norm_eps;
+    const float   *residual[B200_GEMV_MAX_JOBS];
 };
 
 template <int TYPE>
@@ -73,9 +78,26 @@ __device__ __forceinline__ ActView act_view(unsigned char *base, int n_it, int c
 
 // Quantise X[n][0..K) (f32, global) into the CTA's shared activation store.  All threads of the CTA call this.
 template <int NCOLS>
-__device__ void load_activations(unsigned char *act_base, const float *__restrict__ X, int64_t x_stride, int64_t K, int n_it) {
+__device__ void load_activations(unsigned char *act_base, const float *__restrict__ X, int64_t x_stride, int64_t K, int n_it,
+                                 const float *__restrict__ norm_w, float norm_eps, float *red) {
     const int n4 = (int)(K / 4);
     for (int n = 0; n < NCOLS; n++) {
+        float nscale = 1.0f;
+        if (norm_w != nullptr) {  // RMS_NORM folded into the quantiser: scale = rsqrt(mean(x^2) + eps)  (ggml.c:12060-12110)
+            const float *xs = X + (int64_t)n * x_stride;
+            float ss = 0.f;
+            for (int i4 = threadIdx.x; i4 < n4; i4 += MMVQ_THREADS) {
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(xs) + i4);
+                ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+            }
+            ss = warp_sum(ss);
+            __syncthreads();  // red[] may still be read by the previous column
+            if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+            __syncthreads();
+            float t = (threadIdx.x & 31) < MMVQ_NW ? red[threadIdx.x & 31] : 0.f;
+            t = warp_sum(t);
+            nscale = rsqrtf(t / (float)K + norm_eps);
+        }
         unsigned char *p = act_base + (size_t)n * act_col_bytes(n_it);
         int   *aq = (int *)p;
         float *ad = (float *)(p + (size_t)n_it * 4096);
@@ -90,6 +112,11 @@ __device__ void load_activations(unsigned char *act_base, const float *__restric
             for (int u = 0; u < 4; u++) {
                 const int i4 = base + u * MMVQ_THREADS + threadIdx.x;
                 v[u] = i4 < n4 ? __ldg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                if (norm_w != nullptr && i4 < n4) {  // (x * scale) * w, the order of the RMS_NORM -> MUL node pair
+                    const float4 ww = __ldg(reinterpret_cast<const float4 *>(norm_w) + i4);
+                    v[u].x = v[u].x * nscale * ww.x; v[u].y = v[u].y * nscale * ww.y;
+                    v[u].z = v[u].z * nscale * ww.z; v[u].w = v[u].w * nscale * ww.w;
+                }
             }
 #pragma unroll
             for (int u = 0; u < 4; u++) {
@@ -400,6 +427,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
     TRACE(0);
     constexpr bool ALIGNED16 = (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K);  // host guarantees 16-byte rows
     extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ float red[MMVQ_NW];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_stage = p.n_stage, n_it = p.n_it;
@@ -496,7 +524,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         const float *xj = p.jobs[job].X;
         if (loaded_x != xj && nrows > 0) {
             if (loaded_x != nullptr) __syncthreads();  // everyone is done with the previous activations
-            load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it);
+            load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red);
             __syncthreads();
             loaded_x = xj;
             TRACE(4);
@@ -505,13 +533,16 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
             const int lr = warp + k * MMVQ_NW;
             uintptr_t src;
             float *dst;
+            const float *res;
             if constexpr (MULTI) {
                 if (rjob[lr] != job) break;
                 src = (uintptr_t)rsrc[lr];
                 dst = rdst[lr];
+                res = p.residual[job] ? p.residual[job] + (dst - p.jobs[job].dst) : nullptr;
             } else {
                 src = (uintptr_t)w0 + (size_t)(r0 + lr) * p.w_row_bytes;
                 dst = p.jobs[0].dst + (r0 + lr);
+                res = p.residual[0] ? p.residual[0] + (r0 + lr) : nullptr;
             }
             for (int it = 0; it < n_it; it++) {
                 mbar_wait(&my_bars[cstage], cphase);
@@ -531,7 +562,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
             for (int n = 0; n < NCOLS; n++) {
                 float v = warp_sum(acc[n]);
                 if (MULTI && src == 0) v = __int_as_float(0x7fc00000);
-                if (lane == 0) dst[(int64_t)n * p.dst_stride] = v;
+                if (lane == 0) dst[(int64_t)n * p.dst_stride] = res ? v + res[(int64_t)n * p.dst_stride] : v;
                 acc[n] = 0.f;
             }
             if (k == 0) TRACE(6);
@@ -634,7 +665,8 @@ static int dispatch_cols(MmvqParams &p, int N, cudaStream_t st, bool pdl) {
 bool g_mmvq_pdl = false;  // set by the backend when it launches chains of dependent kernels
 
 int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride, int64_t dst_stride,
-                int64_t K, int64_t N, const int32_t *ids, size_t expert_bytes, int32_t n_expert, cudaStream_t st) {
+                int64_t K, int64_t N, const int32_t *ids, size_t expert_bytes, int32_t n_expert, cudaStream_t st,
+                const b200_gemv_fuse *fuse = nullptr) {
     if (!jobs || n_jobs < 1 || n_jobs > B200_GEMV_MAX_JOBS) { set_error("b200_mul_mat_vec_q: n_jobs=%d out of range", n_jobs); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
@@ -656,6 +688,12 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
     p.ids = ids;
     p.expert_bytes = expert_bytes;
     p.n_expert = n_expert;
+    if (fuse) {
+        p.norm_w = fuse->norm_weight;
+        p.norm_eps = fuse->norm_eps;
+        if (fuse->norm_weight && ((uintptr_t)fuse->norm_weight & 15)) { set_error("b200_mul_mat_vec_q_fused: norm weight must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
+        for (int j = 0; j < n_jobs; j++) p.residual[j] = fuse->residual[j];
+    }
     int64_t total = 0;
     const bool need16 = (type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K);
     for (int j = 0; j < n_jobs; j++) {
@@ -704,6 +742,11 @@ extern "C" int b200_mul_mat_vec_q_multi(int type, const b200_gemv_job *jobs, int
                                         int64_t dst_stride, int64_t K, int64_t N, const int32_t *ids, size_t expert_bytes,
                                         int32_t n_expert, b200_stream_t stream) {
     return mmvq_launch(type, jobs, n_jobs, w_row_bytes, x_stride, dst_stride, K, N, ids, expert_bytes, n_expert, (cudaStream_t)stream);
+}
+
+extern "C" int b200_mul_mat_vec_q_fused(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride,
+                                        int64_t dst_stride, int64_t K, int64_t N, const b200_gemv_fuse *fuse, b200_stream_t stream) {
+    return mmvq_launch(type, jobs, n_jobs, w_row_bytes, x_stride, dst_stride, K, N, nullptr, 0, 0, (cudaStream_t)stream, fuse);
 }
 
 extern "C" int b200_mul_mat_id_vec_q(int type, const void *as, size_t w_row_bytes, size_t expert_bytes, int32_t n_expert,

