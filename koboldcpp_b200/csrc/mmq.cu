@@ -1,14 +1,430 @@
 // mmq.cu -- (a7) prefill GEMM over GGUF block formats on the 5th-generation tensor cores (tcgen05 + TMEM).
-// Placeholder translation unit until the tcgen05 kernel lands: the entry points exist so the C ABI is complete
-// and report B200_ERR_UNSUPPORTED (there is deliberately no CPU or cuBLAS fallback).
+//
+//   dst[n][m] = sum_k W[m][k] * X[n][k],  W quantised (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K), X f32, any N.
+//
+// Replaces ggml_cuda_op_mul_mat_q / mul_mat_q<type,...> (mma.sync m16n8k32 int8 tiles with ALU-side unpack and two CTA
+// barriers per 128-K half step, /root/reference/ggml/src/ggml-cuda/mmq.cuh:2495-2905) and the cuBLAS dequantise-then-GEMM
+// fallback that koboldcpp uses by default (ggml-cuda.cu:1186-1284: whole-tensor dequant to f16 in HBM, then cublasGemmEx).
+//
+// B200 design (the one dense contraction of the path: tensor-pipe bound once N is a few hundred):
+//   * weights are dequantised ON THE FLY into bf16 operand tiles in shared memory (never to HBM) by 4 producer warps --
+//     thread t owns weight row t of the 128-row tile and writes its 64-value K-step straight into the 128-byte-swizzled
+//     K-major layout the tensor core reads; activations are converted f32 -> bf16 once per call by a pre-pass and staged
+//     with 16-byte cp.async into the same swizzled layout;
+//   * one elected thread issues tcgen05.mma (kind::f16, bf16 x bf16 -> f32, M=128, N<=256, K=16 x4 per stage); the f32
+//     accumulator tile lives in TMEM (N columns x 128 lanes), so the producers' registers are free for unpacking;
+//   * 4-stage shared-memory ring with mbarrier full/empty pairs; tcgen05.commit releases a stage when the MMAs that read
+//     it retire -- no CTA-wide barrier in the K loop;
+//   * epilogue: the same 4 warps read their TMEM lane quarter (tcgen05.ld 32x32b) and store f32 rows coalesced along m.
+// Why bf16 and not kind::i8: per-32 (per-16 for Q6_K) group scales would force a TMEM read-out after every K=32 MMA,
+// which is epilogue-bound; bf16 operands keep the whole K loop inside the tensor pipe.  Activations carry 8 mantissa bits
+// (q8_1 carries 7 + sign per 32-block), weights are rounded once from their exact f32 dequantised value.
 #include "b200_common.cuh"
+
+#include <cuda_bf16.h>
+
+namespace b200 {
+
+constexpr int MQ_BM = 128, MQ_BK = 64, MQ_STAGES = 4;
+constexpr int MQ_PRODUCERS = 128;              // threads; warps 0..3
+constexpr int MQ_THREADS = MQ_PRODUCERS + 32;  // + the MMA warp
+
+// ---------------------------------------------------------------- tcgen05 / TMEM wrappers (PTX ISA 8.6+, sm_100a)
+__device__ __forceinline__ void tmem_alloc(unsigned *smem_dst, unsigned ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(unsigned taddr, unsigned ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(unsigned long long *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(unsigned tmem_d, unsigned long long adesc, unsigned long long bdesc, unsigned idesc, unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 consecutive f32 accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(unsigned taddr, float (&v)[32]) {
+    unsigned r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+          "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+          "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]),
+          "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
+// UMMA shared-memory descriptor, K-major operand tile with 128-byte swizzle (cute/arch/mma_sm100_desc.hpp SmemDescriptor):
+// start address >> 4 in [0,14), LBO [16,30) (unused for swizzled K-major: 1), SBO [32,46) = 1024 B >> 4 (8 rows x 128 B),
+// version [46,48) = 1 (sm_100), layout [61,64) = 2 (SWIZZLE_128B).
+__device__ __forceinline__ unsigned long long umma_desc_sw128(unsigned smem_addr) {
+    unsigned long long d = 0;
+    d |= (unsigned long long)((smem_addr & 0x3FFFFu) >> 4);
+    d |= (unsigned long long)1 << 16;
+    d |= (unsigned long long)(1024 >> 4) << 32;
+    d |= (unsigned long long)1 << 46;
+    d |= (unsigned long long)2 << 61;
+    return d;
+}
+// instruction descriptor (InstrDescriptor): D f32 [4,6)=1, A bf16 [7,10)=1, B bf16 [10,13)=1, both K-major, N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr unsigned umma_idesc_bf16(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(N >> 3) << 17) | ((unsigned)(M >> 4) << 24);
+}
+
+// ---------------------------------------------------------------- raw block loads from 2-byte aligned global addresses
+template <int NW>
+__device__ __forceinline__ void ldg_words(const unsigned char *p, unsigned (&w)[NW]) {
+    const uintptr_t a = (uintptr_t)p;
+    const unsigned *q = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
+    const unsigned sh = (unsigned)(a & 3) * 8;
+    if (sh == 0) {
+#pragma unroll
+        for (int i = 0; i < NW; i++) w[i] = __ldg(q + i);
+    } else {
+        unsigned prev = __ldg(q);
+#pragma unroll
+        for (int i = 0; i < NW; i++) {
+            const unsigned nxt = __ldg(q + i + 1);
+            w[i] = __funnelshift_r(prev, nxt, sh);
+            prev = nxt;
+        }
+    }
+}
+__device__ __forceinline__ float f16lo(unsigned w) { return __half2float(__ushort_as_half((unsigned short)(w & 0xffff))); }
+__device__ __forceinline__ float f16hi(unsigned w) { return __half2float(__ushort_as_half((unsigned short)(w >> 16))); }
+__device__ __forceinline__ unsigned pack_bf16(float a, float b) {
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<const unsigned *>(&h);
+}
+
+// ---------------------------------------------------------------- 64 consecutive weights of one row -> 32 packed bf16x2 words
+// `row` points at the row's first block, kb is the 64-value step.  Arithmetic follows dequantize_row_* (ggml-quants.c:1523,
+// 1617, 2556, 2764, 2978) in f32; the result is rounded once to bf16.
+#define BYTE_OF(w, i) (((w)[(i) >> 2] >> (8 * ((i) & 3))) & 0xffu)
+
+template <int TYPE>
+struct Dequant64;
+
+template <>
+struct Dequant64<B200_TYPE_Q4_0> {
+    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
+        unsigned w[9];
+        ldg_words<9>(row + (size_t)kb * 2 * Q4_0_BYTES, w);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const float d = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, 18 * b) | (BYTE_OF(w, 18 * b + 1) << 8))));
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                const unsigned q0 = BYTE_OF(w, 18 * b + 2 + j), q1 = BYTE_OF(w, 18 * b + 3 + j);
+                o[16 * b + j / 2]     = pack_bf16(d * (float)((int)(q0 & 15) - 8), d * (float)((int)(q1 & 15) - 8));
+                o[16 * b + 8 + j / 2] = pack_bf16(d * (float)((int)(q0 >> 4) - 8), d * (float)((int)(q1 >> 4) - 8));
+            }
+        }
+    }
+};
+
+template <>
+struct Dequant64<B200_TYPE_Q8_0> {
+    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
+        unsigned w[17];
+        ldg_words<17>(row + (size_t)kb * 2 * Q8_0_BYTES, w);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const float d = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, 34 * b) | (BYTE_OF(w, 34 * b + 1) << 8))));
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+                const int q0 = (int)(signed char)BYTE_OF(w, 34 * b + 2 + j), q1 = (int)(signed char)BYTE_OF(w, 34 * b + 3 + j);
+                o[16 * b + j / 2] = pack_bf16(d * (float)q0, d * (float)q1);
+            }
+        }
+    }
+};
+
+template <int TYPE>
+struct DequantK45 {  // Q4_K / Q5_K: half d, half dmin, u8 scales[12], (u8 qh[32],) u8 qs[128]
+    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
+        constexpr int BB = TYPE == B200_TYPE_Q4_K ? Q4_K_BYTES : Q5_K_BYTES;
+        const unsigned char *blk = row + (size_t)(kb >> 2) * BB;
+        const int c = kb & 3;
+        const uint4 hdr = __ldg(reinterpret_cast<const uint4 *>(blk));  // rows are 16-byte aligned (checked on the host)
+        const float d = f16lo(hdr.x), dmin = f16hi(hdr.x);
+        const unsigned sw[3] = {hdr.y, hdr.z, hdr.w};
+        const uint4 *qp = reinterpret_cast<const uint4 *>(blk + (TYPE == B200_TYPE_Q4_K ? 16 : 48) + 32 * c);
+        const uint4 qa = __ldg(qp), qb = __ldg(qp + 1);
+        const unsigned q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
+        unsigned h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        if constexpr (TYPE == B200_TYPE_Q5_K) {
+            const uint4 ha = __ldg(reinterpret_cast<const uint4 *>(blk + 16)), hb = __ldg(reinterpret_cast<const uint4 *>(blk + 32));
+            h[0] = ha.x; h[1] = ha.y; h[2] = ha.z; h[3] = ha.w; h[4] = hb.x; h[5] = hb.y; h[6] = hb.z; h[7] = hb.w;
+        }
+#pragma unroll
+        for (int hf = 0; hf < 2; hf++) {  // hf = 0: low nibbles (sub-block 2c), 1: high nibbles (sub-block 2c+1)
+            const int sb = 2 * c + hf;
+            int sc, mn;
+            k4_scale_min(sw, sb, sc, mn);
+            const float d1 = d * (float)sc, m1 = dmin * (float)mn;
+#pragma unroll
+            for (int l = 0; l < 32; l += 2) {
+                unsigned q0 = (BYTE_OF(q, l) >> (4 * hf)) & 15, q1 = (BYTE_OF(q, l + 1) >> (4 * hf)) & 15;
+                if constexpr (TYPE == B200_TYPE_Q5_K) {
+                    q0 += ((BYTE_OF(h, l) >> sb) & 1) << 4;
+                    q1 += ((BYTE_OF(h, l + 1) >> sb) & 1) << 4;
+                }
+                o[16 * hf + l / 2] = pack_bf16(d1 * (float)q0 - m1, d1 * (float)q1 - m1);
+            }
+        }
+    }
+};
+template <> struct Dequant64<B200_TYPE_Q4_K> : DequantK45<B200_TYPE_Q4_K> {};
+template <> struct Dequant64<B200_TYPE_Q5_K> : DequantK45<B200_TYPE_Q5_K> {};
+
+template <>
+struct Dequant64<B200_TYPE_Q6_K> {  // u8 ql[128], u8 qh[64], i8 scales[16], half d   (2-byte aligned blocks)
+    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
+        const unsigned char *blk = row + (size_t)(kb >> 2) * Q6_K_BYTES;
+        const int c = kb & 3, half = c >> 1, hi = c & 1;
+        unsigned ql[16], qh[8], sc[1], dw[1];
+        ldg_words<16>(blk + 64 * half, ql);
+        ldg_words<8>(blk + 128 + 32 * half, qh);
+        ldg_words<1>(blk + 192 + 8 * half + 4 * hi, sc);
+        ldg_words<1>(blk + 208, dw);
+        const float d = f16lo(dw[0]);
+#pragma unroll
+        for (int g = 0; g < 4; g++) {  // 16-value groups: jj = 16g .. 16g+15, one int8 scale each
+            const float ds = d * (float)(int)(signed char)BYTE_OF(sc, g);
+            const int rlow = g >> 1, r = 2 * hi + rlow;
+#pragma unroll
+            for (int e = 0; e < 16; e += 2) {
+                const int l = 16 * (g & 1) + e;
+                const unsigned b0 = BYTE_OF(ql, 32 * rlow + l), b1 = BYTE_OF(ql, 32 * rlow + l + 1);
+                const unsigned n0 = hi ? (b0 >> 4) : (b0 & 15), n1 = hi ? (b1 >> 4) : (b1 & 15);
+                const unsigned h0 = (BYTE_OF(qh, l) >> (2 * r)) & 3, h1 = (BYTE_OF(qh, l + 1) >> (2 * r)) & 3;
+                o[8 * g + e / 2] = pack_bf16(ds * (float)((int)(n0 | (h0 << 4)) - 32), ds * (float)((int)(n1 | (h1 << 4)) - 32));
+            }
+        }
+    }
+};
+
+// ---------------------------------------------------------------- activation pre-pass: f32 [N][K] -> bf16 [N_pad][K] (pad rows zero)
+__global__ void mmq_x_to_bf16_kernel(const float *__restrict__ x, int64_t x_stride, int64_t K, int64_t N, int64_t n_pad, __nv_bfloat16 *__restrict__ out) {
+    const int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // float4 index within a row
+    const int64_t n = blockIdx.y;
+    if (i4 * 4 >= K) return;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n < N) v = __ldg(reinterpret_cast<const float4 *>(x + n * x_stride) + i4);
+    uint2 pk;
+    pk.x = pack_bf16(v.x, v.y);
+    pk.y = pack_bf16(v.z, v.w);
+    *reinterpret_cast<uint2 *>(out + n * K + i4 * 4) = pk;
+}
+
+struct MmqParams {
+    const unsigned char *W;
+    size_t w_row_bytes;
+    const __nv_bfloat16 *Xb;  // [n_pad][K]
+    float *dst;
+    int64_t dst_stride, K, M, N;
+};
+
+template <int TYPE, int BN>
+__global__ void __launch_bounds__(MQ_THREADS, 1) mmq_tc_kernel(const __grid_constant__ MmqParams p) {
+    constexpr int A_BYTES = MQ_BM * MQ_BK * 2, B_BYTES = BN * MQ_BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);  // SW128 atoms: 1024-byte aligned
+    __shared__ __align__(8) unsigned long long full_bar[MQ_STAGES], empty_bar[MQ_STAGES], tmem_full_bar;
+    __shared__ unsigned tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+    const int64_t m0 = (int64_t)blockIdx.x * MQ_BM, n0 = (int64_t)blockIdx.y * BN;
+    const int nkb = (int)(p.K / MQ_BK);
+
+    if (tid == 0) {
+        for (int s = 0; s < MQ_STAGES; s++) { mbar_init(&full_bar[s], MQ_PRODUCERS); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&tmem_full_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 4) tmem_alloc(&tmem_base_s, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const unsigned tmem_base = tmem_base_s;
+
+    if (warp < 4) {
+        // ===== producers: thread t owns weight row m0 + t and activation rows t, t + 128 of the tile
+        const int64_t m = m0 + tid;
+        const bool row_ok = m < p.M;
+        const unsigned char *wrow = p.W + (size_t)(row_ok ? m : 0) * p.w_row_bytes;
+        const unsigned a_off = (unsigned)((tid >> 3) * 1024 + (tid & 7) * 128);
+        for (int kb = 0; kb < nkb; kb++) {
+            const int s = kb % MQ_STAGES;
+            const unsigned ph = (unsigned)(kb / MQ_STAGES) & 1u;
+            mbar_wait(&empty_bar[s], ph ^ 1u);
+            unsigned char *a_s = smem + (size_t)s * STAGE_BYTES, *b_s = a_s + A_BYTES;
+#pragma unroll
+            for (int r0 = 0; r0 < BN; r0 += MQ_PRODUCERS) {
+                const int r = r0 + tid;
+                if (r < BN) {
+                    const unsigned char *src = reinterpret_cast<const unsigned char *>(p.Xb + (n0 + r) * p.K + (int64_t)kb * MQ_BK);
+                    unsigned char *drow = b_s + (r >> 3) * 1024 + (r & 7) * 128;
+#pragma unroll
+                    for (int c = 0; c < 8; c++) cp_async16(drow + ((c ^ (r & 7)) << 4), src + 16 * c);
+                }
+            }
+            cp_async_commit();
+            unsigned o[32];
+            if (row_ok) Dequant64<TYPE>::run(wrow, kb, o);
+            else {
+#pragma unroll
+                for (int i = 0; i < 32; i++) o[i] = 0u;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; c++)
+                *reinterpret_cast<uint4 *>(a_s + a_off + ((c ^ (tid & 7)) << 4)) = make_uint4(o[4 * c], o[4 * c + 1], o[4 * c + 2], o[4 * c + 3]);
+            cp_async_wait<0>();
+            fence_proxy_async_smem();  // generic-proxy writes (st.shared, cp.async) -> visible to the tensor core's async proxy
+            mbar_arrive(&full_bar[s]);
+        }
+        // ===== epilogue: TMEM lane quarter `warp` -> dst[n][m]
+        mbar_wait(&tmem_full_bar, 0u);
+        tc_fence_after();
+        float *drow = p.dst + m;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(tmem_base + ((unsigned)(warp * 32) << 16) + (unsigned)c0, v);
+            if (row_ok) {
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    const int64_t n = n0 + c0 + j;
+                    if (n < p.N) drow[n * p.dst_stride] = v[j];
+                }
+            }
+        }
+        tc_fence_before();
+    } else {
+        // ===== MMA issuer
+        constexpr unsigned idesc = umma_idesc_bf16(MQ_BM, BN);
+        for (int kb = 0; kb < nkb; kb++) {
+            const int s = kb % MQ_STAGES;
+            const unsigned ph = (unsigned)(kb / MQ_STAGES) & 1u;
+            mbar_wait(&full_bar[s], ph);
+            tc_fence_after();
+            if (lane == 0) {
+                const unsigned a_addr = smem_u32(smem + (size_t)s * STAGE_BYTES), b_addr = a_addr + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < MQ_BK / 16; k++) {
+                    // 16 bf16 = 32 bytes further along K inside the swizzle atom: +2 in the (address >> 4) field
+                    tc_mma_bf16(tmem_base, umma_desc_sw128(a_addr) + 2u * k, umma_desc_sw128(b_addr) + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                }
+                tc_commit(&empty_bar[s]);
+                if (kb == nkb - 1) tc_commit(&tmem_full_bar);
+            }
+            __syncwarp();
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN);
+    }
+}
+
+// ---------------------------------------------------------------- host side
+static int64_t mmq_bn(int64_t N) { return N <= 32 ? 32 : N <= 64 ? 64 : N <= 128 ? 128 : 256; }
+static int64_t mmq_n_pad(int64_t N) { const int64_t bn = mmq_bn(N); return (N + bn - 1) / bn * bn; }
+
+template <int TYPE, int BN>
+static int mmq_launch(const MmqParams &p, cudaStream_t st) {
+    constexpr size_t smem = (size_t)MQ_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    dim3 grid((unsigned)((p.M + MQ_BM - 1) / MQ_BM), (unsigned)((p.N + BN - 1) / BN));
+    mmq_tc_kernel<TYPE, BN><<<grid, MQ_THREADS, smem, st>>>(p);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+template <int TYPE>
+static int mmq_dispatch_bn(const MmqParams &p, cudaStream_t st) {
+    switch (mmq_bn(p.N)) {
+        case 32: return mmq_launch<TYPE, 32>(p, st);
+        case 64: return mmq_launch<TYPE, 64>(p, st);
+        case 128: return mmq_launch<TYPE, 128>(p, st);
+        default: return mmq_launch<TYPE, 256>(p, st);
+    }
+}
+
+}  // namespace b200
 
 using namespace b200;
 
-extern "C" size_t b200_mul_mat_q_workspace_bytes(int, int64_t, int64_t, int64_t) { return 0; }
+extern "C" size_t b200_mul_mat_q_workspace_bytes(int type, int64_t K, int64_t M, int64_t N) {
+    (void)type; (void)M;
+    if (K <= 0 || N <= 0) return 0;
+    return (size_t)mmq_n_pad(N) * (size_t)K * 2 + 256;
+}
 
-extern "C" int b200_mul_mat_q(int, const void *, size_t, const float *, int64_t, float *, int64_t, int64_t, int64_t, int64_t, void *,
-                              size_t, b200_stream_t) {
-    set_error("b200_mul_mat_q: tcgen05 prefill GEMM not built yet");
+extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const float *X, int64_t x_stride, float *dst, int64_t dst_stride,
+                              int64_t K, int64_t M, int64_t N, void *workspace, size_t workspace_bytes, b200_stream_t stream) {
+    if (!W || !X || !dst) { set_error("b200_mul_mat_q: NULL argument"); return B200_ERR_INVALID; }
+    const int bv = type_block_values(type);
+    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
+        set_error("b200_mul_mat_q: unsupported weight type %d", type);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (K <= 0 || K % bv || M < 0 || N < 0) { set_error("b200_mul_mat_q: bad shape K=%lld M=%lld N=%lld", (long long)K, (long long)M, (long long)N); return B200_ERR_INVALID; }
+    if (K % MQ_BK) { set_error("b200_mul_mat_q: K=%lld must be a multiple of %d", (long long)K, MQ_BK); return B200_ERR_UNSUPPORTED; }
+    if (M == 0 || N == 0) return B200_OK;
+    const size_t row_bytes = (size_t)(K / bv) * type_block_bytes(type);
+    if (w_row_bytes < row_bytes || (w_row_bytes & 1) || ((uintptr_t)W & 1)) { set_error("b200_mul_mat_q: weight stride/alignment"); return B200_ERR_INVALID; }
+    if ((type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K) && ((w_row_bytes & 15) || ((uintptr_t)W & 15))) {
+        set_error("b200_mul_mat_q: q4_K/q5_K rows must be 16-byte aligned");
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (((uintptr_t)X & 15) || (x_stride & 3)) { set_error("b200_mul_mat_q: X must be 16-byte aligned with a row stride multiple of 4"); return B200_ERR_UNSUPPORTED; }
+    const size_t need = b200_mul_mat_q_workspace_bytes(type, K, M, N);
+    if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 15)) {
+        set_error("b200_mul_mat_q: workspace of %zu bytes (16-byte aligned) required, %zu given", need, workspace_bytes);
+        return B200_ERR_INVALID;
+    }
+    const cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n_pad = mmq_n_pad(N);
+    if (n_pad > 65535) { set_error("b200_mul_mat_q: N too large"); return B200_ERR_UNSUPPORTED; }
+    __nv_bfloat16 *xb = (__nv_bfloat16 *)workspace;
+    dim3 g1((unsigned)((K / 4 + 255) / 256), (unsigned)n_pad);
+    mmq_x_to_bf16_kernel<<<g1, 256, 0, st>>>(X, x_stride, K, N, n_pad, xb);
+    B200_CUDA_TRY(cudaGetLastError());
+    MmqParams p;
+    p.W = (const unsigned char *)W; p.w_row_bytes = w_row_bytes; p.Xb = xb; p.dst = dst; p.dst_stride = dst_stride; p.K = K; p.M = M; p.N = N;
+    switch (type) {
+        case B200_TYPE_Q4_0: return mmq_dispatch_bn<B200_TYPE_Q4_0>(p, st);
+        case B200_TYPE_Q8_0: return mmq_dispatch_bn<B200_TYPE_Q8_0>(p, st);
+        case B200_TYPE_Q4_K: return mmq_dispatch_bn<B200_TYPE_Q4_K>(p, st);
+        case B200_TYPE_Q5_K: return mmq_dispatch_bn<B200_TYPE_Q5_K>(p, st);
+        case B200_TYPE_Q6_K: return mmq_dispatch_bn<B200_TYPE_Q6_K>(p, st);
+    }
     return B200_ERR_UNSUPPORTED;
 }

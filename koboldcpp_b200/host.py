@@ -152,3 +152,18 @@ def flash_attn_ext(q: np.ndarray, k: np.ndarray, v: np.ndarray, mask: np.ndarray
     out = dd.to_numpy(np.float32, (N, n_head, D))
     # the kernel must leave its ticket counters zeroed for the next launch
     return out
+
+
+def mul_mat_q(t: int, w: np.ndarray, x: np.ndarray, K: int, M: int) -> np.ndarray:
+    """Prefill GEMM on the tensor cores (b200_mul_mat_q): w packed rows [M, row_bytes], x f32 [N, K] -> f32 [N, M]."""
+    require_gpu()
+    x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, K)
+    N = x.shape[0]
+    rs = row_size(t, K)
+    dw = DeviceBuffer.from_numpy(np.ascontiguousarray(w).reshape(-1), pad=256)
+    dx = DeviceBuffer.from_numpy(x)
+    dd = DeviceBuffer(4 * N * M + 256)
+    ws_bytes = lib().b200_mul_mat_q_workspace_bytes(t, K, M, N)
+    ws = DeviceBuffer(ws_bytes + 16)
+    check(lib().b200_mul_mat_q(t, dw.ptr, rs, dx.ptr, K, dd.ptr, M, K, M, N, ws.ptr, ws_bytes, None), "b200_mul_mat_q")
+    return dd.to_numpy(np.float32, (N, M))
