@@ -23,6 +23,8 @@
 
 #include <cuda_bf16.h>
 
+#include <cstdlib>
+
 namespace b200 {
 
 constexpr int MQ_BM = 128, MQ_BK = 64, MQ_STAGES = 4;
@@ -91,19 +93,22 @@ __host__ __device__ constexpr unsigned umma_idesc_bf16(int M, int N) {
 }
 
 // ---------------------------------------------------------------- raw block loads from 2-byte aligned global addresses
-template <int NW>
-__device__ __forceinline__ void ldg_words(const unsigned char *p, unsigned (&w)[NW]) {
+// G = true: global memory through the read-only path; false: shared memory (raw blocks staged by the bulk-copy engine)
+template <bool G> __device__ __forceinline__ unsigned ld32(const unsigned *q) { if constexpr (G) return __ldg(q); else return *q; }
+template <bool G> __device__ __forceinline__ uint4 ld128(const uint4 *q) { if constexpr (G) return __ldg(q); else return *q; }
+template <bool G, int NW>
+__device__ __forceinline__ void ld_words(const unsigned char *p, unsigned (&w)[NW]) {
     const uintptr_t a = (uintptr_t)p;
     const unsigned *q = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
     const unsigned sh = (unsigned)(a & 3) * 8;
     if (sh == 0) {
 #pragma unroll
-        for (int i = 0; i < NW; i++) w[i] = __ldg(q + i);
+        for (int i = 0; i < NW; i++) w[i] = ld32<G>(q + i);
     } else {
-        unsigned prev = __ldg(q);
+        unsigned prev = ld32<G>(q);
 #pragma unroll
         for (int i = 0; i < NW; i++) {
-            const unsigned nxt = __ldg(q + i + 1);
+            const unsigned nxt = ld32<G>(q + i + 1);
             w[i] = __funnelshift_r(prev, nxt, sh);
             prev = nxt;
         }
@@ -121,14 +126,17 @@ __device__ __forceinline__ unsigned pack_bf16(float a, float b) {
 // 1617, 2556, 2764, 2978) in f32; the result is rounded once to bf16.
 #define BYTE_OF(w, i) (((w)[(i) >> 2] >> (8 * ((i) & 3))) & 0xffu)
 
-template <int TYPE>
-struct Dequant64;
+// bytes of the 256-value group a K-step of 64 belongs to (one K-quant super-block, or 8 q4_0 / q8_0 blocks)
+__host__ __device__ constexpr int group256_bytes(int t) { return type_block_bytes(t) * 256 / type_block_values(t); }
 
-template <>
-struct Dequant64<B200_TYPE_Q4_0> {
-    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
+template <int TYPE, bool G>
+struct Dequant64;  // run(g, c, o): g -> first byte of the 256-value group, c = 64-value chunk 0..3 inside it
+
+template <bool G>
+struct Dequant64<B200_TYPE_Q4_0, G> {
+    static __device__ __forceinline__ void run(const unsigned char *g, int c, unsigned (&o)[32]) {
         unsigned w[9];
-        ldg_words<9>(row + (size_t)kb * 2 * Q4_0_BYTES, w);
+        ld_words<G, 9>(g + c * 2 * Q4_0_BYTES, w);
 #pragma unroll
         for (int b = 0; b < 2; b++) {
             const float d = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, 18 * b) | (BYTE_OF(w, 18 * b + 1) << 8))));
@@ -142,11 +150,11 @@ struct Dequant64<B200_TYPE_Q4_0> {
     }
 };
 
-template <>
-struct Dequant64<B200_TYPE_Q8_0> {
-    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
+template <bool G>
+struct Dequant64<B200_TYPE_Q8_0, G> {
+    static __device__ __forceinline__ void run(const unsigned char *g, int c, unsigned (&o)[32]) {
         unsigned w[17];
-        ldg_words<17>(row + (size_t)kb * 2 * Q8_0_BYTES, w);
+        ld_words<G, 17>(g + c * 2 * Q8_0_BYTES, w);
 #pragma unroll
         for (int b = 0; b < 2; b++) {
             const float d = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, 34 * b) | (BYTE_OF(w, 34 * b + 1) << 8))));
@@ -159,21 +167,18 @@ struct Dequant64<B200_TYPE_Q8_0> {
     }
 };
 
-template <int TYPE>
+template <int TYPE, bool G>
 struct DequantK45 {  // Q4_K / Q5_K: half d, half dmin, u8 scales[12], (u8 qh[32],) u8 qs[128]
-    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
-        constexpr int BB = TYPE == B200_TYPE_Q4_K ? Q4_K_BYTES : Q5_K_BYTES;
-        const unsigned char *blk = row + (size_t)(kb >> 2) * BB;
-        const int c = kb & 3;
-        const uint4 hdr = __ldg(reinterpret_cast<const uint4 *>(blk));  // rows are 16-byte aligned (checked on the host)
+    static __device__ __forceinline__ void run(const unsigned char *blk, int c, unsigned (&o)[32]) {
+        const uint4 hdr = ld128<G>(reinterpret_cast<const uint4 *>(blk));  // rows are 16-byte aligned (checked on the host)
         const float d = f16lo(hdr.x), dmin = f16hi(hdr.x);
         const unsigned sw[3] = {hdr.y, hdr.z, hdr.w};
         const uint4 *qp = reinterpret_cast<const uint4 *>(blk + (TYPE == B200_TYPE_Q4_K ? 16 : 48) + 32 * c);
-        const uint4 qa = __ldg(qp), qb = __ldg(qp + 1);
+        const uint4 qa = ld128<G>(qp), qb = ld128<G>(qp + 1);
         const unsigned q[8] = {qa.x, qa.y, qa.z, qa.w, qb.x, qb.y, qb.z, qb.w};
         unsigned h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         if constexpr (TYPE == B200_TYPE_Q5_K) {
-            const uint4 ha = __ldg(reinterpret_cast<const uint4 *>(blk + 16)), hb = __ldg(reinterpret_cast<const uint4 *>(blk + 32));
+            const uint4 ha = ld128<G>(reinterpret_cast<const uint4 *>(blk + 16)), hb = ld128<G>(reinterpret_cast<const uint4 *>(blk + 32));
             h[0] = ha.x; h[1] = ha.y; h[2] = ha.z; h[3] = ha.w; h[4] = hb.x; h[5] = hb.y; h[6] = hb.z; h[7] = hb.w;
         }
 #pragma unroll
@@ -194,19 +199,18 @@ struct DequantK45 {  // Q4_K / Q5_K: half d, half dmin, u8 scales[12], (u8 qh[32
         }
     }
 };
-template <> struct Dequant64<B200_TYPE_Q4_K> : DequantK45<B200_TYPE_Q4_K> {};
-template <> struct Dequant64<B200_TYPE_Q5_K> : DequantK45<B200_TYPE_Q5_K> {};
+template <bool G> struct Dequant64<B200_TYPE_Q4_K, G> : DequantK45<B200_TYPE_Q4_K, G> {};
+template <bool G> struct Dequant64<B200_TYPE_Q5_K, G> : DequantK45<B200_TYPE_Q5_K, G> {};
 
-template <>
-struct Dequant64<B200_TYPE_Q6_K> {  // u8 ql[128], u8 qh[64], i8 scales[16], half d   (2-byte aligned blocks)
-    static __device__ __forceinline__ void run(const unsigned char *row, int kb, unsigned (&o)[32]) {
-        const unsigned char *blk = row + (size_t)(kb >> 2) * Q6_K_BYTES;
-        const int c = kb & 3, half = c >> 1, hi = c & 1;
+template <bool G>
+struct Dequant64<B200_TYPE_Q6_K, G> {  // u8 ql[128], u8 qh[64], i8 scales[16], half d   (2-byte aligned blocks)
+    static __device__ __forceinline__ void run(const unsigned char *blk, int c, unsigned (&o)[32]) {
+        const int half = c >> 1, hi = c & 1;
         unsigned ql[16], qh[8], sc[1], dw[1];
-        ldg_words<16>(blk + 64 * half, ql);
-        ldg_words<8>(blk + 128 + 32 * half, qh);
-        ldg_words<1>(blk + 192 + 8 * half + 4 * hi, sc);
-        ldg_words<1>(blk + 208, dw);
+        ld_words<G, 16>(blk + 64 * half, ql);
+        ld_words<G, 8>(blk + 128 + 32 * half, qh);
+        ld_words<G, 1>(blk + 192 + 8 * half + 4 * hi, sc);
+        ld_words<G, 1>(blk + 208, dw);
         const float d = f16lo(dw[0]);
 #pragma unroll
         for (int g = 0; g < 4; g++) {  // 16-value groups: jj = 16g .. 16g+15, one int8 scale each
@@ -291,7 +295,7 @@ __global__ void __launch_bounds__(MQ_THREADS, 1) mmq_tc_kernel(const __grid_cons
             }
             cp_async_commit();
             unsigned o[32];
-            if (row_ok) Dequant64<TYPE>::run(wrow, kb, o);
+            if (row_ok) Dequant64<TYPE, true>::run(wrow + (size_t)(kb >> 2) * group256_bytes(TYPE), kb & 3, o);
             else {
 #pragma unroll
                 for (int i = 0; i < 32; i++) o[i] = 0u;
@@ -349,6 +353,249 @@ __global__ void __launch_bounds__(MQ_THREADS, 1) mmq_tc_kernel(const __grid_cons
     }
 }
 
+// ---------------------------------------------------------------- register-resident variant (software-pipelined producers)
+// A thread keeps the raw bytes of one 256-value group of its row in registers (w[], block start at word 0) and unpacks chunk
+// C (compile time) from them.  Small integers become floats without I2F: PRMT drops the byte into the mantissa of 2^23
+// (0x4B0000bb = 8388608 + b), one exact FADD removes the bias.
+__host__ __device__ constexpr int group256_words(int t) { return (group256_bytes(t) + 3) / 4; }
+template <int K> __device__ __forceinline__ float byte_f(unsigned x) {  // float(byte K of x), exact
+    return __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7650 + K)) - 8388608.0f;
+}
+__device__ __forceinline__ float f16_at(const unsigned *w, int byte_off) {  // fp16 at an even byte offset
+    return (byte_off & 2) ? f16hi(w[byte_off >> 2]) : f16lo(w[byte_off >> 2]);
+}
+
+template <int TYPE, int C>
+struct DequantR;
+
+template <int C>
+struct DequantR<B200_TYPE_Q4_0, C> {
+    static __device__ __forceinline__ void run(const unsigned (&w)[36], unsigned (&o)[32]) {
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            constexpr int dummy = 0; (void)dummy;
+            const int base = 36 * C + 18 * b;  // byte offset of the block
+            const float d = f16_at(w, base), m8 = d * 8.0f;
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                const unsigned q0 = BYTE_OF(w, base + 2 + j), q1 = BYTE_OF(w, base + 3 + j);
+                o[16 * b + j / 2]     = pack_bf16(d * byte_f<0>(q0 & 15) - m8, d * byte_f<0>(q1 & 15) - m8);
+                o[16 * b + 8 + j / 2] = pack_bf16(d * byte_f<0>(q0 >> 4) - m8, d * byte_f<0>(q1 >> 4) - m8);
+            }
+        }
+    }
+};
+
+template <int C>
+struct DequantR<B200_TYPE_Q8_0, C> {
+    static __device__ __forceinline__ void run(const unsigned (&w)[68], unsigned (&o)[32]) {
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const int base = 68 * C + 34 * b;
+            const float d = f16_at(w, base), m128 = d * 128.0f;
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+                // int8 -> biased uint8 (x ^ 0x80 = x + 128), unbias after the multiply
+                const unsigned q0 = BYTE_OF(w, base + 2 + j) ^ 0x80u, q1 = BYTE_OF(w, base + 3 + j) ^ 0x80u;
+                o[16 * b + j / 2] = pack_bf16(d * byte_f<0>(q0) - m128, d * byte_f<0>(q1) - m128);
+            }
+        }
+    }
+};
+
+template <int TYPE, int C>
+struct DequantRK45 {
+    static constexpr int NW = TYPE == B200_TYPE_Q4_K ? 36 : 44;
+    static __device__ __forceinline__ void run(const unsigned (&w)[NW], unsigned (&o)[32]) {
+        constexpr int QS = (TYPE == B200_TYPE_Q4_K ? 4 : 12) + 8 * C;  // first word of this chunk's 32 qs bytes
+        const float d = f16lo(w[0]), dmin = f16hi(w[0]);
+        const unsigned sw[3] = {w[1], w[2], w[3]};
+#pragma unroll
+        for (int hf = 0; hf < 2; hf++) {
+            constexpr int dummy = 0; (void)dummy;
+            const int sb = 2 * C + hf;
+            int sc, mn;
+            k4_scale_min(sw, sb, sc, mn);
+            const float d1 = d * (float)sc, m1 = dmin * (float)mn;
+#pragma unroll
+            for (int i = 0; i < 8; i++) {  // word i holds bytes l = 4i .. 4i+3
+                unsigned x = (w[QS + i] >> (4 * hf)) & 0x0F0F0F0Fu;
+                if constexpr (TYPE == B200_TYPE_Q5_K) x |= ((w[4 + i] >> sb) & 0x01010101u) << 4;
+                o[16 * hf + 2 * i]     = pack_bf16(d1 * byte_f<0>(x) - m1, d1 * byte_f<1>(x) - m1);
+                o[16 * hf + 2 * i + 1] = pack_bf16(d1 * byte_f<2>(x) - m1, d1 * byte_f<3>(x) - m1);
+            }
+        }
+    }
+};
+template <int C> struct DequantR<B200_TYPE_Q4_K, C> : DequantRK45<B200_TYPE_Q4_K, C> {};
+template <int C> struct DequantR<B200_TYPE_Q5_K, C> : DequantRK45<B200_TYPE_Q5_K, C> {};
+
+template <int C>
+struct DequantR<B200_TYPE_Q6_K, C> {
+    static __device__ __forceinline__ void run(const unsigned (&w)[53], unsigned (&o)[32]) {
+        constexpr int half = C >> 1, hi = C & 1;
+        const float d = f16lo(w[52]);
+        const unsigned scw = w[48 + 2 * half + hi];  // 4 int8 scales of this chunk
+#pragma unroll
+        for (int g = 0; g < 4; g++) {
+            const int rlow = g >> 1, r = 2 * hi + rlow;
+            const float ds = d * (float)(int)(signed char)((scw >> (8 * g)) & 0xff), m32 = ds * 32.0f;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {  // 4 values per word: l = 16*(g&1) + 4i ..
+                const int lw = 4 * (g & 1) + i;  // word index inside the 32-byte row
+                const unsigned lo = (w[16 * half + 8 * rlow + lw] >> (4 * hi)) & 0x0F0F0F0Fu;
+                const unsigned h2 = ((w[32 + 8 * half + lw] >> (2 * r)) & 0x03030303u) << 4;
+                const unsigned x = lo | h2;
+                o[8 * g + 2 * i]     = pack_bf16(ds * byte_f<0>(x) - m32, ds * byte_f<1>(x) - m32);
+                o[8 * g + 2 * i + 1] = pack_bf16(ds * byte_f<2>(x) - m32, ds * byte_f<3>(x) - m32);
+            }
+        }
+    }
+};
+
+// ================================================================ v2: asynchronous operand supply
+// Same tensor-core pipeline, but neither operand waits on a global load inside the producers:
+//   * B (bf16 activations) arrives by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle applied by the copy engine) issued by
+//     a dedicated warp as soon as a stage is free;
+//   * the raw quantised blocks of the NEXT 256-value group of each of the 128 rows are staged in shared memory by 1-D bulk
+//     copies (one per row, issued by the row's own thread, aligned-down windows like the decode GEMV) two groups ahead, so the
+//     producers unpack from shared memory.  A thread only ever reads its own row's slot: re-arming a slot needs no CTA barrier.
+constexpr int MQ2_STAGES = 3, MQ2_RAW = 2;
+constexpr int MQ2_THREADS = MQ_PRODUCERS + 64;  // + MMA warp + TMA warp
+// per-row slot stride: >= group bytes + 14 bytes of head misalignment (2-byte aligned formats), rounded to 16, and an ODD
+// number of 16-byte units so that the 8 threads of a quarter-warp hit distinct bank groups with 16-byte accesses
+__host__ __device__ constexpr int raw_stride(int t) {
+    return t == B200_TYPE_Q4_K ? 144 : t == B200_TYPE_Q5_K ? 176 : t == B200_TYPE_Q6_K ? 240 : t == B200_TYPE_Q8_0 ? 304 : 176;
+}
+
+__device__ __forceinline__ void tma_load_2d(void *dst, const void *tmap, int c0, int c1, unsigned long long *bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(smem_u32(dst)),
+                 "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+struct alignas(64) TmapBytes { unsigned char b[128]; };  // CUtensorMap without pulling <cuda.h> into device code
+
+template <int TYPE, int BN>
+__global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_constant__ TmapBytes tmB, const __grid_constant__ MmqParams p) {
+    constexpr int A_BYTES = MQ_BM * MQ_BK * 2, B_BYTES = BN * MQ_BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr int RS = raw_stride(TYPE), G256 = group256_bytes(TYPE), RAW_BYTES = MQ_BM * RS;
+    constexpr bool ALIGNED16 = (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K);
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    unsigned char *raw = smem + (size_t)MQ2_STAGES * STAGE_BYTES;
+    __shared__ __align__(8) unsigned long long full_bar[MQ2_STAGES], empty_bar[MQ2_STAGES], raw_bar[MQ2_RAW], tmem_full_bar;
+    __shared__ unsigned tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+    const int64_t m0 = (int64_t)blockIdx.x * MQ_BM, n0 = (int64_t)blockIdx.y * BN;
+    const int nsb = (int)(p.K / 256), nkb = nsb * 4;
+
+    if (tid == 0) {
+        for (int s = 0; s < MQ2_STAGES; s++) { mbar_init(&full_bar[s], MQ_PRODUCERS + 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < MQ2_RAW; s++) mbar_init(&raw_bar[s], MQ_PRODUCERS);
+        mbar_init(&tmem_full_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 4) tmem_alloc(&tmem_base_s, BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const unsigned tmem_base = tmem_base_s;
+
+    if (warp < 4) {
+        const int64_t m = m0 + tid;
+        const bool row_ok = m < p.M;
+        const unsigned char *wrow = p.W + (size_t)(row_ok ? m : 0) * p.w_row_bytes;
+        const unsigned a_off = (unsigned)((tid >> 3) * 1024 + (tid & 7) * 128);
+        auto arm = [&](int sb) {  // stage the raw bytes of group sb of this thread's row
+            unsigned long long *bar = &raw_bar[sb % MQ2_RAW];
+            if (!row_ok) { mbar_arrive(bar); return; }
+            const unsigned char *src = wrow + (size_t)sb * G256;
+            const unsigned mis = ALIGNED16 ? 0u : (unsigned)((uintptr_t)src & 15);
+            const unsigned len = (mis + (unsigned)G256 + 15u) & ~15u;
+            mbar_expect_tx(bar, len);
+            bulk_g2s(raw + (size_t)(sb % MQ2_RAW) * RAW_BYTES + (size_t)tid * RS, src - mis, len, bar);
+        };
+        for (int sb = 0; sb < MQ2_RAW && sb < nsb; sb++) arm(sb);
+        for (int sb = 0; sb < nsb; sb++) {
+            mbar_wait(&raw_bar[sb % MQ2_RAW], (unsigned)(sb / MQ2_RAW) & 1u);
+            const unsigned char *src = wrow + (size_t)sb * G256;
+            const unsigned mis = ALIGNED16 ? 0u : (unsigned)((uintptr_t)src & 15);
+            const unsigned char *g = raw + (size_t)(sb % MQ2_RAW) * RAW_BYTES + (size_t)tid * RS + mis;
+#pragma unroll 1
+            for (int c = 0; c < 4; c++) {
+                const int kb = sb * 4 + c, s = kb % MQ2_STAGES;
+                unsigned o[32];
+                if (row_ok) Dequant64<TYPE, false>::run(g, c, o);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 32; i++) o[i] = 0u;
+                }
+                mbar_wait(&empty_bar[s], ((unsigned)(kb / MQ2_STAGES) & 1u) ^ 1u);
+                unsigned char *a_s = smem + (size_t)s * STAGE_BYTES;
+#pragma unroll
+                for (int q = 0; q < 8; q++)
+                    *reinterpret_cast<uint4 *>(a_s + a_off + ((q ^ (tid & 7)) << 4)) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+                fence_proxy_async_smem();
+                mbar_arrive(&full_bar[s]);
+            }
+            if (sb + MQ2_RAW < nsb) {
+                fence_proxy_async_smem();  // our generic reads of the slot precede the bulk write that refills it
+                arm(sb + MQ2_RAW);
+            }
+        }
+        mbar_wait(&tmem_full_bar, 0u);
+        tc_fence_after();
+        float *drow = p.dst + m;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            float v[32];
+            tmem_ld32(tmem_base + ((unsigned)(warp * 32) << 16) + (unsigned)c0, v);
+            if (row_ok) {
+#pragma unroll
+                for (int j = 0; j < 32; j++) {
+                    const int64_t n = n0 + c0 + j;
+                    if (n < p.N) drow[n * p.dst_stride] = v[j];
+                }
+            }
+        }
+        tc_fence_before();
+    } else if (warp == 4) {
+        constexpr unsigned idesc = umma_idesc_bf16(MQ_BM, BN);
+        for (int kb = 0; kb < nkb; kb++) {
+            const int s = kb % MQ2_STAGES;
+            mbar_wait(&full_bar[s], (unsigned)(kb / MQ2_STAGES) & 1u);
+            tc_fence_after();
+            if (lane == 0) {
+                const unsigned a_addr = smem_u32(smem + (size_t)s * STAGE_BYTES), b_addr = a_addr + A_BYTES;
+#pragma unroll
+                for (int k = 0; k < MQ_BK / 16; k++)
+                    tc_mma_bf16(tmem_base, umma_desc_sw128(a_addr) + 2u * k, umma_desc_sw128(b_addr) + 2u * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                tc_commit(&empty_bar[s]);
+                if (kb == nkb - 1) tc_commit(&tmem_full_bar);
+            }
+            __syncwarp();
+        }
+        tc_fence_before();
+    } else {
+        // ===== TMA warp: activation tiles [BN rows x 64 bf16] into the swizzled B slot of each free stage
+        if (lane == 0) {
+            for (int kb = 0; kb < nkb; kb++) {
+                const int s = kb % MQ2_STAGES;
+                mbar_wait(&empty_bar[s], ((unsigned)(kb / MQ2_STAGES) & 1u) ^ 1u);
+                mbar_expect_tx(&full_bar[s], (unsigned)B_BYTES);
+                tma_load_2d(smem + (size_t)s * STAGE_BYTES + A_BYTES, &tmB, kb * MQ_BK, (int)n0, &full_bar[s]);
+            }
+        }
+    }
+    __syncthreads();
+    if (warp == 4) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, BN);
+    }
+}
+
 // ---------------------------------------------------------------- host side
 static int64_t mmq_bn(int64_t N) { return N <= 32 ? 32 : N <= 64 ? 64 : N <= 128 ? 128 : 256; }
 static int64_t mmq_n_pad(int64_t N) { const int64_t bn = mmq_bn(N); return (N + bn - 1) / bn * bn; }
@@ -367,8 +614,53 @@ static int mmq_launch(const MmqParams &p, cudaStream_t st) {
     return B200_OK;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on a particular libcuda)
+typedef int (*EncodeTiledFn)(void *, int, unsigned, void *, const unsigned long long *, const unsigned long long *, const unsigned *, const unsigned *, int, int, int, int);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *sym = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qr) == cudaSuccess && qr == cudaDriverEntryPointSuccess) fn = (EncodeTiledFn)sym;
+    }
+    return fn;
+}
+
+template <int TYPE, int BN>
+static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st) {
+    constexpr size_t smem = (size_t)MQ2_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + (size_t)MQ2_RAW * MQ_BM * raw_stride(TYPE) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc2_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) { set_error("b200_mul_mat_q: cuTensorMapEncodeTiled not available"); return B200_ERR_CUDA; }
+    TmapBytes tm;
+    const unsigned long long gdim[2] = {(unsigned long long)p.K, (unsigned long long)n_pad};
+    const unsigned long long gstr[1] = {(unsigned long long)p.K * 2};
+    const unsigned box[2] = {(unsigned)MQ_BK, (unsigned)BN};
+    const unsigned estr[2] = {1, 1};
+    // CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 = 9, INTERLEAVE_NONE = 0, SWIZZLE_128B = 3, L2_PROMOTION_L2_256B = 3, FLOAT_OOB_FILL_NONE = 0
+    const int rc = enc(&tm, 9, 2, (void *)p.Xb, gdim, gstr, box, estr, 0, 3, 3, 0);
+    if (rc != 0) { set_error("b200_mul_mat_q: cuTensorMapEncodeTiled failed (%d)", rc); return B200_ERR_CUDA; }
+    dim3 grid((unsigned)((p.M + MQ_BM - 1) / MQ_BM), (unsigned)((p.N + BN - 1) / BN));
+    mmq_tc2_kernel<TYPE, BN><<<grid, MQ2_THREADS, smem, st>>>(tm, p);
+    B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
 template <int TYPE>
 static int mmq_dispatch_bn(const MmqParams &p, cudaStream_t st) {
+    if (p.K % 256 == 0 && !getenv("B200_MMQ_V1")) {
+        const int64_t n_pad = mmq_n_pad(p.N);
+        switch (mmq_bn(p.N)) {
+            case 32: return mmq2_launch<TYPE, 32>(p, n_pad, st);
+            case 64: return mmq2_launch<TYPE, 64>(p, n_pad, st);
+            case 128: return mmq2_launch<TYPE, 128>(p, n_pad, st);
+            default: return mmq2_launch<TYPE, 256>(p, n_pad, st);
+        }
+    }
     switch (mmq_bn(p.N)) {
         case 32: return mmq_launch<TYPE, 32>(p, st);
         case 64: return mmq_launch<TYPE, 64>(p, st);

@@ -67,6 +67,35 @@ def test_decode_matches_fp64_reference(cfg, type_kv):
         m.close()
 
 
+@pytest.mark.parametrize("cfg,type_kv,n_prompt", [("test-dense", F16, 70), ("test-dense", Q8_0, 33)])
+def test_prefill_batch_matches_fp64_reference(cfg, type_kv, n_prompt):
+    """A prompt processed as ONE batch (N > 8: tensor-core GEMM + multi-column flash attention), then decode on top of the
+    cache it wrote.  bf16 tensor-core operands: logits within 4e-2 of their RMS like the decode path."""
+    from llama_ref import RefModel
+    shape = SHAPES[cfg]
+    tensors = make_tensors(shape, 21)
+    ref = RefModel(shape, tensors, 512, type_kv)
+    m = build(shape, tensors, 512, type_kv, max_batch=128)
+    try:
+        prompt = [(i * 7919 + 11) % shape.n_vocab for i in range(n_prompt)]
+        got = m.decode(prompt, 0, logits_all=True).copy()
+        exp = ref.decode(prompt, 0)
+        assert np.isfinite(got).all()
+        assert rel_rms(got, exp) < 4e-2, rel_rms(got, exp)
+        got1 = m.decode([5], n_prompt).copy()
+        exp1 = ref.decode([5], n_prompt)
+        assert rel_rms(got1[0], exp1[0]) < 4e-2
+        # last-token-only logits (inp_out_ids path, src/llama.cpp:10541-10546) equal the last row of logits_all
+        m2 = build(shape, tensors, 512, type_kv, max_batch=128)
+        try:
+            last = m2.decode(prompt, 0, logits_all=False).copy()
+            assert rel_rms(last[0], got[-1]) < 2e-2  # last layer runs as GEMV (q8_1) here, as GEMM (bf16) above
+        finally:
+            m2.close()
+    finally:
+        m.close()
+
+
 def test_executor_variants_agree():
     """CUDA-graph replay and node fusion must not change results: graphs on/off bit-identical, fusion on/off within
     float reassociation (the fused kernels do the same arithmetic per element)."""
