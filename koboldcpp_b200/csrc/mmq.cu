@@ -460,7 +460,7 @@ struct DequantR<B200_TYPE_Q6_K, C> {
 //   * the raw quantised blocks of the NEXT 256-value group of each of the 128 rows are staged in shared memory by 1-D bulk
 //     copies (one per row, issued by the row's own thread, aligned-down windows like the decode GEMV) two groups ahead, so the
 //     producers unpack from shared memory.  A thread only ever reads its own row's slot: re-arming a slot needs no CTA barrier.
-constexpr int MQ2_STAGES = 3, MQ2_RAW = 2;
+constexpr int MQ2_STAGES = 4;
 constexpr int MQ2_THREADS = MQ_PRODUCERS + 64;  // + MMA warp + TMA warp
 // per-row slot stride: >= group bytes + 14 bytes of head misalignment (2-byte aligned formats), rounded to 16, and an ODD
 // number of 16-byte units so that the 8 threads of a quarter-warp hit distinct bank groups with 16-byte accesses
@@ -479,12 +479,10 @@ struct alignas(64) TmapBytes { unsigned char b[128]; };  // CUtensorMap without 
 template <int TYPE, int BN>
 __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_constant__ TmapBytes tmB, const __grid_constant__ MmqParams p) {
     constexpr int A_BYTES = MQ_BM * MQ_BK * 2, B_BYTES = BN * MQ_BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
-    constexpr int RS = raw_stride(TYPE), G256 = group256_bytes(TYPE), RAW_BYTES = MQ_BM * RS;
-    constexpr bool ALIGNED16 = (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K);
+    constexpr int G256 = group256_bytes(TYPE);
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    unsigned char *raw = smem + (size_t)MQ2_STAGES * STAGE_BYTES;
-    __shared__ __align__(8) unsigned long long full_bar[MQ2_STAGES], empty_bar[MQ2_STAGES], raw_bar[MQ2_RAW], tmem_full_bar;
+    __shared__ __align__(8) unsigned long long full_bar[MQ2_STAGES], empty_bar[MQ2_STAGES], tmem_full_bar;
     __shared__ unsigned tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
@@ -493,7 +491,6 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
 
     if (tid == 0) {
         for (int s = 0; s < MQ2_STAGES; s++) { mbar_init(&full_bar[s], MQ_PRODUCERS + 1); mbar_init(&empty_bar[s], 1); }
-        for (int s = 0; s < MQ2_RAW; s++) mbar_init(&raw_bar[s], MQ_PRODUCERS);
         mbar_init(&tmem_full_bar, 1);
         mbar_fence_init();
     }
@@ -508,42 +505,65 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
         const bool row_ok = m < p.M;
         const unsigned char *wrow = p.W + (size_t)(row_ok ? m : 0) * p.w_row_bytes;
         const unsigned a_off = (unsigned)((tid >> 3) * 1024 + (tid & 7) * 128);
-        auto arm = [&](int sb) {  // stage the raw bytes of group sb of this thread's row
-            unsigned long long *bar = &raw_bar[sb % MQ2_RAW];
-            if (!row_ok) { mbar_arrive(bar); return; }
-            const unsigned char *src = wrow + (size_t)sb * G256;
-            const unsigned mis = ALIGNED16 ? 0u : (unsigned)((uintptr_t)src & 15);
-            const unsigned len = (mis + (unsigned)G256 + 15u) & ~15u;
-            mbar_expect_tx(bar, len);
-            bulk_g2s(raw + (size_t)(sb % MQ2_RAW) * RAW_BYTES + (size_t)tid * RS, src - mis, len, bar);
-        };
-        for (int sb = 0; sb < MQ2_RAW && sb < nsb; sb++) arm(sb);
-        for (int sb = 0; sb < nsb; sb++) {
-            mbar_wait(&raw_bar[sb % MQ2_RAW], (unsigned)(sb / MQ2_RAW) & 1u);
-            const unsigned char *src = wrow + (size_t)sb * G256;
-            const unsigned mis = ALIGNED16 ? 0u : (unsigned)((uintptr_t)src & 15);
-            const unsigned char *g = raw + (size_t)(sb % MQ2_RAW) * RAW_BYTES + (size_t)tid * RS + mis;
-#pragma unroll 1
-            for (int c = 0; c < 4; c++) {
-                const int kb = sb * 4 + c, s = kb % MQ2_STAGES;
-                unsigned o[32];
-                if (row_ok) Dequant64<TYPE, false>::run(g, c, o);
-                else {
+        // software pipeline: the raw bytes of group sb+1 are in flight (registers) while group sb is unpacked
+        constexpr int NW = group256_words(TYPE);
+        unsigned cur[NW], nxt[NW];
+        auto fetch = [&](unsigned (&w)[NW], int sb) {
+            if (row_ok) {
+                if constexpr (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K) {  // 16-byte aligned rows: LDG.128
+                    const uint4 *q4 = reinterpret_cast<const uint4 *>(wrow + (size_t)sb * G256);
 #pragma unroll
-                    for (int i = 0; i < 32; i++) o[i] = 0u;
+                    for (int i = 0; i < NW / 4; i++) {
+                        const uint4 v = __ldg(q4 + i);
+                        w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+                    }
+                } else {
+                    // 2-byte aligned rows: 16-byte loads from the aligned-down address (a quarter of the LSU sector traffic of
+                    // 4-byte loads), then a word select (offset 0..3 words) and a funnel shift (0 or 2 bytes) per word
+                    const uintptr_t a = (uintptr_t)(wrow + (size_t)sb * G256);
+                    const uint4 *q4 = reinterpret_cast<const uint4 *>(a & ~(uintptr_t)15);
+                    const unsigned off = (unsigned)(a & 15) >> 2, sh = (unsigned)(a & 3) * 8;
+                    constexpr int NV = (NW + 1 + 3 + 3) / 4;
+                    unsigned t[NV * 4];
+#pragma unroll
+                    for (int i = 0; i < NV; i++) {
+                        const uint4 v = __ldg(q4 + i);
+                        t[4 * i] = v.x; t[4 * i + 1] = v.y; t[4 * i + 2] = v.z; t[4 * i + 3] = v.w;
+                    }
+                    unsigned prev = (off & 2) ? ((off & 1) ? t[3] : t[2]) : ((off & 1) ? t[1] : t[0]);
+#pragma unroll
+                    for (int i = 0; i < NW; i++) {
+                        const unsigned nx = (off & 2) ? ((off & 1) ? t[i + 4] : t[i + 3]) : ((off & 1) ? t[i + 2] : t[i + 1]);
+                        w[i] = __funnelshift_r(prev, nx, sh);
+                        prev = nx;
+                    }
                 }
-                mbar_wait(&empty_bar[s], ((unsigned)(kb / MQ2_STAGES) & 1u) ^ 1u);
-                unsigned char *a_s = smem + (size_t)s * STAGE_BYTES;
+            } else {
 #pragma unroll
-                for (int q = 0; q < 8; q++)
-                    *reinterpret_cast<uint4 *>(a_s + a_off + ((q ^ (tid & 7)) << 4)) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
-                fence_proxy_async_smem();
-                mbar_arrive(&full_bar[s]);
+                for (int i = 0; i < NW; i++) w[i] = 0u;
             }
-            if (sb + MQ2_RAW < nsb) {
-                fence_proxy_async_smem();  // our generic reads of the slot precede the bulk write that refills it
-                arm(sb + MQ2_RAW);
-            }
+        };
+        auto publish = [&](int kb, const unsigned (&o)[32]) {
+            const int s = kb % MQ2_STAGES;
+            mbar_wait(&empty_bar[s], ((unsigned)(kb / MQ2_STAGES) & 1u) ^ 1u);
+            unsigned char *a_s = smem + (size_t)s * STAGE_BYTES;
+#pragma unroll
+            for (int q = 0; q < 8; q++)
+                *reinterpret_cast<uint4 *>(a_s + a_off + ((q ^ (tid & 7)) << 4)) = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+            fence_proxy_async_smem();
+            mbar_arrive(&full_bar[s]);
+        };
+        fetch(cur, 0);
+#pragma unroll 1
+        for (int sb = 0; sb < nsb; sb++) {
+            if (sb + 1 < nsb) fetch(nxt, sb + 1);
+            unsigned o[32];
+            DequantR<TYPE, 0>::run(cur, o); publish(sb * 4 + 0, o);
+            DequantR<TYPE, 1>::run(cur, o); publish(sb * 4 + 1, o);
+            DequantR<TYPE, 2>::run(cur, o); publish(sb * 4 + 2, o);
+            DequantR<TYPE, 3>::run(cur, o); publish(sb * 4 + 3, o);
+#pragma unroll
+            for (int i = 0; i < NW; i++) cur[i] = nxt[i];
         }
         mbar_wait(&tmem_full_bar, 0u);
         tc_fence_after();
@@ -628,7 +648,7 @@ static EncodeTiledFn encode_tiled_fn() {
 
 template <int TYPE, int BN>
 static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st) {
-    constexpr size_t smem = (size_t)MQ2_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + (size_t)MQ2_RAW * MQ_BM * raw_stride(TYPE) + 1024;
+    constexpr size_t smem = (size_t)MQ2_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + 1024;
     static bool attr_set = false;
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc2_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
