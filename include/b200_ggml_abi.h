@@ -7,8 +7,8 @@
  * that cross the boundary, and only the enum VALUES the backend dispatches on.
  *
  * Every definition cites the reference declaration it mirrors (paths under /root/reference/ggml/), and
- * tests/cpp/abi_check.cpp compiles this file next to the real headers and static_asserts every size, offset and
- * enum value.  A maintainer integrating into a ggml tree compiles the backend with -DB200_USE_GGML_HEADERS instead,
+ * tests/cpp/abi_probe.cpp is compiled once against this file and once against the real headers and
+ * tests/test_abi.py diffs every size, offset and enum value.  A maintainer integrating into a ggml tree compiles the backend with -DB200_USE_GGML_HEADERS instead,
  * which makes b200_ggml_backend.cpp include the tree's own ggml.h / ggml-backend-impl.h and skip this file.
  */
 #ifndef B200_GGML_ABI_H

@@ -67,3 +67,21 @@ def test_product_does_not_import_the_oracle():
         if p.is_file() and p.suffix in (".py", ".cu", ".cuh", ".cpp", ".h"):
             txt = p.read_text()
             assert "ggml_oracle" not in txt and "oracle/" not in txt and "import orc" not in txt, p
+
+
+def test_abi_restatement_matches_reference_headers(tmp_path):
+    """include/b200_ggml_abi.h restates the structs that cross the ggml_backend boundary; where the reference checkout
+    exists, every size / offset / enum value is diffed against the real headers (tests/cpp/abi_probe.cpp)."""
+    import subprocess
+
+    import pytest
+    ref = Path("/root/reference/ggml")
+    if not (ref / "include" / "ggml.h").exists():
+        pytest.skip("reference checkout not present on this machine")
+    src = ROOT / "tests" / "cpp" / "abi_probe.cpp"
+    outs = []
+    for name, flags in (("ref", ["-DUSE_REF", "-I", str(ref / "include"), "-I", str(ref / "src")]), ("abi", ["-I", str(ROOT / "include")])):
+        exe = tmp_path / name
+        subprocess.run(["g++", "-std=c++17", "-Wno-invalid-offsetof", *flags, str(src), "-o", str(exe)], check=True)
+        outs.append(subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    assert outs[0] == outs[1], [(a, b) for a, b in zip(*outs) if a != b]
