@@ -6,6 +6,7 @@
 namespace b200 {
 
 struct ExecCtx {
+    int device;            // the device graph_compute runs on (main device of a row-split model)
     cudaStream_t stream;
     void  *scratch;        // workspace of the prefill GEMM (b200_mul_mat_q)
     size_t scratch_bytes;

@@ -484,10 +484,17 @@ enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cg) {
     ensure_workspaces(g, cg, n_slots);
     upload_slots(g, cg, n_slots);
     ExecCtx x;
-    x.stream = g->stream; x.scratch = g->scratch; x.scratch_bytes = g->scratch_bytes; x.fa_ws = g->fa_ws; x.fa_ws_bytes = g->fa_ws_bytes; x.launches = 0;
+    x.device = g->device; x.stream = g->stream; x.scratch = g->scratch; x.scratch_bytes = g->scratch_bytes; x.fa_ws = g->fa_ws; x.fa_ws_bytes = g->fa_ws_bytes; x.launches = 0;
 
     // graphs with a handful of nodes (op tests, K-shift) are not worth an instantiate
-    const bool use_graph = g_use_graphs && cg->n_nodes >= 16;
+    // row-split weights fan a matmul out over several devices and streams: run those graphs eagerly (the reference also
+    // turns CUDA graphs off for split buffers, ggml-cuda.cu:2561-2568)
+    bool has_split = false;
+    for (int i = 0; i < cg->n_nodes && !has_split; i++) {
+        const ggml_tensor *w = cg->nodes[i]->src[0];
+        has_split = cg->nodes[i]->op == GGML_OP_MUL_MAT && w && w->buffer && buft_is_b200_split(w->buffer->buft);
+    }
+    const bool use_graph = g_use_graphs && cg->n_nodes >= 16 && !has_split;
     if (!use_graph) {
         plan_steps(g, cg);
         for (const Step &s : g->steps) run_step(g, x, s);

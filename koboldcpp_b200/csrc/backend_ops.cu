@@ -97,8 +97,101 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
 }
 
 // ------------------------------------------------------------------------------------------------ single-node execution
+// ---- (a14) MUL_MAT with a row-split weight: every device computes its row slice, the main device gathers.
+// Replaces the split branch of ggml_cuda_op_mul_mat (ggml-cuda.cu:1519-1657): activations are broadcast with peer copies,
+// each device runs the same GEMV / tensor-core GEMM on its slice on its own stream, slices land directly in dst rows.
+struct SplitPeer {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t done = nullptr;
+    float *x = nullptr; size_t x_bytes = 0;
+    float *y = nullptr; size_t y_bytes = 0;
+    void *ws = nullptr; size_t ws_bytes = 0;
+};
+static SplitPeer g_peer[GGML_B200_MAX_DEVICES];
+static cudaEvent_t g_split_in = nullptr;
+static bool g_peer_enabled[GGML_B200_MAX_DEVICES][GGML_B200_MAX_DEVICES];
+
+static void peer_prepare(int main_dev, int d, size_t xb, size_t yb, size_t wsb) {
+    SplitPeer &p = g_peer[d];
+    B200_CHECK_CUDA(cudaSetDevice(d));
+    if (!p.stream) {
+        B200_CHECK_CUDA(cudaStreamCreateWithFlags(&p.stream, cudaStreamNonBlocking));
+        B200_CHECK_CUDA(cudaEventCreateWithFlags(&p.done, cudaEventDisableTiming));
+    }
+    if (!g_peer_enabled[d][main_dev]) {  // ggml_cuda_set_peer_access, ggml-cuda.cu:1286-1336
+        int can = 0;
+        B200_CHECK_CUDA(cudaDeviceCanAccessPeer(&can, d, main_dev));
+        if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(main_dev, 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) backend_abort("cudaDeviceEnablePeerAccess", cudaGetErrorString(e)); cudaGetLastError(); }
+        g_peer_enabled[d][main_dev] = true;
+        B200_CHECK_CUDA(cudaSetDevice(main_dev));
+        B200_CHECK_CUDA(cudaDeviceCanAccessPeer(&can, main_dev, d));
+        if (can) { cudaError_t e = cudaDeviceEnablePeerAccess(d, 0); if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) backend_abort("cudaDeviceEnablePeerAccess", cudaGetErrorString(e)); cudaGetLastError(); }
+        B200_CHECK_CUDA(cudaSetDevice(d));
+    }
+    auto grow = [&](void **ptr, size_t *have, size_t need) {
+        if (need <= *have) return;
+        B200_CHECK_CUDA(cudaStreamSynchronize(p.stream));
+        if (*ptr) B200_CHECK_CUDA(cudaFree(*ptr));
+        B200_CHECK_CUDA(cudaMalloc(ptr, need + 256));
+        *have = need;
+    };
+    grow((void **)&p.x, &p.x_bytes, xb);
+    grow((void **)&p.y, &p.y_bytes, yb);
+    grow(&p.ws, &p.ws_bytes, wsb);
+}
+
+static void gemm_slice(int type, const void *W, size_t wrb, const float *X, int64_t xs, float *dst, int64_t ds, int64_t K, int64_t M, int64_t N,
+                       void *ws, size_t wsb, cudaStream_t st, int64_t &launches) {
+    if (N > 8 && ws) {
+        const int rc = b200_mul_mat_q(type, W, wrb, X, xs, dst, ds, K, M, N, ws, wsb, st);
+        if (rc == B200_OK) { launches += 2; return; }
+        if (rc != B200_ERR_UNSUPPORTED) backend_abort("b200_mul_mat_q", b200_last_error());
+    }
+    for (int64_t c0 = 0; c0 < N; c0 += 8) {
+        const int64_t nc = N - c0 < 8 ? N - c0 : 8;
+        B200_CHECK_RC(b200_mul_mat_vec_q(type, W, wrb, X + c0 * xs, xs, dst + c0 * ds, ds, K, M, nc, st));
+        launches++;
+    }
+}
+
+static void run_mul_mat_split(ExecCtx &x, const ggml_tensor *n) {
+    const ggml_tensor *w = n->src[0], *a = n->src[1];
+    const SplitTensorExtra *e = (const SplitTensorExtra *)w->extra;
+    const SplitBuftCtx *sc = (const SplitBuftCtx *)w->buffer->buft->context;
+    const int64_t K = w->ne[0], N = a->ne[1];
+    const int64_t xs = (int64_t)(a->nb[1] / 4), ds = (int64_t)(n->nb[1] / 4);
+    const size_t wrb = row_size(w->type, K);
+    if (!g_split_in) B200_CHECK_CUDA(cudaEventCreateWithFlags(&g_split_in, cudaEventDisableTiming));
+    B200_CHECK_CUDA(cudaEventRecord(g_split_in, x.stream));  // activations are ready on the main device
+    const size_t wsb_main = N > 8 ? b200_mul_mat_q_workspace_bytes(w->type, K, 1, N) : 0;
+    for (int d = 0; d < sc->n_dev; d++) {
+        const int64_t lo = e->row_low[d], nr = e->row_high[d] - lo;
+        if (nr <= 0) continue;
+        if (d == x.device) {
+            gemm_slice(w->type, e->data[d], wrb, (const float *)a->data, xs, (float *)n->data + lo, ds, K, nr, N, wsb_main <= x.scratch_bytes ? x.scratch : nullptr,
+                       x.scratch_bytes, x.stream, x.launches);
+            continue;
+        }
+        peer_prepare(x.device, d, (size_t)N * K * 4, (size_t)N * nr * 4, wsb_main);
+        SplitPeer &p = g_peer[d];
+        B200_CHECK_CUDA(cudaStreamWaitEvent(p.stream, g_split_in, 0));
+        // broadcast the activation rows (contiguous K floats each) and compute the slice on device d
+        B200_CHECK_CUDA(cudaMemcpy2DAsync(p.x, (size_t)K * 4, a->data, a->nb[1], (size_t)K * 4, (size_t)N, cudaMemcpyDefault, p.stream));
+        gemm_slice(w->type, e->data[d], wrb, p.x, K, p.y, nr, K, nr, N, p.ws, p.ws_bytes, p.stream, x.launches);
+        // gather: slice rows [lo, lo+nr) of every column of dst on the main device
+        B200_CHECK_CUDA(cudaMemcpy2DAsync((float *)n->data + lo, n->nb[1], p.y, (size_t)nr * 4, (size_t)nr * 4, (size_t)N, cudaMemcpyDefault, p.stream));
+        B200_CHECK_CUDA(cudaEventRecord(p.done, p.stream));
+    }
+    B200_CHECK_CUDA(cudaSetDevice(x.device));
+    for (int d = 0; d < sc->n_dev; d++) {
+        if (d == x.device || e->row_high[d] - e->row_low[d] <= 0) continue;
+        B200_CHECK_CUDA(cudaStreamWaitEvent(x.stream, g_peer[d].done, 0));
+    }
+}
+
 static void run_mul_mat(ExecCtx &x, const ggml_tensor *n) {
     const ggml_tensor *w = n->src[0], *a = n->src[1];
+    if (in_split_buffer(w)) { run_mul_mat_split(x, n); return; }
     if (!is_quantized(w->type)) {
         b200_tensor tw = as_b200(w), ta = as_b200(a), td = as_b200(n);
         B200_CHECK_RC(b200_op_mul_mat_float(&tw, &ta, &td, x.stream));

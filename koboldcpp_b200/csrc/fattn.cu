@@ -427,7 +427,10 @@ static int fa_launch(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool 
     size_t smem = (size_t)FA_NW * FA_NBUF * 2 * G::TILE_BYTES;
     const size_t red = (size_t)FA_NW * C * (D + 2) * sizeof(float);
     if (red > smem) smem = red;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(fattn_kernel<TYPE, D, C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;

@@ -623,7 +623,10 @@ static int64_t mmq_n_pad(int64_t N) { const int64_t bn = mmq_bn(N); return (N + 
 template <int TYPE, int BN>
 static int mmq_launch(const MmqParams &p, cudaStream_t st) {
     constexpr size_t smem = (size_t)MQ_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + 1024;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
@@ -649,7 +652,10 @@ static EncodeTiledFn encode_tiled_fn() {
 template <int TYPE, int BN>
 static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st) {
     constexpr size_t smem = (size_t)MQ2_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + 1024;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc2_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;

@@ -608,7 +608,10 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     if (ns > (size_t)MMVQ_MAX_STAGE) ns = MMVQ_MAX_STAGE;
     p.n_stage = (int)ns;
     const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * G::STAGE_BYTES + tab_bytes;
-    static bool attr_set = false;
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
     if (!attr_set) {
         B200_CUDA_TRY(cudaFuncSetAttribute(mmvq_kernel<TYPE, NCOLS, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)(g_smem_optin - 256)));
