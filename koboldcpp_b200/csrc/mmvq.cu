@@ -37,6 +37,7 @@ struct MmvqParams {
     int            n_it;          // ceil(K / 4096): steps per row
     int            n_expert;
     int            rows_q, rows_rem;   // rows per CTA = rows_q (+1 for the first rows_rem CTAs)
+    int            tab_rows;           // MULTI: capacity of the per-CTA row table
     int64_t        K;
     int64_t        total_rows;
     size_t         w_row_bytes;   // row stride
@@ -439,8 +440,8 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
     // MULTI row table lives behind the ring
     unsigned char *tab_base = ring + (size_t)MMVQ_NW * n_stage * G::STAGE_BYTES;
     const unsigned char **rsrc = reinterpret_cast<const unsigned char **>(tab_base);
-    float **rdst = reinterpret_cast<float **>(tab_base + 8 * MMVQ_MAX_TAB);
-    signed char *rjob = reinterpret_cast<signed char *>(tab_base + 16 * MMVQ_MAX_TAB);
+    float **rdst = reinterpret_cast<float **>(tab_base + 8 * (size_t)p.tab_rows);
+    signed char *rjob = reinterpret_cast<signed char *>(tab_base + 16 * (size_t)p.tab_rows);
 
     // contiguous row range, balanced to one row: the first rows_rem CTAs take rows_q + 1 rows
     const int bid = blockIdx.x;
@@ -595,12 +596,23 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     if (rc) return rc;
     const size_t bar_bytes = MMVQ_BAR_BYTES;
     const size_t act_bytes = ((size_t)NCOLS * act_col_bytes(p.n_it) + 127) / 128 * 128;
-    const size_t tab_bytes = MULTI ? (size_t)17 * MMVQ_MAX_TAB + 64 : 0;
-    const size_t budget = g_smem_optin - 256 - tab_bytes;
-    if (bar_bytes + act_bytes + 2 * (size_t)MMVQ_NW * G::STAGE_BYTES > budget) {
+    const int64_t grid = p.total_rows < g_sm_count ? p.total_rows : g_sm_count;
+    const int64_t rows_per_cta = (p.total_rows + grid - 1) / grid;
+    if (MULTI && rows_per_cta > MMVQ_MAX_TAB) {
+        set_error("b200_mul_mat_vec_q_multi: %lld rows exceed the per-CTA row table", (long long)p.total_rows);
+        return B200_ERR_UNSUPPORTED;
+    }
+    p.tab_rows = MULTI ? (int)((rows_per_cta + 63) / 64 * 64) : 0;
+    const size_t tab_bytes = MULTI ? (size_t)17 * p.tab_rows + 64 : 0;
+    // (measured: 8 warps + half-SM rings so that consecutive launches overlap under PDL lost 15 %: a 93 KB ring cannot cover
+    // the HBM latency-bandwidth product of one SM on the large matrices)
+    const size_t min_need = bar_bytes + act_bytes + 2 * (size_t)MMVQ_NW * G::STAGE_BYTES + tab_bytes + 256;
+    const size_t cap = g_smem_optin;
+    if (min_need > cap) {
         set_error("b200_mul_mat_vec_q: K=%lld x N=%d activations do not fit in shared memory", (long long)p.K, NCOLS);
         return B200_ERR_UNSUPPORTED;
     }
+    const size_t budget = cap - 256 - tab_bytes;
     size_t ns = (budget - bar_bytes - act_bytes) / ((size_t)MMVQ_NW * G::STAGE_BYTES);
     // no point in more stages than a warp has steps: rows per warp ~ total_rows / (SMs * NW)
     const int64_t steps = ((p.total_rows + g_sm_count - 1) / g_sm_count + MMVQ_NW - 1) / MMVQ_NW * p.n_it;
@@ -617,13 +629,8 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
                                            (int)(g_smem_optin - 256)));
         attr_set = true;
     }
-    const int64_t grid = p.total_rows < g_sm_count ? p.total_rows : g_sm_count;
     p.rows_q = (int)(p.total_rows / grid);
     p.rows_rem = (int)(p.total_rows % grid);
-    if (MULTI && (p.total_rows + grid - 1) / grid > MMVQ_MAX_TAB) {
-        set_error("b200_mul_mat_vec_q_multi: %lld rows exceed the per-CTA row table", (long long)p.total_rows);
-        return B200_ERR_UNSUPPORTED;
-    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(MMVQ_THREADS);

@@ -36,6 +36,24 @@ static bool same_shape(const b200_tensor *a, const b200_tensor *b) {
         }                                         \
     } while (0)
 
+// Launch with the programmatic-dependent-launch attribute when the backend asked for it: the kernel may be scheduled while
+// its producer drains (it begins with griddepcontrol.wait) and lets its consumer's prologue start at once.
+extern bool g_mmvq_pdl;
+#define LAUNCH_PDL(kernel, grid, block, st, ...)                                       \
+    do {                                                                               \
+        cudaLaunchConfig_t cfg__ = {};                                                 \
+        cfg__.gridDim = dim3(grid);                                                    \
+        cfg__.blockDim = dim3(block);                                                  \
+        cfg__.stream = (st);                                                           \
+        cudaLaunchAttribute at__[1];                                                   \
+        at__[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;               \
+        at__[0].val.programmaticStreamSerializationAllowed = 1;                        \
+        cfg__.attrs = at__;                                                            \
+        cfg__.numAttrs = g_mmvq_pdl ? 1 : 0;                                           \
+        B200_CUDA_TRY(cudaLaunchKernelEx(&cfg__, kernel, __VA_ARGS__));                \
+    } while (0)
+__device__ __forceinline__ void pdl_enter() { pdl_wait(); pdl_trigger(); }
+
 __device__ __forceinline__ float block_sum(float v, float *sh) {
     v = warp_sum(v);
     const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = blockDim.x >> 5;
@@ -100,6 +118,7 @@ __global__ void rms_norm_kernel(TD x, const float *__restrict__ w, TD dst, float
 
 // fused SILU(gate) * up; optionally also stores SILU(gate) (the intermediate ggml node)
 __global__ void silu_mul_kernel(const float *__restrict__ g, const float *__restrict__ u, float *__restrict__ act, float *__restrict__ dst, int64_t n) {
+    pdl_enter();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float x = g[i];
@@ -263,6 +282,7 @@ __device__ __forceinline__ float4 rope4(float4 v, int ip, int pos, const float *
     return make_float4(r[0], r[1], r[2], r[3]);
 }
 __global__ void rope_kv_store_kernel(RopeKvDev a, const int32_t *__restrict__ pos, const float *__restrict__ ff, RopeDev rp) {
+    pdl_enter();
     const int64_t t4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // float4 index over [Q | K | V]
     const int64_t nq = (int64_t)a.D * a.H * a.T / 4, nk = (int64_t)a.D * a.HK * a.T / 4;
     // whole warps fall in one region (D*H*T/4 and D*HK*T/4 are multiples of 8; regions are padded to 32 by the launcher)
@@ -540,8 +560,7 @@ extern "C" int b200_op_rms_norm_mul(const b200_tensor *x, const float *w, float 
 extern "C" int b200_op_silu_mul(const float *gate, const float *up, float *act_out, float *dst, int64_t n, b200_stream_t stream) {
     REQUIRE(gate && up && dst && n >= 0, B200_ERR_INVALID, "b200_op_silu_mul: NULL argument");
     if (n == 0) return B200_OK;
-    silu_mul_kernel<<<grid1d(n, 256), 256, 0, (cudaStream_t)stream>>>(gate, up, act_out, dst, n);
-    B200_CUDA_TRY(cudaGetLastError());
+    LAUNCH_PDL(silu_mul_kernel, grid1d(n, 256), 256, (cudaStream_t)stream, gate, up, act_out, dst, n);
     return B200_OK;
 }
 
@@ -655,8 +674,8 @@ extern "C" int b200_op_rope_kv_store(const b200_tensor *q, const b200_tensor *q_
     const int64_t nq = nelements(q) / 4, nk = nelements(k) / 4;
     if (nq + nk == 0) return B200_OK;
     const int64_t total = (nq + 31) / 32 * 32 + 2 * ((nk + 31) / 32 * 32);
-    rope_kv_store_kernel<<<grid1d(total, 256), 256, 0, (cudaStream_t)stream>>>(a, pos, freq_factors, rope_dev(rp));
-    B200_CUDA_TRY(cudaGetLastError());
+    const RopeDev rd = rope_dev(rp);
+    LAUNCH_PDL(rope_kv_store_kernel, grid1d(total, 256), 256, (cudaStream_t)stream, a, pos, freq_factors, rd);
     return B200_OK;
 }
 
