@@ -148,6 +148,49 @@ typedef struct {
 B200_API int b200_mul_mat_vec_q_fused(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride,
                                       int64_t dst_stride, int64_t K, int64_t N, const b200_gemv_fuse *fuse, b200_stream_t stream);
 
+/* ---- decode chain: the dependent GEMVs of a layer (and the small ops between them) in ONE persistent launch ---------------
+ * replaces: the per-node launch sequence of ggml_backend_cuda_graph_compute for batch-1 decode (ggml-cuda.cu:2508-2823), i.e.
+ * quantize_q8_1 + mul_mat_vec_q per matmul plus rms_norm / add / silu / mul / rope / cpy launches between them.
+ * One CTA per SM stays resident for the whole chain; phases are separated by grid barriers, and because weights do not depend
+ * on activations every warp keeps its TMA weight ring filling ACROSS phase boundaries, so HBM streaming does not stop while
+ * activations are exchanged.  N = 1 (one token).  Phases run in order:
+ *   B200_CHAIN_GEMV:  dst_j = W_j . x (+ residual_j);  x = X, or RMS_NORM(X, eps) * norm_weight when norm_weight != NULL;
+ *                     jobs may mix weight types.  silu_pair != 0: jobs[0] = gate, jobs[1] = up (same M):
+ *                     jobs[0].dst[m] = silu(gate[m] . x) * (up[m] . x)   (UNARY(SILU) + MUL of llm_build_ffn folded in);
+ *   B200_CHAIN_ROPE_KV: the b200_op_rope_kv_store work (include/b200_ggml_ops.h) for T = 1. */
+enum { B200_CHAIN_GEMV = 0, B200_CHAIN_ROPE_KV = 1 };
+#define B200_CHAIN_MAX_PHASES 12
+#define B200_CHAIN_MAX_JOBS 4
+typedef struct {
+    const void  *W;
+    float       *dst;
+    const float *residual; /* or NULL */
+    size_t       w_row_bytes;
+    int32_t      M, type;
+} b200_chain_job;
+typedef struct {
+    int32_t kind, n_jobs, K, silu_pair;
+    float   norm_eps;
+    int32_t _pad[3];
+    const float *X, *norm_weight;
+    union {
+        b200_chain_job jobs[B200_CHAIN_MAX_JOBS];
+        struct { /* ROPE_KV: q [D, H], k [D, HK], v [D*HK] f32 contiguous; cache rows at *k_slot / *v_slot (or k_cache / v_cache) */
+            const float *q, *k, *v;
+            float *q_out, *k_out;
+            void *k_cache, *v_cache;
+            void *const *k_slot, *const *v_slot;
+            const int32_t *pos;
+            const float *freq_factors;
+            int32_t D, H, HK, kv_type;
+            int32_t n_dims, mode, n_ctx_orig;
+            float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
+        } rope;
+    } u;
+} b200_chain_phase;
+/* barrier: 4 bytes of device memory that are ZERO when the kernel starts (the kernel leaves them zero again). */
+B200_API int b200_decode_chain(const b200_chain_phase *phases, int n_phases, unsigned *barrier, b200_stream_t stream);
+
 /* ---- (a9) MUL_MAT_ID (expert GEMV), ids read on the device ------------------------------------------
  * replaces: ggml_cuda_mul_mat_id incl. its cudaMemcpyAsync(ids)+cudaStreamSynchronize and the
  * k_copy_src1_to_contiguous / k_copy_dst_from_contiguous gather-scatter, ggml/src/ggml-cuda.cu:1954-2139

@@ -48,6 +48,28 @@ class RopeParams(C.Structure):
                 ("ext_factor", C.c_float), ("attn_factor", C.c_float), ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
 
 
+class ChainJob(C.Structure):
+    _fields_ = [("W", C.c_void_p), ("dst", C.c_void_p), ("residual", C.c_void_p), ("w_row_bytes", C.c_size_t), ("M", C.c_int32), ("type", C.c_int32)]
+
+
+class ChainRope(C.Structure):
+    _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("q_out", C.c_void_p), ("k_out", C.c_void_p), ("k_cache", C.c_void_p),
+                ("v_cache", C.c_void_p), ("k_slot", C.c_void_p), ("v_slot", C.c_void_p), ("pos", C.c_void_p), ("freq_factors", C.c_void_p),
+                ("D", C.c_int32), ("H", C.c_int32), ("HK", C.c_int32), ("kv_type", C.c_int32), ("n_dims", C.c_int32), ("mode", C.c_int32),
+                ("n_ctx_orig", C.c_int32), ("freq_base", C.c_float), ("freq_scale", C.c_float), ("ext_factor", C.c_float), ("attn_factor", C.c_float),
+                ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
+
+
+class ChainU(C.Union):
+    _fields_ = [("jobs", ChainJob * 4), ("rope", ChainRope)]
+
+
+class ChainPhase(C.Structure):
+    """b200_chain_phase (include/b200_ggml.h)."""
+    _fields_ = [("kind", C.c_int32), ("n_jobs", C.c_int32), ("K", C.c_int32), ("silu_pair", C.c_int32), ("norm_eps", C.c_float), ("_pad", C.c_int32 * 3),
+                ("X", C.c_void_p), ("norm_weight", C.c_void_p), ("u", ChainU)]
+
+
 class FattnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("mask", C.c_void_p), ("dst", C.c_void_p),
                 ("D", C.c_int64), ("N", C.c_int64), ("n_head", C.c_int64), ("n_head_kv", C.c_int64), ("n_kv", C.c_int64),
@@ -90,6 +112,7 @@ _SIGS = {
     "b200_mul_mat_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_vec_q_multi": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p]),
     "b200_mul_mat_vec_q_fused": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(GemvFuse), C.c_void_p]),
+    "b200_decode_chain": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b200_mul_mat_id_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
                                         C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_q_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int64, C.c_int64, C.c_int64]),
