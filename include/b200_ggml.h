@@ -157,9 +157,17 @@ B200_API int b200_mul_mat_vec_q_fused(int type, const b200_gemv_job *jobs, int n
  *   B200_CHAIN_GEMV:  dst_j = W_j . x (+ residual_j);  x = X, or RMS_NORM(X, eps) * norm_weight when norm_weight != NULL;
  *                     jobs may mix weight types.  silu_pair != 0: jobs[0] = gate, jobs[1] = up (same M):
  *                     jobs[0].dst[m] = silu(gate[m] . x) * (up[m] . x)   (UNARY(SILU) + MUL of llm_build_ffn folded in);
- *   B200_CHAIN_ROPE_KV: the b200_op_rope_kv_store work (include/b200_ggml_ops.h) for T = 1. */
-enum { B200_CHAIN_GEMV = 0, B200_CHAIN_ROPE_KV = 1 };
-#define B200_CHAIN_MAX_PHASES 12
+ *                     M of every job must be even: a warp streams two rows at a time and shares the activation registers;
+ *                     sumsq_out != NULL: every CTA stores the sum of squares of the jobs[0] outputs it produced at
+ *                     sumsq_out[blockIdx.x] (b200_decode_chain_sumsq_slots() floats, no initialisation needed);
+ *                     sumsq_in != NULL (with norm_weight): sum(X^2) is taken from those partial sums of the producing phase
+ *                     instead of a second pass over X;
+ *   B200_CHAIN_ROPE_KV: the b200_op_rope_kv_store work (include/b200_ggml_ops.h) for T = 1;
+ *   B200_CHAIN_ATTN:  FLASH_ATTN_EXT for one query token (N = 1): the (kv-head, 16-row tile) space is cut into one contiguous
+ *                     range per CTA, K/V rows go straight from HBM to registers, the last CTA of a kv-head merges its partial
+ *                     results (ticket).  Same layouts and semantics as b200_flash_attn_ext below. */
+enum { B200_CHAIN_GEMV = 0, B200_CHAIN_ROPE_KV = 1, B200_CHAIN_ATTN = 2 };
+#define B200_CHAIN_MAX_PHASES 12 /* b200_decode_chain: the program travels as kernel parameters */
 #define B200_CHAIN_MAX_JOBS 4
 typedef struct {
     const void  *W;
@@ -171,8 +179,10 @@ typedef struct {
 typedef struct {
     int32_t kind, n_jobs, K, silu_pair;
     float   norm_eps;
-    int32_t _pad[3];
+    int32_t _pad;
     const float *X, *norm_weight;
+    float       *sumsq_out;
+    const float *sumsq_in;
     union {
         b200_chain_job jobs[B200_CHAIN_MAX_JOBS];
         struct { /* ROPE_KV: q [D, H], k [D, HK], v [D*HK] f32 contiguous; cache rows at *k_slot / *v_slot (or k_cache / v_cache) */
@@ -186,10 +196,26 @@ typedef struct {
             int32_t n_dims, mode, n_ctx_orig;
             float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
         } rope;
+        struct { /* ATTN: q f32 [D, H] contiguous; k/v [D, n_kv, HK] cache views (byte strides); mask f16 [n_kv] or NULL; dst f32 [D, H] */
+            const float *q;
+            const void *k, *v, *mask;
+            float *dst;
+            void *workspace; /* b200_decode_chain_attn_workspace_bytes(); its first 4*HK bytes are zero between launches */
+            size_t k_nb1, k_nb2, v_nb1, v_nb2;
+            int32_t D, H, HK, n_kv, kv_type;
+            float scale, max_bias, logit_softcap;
+        } attn;
     } u;
 } b200_chain_phase;
 /* barrier: 4 bytes of device memory that are ZERO when the kernel starts (the kernel leaves them zero again). */
 B200_API int b200_decode_chain(const b200_chain_phase *phases, int n_phases, unsigned *barrier, b200_stream_t stream);
+/* Long programs (a whole token): compile the phases on the host into a blob of b200_decode_chain_program_bytes() bytes,
+ * copy the blob to device memory (any way the caller likes), and launch it from there. */
+B200_API size_t b200_decode_chain_program_bytes(const b200_chain_phase *phases, int n_phases);
+B200_API int b200_decode_chain_compile(const b200_chain_phase *phases, int n_phases, void *program_host);
+B200_API int b200_decode_chain_run(const void *program_dev, const void *geometry /* first 16 bytes of the host blob */, unsigned *barrier, b200_stream_t stream);
+B200_API int b200_decode_chain_sumsq_slots(void);
+B200_API size_t b200_decode_chain_attn_workspace_bytes(int32_t D, int32_t H, int32_t HK);
 
 /* ---- (a9) MUL_MAT_ID (expert GEMV), ids read on the device ------------------------------------------
  * replaces: ggml_cuda_mul_mat_id incl. its cudaMemcpyAsync(ids)+cudaStreamSynchronize and the

@@ -1,0 +1,405 @@
+// mmvq_core.cuh -- shared device code of the decode GEMV kernels (mmvq.cu: one launch per matmul; chain.cu: the persistent
+// decode chain): activation quantisation into the lane-major shared-memory layout, and the per-type 128-weight slice dots.
+#pragma once
+#include "b200_common.cuh"
+
+namespace b200 {
+
+constexpr int MMVQ_NW        = 16;                 // warps per CTA
+constexpr int MMVQ_THREADS   = MMVQ_NW * 32;
+constexpr int MMVQ_MAX_STAGE = 8;
+constexpr int MMVQ_BAR_BYTES = 128 * ((MMVQ_NW * MMVQ_MAX_STAGE * 8 + 127) / 128);
+
+struct MmvqParams {
+    b200_gemv_job  jobs[B200_GEMV_MAX_JOBS];
+    int            n_jobs;
+    int            n_stage;
+    int            n_it;          // ceil(K / 4096): steps per row
+    int            n_expert;
+    int            rows_q, rows_rem;   // rows per CTA = rows_q (+1 for the first rows_rem CTAs)
+    int            tab_rows;           // MULTI: capacity of the per-CTA row table
+    int64_t        K;
+    int64_t        total_rows;
+    size_t         w_row_bytes;   // row stride
+    unsigned       row_bytes;     // payload bytes of one row
+    int64_t        x_stride, dst_stride;
+    const int32_t *ids;
+    size_t         expert_bytes;
+    // fused prologue / epilogue (b200_mul_mat_vec_q_fused): X is RMS-normalised and scaled by norm_w while it is quantised;
+    // residual[j] (same layout as jobs[j].dst) is added to the result of job j
+    const float   *norm_w;
+    float          norm_eps;
+    const float   *residual[B200_GEMV_MAX_JOBS];
+};
+
+template <int TYPE>
+struct Geo {
+    static constexpr int SLICE_BYTES = type_slice_bytes(TYPE);          // 128 weights
+    static constexpr int SEG_BYTES   = SLICE_BYTES * 32;               // 4096 weights: one warp step
+    static constexpr int STAGE_BYTES = ((SEG_BYTES + 32 + 15) / 16) * 16;  // head misalignment (<16) + word over-read slack
+};
+
+// per-column activation storage for n_it steps: qs [it][8][32] int4, d [it][32] float4, s [it][32] float4, g [it][32] int4
+__host__ __device__ constexpr int act_col_bytes(int n_it) { return n_it * (4096 + 3 * 512); }
+
+struct ActView {
+    const int4   *q;
+    const float4 *d, *s;
+    const int4   *g;
+};
+__device__ __forceinline__ ActView act_view(unsigned char *base, int n_it, int col) {
+    unsigned char *p = base + (size_t)col * act_col_bytes(n_it);
+    ActView v;
+    v.q = (const int4 *)p;
+    v.d = (const float4 *)(p + (size_t)n_it * 4096);
+    v.s = (const float4 *)(p + (size_t)n_it * (4096 + 512));
+    v.g = (const int4 *)(p + (size_t)n_it * (4096 + 1024));
+    return v;
+}
+
+// rsqrt(mean(x^2) + eps) of one activation row, computed by the whole CTA (RMS_NORM, ggml.c:12060-12110)
+// BAR == 0: all threads of the CTA take part (__syncthreads); BAR > 0: the first MMVQ_THREADS threads only (named barrier BAR)
+template <int BAR, int NT>
+__device__ __forceinline__ void cta_sync() {
+    if constexpr (BAR == 0) __syncthreads();
+    else asm volatile("bar.sync %0, %1;" ::"n"(BAR), "n"(NT) : "memory");
+}
+template <int BAR = 0, int NT = MMVQ_THREADS>
+__device__ __forceinline__ float rms_scale(const float *__restrict__ xs, int64_t K, float norm_eps, float *red) {
+    const int n4 = (int)(K / 4);
+    float ss = 0.f;
+    for (int i4 = threadIdx.x; i4 < n4; i4 += NT) {
+        const float4 v = __ldcg(reinterpret_cast<const float4 *>(xs) + i4);
+        ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = warp_sum(ss);
+    cta_sync<BAR, NT>();  // red[] may still be read by a previous call
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    cta_sync<BAR, NT>();
+    float t = (threadIdx.x & 31) < NT / 32 ? red[threadIdx.x & 31] : 0.f;
+    t = warp_sum(t);
+    return rsqrtf(t / (float)K + norm_eps);
+}
+
+// Quantise one row x[0..K) (f32, global) into the column store `p` (q8_1 arithmetic of quantize_row_q8_1_ref).  With norm_w the
+// value quantised is (x * nscale) * w, the order of the RMS_NORM -> MUL node pair.  All threads of the CTA call this.
+template <int NT = MMVQ_THREADS>
+__device__ __forceinline__ void quantize_activation_row(unsigned char *p, const float *__restrict__ x, int64_t K, int n_it,
+                                                        const float *__restrict__ norm_w, float nscale) {
+    const int n4 = (int)(K / 4);
+    int   *aq = (int *)p;
+    float *ad = (float *)(p + (size_t)n_it * 4096);
+    float *as = (float *)(p + (size_t)n_it * (4096 + 512));
+    int   *ag = (int *)(p + (size_t)n_it * (4096 + 1024));
+    // 4 independent 16-byte loads per thread are issued before any of them is consumed (one L2 round trip per
+    // 8192 activations instead of one per 2048)
+    for (int base = 0; base < n4; base += 4 * NT) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i4 = base + u * NT + threadIdx.x;
+            v[u] = i4 < n4 ? __ldcg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (norm_w != nullptr && i4 < n4) {
+                const float4 ww = __ldg(reinterpret_cast<const float4 *>(norm_w) + i4);
+                v[u].x = v[u].x * nscale * ww.x; v[u].y = v[u].y * nscale * ww.y;
+                v[u].z = v[u].z * nscale * ww.z; v[u].w = v[u].w * nscale * ww.w;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int i4 = base + u * NT + threadIdx.x;
+            if (base + u * NT >= n4) break;  // warp-uniform: the whole batch is past the end
+            const bool active = i4 < n4;
+            float d, s;
+            int sum4;
+            const int packed = quantize_q8_1_group8(v[u], d, s, sum4);
+            const int hi4 = __shfl_xor_sync(0xffffffffu, sum4, 4);
+            if (active) {
+                const int blk = i4 >> 3, part = i4 & 7;
+                const int slice = blk >> 2, b = blk & 3;
+                const int it = slice >> 5, lane = slice & 31;
+                const int j = b * 2 + (part >> 2);
+                aq[(((it * 8 + j) * 32 + lane) << 2) + (part & 3)] = packed;
+                if (part == 0) {
+                    const int o = ((it * 32 + lane) << 2) + b;
+                    ad[o] = d;
+                    as[o] = s;
+                    ag[o] = (sum4 & 0xffff) | (hi4 << 16);  // 16-wide integer sums (q6_K offset term)
+                }
+            }
+        }
+    }
+}
+
+// Quantise X[n][0..K) (f32, global) into the CTA's shared activation store.  All threads of the CTA call this.
+template <int NCOLS>
+__device__ void load_activations(unsigned char *act_base, const float *__restrict__ X, int64_t x_stride, int64_t K, int n_it,
+                                 const float *__restrict__ norm_w, float norm_eps, float *red) {
+    for (int n = 0; n < NCOLS; n++) {
+        const float *x = X + (int64_t)n * x_stride;
+        const float nscale = norm_w != nullptr ? rms_scale(x, K, norm_eps, red) : 1.0f;
+        quantize_activation_row(act_base + (size_t)n * act_col_bytes(n_it), x, K, n_it, norm_w, nscale);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ per-type slice dot
+// Each returns, for every column, the contribution of this lane's 128-weight slice.
+template <int TYPE, int NCOLS>
+struct SliceDot;
+
+// ---- Q4_K: half a super-block per lane.  block: half d, half dmin, u8 scales[12], u8 qs[128]  (ggml-common.h:286-298)
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q4_K, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * Q4_K_BYTES;
+        const int h = lane & 1;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(b);
+        const float d = h2f((unsigned short)(hdr.x & 0xffff)), dmin = h2f((unsigned short)(hdr.x >> 16));
+        unsigned scw, mnw;  // 4 scales / 4 mins of sub-blocks 4h..4h+3, one per byte (get_scale_min_k4)
+        if (h == 0) {
+            scw = hdr.y & 0x3f3f3f3fu;
+            mnw = hdr.z & 0x3f3f3f3fu;
+        } else {
+            scw = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+            mnw = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+        }
+        const uint4 *qp = reinterpret_cast<const uint4 *>(b + 16 + 64 * h);
+        unsigned v[16];
+        *reinterpret_cast<uint4 *>(v + 0)  = qp[0];
+        *reinterpret_cast<uint4 *>(v + 4)  = qp[1];
+        *reinterpret_cast<uint4 *>(v + 8)  = qp[2];
+        *reinterpret_cast<uint4 *>(v + 12) = qp[3];
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            int sumi[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int cc = 0; cc < 2; cc++) {       // 64-value chunk: low nibbles -> sub-block 2cc, high -> 2cc+1
+#pragma unroll
+                for (int hq = 0; hq < 2; hq++) {   // which 16 bytes of the chunk
+                    const int4 ulo = a.q[((it * 8 + (2 * cc) * 2 + hq) * 32) + lane];
+                    const int4 uhi = a.q[((it * 8 + (2 * cc + 1) * 2 + hq) * 32) + lane];
+                    const unsigned *w = v + 8 * cc + 4 * hq;
+                    sumi[2 * cc]     = dp4a((int)(w[0] & 0x0f0f0f0fu), ulo.x, sumi[2 * cc]);
+                    sumi[2 * cc]     = dp4a((int)(w[1] & 0x0f0f0f0fu), ulo.y, sumi[2 * cc]);
+                    sumi[2 * cc]     = dp4a((int)(w[2] & 0x0f0f0f0fu), ulo.z, sumi[2 * cc]);
+                    sumi[2 * cc]     = dp4a((int)(w[3] & 0x0f0f0f0fu), ulo.w, sumi[2 * cc]);
+                    // high nibbles stay in place (value * 16, unsigned byte): exact >> 4 after the accumulation
+                    sumi[2 * cc + 1] = dp4a_u(w[0] & 0xf0f0f0f0u, uhi.x, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a_u(w[1] & 0xf0f0f0f0u, uhi.y, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a_u(w[2] & 0xf0f0f0f0u, uhi.z, sumi[2 * cc + 1]);
+                    sumi[2 * cc + 1] = dp4a_u(w[3] & 0xf0f0f0f0u, uhi.w, sumi[2 * cc + 1]);
+                }
+            }
+            sumi[1] >>= 4;
+            sumi[3] >>= 4;
+            const float4 d8 = a.d[it * 32 + lane], s8 = a.s[it * 32 + lane];
+            const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
+                             d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
+            const float sm = s8.x * (float)(mnw & 0xff) + s8.y * (float)((mnw >> 8) & 0xff) + s8.z * (float)((mnw >> 16) & 0xff) +
+                             s8.w * (float)(mnw >> 24);
+            acc[n] += d * sd - dmin * sm;
+        }
+    }
+};
+
+// ---- Q5_K: half d, half dmin, u8 scales[12], u8 qh[32], u8 qs[128]  (ggml-common.h:303-316)
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q5_K, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * Q5_K_BYTES;
+        const int h = lane & 1;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(b);
+        const float d = h2f((unsigned short)(hdr.x & 0xffff)), dmin = h2f((unsigned short)(hdr.x >> 16));
+        unsigned scw, mnw;
+        if (h == 0) {
+            scw = hdr.y & 0x3f3f3f3fu;
+            mnw = hdr.z & 0x3f3f3f3fu;
+        } else {
+            scw = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+            mnw = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+        }
+        unsigned qh[8], v[16];
+        *reinterpret_cast<uint4 *>(qh + 0) = *reinterpret_cast<const uint4 *>(b + 16);
+        *reinterpret_cast<uint4 *>(qh + 4) = *reinterpret_cast<const uint4 *>(b + 32);
+        const uint4 *qp = reinterpret_cast<const uint4 *>(b + 48 + 64 * h);
+        *reinterpret_cast<uint4 *>(v + 0)  = qp[0];
+        *reinterpret_cast<uint4 *>(v + 4)  = qp[1];
+        *reinterpret_cast<uint4 *>(v + 8)  = qp[2];
+        *reinterpret_cast<uint4 *>(v + 12) = qp[3];
+        // 5-bit values: sub-block sb = 4h + 2cc + {0: low nibble, 1: high nibble}; fifth bit = bit sb of qh[l] (ggml-quants.c:2783-2786)
+        unsigned q5[4][8];
+#pragma unroll
+        for (int cc = 0; cc < 2; cc++) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const unsigned w = v[8 * cc + i], hb = qh[i] >> (4 * h + 2 * cc);
+                q5[2 * cc][i]     = (w & 0x0f0f0f0fu) | ((hb << 4) & 0x10101010u);
+                q5[2 * cc + 1][i] = ((w >> 4) & 0x0f0f0f0fu) | ((hb << 3) & 0x10101010u);
+            }
+        }
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            int sumi[4] = {0, 0, 0, 0};
+#pragma unroll
+            for (int sb = 0; sb < 4; sb++) {
+#pragma unroll
+                for (int hq = 0; hq < 2; hq++) {
+                    const int4 u = a.q[((it * 8 + sb * 2 + hq) * 32) + lane];
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 0], u.x, sumi[sb]);
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 1], u.y, sumi[sb]);
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 2], u.z, sumi[sb]);
+                    sumi[sb] = dp4a((int)q5[sb][4 * hq + 3], u.w, sumi[sb]);
+                }
+            }
+            const float4 d8 = a.d[it * 32 + lane], s8 = a.s[it * 32 + lane];
+            const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
+                             d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
+            const float sm = s8.x * (float)(mnw & 0xff) + s8.y * (float)((mnw >> 8) & 0xff) + s8.z * (float)((mnw >> 16) & 0xff) +
+                             s8.w * (float)(mnw >> 24);
+            acc[n] += d * sd - dmin * sm;
+        }
+    }
+};
+
+// consecutive 32-bit words from a shared-memory byte run that is only 2-byte aligned
+template <int NW>
+__device__ __forceinline__ void lds_words(const unsigned char *p, unsigned (&out)[NW]) {
+    const unsigned *w = reinterpret_cast<const unsigned *>((uintptr_t)p & ~(uintptr_t)3);
+    const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
+    unsigned prev = w[0];
+#pragma unroll
+    for (int i = 0; i < NW; i++) {
+        const unsigned nxt = w[i + 1];  // one word of over-read at most: stages carry 16 bytes of slack
+        out[i] = __funnelshift_r(prev, nxt, sh);
+        prev = nxt;
+    }
+}
+
+// ---- Q6_K: u8 ql[128], u8 qh[64], i8 scales[16], half d  (ggml-common.h:321-327); 210 bytes => 2-byte aligned
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q6_K, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * Q6_K_BYTES;
+        const int h = lane & 1;
+        unsigned ql[16], qh[8], scw[2];
+        lds_words<16>(b + 64 * h, ql);
+        lds_words<8>(b + 128 + 32 * h, qh);
+        lds_words<2>(b + 192 + 8 * h, scw);
+        const float d = h2f(*reinterpret_cast<const unsigned short *>(b + 208));
+        // q[r][i]: 4 values of row-group r (= q8_1 block r of this slice), word i (ggml-quants.c:2990-2999)
+        unsigned q[4][8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const unsigned l0 = ql[i], l1 = ql[8 + i], hb = qh[i];
+            q[0][i] = (l0 & 0x0f0f0f0fu) | ((hb << 4) & 0x30303030u);
+            q[1][i] = (l1 & 0x0f0f0f0fu) | ((hb << 2) & 0x30303030u);
+            q[2][i] = ((l0 >> 4) & 0x0f0f0f0fu) | (hb & 0x30303030u);
+            q[3][i] = ((l1 >> 4) & 0x0f0f0f0fu) | ((hb >> 2) & 0x30303030u);
+        }
+        const signed char *sc = reinterpret_cast<const signed char *>(scw);
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            const float4 d8 = a.d[it * 32 + lane];
+            const int4 g = a.g[it * 32 + lane];
+            const float d8v[4] = {d8.x, d8.y, d8.z, d8.w};
+            const int gv[4] = {g.x, g.y, g.z, g.w};
+            float sd = 0.f;
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                const int4 u0 = a.q[((it * 8 + r * 2 + 0) * 32) + lane];
+                const int4 u1 = a.q[((it * 8 + r * 2 + 1) * 32) + lane];
+                int s0 = dp4a((int)q[r][0], u0.x, 0);
+                s0 = dp4a((int)q[r][1], u0.y, s0);
+                s0 = dp4a((int)q[r][2], u0.z, s0);
+                s0 = dp4a((int)q[r][3], u0.w, s0);
+                int s1 = dp4a((int)q[r][4], u1.x, 0);
+                s1 = dp4a((int)q[r][5], u1.y, s1);
+                s1 = dp4a((int)q[r][6], u1.z, s1);
+                s1 = dp4a((int)q[r][7], u1.w, s1);
+                // stored values are q+32: subtract 32 * (sum of the 16 activations of the group)
+                s0 -= 32 * (int)(short)(gv[r] & 0xffff);
+                s1 -= 32 * (gv[r] >> 16);
+                sd += d8v[r] * (float)(s0 * (int)sc[2 * r] + s1 * (int)sc[2 * r + 1]);
+            }
+            acc[n] += d * sd;
+        }
+    }
+};
+
+// ---- Q8_0: half d, i8 qs[32] (ggml-common.h:186-191); 4 blocks (136 bytes) per lane
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q8_0, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int nblk, float acc[NCOLS]) {
+        const unsigned char *b = seg + lane * (4 * Q8_0_BYTES);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+                const unsigned char *bk = b + k * Q8_0_BYTES;
+                const float d = h2f(*reinterpret_cast<const unsigned short *>(bk));
+                unsigned w[8];
+                lds_words<8>(bk + 2, w);
+#pragma unroll
+                for (int n = 0; n < NCOLS; n++) {
+                    const ActView a = act_view(act_base, n_it, n);
+                    const int4 u0 = a.q[((it * 8 + k * 2 + 0) * 32) + lane];
+                    const int4 u1 = a.q[((it * 8 + k * 2 + 1) * 32) + lane];
+                    int s = dp4a((int)w[0], u0.x, 0);
+                    s = dp4a((int)w[1], u0.y, s);
+                    s = dp4a((int)w[2], u0.z, s);
+                    s = dp4a((int)w[3], u0.w, s);
+                    s = dp4a((int)w[4], u1.x, s);
+                    s = dp4a((int)w[5], u1.y, s);
+                    s = dp4a((int)w[6], u1.z, s);
+                    s = dp4a((int)w[7], u1.w, s);
+                    const float d8 = reinterpret_cast<const float *>(a.d)[((it * 32 + lane) << 2) + k];
+                    acc[n] += d * d8 * (float)s;
+                }
+            }
+        }
+    }
+};
+
+// ---- Q4_0: half d, u8 qs[16] (ggml-common.h:144-149); values 0..15 in low nibbles, 16..31 in high nibbles; 4 blocks (72 B) per lane
+template <int NCOLS>
+struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int nblk, float acc[NCOLS]) {
+        const unsigned char *b = seg + lane * (4 * Q4_0_BYTES);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+                const unsigned char *bk = b + k * Q4_0_BYTES;
+                const float d = h2f(*reinterpret_cast<const unsigned short *>(bk));
+                unsigned w[4];
+                lds_words<4>(bk + 2, w);
+#pragma unroll
+                for (int n = 0; n < NCOLS; n++) {
+                    const ActView a = act_view(act_base, n_it, n);
+                    const int4 u0 = a.q[((it * 8 + k * 2 + 0) * 32) + lane];
+                    const int4 u1 = a.q[((it * 8 + k * 2 + 1) * 32) + lane];
+                    int s = dp4a((int)(w[0] & 0x0f0f0f0fu), u0.x, 0);
+                    s = dp4a((int)(w[1] & 0x0f0f0f0fu), u0.y, s);
+                    s = dp4a((int)(w[2] & 0x0f0f0f0fu), u0.z, s);
+                    s = dp4a((int)(w[3] & 0x0f0f0f0fu), u0.w, s);
+                    int sh = dp4a_u(w[0] & 0xf0f0f0f0u, u1.x, 0);
+                    sh = dp4a_u(w[1] & 0xf0f0f0f0u, u1.y, sh);
+                    sh = dp4a_u(w[2] & 0xf0f0f0f0u, u1.z, sh);
+                    sh = dp4a_u(w[3] & 0xf0f0f0f0u, u1.w, sh);
+                    s += sh >> 4;
+                    const int o = ((it * 32 + lane) << 2) + k;
+                    const float d8 = reinterpret_cast<const float *>(a.d)[o], s8 = reinterpret_cast<const float *>(a.s)[o];
+                    acc[n] += d * (d8 * (float)s - 8.0f * s8);  // sum (v-8)*u*d8 = d8*sum(v*u) - 8*s8  (vecdotq.cuh:23-42)
+                }
+            }
+        }
+    }
+};
+
+}  // namespace b200

@@ -60,14 +60,21 @@ class ChainRope(C.Structure):
                 ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
 
 
+class ChainAttn(C.Structure):
+    _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("mask", C.c_void_p), ("dst", C.c_void_p), ("workspace", C.c_void_p),
+                ("k_nb1", C.c_size_t), ("k_nb2", C.c_size_t), ("v_nb1", C.c_size_t), ("v_nb2", C.c_size_t),
+                ("D", C.c_int32), ("H", C.c_int32), ("HK", C.c_int32), ("n_kv", C.c_int32), ("kv_type", C.c_int32),
+                ("scale", C.c_float), ("max_bias", C.c_float), ("logit_softcap", C.c_float)]
+
+
 class ChainU(C.Union):
-    _fields_ = [("jobs", ChainJob * 4), ("rope", ChainRope)]
+    _fields_ = [("jobs", ChainJob * 4), ("rope", ChainRope), ("attn", ChainAttn)]
 
 
 class ChainPhase(C.Structure):
     """b200_chain_phase (include/b200_ggml.h)."""
-    _fields_ = [("kind", C.c_int32), ("n_jobs", C.c_int32), ("K", C.c_int32), ("silu_pair", C.c_int32), ("norm_eps", C.c_float), ("_pad", C.c_int32 * 3),
-                ("X", C.c_void_p), ("norm_weight", C.c_void_p), ("u", ChainU)]
+    _fields_ = [("kind", C.c_int32), ("n_jobs", C.c_int32), ("K", C.c_int32), ("silu_pair", C.c_int32), ("norm_eps", C.c_float), ("_pad", C.c_int32),
+                ("X", C.c_void_p), ("norm_weight", C.c_void_p), ("sumsq_out", C.c_void_p), ("sumsq_in", C.c_void_p), ("u", ChainU)]
 
 
 class FattnArgs(C.Structure):
@@ -113,6 +120,11 @@ _SIGS = {
     "b200_mul_mat_vec_q_multi": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p]),
     "b200_mul_mat_vec_q_fused": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(GemvFuse), C.c_void_p]),
     "b200_decode_chain": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "b200_decode_chain_program_bytes": (C.c_size_t, [C.c_void_p, C.c_int]),
+    "b200_decode_chain_compile": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
+    "b200_decode_chain_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_decode_chain_sumsq_slots": (C.c_int, []),
+    "b200_decode_chain_attn_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "b200_mul_mat_id_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
                                         C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_q_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int64, C.c_int64, C.c_int64]),
