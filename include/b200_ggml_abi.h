@@ -95,6 +95,7 @@ enum ggml_op {
     GGML_OP_ARGSORT        = 58,
     GGML_OP_FLASH_ATTN_EXT = 60,
     GGML_OP_UNARY          = 69,
+    GGML_OP_MAP_CUSTOM1    = 75, /* carries the tensor-parallel collectives (b200_comm.h); llama.cpp never emits it */
     GGML_OP_COUNT          = 81,
 };
 

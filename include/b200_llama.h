@@ -31,6 +31,12 @@ typedef struct {
     int32_t main_device;             /* device that runs the graph */
     int32_t n_split_devices;         /* 0/1: everything on main_device; >1: weight matrices in the row-split buffer type */
     float   tensor_split[16];        /* all zero: equal split */
+    /* tensor-parallel mode, one process per GPU (b200_comm.h; a communicator of tp_world ranks must exist): the caller uploads
+     * this rank's SHARD of every matrix -- attn_q/k/v, ffn_gate/up and output split by output rows (heads r*n_head/W ..,
+     * ffn columns, vocabulary rows), attn_output and ffn_down split along K (their ne0 is n_embd/W resp. n_ff/W) -- while
+     * token_embd and the norm vectors are replicated.  The graph then holds n_head/W heads and n_head_kv/W KV heads per rank,
+     * one all-reduce after attn_output and one after ffn_down, and an all-gather of the logits.  0 / 1 = off. */
+    int32_t tp_rank, tp_world;
 } b200_llama_params;
 
 typedef struct b200_llama b200_llama; /* opaque */

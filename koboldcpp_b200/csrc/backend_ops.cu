@@ -1,6 +1,7 @@
 // backend_ops.cu -- per-node dispatch of the B200 ggml backend: supports_op (exact: graph_compute aborts on anything it
 // said yes to and cannot run, like the reference, ggml-cuda.cu:2671-2675) and the node -> C-ABI kernel mapping.
 // Replaces ggml_cuda_compute_forward / ggml_backend_cuda_device_supports_op (ggml-cuda.cu:2145-2340, 2959-3185).
+#include "../../include/b200_comm.h"
 #include "backend_exec.h"
 
 namespace b200 {
@@ -30,6 +31,12 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
     switch (op->op) {
         case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
             return true;
+        case GGML_OP_MAP_CUSTOM1:  // a collective of the tensor-parallel decoder (b200_comm.h)
+            if (!s0 || (uint32_t)op->op_params[0] != B200_COLLECTIVE_TAG || b200_comm_world() < 1) return false;
+            if (s0->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || !is_contiguous(s0) || !is_contiguous(op)) return false;
+            if (op->op_params[1] == B200_COLLECTIVE_ALL_REDUCE_SUM) return nelements(op) == nelements(s0);
+            if (op->op_params[1] == B200_COLLECTIVE_ALL_GATHER) return nelements(op) == nelements(s0) * b200_comm_world();
+            return false;
         case GGML_OP_MUL_MAT:
             if (!s0 || !s1) return false;
             if (is_quantized(s0->type)) return mul_mat_q_ok(s0, s1, op);
@@ -278,6 +285,15 @@ void run_node(ExecCtx &x, const ggml_tensor *n, void *const *dst_slot) {
     switch (n->op) {
         case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
             return;
+        case GGML_OP_MAP_CUSTOM1: {
+            if (n->op_params[1] == B200_COLLECTIVE_ALL_REDUCE_SUM) {
+                if (n->data != s0->data) B200_CHECK_CUDA(cudaMemcpyAsync(n->data, s0->data, nbytes(s0), cudaMemcpyDeviceToDevice, x.stream));
+                B200_CHECK_RC(b200_all_reduce_sum_f32((float *)n->data, nelements(n), x.stream));
+            } else {
+                B200_CHECK_RC(b200_all_gather_f32((const float *)s0->data, (float *)n->data, nelements(s0), x.stream));
+            }
+            break;
+        }
         case GGML_OP_MUL_MAT: run_mul_mat(x, n); return;
         case GGML_OP_MUL_MAT_ID: run_mul_mat_id(x, n); return;
         case GGML_OP_FLASH_ATTN_EXT: run_flash_attn(x, n); return;

@@ -9,6 +9,7 @@
 #include <map>
 #include <unordered_set>
 
+#include "../../include/b200_comm.h"
 #include "../../include/b200_llama.h"
 #include "backend_internal.h"
 
@@ -198,6 +199,20 @@ struct Builder {
         t->nb[1] = s->nb[1]; t->nb[2] = s->nb[2]; t->nb[3] = s->nb[3];
         return t;
     }
+    // an exchange between the ranks of a tensor-parallel model (b200_comm.h): all-reduce in place, or all-gather along ne0
+    ggml_tensor *collective(ggml_tensor *a, int kind, int world) {
+        ggml_tensor *t;
+        if (kind == B200_COLLECTIVE_ALL_REDUCE_SUM) {
+            t = view_of(a, GGML_OP_MAP_CUSTOM1, 0);
+            set_shape(t, a->type, a->ne[0], a->ne[1], a->ne[2], a->ne[3]);
+        } else {
+            t = alloc_result(GGML_TYPE_F32, a->ne[0] * world, a->ne[1], a->ne[2], a->ne[3]);
+            op(t, GGML_OP_MAP_CUSTOM1, a);
+        }
+        t->op_params[0] = (int32_t)B200_COLLECTIVE_TAG;
+        t->op_params[1] = kind;
+        return t;
+    }
     ggml_tensor *sum_rows(ggml_tensor *a) { return op(alloc_result(GGML_TYPE_F32, 1, a->ne[1], a->ne[2], a->ne[3]), GGML_OP_SUM_ROWS, a); }
 };
 
@@ -288,8 +303,16 @@ extern "C" int b200_llama_new(const b200_llama_params *p, b200_llama **out) {
     LL_REQUIRE((p->type_k == B200_TYPE_F16 || p->type_k == B200_TYPE_Q8_0) && p->type_v == p->type_k, B200_ERR_UNSUPPORTED,
                "b200_llama_new: KV cache types must be f16/f16 or q8_0/q8_0");
     LL_REQUIRE(ggml_backend_b200_get_device_count() > 0, B200_ERR_CUDA, "b200_llama_new: no CUDA device (there is no CPU fallback)");
+    if (p->tp_world > 1) {
+        LL_REQUIRE(p->tp_rank >= 0 && p->tp_rank < p->tp_world && b200_comm_world() == p->tp_world && b200_comm_rank() == p->tp_rank, B200_ERR_INVALID,
+                   "b200_llama_new: tensor-parallel mode needs a communicator of %d ranks (b200_comm_init)", p->tp_world);
+        LL_REQUIRE(p->n_head % p->tp_world == 0 && p->n_head_kv % p->tp_world == 0 && p->n_ff % p->tp_world == 0 && p->n_vocab % p->tp_world == 0 &&
+                   (p->n_ff / p->tp_world) % 256 == 0, B200_ERR_UNSUPPORTED, "b200_llama_new: heads / ffn / vocabulary do not divide over %d ranks", p->tp_world);
+        LL_REQUIRE(p->n_expert == 0 && p->n_split_devices <= 1, B200_ERR_UNSUPPORTED, "b200_llama_new: tensor-parallel mode is for dense models without the in-process split");
+    }
     b200_llama *m = new b200_llama();
     m->hp = *p;
+    if (m->hp.tp_world < 1) { m->hp.tp_world = 1; m->hp.tp_rank = 0; }
     if (m->hp.n_embd_head == 0) m->hp.n_embd_head = p->n_embd / p->n_head;
     if (m->hp.n_ctx_orig == 0) m->hp.n_ctx_orig = p->n_ctx;
     if (m->hp.rope_freq_base == 0.0f) m->hp.rope_freq_base = 10000.0f;
@@ -408,7 +431,7 @@ extern "C" int b200_llama_finalize(b200_llama *m, int32_t max_batch) {
         }
     }
     // KV cache: per layer one 1-D tensor of n_embd_gqa * n_ctx elements, zero-initialised (llama_kv_cache_init, src/llama.cpp:3534-3600)
-    const int64_t n_embd_gqa = (int64_t)hp.n_embd_head * hp.n_head_kv;
+    const int64_t n_embd_gqa = (int64_t)hp.n_embd_head * (hp.n_head_kv / hp.tp_world);  // this rank's KV heads
     for (int il = 0; il < hp.n_layer; il++) {
         for (int v = 0; v < 2; v++) {
             m->weight_pool.emplace_back();
@@ -462,7 +485,7 @@ extern "C" int b200_llama_kv_write(b200_llama *m, int32_t il, int32_t is_v, int3
     LL_REQUIRE(m && m->finalized && data, B200_ERR_INVALID, "b200_llama_kv_write: bad argument");
     LL_REQUIRE(il >= 0 && il < m->hp.n_layer && cell0 >= 0 && n >= 0 && cell0 + n <= m->hp.n_ctx, B200_ERR_INVALID, "b200_llama_kv_write: range");
     ggml_tensor *t = (is_v ? m->v_l : m->k_l)[(size_t)il];
-    const size_t row = row_size(t->type, (int64_t)m->hp.n_embd_head * m->hp.n_head_kv);
+    const size_t row = row_size(t->type, (int64_t)m->hp.n_embd_head * (m->hp.n_head_kv / m->hp.tp_world));
     t->buffer->iface.set_tensor(t->buffer, t, data, row * (size_t)cell0, row * (size_t)n);
     return B200_OK;
 }
@@ -471,7 +494,7 @@ extern "C" int b200_llama_kv_read(b200_llama *m, int32_t il, int32_t is_v, int32
     LL_REQUIRE(m && m->finalized && data, B200_ERR_INVALID, "b200_llama_kv_read: bad argument");
     LL_REQUIRE(il >= 0 && il < m->hp.n_layer && cell0 >= 0 && n >= 0 && cell0 + n <= m->hp.n_ctx, B200_ERR_INVALID, "b200_llama_kv_read: range");
     ggml_tensor *t = (is_v ? m->v_l : m->k_l)[(size_t)il];
-    const size_t row = row_size(t->type, (int64_t)m->hp.n_embd_head * m->hp.n_head_kv);
+    const size_t row = row_size(t->type, (int64_t)m->hp.n_embd_head * (m->hp.n_head_kv / m->hp.tp_world));
     m->be->iface.synchronize(m->be);
     t->buffer->iface.get_tensor(t->buffer, t, data, row * (size_t)cell0, row * (size_t)n);
     return B200_OK;
@@ -482,7 +505,8 @@ namespace {
 
 int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outputs) {
     const b200_llama_params &hp = m->hp;
-    const int64_t D = hp.n_embd_head, n_head = hp.n_head, n_head_kv = hp.n_head_kv;
+    const int W = hp.tp_world;  // tensor-parallel ranks: this rank's graph holds 1/W of the heads
+    const int64_t D = hp.n_embd_head, n_head = hp.n_head / W, n_head_kv = hp.n_head_kv / W;
     const int64_t n_embd_gqa = D * n_head_kv;
     const int32_t kv_head = n_past;
     // kv_self.n = min(size, max(pad, GGML_PAD(cell_max, pad)))  (src/llama.cpp:17163-17171)
@@ -546,6 +570,7 @@ int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outpu
         cur = b.reshape(cur, D * n_head, n_tokens);
         b.expand(cur);
         cur = b.mul_mat(L.wo, cur);
+        if (W > 1) cur = b.collective(cur, B200_COLLECTIVE_ALL_REDUCE_SUM, W);  // wo is split along K: partial sums
         if (il == hp.n_layer - 1 && n_outputs < n_tokens) {
             // skip computing output for unused tokens (:10541-10546)
             ggml_tensor *ids = input_view(m->inp_out_ids, n_outputs, 1);
@@ -561,6 +586,7 @@ int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outpu
             cur = b.silu(cur);
             cur = b.binary(GGML_OP_MUL, cur, tmp);
             cur = b.mul_mat(L.ffn_down, cur);
+            if (W > 1) cur = b.collective(cur, B200_COLLECTIVE_ALL_REDUCE_SUM, W);  // ffn_down is split along K
         } else {
             // llm_build_moe_ffn (:9416-9515), norm_w = true
             const int64_t n_expert = hp.n_expert, n_used = hp.n_expert_used, n_tok = cur->ne[1], n_embd = cur->ne[0];
@@ -592,6 +618,10 @@ int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outpu
     region(t0, buf_size);
     cur = b.binary(GGML_OP_MUL, b.rms_norm(inpL, hp.rms_eps), m->output_norm);
     cur = b.mul_mat(m->output, cur);
+    if (W > 1) {  // the head is split by vocabulary rows
+        LL_REQUIRE(n_outputs == 1, B200_ERR_UNSUPPORTED, "b200_llama_decode: tensor-parallel mode returns the logits of the last token only");
+        cur = b.collective(cur, B200_COLLECTIVE_ALL_GATHER, W);
+    }
     b.expand(cur);
     bp.size = buf_size;
     LL_REQUIRE(!b.oom, B200_ERR_NOMEM, "b200_llama_decode: compute buffer too small for this batch");

@@ -18,7 +18,8 @@ class LlamaParams(C.Structure):
                 ("n_ff", C.c_int32), ("n_vocab", C.c_int32), ("n_expert", C.c_int32), ("n_expert_used", C.c_int32), ("n_ctx", C.c_int32),
                 ("type_k", C.c_int32), ("type_v", C.c_int32), ("rope_neox", C.c_int32), ("n_ctx_orig", C.c_int32),
                 ("rms_eps", C.c_float), ("rope_freq_base", C.c_float), ("rope_freq_scale", C.c_float),
-                ("main_device", C.c_int32), ("n_split_devices", C.c_int32), ("tensor_split", C.c_float * 16)]
+                ("main_device", C.c_int32), ("n_split_devices", C.c_int32), ("tensor_split", C.c_float * 16),
+                ("tp_rank", C.c_int32), ("tp_world", C.c_int32)]
 
 
 _SIGS = {
@@ -206,17 +207,22 @@ def random_blocks(rng: np.random.Generator, ty: int, n_rows: int, ne0: int) -> n
 class LlamaModel:
     """A model resident on the device(s), driven through b200_llama_* (include/b200_llama.h)."""
 
-    def __init__(self, shape: ModelShape, n_ctx: int, type_kv: int = F16, n_split_devices: int = 0, main_device: int = 0):
+    def __init__(self, shape: ModelShape, n_ctx: int, type_kv: int = F16, n_split_devices: int = 0, main_device: int = 0,
+                 tp_rank: int = 0, tp_world: int = 1):
         L = _l()
         if L.ggml_backend_b200_get_device_count() <= 0:
             raise B200Error("no CUDA device: the B200 backend has no CPU fallback")
         self.shape = shape
         self.n_ctx = n_ctx
         self.type_kv = type_kv
+        self.tp_rank, self.tp_world = tp_rank, max(1, tp_world)
+        if self.tp_world > 1:
+            from . import tp
+            tp.check_divisible(shape.n_head, shape.n_head_kv, shape.n_ff, shape.n_vocab, shape.head_dim, self.tp_world)
         p = LlamaParams(n_embd=shape.n_embd, n_layer=shape.n_layer, n_head=shape.n_head, n_head_kv=shape.n_head_kv, n_embd_head=shape.head_dim,
                         n_ff=shape.n_ff, n_vocab=shape.n_vocab, n_expert=shape.n_expert, n_expert_used=shape.n_expert_used, n_ctx=n_ctx,
                         type_k=type_kv, type_v=type_kv, rope_neox=0, n_ctx_orig=n_ctx, rms_eps=shape.rms_eps, rope_freq_base=shape.rope_freq_base,
-                        rope_freq_scale=1.0, main_device=main_device, n_split_devices=n_split_devices)
+                        rope_freq_scale=1.0, main_device=main_device, n_split_devices=n_split_devices, tp_rank=tp_rank, tp_world=self.tp_world)
         h = C.c_void_p()
         check(L.b200_llama_new(C.byref(p), C.byref(h)), "b200_llama_new")
         self.h = h
@@ -261,7 +267,11 @@ class LlamaModel:
             if replicate_layers and key in seen:
                 self.clone_tensor(name, seen[key])
                 continue
-            data = random_blocks(rng, ty, ne[1] * ne[2], ne[0])
+            data = random_blocks(rng, ty, ne[1] * ne[2], ne[0])  # every rank draws the FULL tensor from the same stream ...
+            if self.tp_world > 1:                                 # ... and keeps its shard
+                from . import tp
+                data = tp.shard_tensor(name, ty, ne, data, self.tp_rank, self.tp_world)
+                ne = tp.shard_shape(name, ne, self.tp_world)
             self.set_tensor(name, ty, ne, data)
             seen[key] = name
 
@@ -279,13 +289,16 @@ class LlamaModel:
             d = (amax / 127.0).astype(np.float32)
             q = np.where(d[..., None] > 0, np.round(xb / np.where(d[..., None] > 0, d[..., None], 1)), 0).astype(np.int8)
             rows = np.concatenate([d.astype(np.float16).view(np.uint8).reshape(n_cells, width // 32, 2), q.view(np.uint8)], axis=2).reshape(n_cells, -1)
+        if self.tp_world > 1:
+            from . import tp
+            rows = tp.shard_kv_rows(rows, self.type_kv, s.n_head_kv, s.head_dim, self.tp_rank, self.tp_world)
         rows = np.ascontiguousarray(rows)
         for il in range(s.n_layer):
             for is_v in (0, 1):
                 check(_l().b200_llama_kv_write(self.h, il, is_v, 0, n_cells, rows.ctypes.data), "kv_write")
 
     def kv_read(self, il: int, is_v: int, cell0: int, n: int) -> np.ndarray:
-        row = row_size(self.type_kv, self.shape.head_dim * self.shape.n_head_kv)
+        row = row_size(self.type_kv, self.shape.head_dim * self.shape.n_head_kv // self.tp_world)
         out = np.empty((n, row), dtype=np.uint8)
         check(_l().b200_llama_kv_read(self.h, il, is_v, cell0, n, out.ctypes.data), "kv_read")
         return out

@@ -1,0 +1,77 @@
+"""Worker of test_gpu_tp.py (launched with torch.distributed.run, one rank per GPU): the tensor-parallel model must produce
+the logits and the greedy tokens of the same model held on one GPU (which rank 0 builds for the comparison)."""
+from __future__ import annotations
+
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+def main() -> int:
+    import torch
+    import torch.distributed as dist
+
+    from koboldcpp_b200 import tp
+    from koboldcpp_b200.lib import F16, Q8_0, check, lib
+    from koboldcpp_b200.llama import SHAPES, LlamaModel, tensor_shape
+    from test_gpu_llama import make_tensors, rel_rms
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    check(lib().b200_set_device(local))
+    tp.comm_init_from_torch(rank, world)
+    shape = SHAPES["test-dense"]
+    tensors = make_tensors(shape, 31)
+    bad = 0
+    for type_kv in (F16, Q8_0):
+        m = LlamaModel(shape, 512, type_kv, main_device=local, tp_rank=rank, tp_world=world)
+        for name, (ty, raw) in tensors.items():
+            ne = tensor_shape(shape, name)
+            m.set_tensor(name, ty, tp.shard_shape(name, ne, world), tp.shard_tensor(name, ty, ne, raw, rank, world))
+        m.finalize(64)
+        one = None
+        if rank == 0:
+            one = LlamaModel(shape, 512, type_kv, main_device=local)
+            for name, (ty, raw) in tensors.items():
+                one.set_tensor(name, ty, tensor_shape(shape, name), raw)
+            one.finalize(64)
+        prompt = [(i * 7919 + 5) % shape.n_vocab for i in range(40)]  # N > 8: tensor-core GEMM + multi-column attention
+        b = m.decode(prompt, 0).copy()
+        tok_tp, tok_one = [], []
+        if rank == 0:
+            a = one.decode(prompt, 0).copy()
+            e = rel_rms(b, a)
+            print(f"kv {type_kv}: prefill last-token logits rel rms {e:.2e}", flush=True)
+            bad += e > 5e-3
+        n_past = len(prompt)
+        tok = int(np.argmax(b[0]))
+        for t in range(16):  # greedy decode: every rank feeds the same token (the logits are all-gathered)
+            lt = m.decode([tok], n_past).copy()
+            if rank == 0:
+                lo = one.decode([tok], n_past).copy()
+                bad += rel_rms(lt[0], lo[0]) > 5e-3
+                tok_one.append(int(np.argmax(lo[0])))
+            tok = int(np.argmax(lt[0]))
+            tok_tp.append(tok)
+            n_past += 1
+        if rank == 0:
+            print(f"kv {type_kv}: greedy tokens tp {tok_tp} one {tok_one}", flush=True)
+            bad += tok_tp != tok_one
+            one.close()
+        m.close()
+    flag = torch.tensor([int(bad)], device="cuda")
+    dist.all_reduce(flag)
+    tp.comm_destroy()
+    dist.destroy_process_group()
+    return 1 if int(flag.item()) else 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
