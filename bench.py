@@ -11,8 +11,11 @@ Legs (all printed in ONE JSON line by rank 0):
   roofline   the decode GEMV family: the token's GEMV launch sequence (same types, shapes and order, rotating weight sets
              larger than L2) timed alone with CUDA events; achieved = algorithmic bytes / time against the measured HBM peak.
   cpu_baseline  the reference's own CPU backend (oracle/_ref) timed on this box's host cores on a bounded sample.
-`--impl reference` prints the CPU arm only.   N > 1: one replica per rank (weak scaling, no data-path collective yet; the
-row-split tensor-parallel path is DESIGN.md section "multi-GPU").
+  tp_70b     auxiliary: BASELINE.json configs[4], ONE Llama-3-70B-shaped Q4_K_M model sharded over all N ranks (strong scaling,
+             NCCL all-reduce / all-gather in the captured graph); at N = 1 the same model on one GPU, so 1 -> N speed-up is
+             the ratio of the tp_70b values of two runs.
+`--impl reference` prints the CPU arm only.   N > 1: the headline legs run one 7B replica per rank (weak scaling, no data-path
+collective: the 7B model does not need sharding); the sharded path is the tp_70b leg.
 """
 from __future__ import annotations
 
@@ -216,6 +219,93 @@ def gemv_leg(shape, steps: int, warmup: int) -> dict:
             "avg_launch_us": per_token_ms * 1e3 / n_launch, "gbs": alg_bytes / per_token_ms / 1e6}
 
 
+# ------------------------------------------------------------------------------------------------ 70B tensor-parallel leg
+TP_WORKLOAD = "llama3-70b-q4_k_m"
+
+
+def tp_leg(rank: int, world: int, local_rank: int, dist, steps: int, warmup: int) -> dict:
+    """BASELINE.json configs[4]: Llama-3-70B-shaped Q4_K_M, ONE model sharded over all `world` ranks (strong scaling): q/k/v, gate/up
+    and the head split by rows (whole heads per rank), attn_output / ffn_down split along K with one NCCL all-reduce each, the
+    logits all-gathered (koboldcpp_b200/tp.py, csrc/comm.cu).  world == 1 is the same model on one GPU (42 GB of weights).
+    Timed like the main legs: resident replay with CUDA events on the backend stream, and the public call with host tokens in /
+    host logits out; max over ranks."""
+    import koboldcpp_b200.llama as LL
+    from koboldcpp_b200 import tp
+    from koboldcpp_b200.lib import F16, check, lib
+    L = lib()
+    shape = LL.SHAPES[TP_WORKLOAD]
+    t0 = time.time()
+    if world > 1:
+        tp.comm_init_from_torch(rank, world)
+    m = LL.LlamaModel(shape, N_CTX, F16, main_device=local_rank, tp_rank=rank, tp_world=world)
+    m.init_random(seed=4321)            # same stream on every rank: each keeps its shard of the same model
+    m.finalize(max_batch=PP_BATCH)
+    m.kv_fill_random(N_PREFILLED, seed=11)
+    setup_s = time.time() - t0
+    span = N_CTX - N_PREFILLED
+    stream = m.stream
+    ev = [C.c_void_p() for _ in range(4)]
+    for e in ev:
+        check(L.b200_event_create(C.byref(e)))
+
+    def barrier():
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier()
+        m.synchronize()
+
+    tok = 1
+    for i in range(warmup):
+        tok = int(np.argmax(m.decode([tok], N_PREFILLED + i % span)[0]))
+    barrier()
+    check(L.b200_event_record(ev[0], stream))
+    t1 = time.perf_counter()
+    for i in range(steps):
+        tok = int(np.argmax(m.decode([tok], N_PREFILLED + (warmup + i) % span)[0]))
+    check(L.b200_event_record(ev[1], stream))
+    ms = C.c_float()
+    check(L.b200_event_elapsed_ms(ev[0], ev[1], C.byref(ms)))
+    e2e_ms = max(ms.value, (time.perf_counter() - t1) * 1e3)
+    st = m.stats()
+    barrier()
+    for _ in range(warmup):
+        m.replay()
+    barrier()
+    check(L.b200_event_record(ev[2], stream))
+    for _ in range(steps):
+        m.replay()
+    check(L.b200_event_record(ev[3], stream))
+    check(L.b200_event_elapsed_ms(ev[2], ev[3], C.byref(ms)))
+    res_ms = ms.value
+    barrier()
+    pp_tokens = [(i * 7919) % shape.n_vocab for i in range(PP_BATCH)]
+    pp_ms = []
+    for _ in range(3):
+        barrier()
+        t2 = time.perf_counter()
+        m.decode(pp_tokens, 0)
+        pp_ms.append((time.perf_counter() - t2) * 1e3)
+    pp_best = min(pp_ms[1:])
+    if dist is not None:
+        import torch
+        t = torch.tensor([res_ms, e2e_ms, pp_best], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        res_ms, e2e_ms, pp_best = float(t[0]), float(t[1]), float(t[2])
+    m.close()
+    if world > 1:
+        tp.comm_destroy()
+    peak, _ = peaks()
+    alg = LL.weight_bytes_per_token(shape) + LL.kv_bytes_per_token(shape, N_CTX, F16)
+    return {"workload": f"{shape.name} random-init, batch-1 greedy decode at n_kv={N_CTX}, f16 KV; ONE model over {world} GPU(s)",
+            "parallelism": f"tp{world}" if world > 1 else "single", "scaling": "strong", "steps": steps, "warmup": warmup,
+            "value": steps / (res_ms / 1e3), "unit": UNIT, "ms_per_step": res_ms / steps,
+            "e2e": {"value": steps / (e2e_ms / 1e3), "unit": UNIT, "ms_per_step": e2e_ms / steps},
+            "pp512_tokens_per_s": PP_BATCH / (pp_best / 1e3), "pp512_ms": pp_best,
+            "alg_bytes_per_step": alg, "hbm_frac_of_aggregate_peak": alg / (res_ms / steps) / 1e6 / (peak * world),
+            "launches_per_step": int(st["n_kernels"]), "collectives_per_step": (2 * shape.n_layer + 1) if world > 1 else 0, "setup_s": setup_s}
+
+
 # ------------------------------------------------------------------------------------------------ product arm
 def product_arm(args, rank: int, world: int, local_rank: int) -> int:
     import koboldcpp_b200.llama as LL
@@ -305,6 +395,13 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
         res_ms, e2e_ms = float(t[0]), float(t[1])
     m.close()
 
+    tp70 = None
+    if not args.no_tp70:
+        try:
+            tp70 = tp_leg(rank, world, local_rank, dist, min(steps, 32), 3)
+        except Exception as ex:  # the auxiliary leg must not hide the headline numbers
+            tp70 = {"error": f"{type(ex).__name__}: {ex}"}
+
     if rank == 0:
         peak, peak_src = peaks()
         g = gemv_leg(shape, steps, warmup)
@@ -331,6 +428,8 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
                         "note": "same model, one 512-token batch at n_past=0 through b200_llama_decode (host sync timing, best of 3 after 1 warm-up)"},
             "clocks": clk, "setup_s": setup_s,
         }
+        if tp70 is not None:
+            line["tp_70b"] = tp70
         if world == 1 and not args.no_cpu:
             try:
                 sys.path.insert(0, str(ROOT / "tests"))
@@ -354,6 +453,8 @@ def main() -> int:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--cpu-budget", type=float, default=18.0)
+    ap.add_argument("--no-tp70", action="store_true", default=bool(os.environ.get("B200_BENCH_NO_TP70")),
+                    help="skip the auxiliary 70B tensor-parallel leg (BASELINE.json configs[4])")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

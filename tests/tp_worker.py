@@ -30,42 +30,52 @@ def main() -> int:
     shape = SHAPES["test-dense"]
     tensors = make_tensors(shape, 31)
     bad = 0
-    for type_kv in (F16, Q8_0):
-        m = LlamaModel(shape, 512, type_kv, main_device=local, tp_rank=rank, tp_world=world)
-        for name, (ty, raw) in tensors.items():
-            ne = tensor_shape(shape, name)
-            m.set_tensor(name, ty, tp.shard_shape(name, ne, world), tp.shard_tensor(name, ty, ne, raw, rank, world))
-        m.finalize(64)
-        one = None
-        if rank == 0:
-            one = LlamaModel(shape, 512, type_kv, main_device=local)
+    verbose = bool(os.environ.get("TPW_VERBOSE"))
+    # (prompt length, tolerance).  N <= 8 runs the decode GEMV on every matmul: the K-split partial sums are added in f32 and the
+    # logits must agree to f32 rounding.  N > 8 runs the tensor-core GEMM on bf16 activations and the multi-column attention,
+    # whose tiling follows the per-rank head / row counts: agreement is at the bf16 level (measured 2-6e-3 of the logits' RMS on
+    # B200; both sides are within 4e-2 of the fp64 reference, test_gpu_llama.py), and the greedy tokens must still be identical.
+    for n_prompt, tol in ((4, 1e-5), (int(os.environ.get("TPW_PROMPT", "40")), 2e-2)):
+        for type_kv in (F16, Q8_0):
+            m = LlamaModel(shape, 512, type_kv, main_device=local, tp_rank=rank, tp_world=world)
             for name, (ty, raw) in tensors.items():
-                one.set_tensor(name, ty, tensor_shape(shape, name), raw)
-            one.finalize(64)
-        prompt = [(i * 7919 + 5) % shape.n_vocab for i in range(40)]  # N > 8: tensor-core GEMM + multi-column attention
-        b = m.decode(prompt, 0).copy()
-        tok_tp, tok_one = [], []
-        if rank == 0:
-            a = one.decode(prompt, 0).copy()
-            e = rel_rms(b, a)
-            print(f"kv {type_kv}: prefill last-token logits rel rms {e:.2e}", flush=True)
-            bad += e > 5e-3
-        n_past = len(prompt)
-        tok = int(np.argmax(b[0]))
-        for t in range(16):  # greedy decode: every rank feeds the same token (the logits are all-gathered)
-            lt = m.decode([tok], n_past).copy()
+                ne = tensor_shape(shape, name)
+                m.set_tensor(name, ty, tp.shard_shape(name, ne, world), tp.shard_tensor(name, ty, ne, raw, rank, world))
+            m.finalize(64)
+            one = None
             if rank == 0:
-                lo = one.decode([tok], n_past).copy()
-                bad += rel_rms(lt[0], lo[0]) > 5e-3
-                tok_one.append(int(np.argmax(lo[0])))
-            tok = int(np.argmax(lt[0]))
-            tok_tp.append(tok)
-            n_past += 1
-        if rank == 0:
-            print(f"kv {type_kv}: greedy tokens tp {tok_tp} one {tok_one}", flush=True)
-            bad += tok_tp != tok_one
-            one.close()
-        m.close()
+                one = LlamaModel(shape, 512, type_kv, main_device=local)
+                for name, (ty, raw) in tensors.items():
+                    one.set_tensor(name, ty, tensor_shape(shape, name), raw)
+                one.finalize(64)
+            prompt = [(i * 7919 + 5) % shape.n_vocab for i in range(n_prompt)]
+            b = m.decode(prompt, 0).copy()
+            tok_tp, tok_one, worst = [], [], 0.0
+            if rank == 0:
+                a = one.decode(prompt, 0).copy()
+                e = rel_rms(b, a)
+                print(f"prompt {n_prompt} kv {type_kv}: prefill last-token logits rel rms {e:.2e}", flush=True)
+                bad += e > tol
+            n_past = len(prompt)
+            tok = int(np.argmax(b[0]))
+            for t in range(16):  # greedy decode: every rank feeds the same token (the logits are all-gathered)
+                lt = m.decode([tok], n_past).copy()
+                if rank == 0:
+                    lo = one.decode([tok], n_past).copy()
+                    e = rel_rms(lt[0], lo[0])
+                    worst = max(worst, e)
+                    if verbose:
+                        print(f"prompt {n_prompt} kv {type_kv}: step {t} rel rms {e:.2e}", flush=True)
+                    bad += e > tol
+                    tok_one.append(int(np.argmax(lo[0])))
+                tok = int(np.argmax(lt[0]))
+                tok_tp.append(tok)
+                n_past += 1
+            if rank == 0:
+                print(f"prompt {n_prompt} kv {type_kv}: worst decode rel rms {worst:.2e}; greedy tokens tp {tok_tp} one {tok_one}", flush=True)
+                bad += tok_tp != tok_one
+                one.close()
+            m.close()
     flag = torch.tensor([int(bad)], device="cuda")
     dist.all_reduce(flag)
     tp.comm_destroy()
