@@ -35,6 +35,23 @@ B200_API int b200_all_reduce_sum_f32(float *buf, int64_t n, b200_stream_t stream
 /* dst[r * n .. (r+1) * n) = src of rank r */
 B200_API int b200_all_gather_f32(const float *src, float *dst, int64_t n, b200_stream_t stream);
 
+/* ---- peer window: decode-size all-reduce in ONE kernel over NVLink peer memory (one process per GPU, CUDA IPC).
+ * Replaces, for messages of up to B200_COMM_PEER_MAX_FLOATS floats, the NCCL call AND the residual ADD node behind it: every rank
+ * pushes its partial vector into a window in each peer's HBM, exchanges per-block release/acquire flags, and adds the W partials in
+ * rank order (+ residual), so all ranks hold the bit-identical result.  Set-up: every rank creates its window and obtains a
+ * 64-byte IPC handle, the caller all-gathers the handles (rank order) by any means, every rank attaches.  All ranks must issue the
+ * same sequence of calls (they do: same graph).  Without a window the backend uses the NCCL path above. */
+#define B200_COMM_IPC_BYTES 64            /* sizeof(cudaIpcMemHandle_t) */
+#define B200_COMM_PEER_MAX_FLOATS 16384
+B200_API int b200_comm_peer_window_create(void *handle_out);      /* after b200_comm_init; 2..8 ranks */
+B200_API int b200_comm_peer_window_attach(const void *handles);   /* world x 64 bytes */
+B200_API int b200_comm_peer_window_destroy(void);                 /* also done by b200_comm_destroy */
+B200_API int b200_comm_peer_ready(void);                          /* 1 when attached */
+B200_API int b200_comm_peer_status(void);                         /* 0 ok; 1 a wait timed out (peer lost): results invalid */
+/* dst = (sum over ranks, in rank order, of src) + residual (residual may be NULL; dst may alias src or residual);
+ * n % 4 == 0, n <= B200_COMM_PEER_MAX_FLOATS, 16-byte aligned pointers; capturable in a CUDA graph */
+B200_API int b200_all_reduce_sum_add_f32(const float *src, const float *residual, float *dst, int64_t n, b200_stream_t stream);
+
 /* How a ggml graph asks the backend for an exchange: a GGML_OP_MAP_CUSTOM1 node (ggml.h: dst = f(src0)) whose
  * op_params[0] == B200_COLLECTIVE_TAG and op_params[1] is one of the kinds below.  llama.cpp never emits such a node; the
  * tensor-parallel host decoder (b200_llama.h, tp_world > 1) does. */

@@ -18,6 +18,8 @@ struct ExecCtx {
 // Run one graph node.  dst_slot != NULL (CPY only): the destination base pointer is read on the device from *dst_slot.
 void run_node(ExecCtx &x, const ggml_tensor *n, void *const *dst_slot);
 size_t node_fa_workspace(const ggml_tensor *n);
+// an all-reduce node small enough for the one-kernel peer-memory exchange (comm.cu), with a peer window attached
+bool peer_all_reduce_ok(const ggml_tensor *n);
 size_t node_scratch_bytes(const ggml_tensor *n);
 // a quantised-weight MUL_MAT in the decode regime that may share a launch with its siblings
 bool mul_mat_fusable(const ggml_tensor *n);

@@ -14,11 +14,12 @@
 // There is no CPU fallback: a node supports_op said no to never reaches this file, and anything else aborts like the reference.
 #include <unordered_map>
 
+#include "../../include/b200_comm.h"
 #include "backend_exec.h"
 
 namespace b200 {
 
-enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV };
+enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV, STEP_AR_ADD };
 
 struct Step {
     int kind;
@@ -261,6 +262,25 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
         }
         if (j < n && silu_mul_pair(a, cg->nodes[j])) { s.kind = STEP_SILU_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
 
+        // R3: a decode-size all-reduce whose only reader is ADD(sum, r) with r already computed -> the residual is added by the
+        // exchange kernel itself (peer window, comm.cu); the ADD node disappears
+        if (peer_all_reduce_ok(a)) {
+            const ggml_tensor *d = gi.sole_user(a);
+            if (d && d->op == GGML_OP_ADD && d->type == GGML_TYPE_F32) {
+                const ggml_tensor *r = d->src[0] == a ? d->src[1] : d->src[0];
+                const int pr = r ? gi.pos(r) : n, pd = gi.pos(d);
+                if (r && r != a && r->type == GGML_TYPE_F32 && same_shape(r, a) && same_shape(d, a) && is_contiguous(r) && is_contiguous(d) &&
+                    (((uintptr_t)r->data | (uintptr_t)d->data) & 15) == 0 && pr < i && pd > i && !done[pd]) {
+                    std::vector<int> mem = {i, pd};
+                    if (can_gather(gi, mem, i, done)) {
+                        s.kind = STEP_AR_ADD; s.n2 = d; done[pd] = 1;
+                        steps.push_back(s);
+                        continue;
+                    }
+                }
+            }
+        }
+
         if (a->op == GGML_OP_ROPE) {
             int m[4];
             if (match_rope_kv(gi, i, done, m)) {
@@ -334,6 +354,7 @@ static uint64_t graph_key(const ggml_cgraph *cg) {
     uint64_t h = 0x243f6a8885a308d3ull;
     mix(h, (uint64_t)cg->n_nodes);
     mix(h, (uint64_t)g_use_fusion);
+    mix(h, (uint64_t)b200_comm_peer_ready());
     for (int i = 0; i < cg->n_nodes; i++) {
         const ggml_tensor *t = cg->nodes[i];
         if (is_view_op(t->op)) continue;  // views matter only through the tensors that consume them (hashed as srcs)
@@ -357,6 +378,13 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
         case STEP_NODE:
             run_node(x, s.n, s.slot >= 0 ? (void *const *)(g->slots_dev + s.slot) : nullptr);
             return;
+        case STEP_AR_ADD: {
+            const ggml_tensor *a = s.n, *d = s.n2;
+            const ggml_tensor *r = d->src[0] == a ? d->src[1] : d->src[0];
+            B200_CHECK_RC(b200_all_reduce_sum_add_f32((const float *)a->src[0]->data, (const float *)r->data, (float *)d->data, nelements(d), x.stream));
+            x.launches++;
+            return;
+        }
         case STEP_RMS_MUL: {
             const ggml_tensor *a = s.n, *b = s.n2;
             const ggml_tensor *w = b->src[0] == a ? b->src[1] : b->src[0];

@@ -280,6 +280,13 @@ static int unary_code(int ggml_unary) {
     return -1;
 }
 
+bool peer_all_reduce_ok(const ggml_tensor *n) {
+    const ggml_tensor *s0 = n->src[0];
+    return n->op == GGML_OP_MAP_CUSTOM1 && (uint32_t)n->op_params[0] == B200_COLLECTIVE_TAG && n->op_params[1] == B200_COLLECTIVE_ALL_REDUCE_SUM &&
+           b200_comm_peer_ready() && s0 && s0->type == GGML_TYPE_F32 && n->type == GGML_TYPE_F32 && is_contiguous(s0) && is_contiguous(n) &&
+           nelements(n) <= B200_COMM_PEER_MAX_FLOATS && nelements(n) % 4 == 0 && (((uintptr_t)s0->data | (uintptr_t)n->data) & 15) == 0;
+}
+
 void run_node(ExecCtx &x, const ggml_tensor *n, void *const *dst_slot) {
     const ggml_tensor *s0 = n->src[0], *s1 = n->src[1];
     switch (n->op) {
@@ -287,6 +294,10 @@ void run_node(ExecCtx &x, const ggml_tensor *n, void *const *dst_slot) {
             return;
         case GGML_OP_MAP_CUSTOM1: {
             if (n->op_params[1] == B200_COLLECTIVE_ALL_REDUCE_SUM) {
+                if (peer_all_reduce_ok(n)) {  // decode-size message: one kernel over NVLink peer memory (comm.cu)
+                    B200_CHECK_RC(b200_all_reduce_sum_add_f32((const float *)s0->data, nullptr, (float *)n->data, nelements(n), x.stream));
+                    break;
+                }
                 if (n->data != s0->data) B200_CHECK_CUDA(cudaMemcpyAsync(n->data, s0->data, nbytes(s0), cudaMemcpyDeviceToDevice, x.stream));
                 B200_CHECK_RC(b200_all_reduce_sum_f32((float *)n->data, nelements(n), x.stream));
             } else {

@@ -29,6 +29,8 @@ struct NcclApi {
 static NcclApi g_nccl;
 static nccl_comm_t g_comm = nullptr;
 static int g_rank = -1, g_world = 0;
+static bool g_pw_created = false, g_pw_ready = false;  // peer window (below)
+static void pw_release();
 
 static int nccl_load() {
     if (g_nccl.handle) return B200_OK;
@@ -99,6 +101,7 @@ extern "C" int b200_comm_init(const void *id, int rank, int world) {
 }
 
 extern "C" int b200_comm_destroy(void) {
+    if (g_pw_created) { cudaDeviceSynchronize(); pw_release(); }
     if (g_comm) {
         cudaDeviceSynchronize();
         g_nccl.CommDestroy(g_comm);
@@ -106,6 +109,173 @@ extern "C" int b200_comm_destroy(void) {
     }
     g_rank = -1;
     g_world = 0;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ peer window (NVLink one-shot all-reduce)
+// Decode-size all-reduces (n_embd floats: 16-32 KB) are latency-bound: NCCL costs a launch plus its own protocol per call, and
+// the residual ADD behind it is a third launch.  Here every rank owns a "window" in its HBM that all peers map through CUDA IPC
+// (one process per GPU, NVLink/NVSwitch peer access).  One kernel per rank: PUSH my partial into slot[epoch & 1][my rank] of every
+// peer's window (remote stores are fire-and-forget, one NVLink traversal), release a per-block flag on every peer, acquire the
+// flags the peers set on me, then add the W partials in RANK ORDER out of my own window (+ residual) -- every rank computes the
+// bit-identical sum.  Two alternating slots make a trailing barrier unnecessary: a rank can only reach call e+2 (which rewrites
+// slot e & 1) after every peer has signalled e+1, i.e. finished reading call e.
+namespace b200 {
+
+constexpr int    PW_MAX_WORLD = 8;
+constexpr int    PW_THREADS   = 128;                       // one float4 per thread
+constexpr int    PW_BLOCK_F   = PW_THREADS * 4;            // floats per block
+constexpr int    PW_MAX_N     = B200_COMM_PEER_MAX_FLOATS;
+constexpr int    PW_MAX_BLK   = PW_MAX_N / PW_BLOCK_F;
+constexpr size_t PW_DATA_BYTES = (size_t)2 * PW_MAX_WORLD * PW_MAX_N * sizeof(float);
+constexpr size_t PW_FLAG_BYTES = (size_t)PW_MAX_WORLD * PW_MAX_BLK * sizeof(unsigned);
+constexpr size_t PW_BYTES      = PW_DATA_BYTES + PW_FLAG_BYTES;
+
+struct PeerWin {
+    unsigned char *win[PW_MAX_WORLD];  // win[r]: rank r's window as mapped into this process (win[rank] is the local allocation)
+    unsigned *ctr;                     // local: calls completed per block
+    unsigned *status;                  // local: set to 1 when a wait timed out (a peer died): results are then invalid
+    int rank, world;
+};
+static PeerWin g_pw = {};
+
+__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long pw_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+__global__ void __launch_bounds__(PW_THREADS) all_reduce_push_kernel(const PeerWin w, const float *__restrict__ src, const float *__restrict__ residual,
+                                                                     float *__restrict__ dst, int n) {
+    const int b = blockIdx.x, t = threadIdx.x;
+    const unsigned epoch = w.ctr[b] + 1;  // the number of this call: identical on every rank (same graph, same order)
+    const int slot = (int)(epoch & 1u);
+    const int i = (b * PW_THREADS + t) * 4;
+    const bool active = i < n;            // n % 4 == 0 (checked by the host)
+    if (active) {
+        const float4 v = *reinterpret_cast<const float4 *>(src + i);
+        const size_t off = ((size_t)(slot * PW_MAX_WORLD + w.rank) * PW_MAX_N + (size_t)i) * sizeof(float);
+#pragma unroll
+        for (int p = 0; p < PW_MAX_WORLD; p++)
+            if (p < w.world) *reinterpret_cast<float4 *>(w.win[p] + off) = v;
+    }
+    __threadfence_system();  // my stores are ordered before the flag that follows the CTA barrier
+    __syncthreads();
+    if (t < w.world) {
+        st_release_sys(reinterpret_cast<unsigned *>(w.win[t] + PW_DATA_BYTES) + w.rank * PW_MAX_BLK + b, epoch);
+        const unsigned *mine = reinterpret_cast<const unsigned *>(w.win[w.rank] + PW_DATA_BYTES) + t * PW_MAX_BLK + b;
+        const unsigned long long t0 = pw_now();
+        while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+            if (pw_now() - t0 > 2000000000ull) { *w.status = 1; break; }  // 2 s: a peer is gone; do not hang the GPU
+        }
+    }
+    __syncthreads();
+    if (active) {
+        const unsigned char *base = w.win[w.rank] + ((size_t)slot * PW_MAX_WORLD * PW_MAX_N + (size_t)i) * sizeof(float);
+        float4 acc = __ldcg(reinterpret_cast<const float4 *>(base));
+#pragma unroll
+        for (int r = 1; r < PW_MAX_WORLD; r++) {
+            if (r < w.world) {
+                const float4 v = __ldcg(reinterpret_cast<const float4 *>(base + (size_t)r * PW_MAX_N * sizeof(float)));
+                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            }
+        }
+        if (residual != nullptr) {
+            const float4 v = *reinterpret_cast<const float4 *>(residual + i);
+            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+        *reinterpret_cast<float4 *>(dst + i) = acc;
+    }
+    if (t == 0) w.ctr[b] = epoch;
+}
+
+static void pw_release() {
+    if (g_pw_ready) {
+        for (int r = 0; r < g_pw.world; r++)
+            if (r != g_pw.rank && g_pw.win[r]) cudaIpcCloseMemHandle(g_pw.win[r]);
+    }
+    if (g_pw_created) {
+        if (g_pw.win[g_pw.rank]) cudaFree(g_pw.win[g_pw.rank]);
+        if (g_pw.ctr) cudaFree(g_pw.ctr);
+    }
+    g_pw = PeerWin();
+    g_pw_created = g_pw_ready = false;
+}
+
+}  // namespace b200
+
+extern "C" int b200_comm_peer_window_create(void *handle_out) {
+    if (!handle_out) { set_error("b200_comm_peer_window_create: NULL argument"); return B200_ERR_INVALID; }
+    if (!g_comm || g_world < 2 || g_world > PW_MAX_WORLD) { set_error("b200_comm_peer_window_create: needs a communicator of 2..%d ranks", PW_MAX_WORLD); return B200_ERR_UNSUPPORTED; }
+    if (g_pw_created) { set_error("b200_comm_peer_window_create: a window already exists"); return B200_ERR_INVALID; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == B200_COMM_IPC_BYTES, "cudaIpcMemHandle_t size");
+    unsigned char *win = nullptr;
+    unsigned *ctr = nullptr;
+    B200_CUDA_TRY(cudaMalloc(&win, PW_BYTES));
+    B200_CUDA_TRY(cudaMemset(win, 0, PW_BYTES));
+    B200_CUDA_TRY(cudaMalloc(&ctr, (PW_MAX_BLK + 1) * sizeof(unsigned)));
+    B200_CUDA_TRY(cudaMemset(ctr, 0, (PW_MAX_BLK + 1) * sizeof(unsigned)));
+    B200_CUDA_TRY(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, win);
+    if (e != cudaSuccess) { cudaFree(win); cudaFree(ctr); return cuda_fail(e, "cudaIpcGetMemHandle"); }
+    memcpy(handle_out, &h, sizeof(h));
+    g_pw = PeerWin();
+    g_pw.rank = g_rank;
+    g_pw.world = g_world;
+    g_pw.win[g_rank] = win;
+    g_pw.ctr = ctr;
+    g_pw.status = ctr + PW_MAX_BLK;
+    g_pw_created = true;
+    return B200_OK;
+}
+
+extern "C" int b200_comm_peer_window_attach(const void *handles) {
+    if (!handles || !g_pw_created || g_pw_ready) { set_error("b200_comm_peer_window_attach: create the window first (once)"); return B200_ERR_INVALID; }
+    for (int r = 0; r < g_world; r++) {
+        if (r == g_rank) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const unsigned char *)handles + (size_t)r * B200_COMM_IPC_BYTES, sizeof(h));
+        void *p = nullptr;
+        const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            for (int q = 0; q < r; q++) if (q != g_rank && g_pw.win[q]) { cudaIpcCloseMemHandle(g_pw.win[q]); g_pw.win[q] = nullptr; }
+            return cuda_fail(e, "cudaIpcOpenMemHandle");
+        }
+        g_pw.win[r] = (unsigned char *)p;
+    }
+    g_pw_ready = true;
+    return B200_OK;
+}
+
+extern "C" int b200_comm_peer_window_destroy(void) {
+    if (g_pw_created) cudaDeviceSynchronize();
+    pw_release();
+    return B200_OK;
+}
+
+extern "C" int b200_comm_peer_ready(void) { return g_pw_ready ? 1 : 0; }
+
+extern "C" int b200_comm_peer_status(void) {
+    if (!g_pw_created) return 0;
+    unsigned v = 0;
+    if (cudaMemcpy(&v, g_pw.status, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (int)v;
+}
+
+extern "C" int b200_all_reduce_sum_add_f32(const float *src, const float *residual, float *dst, int64_t n, b200_stream_t stream) {
+    if (!g_pw_ready) { set_error("b200_all_reduce_sum_add_f32: no peer window (b200_comm_peer_window_attach)"); return B200_ERR_INVALID; }
+    if (!src || !dst || n < 0) { set_error("b200_all_reduce_sum_add_f32: bad arguments"); return B200_ERR_INVALID; }
+    if (n == 0) return B200_OK;
+    if (n > PW_MAX_N || (n & 3) || ((uintptr_t)src & 15) || ((uintptr_t)dst & 15) || ((uintptr_t)residual & 15)) {
+        set_error("b200_all_reduce_sum_add_f32: n=%lld must be a multiple of 4 up to %d with 16-byte aligned buffers", (long long)n, PW_MAX_N);
+        return B200_ERR_UNSUPPORTED;
+    }
+    const int grid = (int)((n + PW_BLOCK_F - 1) / PW_BLOCK_F);
+    all_reduce_push_kernel<<<grid, PW_THREADS, 0, (cudaStream_t)stream>>>(g_pw, src, residual, dst, (int)n);
+    B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }
 

@@ -87,7 +87,10 @@ def _l():
         for name, res, args in (("b200_comm_unique_id", C.c_int, [C.c_void_p]), ("b200_comm_init", C.c_int, [C.c_void_p, C.c_int, C.c_int]),
                                 ("b200_comm_destroy", C.c_int, []), ("b200_comm_rank", C.c_int, []), ("b200_comm_world", C.c_int, []),
                                 ("b200_all_reduce_sum_f32", C.c_int, [C.c_void_p, C.c_int64, C.c_void_p]),
-                                ("b200_all_gather_f32", C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p])):
+                                ("b200_all_gather_f32", C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+                                ("b200_comm_peer_window_create", C.c_int, [C.c_void_p]), ("b200_comm_peer_window_attach", C.c_int, [C.c_void_p]),
+                                ("b200_comm_peer_window_destroy", C.c_int, []), ("b200_comm_peer_ready", C.c_int, []), ("b200_comm_peer_status", C.c_int, []),
+                                ("b200_all_reduce_sum_add_f32", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p])):
             f = getattr(L, name)
             f.restype = res
             f.argtypes = args
@@ -95,7 +98,7 @@ def _l():
     return L
 
 
-def comm_init_from_torch(rank: int, world: int) -> None:
+def comm_init_from_torch(rank: int, world: int, peer_window: bool = True) -> None:
     """Create the library's NCCL communicator; the 128-byte id travels through the caller's torch.distributed group."""
     import torch
     import torch.distributed as dist
@@ -109,6 +112,39 @@ def comm_init_from_torch(rank: int, world: int) -> None:
     dist.broadcast(t, 0)
     raw = bytes(t.cpu().tolist())
     check(L.b200_comm_init(raw, rank, world), "b200_comm_init")
+    if peer_window and 2 <= world <= 8:
+        peer_window_init(rank, world)
+
+
+IPC_BYTES = 64
+
+
+def peer_window_init(rank: int, world: int) -> bool:
+    """Map every rank's exchange window into every process (CUDA IPC handles travel through torch.distributed).  Either all
+    ranks end up attached or none does (then the backend keeps the NCCL all-reduce); returns which."""
+    import torch
+    import torch.distributed as dist
+    L = _l()
+    on_gpu = dist.get_backend() == "nccl"
+    h = (C.c_ubyte * IPC_BYTES)()
+    ok = L.b200_comm_peer_window_create(h) == 0
+    mine = torch.tensor(list(bytes(h)) + [1 if ok else 0], dtype=torch.uint8)
+    if on_gpu:
+        mine = mine.cuda()
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine)
+    rows = [bytes(p.cpu().tolist()) for p in parts]
+    ok = all(r[IPC_BYTES] == 1 for r in rows)
+    if ok:
+        ok = L.b200_comm_peer_window_attach(b"".join(r[:IPC_BYTES] for r in rows)) == 0
+    flag = torch.tensor([1 if ok else 0], dtype=torch.int32)
+    if on_gpu:
+        flag = flag.cuda()
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) != 1:
+        L.b200_comm_peer_window_destroy()
+        return False
+    return True
 
 
 def comm_destroy() -> None:

@@ -27,9 +27,39 @@ def main() -> int:
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     check(lib().b200_set_device(local))
     tp.comm_init_from_torch(rank, world)
+    bad = 0
+    # ---- the one-kernel peer-memory all-reduce (+ residual) against the same sum done on the host, many calls back to back
+    # (slot alternation, per-block epochs), several sizes including a partial last block
+    import ctypes as C
+
+    import koboldcpp_b200.host as H
+    L = tp._l()
+    peer = bool(L.b200_comm_peer_ready())
+    print(f"rank {rank}: peer window {'attached' if peer else 'UNAVAILABLE (NCCL path)'}", flush=True)
+    if os.environ.get("TPW_REQUIRE_PEER", "1") == "1":
+        bad += not peer
+    if peer:
+        for n in (4, 512, 4096, 8192 + 4, 16384):
+            for it in range(12):
+                parts = [np.random.default_rng(1000 * r + 17 * it + n).standard_normal(n).astype(np.float32) for r in range(world)]
+                res = np.random.default_rng(5 + it).standard_normal(n).astype(np.float32)
+                exp = parts[0].copy()
+                for r in range(1, world):
+                    exp += parts[r]      # rank order, f32: the kernel's order
+                if it % 2 == 0:
+                    exp += res
+                src, rs, dst = H.DeviceBuffer.from_numpy(parts[rank]), H.DeviceBuffer.from_numpy(res), H.DeviceBuffer(4 * n)
+                check(L.b200_all_reduce_sum_add_f32(src.ptr, rs.ptr if it % 2 == 0 else None, dst.ptr, n, None))
+                H.sync()
+                got = dst.to_numpy(np.float32, (n,))
+                if not np.array_equal(got, exp):
+                    bad += 1
+                    print(f"rank {rank}: all-reduce mismatch n={n} it={it} max diff {np.abs(got - exp).max()}", flush=True)
+                for bfr in (src, rs, dst):
+                    bfr.free()
+        bad += L.b200_comm_peer_status() != 0
     shape = SHAPES["test-dense"]
     tensors = make_tensors(shape, 31)
-    bad = 0
     verbose = bool(os.environ.get("TPW_VERBOSE"))
     # (prompt length, tolerance).  N <= 8 runs the decode GEMV on every matmul: the K-split partial sums are added in f32 and the
     # logits must agree to f32 rounding.  N > 8 runs the tensor-core GEMM on bf16 activations and the multi-column attention,
