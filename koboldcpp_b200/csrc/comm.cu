@@ -30,6 +30,7 @@ static NcclApi g_nccl;
 static nccl_comm_t g_comm = nullptr;
 static int g_rank = -1, g_world = 0;
 static bool g_pw_created = false, g_pw_ready = false;  // peer window (below)
+extern bool g_mmvq_pdl;                                 // mmvq.cu: programmatic dependent launch is on
 static void pw_release();
 
 static int nccl_load() {
@@ -113,23 +114,23 @@ extern "C" int b200_comm_destroy(void) {
 }
 
 // ------------------------------------------------------------------------------------------------ peer window (NVLink one-shot all-reduce)
-// Decode-size all-reduces (n_embd floats: 16-32 KB) are latency-bound: NCCL costs a launch plus its own protocol per call, and
-// the residual ADD behind it is a third launch.  Here every rank owns a "window" in its HBM that all peers map through CUDA IPC
-// (one process per GPU, NVLink/NVSwitch peer access).  One kernel per rank: PUSH my partial into slot[epoch & 1][my rank] of every
-// peer's window (remote stores are fire-and-forget, one NVLink traversal), release a per-block flag on every peer, acquire the
-// flags the peers set on me, then add the W partials in RANK ORDER out of my own window (+ residual) -- every rank computes the
-// bit-identical sum.  Two alternating slots make a trailing barrier unnecessary: a rank can only reach call e+2 (which rewrites
-// slot e & 1) after every peer has signalled e+1, i.e. finished reading call e.
+// Decode-size all-reduces (n_embd floats: 16-32 KB) are latency-bound: NCCL costs ~10 us per call here (launch + its own protocol)
+// and the residual ADD behind it is another launch.  Here every rank owns a "window" in its HBM that all peers map through CUDA
+// IPC (one process per GPU, NVLink/NVSwitch peer access).  One kernel per rank, no fence and no separate flag: every 8-byte word
+// PUSHED into a peer's window carries 4 bytes of payload and the 4-byte number of the call (the idea of NCCL's LL protocol), so a
+// receiver simply polls the words it needs until they show the current call number -- one NVLink traversal end to end.  A
+// 16-byte store holds two such self-validating halves.  Each thread then adds the W partials of its 4 elements in RANK ORDER
+// (+ residual): every rank computes the bit-identical sum.  Two alternating slots make a trailing barrier unnecessary: a rank
+// can only reach call e+2 (which rewrites slot e & 1) after it received every peer's data of call e+1, which a peer sends
+// only after it finished reading call e.
 namespace b200 {
 
 constexpr int    PW_MAX_WORLD = 8;
-constexpr int    PW_THREADS   = 128;                       // one float4 per thread
+constexpr int    PW_THREADS   = 128;                       // 4 floats per thread
 constexpr int    PW_BLOCK_F   = PW_THREADS * 4;            // floats per block
 constexpr int    PW_MAX_N     = B200_COMM_PEER_MAX_FLOATS;
 constexpr int    PW_MAX_BLK   = PW_MAX_N / PW_BLOCK_F;
-constexpr size_t PW_DATA_BYTES = (size_t)2 * PW_MAX_WORLD * PW_MAX_N * sizeof(float);
-constexpr size_t PW_FLAG_BYTES = (size_t)PW_MAX_WORLD * PW_MAX_BLK * sizeof(unsigned);
-constexpr size_t PW_BYTES      = PW_DATA_BYTES + PW_FLAG_BYTES;
+constexpr size_t PW_BYTES     = (size_t)2 * PW_MAX_WORLD * PW_MAX_N * 8;  // [slot][source rank][element] x {payload, call number}
 
 struct PeerWin {
     unsigned char *win[PW_MAX_WORLD];  // win[r]: rank r's window as mapped into this process (win[rank] is the local allocation)
@@ -139,10 +140,12 @@ struct PeerWin {
 };
 static PeerWin g_pw = {};
 
-__device__ __forceinline__ void st_release_sys(unsigned *p, unsigned v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ void st_ll(unsigned char *p, float a, float b, unsigned e) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %2};" ::"l"(p), "r"(__float_as_uint(a)), "r"(e), "r"(__float_as_uint(b)) : "memory");
+}
+__device__ __forceinline__ uint4 ld_ll(const unsigned char *p) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ unsigned long long pw_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
@@ -150,44 +153,49 @@ __device__ __forceinline__ unsigned long long pw_now() { unsigned long long t; a
 __global__ void __launch_bounds__(PW_THREADS) all_reduce_push_kernel(const PeerWin w, const float *__restrict__ src, const float *__restrict__ residual,
                                                                      float *__restrict__ dst, int n) {
     const int b = blockIdx.x, t = threadIdx.x;
-    const unsigned epoch = w.ctr[b] + 1;  // the number of this call: identical on every rank (same graph, same order)
-    const int slot = (int)(epoch & 1u);
     const int i = (b * PW_THREADS + t) * 4;
     const bool active = i < n;            // n % 4 == 0 (checked by the host)
+    pdl_wait();                           // src, and the call counter of the previous exchange, are written by kernels in front of us
+    pdl_trigger();
+    const unsigned epoch = w.ctr[b] + 1;  // the number of this call: identical on every rank (same graph, same order)
+    const int slot = (int)(epoch & 1u);
     if (active) {
         const float4 v = *reinterpret_cast<const float4 *>(src + i);
-        const size_t off = ((size_t)(slot * PW_MAX_WORLD + w.rank) * PW_MAX_N + (size_t)i) * sizeof(float);
+        const size_t off = ((size_t)(slot * PW_MAX_WORLD + w.rank) * PW_MAX_N + (size_t)i) * 8;
 #pragma unroll
-        for (int p = 0; p < PW_MAX_WORLD; p++)
-            if (p < w.world) *reinterpret_cast<float4 *>(w.win[p] + off) = v;
-    }
-    __threadfence_system();  // my stores are ordered before the flag that follows the CTA barrier
-    __syncthreads();
-    if (t < w.world) {
-        st_release_sys(reinterpret_cast<unsigned *>(w.win[t] + PW_DATA_BYTES) + w.rank * PW_MAX_BLK + b, epoch);
-        const unsigned *mine = reinterpret_cast<const unsigned *>(w.win[w.rank] + PW_DATA_BYTES) + t * PW_MAX_BLK + b;
-        const unsigned long long t0 = pw_now();
-        while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
-            if (pw_now() - t0 > 2000000000ull) { *w.status = 1; break; }  // 2 s: a peer is gone; do not hang the GPU
-        }
-    }
-    __syncthreads();
-    if (active) {
-        const unsigned char *base = w.win[w.rank] + ((size_t)slot * PW_MAX_WORLD * PW_MAX_N + (size_t)i) * sizeof(float);
-        float4 acc = __ldcg(reinterpret_cast<const float4 *>(base));
-#pragma unroll
-        for (int r = 1; r < PW_MAX_WORLD; r++) {
-            if (r < w.world) {
-                const float4 v = __ldcg(reinterpret_cast<const float4 *>(base + (size_t)r * PW_MAX_N * sizeof(float)));
-                acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        for (int p = 0; p < PW_MAX_WORLD; p++) {
+            if (p < w.world && p != w.rank) {
+                st_ll(w.win[p] + off, v.x, v.y, epoch);
+                st_ll(w.win[p] + off + 16, v.z, v.w, epoch);
             }
         }
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        const unsigned long long t0 = pw_now();
+#pragma unroll
+        for (int r = 0; r < PW_MAX_WORLD; r++) {
+            if (r >= w.world) continue;
+            float4 x = v;
+            if (r != w.rank) {
+                const unsigned char *q = w.win[w.rank] + ((size_t)(slot * PW_MAX_WORLD + r) * PW_MAX_N + (size_t)i) * 8;
+                uint4 lo = ld_ll(q), hi = ld_ll(q + 16);
+                int spins = 0;
+                while (lo.y != epoch || lo.w != epoch || hi.y != epoch || hi.w != epoch) {
+                    if ((++spins & 1023) == 0 && pw_now() - t0 > 2000000000ull) { *w.status = 1; break; }  // 2 s: a peer is gone; do not hang
+                    lo = ld_ll(q);
+                    hi = ld_ll(q + 16);
+                }
+                x = make_float4(__uint_as_float(lo.x), __uint_as_float(lo.z), __uint_as_float(hi.x), __uint_as_float(hi.z));
+            }
+            if (r == 0) acc = x;
+            else { acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w; }
+        }
         if (residual != nullptr) {
-            const float4 v = *reinterpret_cast<const float4 *>(residual + i);
-            acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+            const float4 x = *reinterpret_cast<const float4 *>(residual + i);
+            acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
         }
         *reinterpret_cast<float4 *>(dst + i) = acc;
     }
+    __syncthreads();
     if (t == 0) w.ctr[b] = epoch;
 }
 
@@ -214,7 +222,7 @@ extern "C" int b200_comm_peer_window_create(void *handle_out) {
     unsigned char *win = nullptr;
     unsigned *ctr = nullptr;
     B200_CUDA_TRY(cudaMalloc(&win, PW_BYTES));
-    B200_CUDA_TRY(cudaMemset(win, 0, PW_BYTES));
+    B200_CUDA_TRY(cudaMemset(win, 0, PW_BYTES));  // call number 0 never occurs
     B200_CUDA_TRY(cudaMalloc(&ctr, (PW_MAX_BLK + 1) * sizeof(unsigned)));
     B200_CUDA_TRY(cudaMemset(ctr, 0, (PW_MAX_BLK + 1) * sizeof(unsigned)));
     B200_CUDA_TRY(cudaDeviceSynchronize());
@@ -274,8 +282,16 @@ extern "C" int b200_all_reduce_sum_add_f32(const float *src, const float *residu
         return B200_ERR_UNSUPPORTED;
     }
     const int grid = (int)((n + PW_BLOCK_F - 1) / PW_BLOCK_F);
-    all_reduce_push_kernel<<<grid, PW_THREADS, 0, (cudaStream_t)stream>>>(g_pw, src, residual, dst, (int)n);
-    B200_CUDA_TRY(cudaGetLastError());
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(PW_THREADS);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = g_mmvq_pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, all_reduce_push_kernel, g_pw, src, residual, dst, (int)n));
     return B200_OK;
 }
 

@@ -24,11 +24,12 @@ constexpr int FA_NBUF  = 3;   // tiles in the per-warp ring
 constexpr int FA_TP    = 16;  // KV rows per tile
 constexpr int FA_MAXC  = 8;   // query columns per CTA
 constexpr int FA_MAX_SPLITS = 32;
+constexpr int FA_RS_PAD = 4;   // floats behind the D accumulators of a partial result: m, l, 2 pad
 
 struct FaParams {
     const unsigned char *q, *k, *v, *mask;
     float *dst;
-    float *part;       // [pair][split][col][D + 2]
+    float *part;       // [pair][split][col][D + FA_RS_PAD]
     int   *tickets;    // [pair]
     int    D, N, n_head, n_head_kv, n_kv, gqa;
     int    n_cols;     // N * gqa query columns per kv-head
@@ -304,8 +305,8 @@ __global__ void __launch_bounds__(FA_NW * 32, 2) fattn_kernel(const __grid_const
     }
     // ---- merge the warps of the CTA through shared memory (reuse the tile ring)
     __syncthreads();
-    float *red = reinterpret_cast<float *>(smem);  // [warp][c][D + 2]
-    constexpr int RS = D + 2;
+    float *red = reinterpret_cast<float *>(smem);  // [warp][c][RS]
+    constexpr int RS = D + FA_RS_PAD;  // m, l behind the D values; padded so that rows stay 16-byte aligned
     if (rsel == 0) {
 #pragma unroll
         for (int c = 0; c < C; c++) {
@@ -355,21 +356,47 @@ __global__ void __launch_bounds__(FA_NW * 32, 2) fattn_kernel(const __grid_const
     __syncthreads();
     if (!is_last) return;
     __threadfence();
+    // The merging CTA is alone on the critical path: keep its loads independent and wide.  Phase 1 fetches the (m, l) pairs of
+    // all splits in one round trip and turns them into normalised weights in shared memory; phase 2 streams the partial
+    // accumulators with 16 independent 16-byte loads in flight per thread.
     const float *all = p.part + (size_t)pair * p.n_splits * C * RS;
-    for (int idx = threadIdx.x; idx < ncol * D; idx += FA_NW * 32) {
-        const int c = idx / D, d = idx % D;
+    float *wts = reinterpret_cast<float *>(smem);            // [C][FA_MAX_SPLITS]: exp(m_s - M) / L
+    float *lss = wts + C * FA_MAX_SPLITS;                     // [C][FA_MAX_SPLITS]: l_s
+    const int ns = p.n_splits;
+    for (int idx = threadIdx.x; idx < ncol * ns; idx += FA_NW * 32) {
+        const int c = idx / ns, s2 = idx - c * ns;
+        const float2 ml = __ldcg(reinterpret_cast<const float2 *>(all + ((size_t)s2 * C + c) * RS + D));
+        wts[c * FA_MAX_SPLITS + s2] = ml.x;
+        lss[c * FA_MAX_SPLITS + s2] = ml.y;
+    }
+    __syncthreads();
+    if (threadIdx.x < ncol) {
+        const int c = threadIdx.x;
         float M = -INFINITY;
-        for (int s2 = 0; s2 < p.n_splits; s2++) M = fmaxf(M, __ldcg(all + ((size_t)s2 * C + c) * RS + D));
-        float a = 0.f, L = 0.f;
-        for (int s2 = 0; s2 < p.n_splits; s2++) {
-            const float *o = all + ((size_t)s2 * C + c) * RS;
-            const float ms = __ldcg(o + D);
+        for (int s2 = 0; s2 < ns; s2++) M = fmaxf(M, wts[c * FA_MAX_SPLITS + s2]);
+        float L = 0.f;
+        for (int s2 = 0; s2 < ns; s2++) {
+            const float ms = wts[c * FA_MAX_SPLITS + s2];
             const float f = ms == -INFINITY ? 0.f : __expf(ms - M);
-            a += f * __ldcg(o + d);
-            L += f * __ldcg(o + D + 1);
+            wts[c * FA_MAX_SPLITS + s2] = f;
+            L += f * lss[c * FA_MAX_SPLITS + s2];
         }
+        lss[c * FA_MAX_SPLITS] = L;
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < ncol * (D / 4); idx += FA_NW * 32) {
+        const int c = idx / (D / 4), d4 = idx - c * (D / 4);
+        const float4 *src = reinterpret_cast<const float4 *>(all + (size_t)c * RS) + d4;
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 16
+        for (int s2 = 0; s2 < ns; s2++) {
+            const float4 v = __ldcg(src + (size_t)s2 * C * RS / 4);
+            const float f = wts[c * FA_MAX_SPLITS + s2];
+            a.x += f * v.x; a.y += f * v.y; a.z += f * v.z; a.w += f * v.w;
+        }
+        const float L = lss[c * FA_MAX_SPLITS];
         const int col = col0 + c, n = col / p.gqa, h = hk * p.gqa + col % p.gqa;
-        p.dst[((size_t)n * p.n_head + h) * D + d] = a / L;
+        *reinterpret_cast<float4 *>(p.dst + ((size_t)n * p.n_head + h) * D + 4 * d4) = make_float4(a.x / L, a.y / L, a.z / L, a.w / L);
     }
 }
 
@@ -417,7 +444,7 @@ static FaPlan fa_plan(const b200_fattn_args *a) {
     pl.n_splits = best;
     pl.tiles_per_split = (n_tiles + best - 1) / best;
     pl.ticket_bytes = ((size_t)pairs * sizeof(int) + 255) / 256 * 256;
-    pl.part_bytes = best > 1 ? (size_t)pairs * best * pl.C * (a->D + 2) * sizeof(float) : 0;
+    pl.part_bytes = best > 1 ? (size_t)pairs * best * pl.C * (a->D + FA_RS_PAD) * sizeof(float) : 0;
     return pl;
 }
 
@@ -425,7 +452,7 @@ template <int TYPE, int D, int C>
 static int fa_launch(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
     using G = KvGeo<TYPE, D>;
     size_t smem = (size_t)FA_NW * FA_NBUF * 2 * G::TILE_BYTES;
-    const size_t red = (size_t)FA_NW * C * (D + 2) * sizeof(float);
+    const size_t red = (size_t)FA_NW * C * (D + FA_RS_PAD) * sizeof(float);
     if (red > smem) smem = red;
     static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
     int cur_dev = 0;
@@ -496,6 +523,10 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     int rc = fa_check(a);
     if (rc) return rc;
     const FaPlan pl = fa_plan(a);
+    if (pl.n_splits > 1 && ((((uintptr_t)workspace) | (uintptr_t)a->dst) & 15)) {
+        set_error("b200_flash_attn_ext: dst and workspace must be 16-byte aligned");
+        return B200_ERR_UNSUPPORTED;
+    }
     if (pl.n_splits > 1 && (!workspace || workspace_bytes < pl.ticket_bytes + pl.part_bytes)) {
         set_error("b200_flash_attn_ext: workspace too small (%zu < %zu)", workspace_bytes, pl.ticket_bytes + pl.part_bytes);
         return B200_ERR_INVALID;
