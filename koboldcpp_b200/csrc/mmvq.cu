@@ -123,11 +123,20 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         if (++iit == n_it) { iit = 0; ik++; }
     };
     TRACE(1);
+    // One column (decode) with a row that fits the register file: the activation loads go out in FRONT of the weight ring
+    // (see act_issue); the wait for the producer therefore comes first -- with one CTA per SM this kernel only starts on an SM
+    // when the producer's CTA there has retired, so little overlap is lost.
+    const bool acts_first = NCOLS == 1 && p.K <= ACT_RR_MAX && nrows > 0;
+    ActRegs aregs;
+    if (acts_first) {
+        pdl_wait();
+        act_issue(aregs, p.jobs[jfirst].X, p.norm_w, p.K);
+    }
     for (int s = 0; s < n_stage && ik < nmy; s++) issue();
     TRACE(2);
 
-    // ---- everything above is independent of the producer kernel's output
-    if (!MULTI || p.ids == nullptr) pdl_wait();
+    // ---- the ring fill above is independent of the producer kernel's output
+    if (!acts_first && (!MULTI || p.ids == nullptr)) pdl_wait();
     TRACE(3);
 
     // lanes past the end of the row in the last step (and, for q4_0/q8_0, a partial last slice)
@@ -146,7 +155,8 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         const float *xj = p.jobs[job].X;
         if (loaded_x != xj && nrows > 0) {
             if (loaded_x != nullptr) __syncthreads();  // everyone is done with the previous activations
-            load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red);
+            if (acts_first && loaded_x == nullptr) act_finish(aregs, act_base, p.K, n_it, p.norm_w != nullptr, p.norm_eps, red);
+            else load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red);
             __syncthreads();
             loaded_x = xj;
             TRACE(4);

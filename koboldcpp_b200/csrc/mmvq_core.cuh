@@ -142,6 +142,82 @@ __device__ void load_activations(unsigned char *act_base, const float *__restric
     }
 }
 
+// Register-resident, two-phase variant for one column (decode): act_issue() puts every load of the row (and of the norm weights)
+// in flight and returns; act_finish() computes the RMS statistics from the registers, quantises and stores.  The GEMV issues the
+// activation loads BEFORE it fills its weight ring: an SM ingests ~64 B/clk, so a load issued behind 190 KB of bulk copies waits
+// ~1.5 us for its turn (measured with tools/trace_mmvq.py), while issued in front of them it returns in one L2 round trip and the
+// quantisation overlaps the arrival of the weights.
+constexpr int ACT_RR     = 8;                               // float4 per thread
+constexpr int ACT_RR_MAX = ACT_RR * 4 * MMVQ_THREADS;       // 16384 values
+struct ActRegs {
+    float4 v[ACT_RR];
+    float4 w[ACT_RR];
+};
+__device__ __forceinline__ void act_issue(ActRegs &r, const float *__restrict__ x, const float *__restrict__ norm_w, int64_t K) {
+    constexpr int NT = MMVQ_THREADS;
+    const int n4 = (int)(K / 4);
+#pragma unroll
+    for (int u = 0; u < ACT_RR; u++) {
+        const int i4 = u * NT + threadIdx.x;
+        r.v[u] = i4 < n4 ? __ldcg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    if (norm_w != nullptr) {
+#pragma unroll
+        for (int u = 0; u < ACT_RR; u++) {
+            const int i4 = u * NT + threadIdx.x;
+            r.w[u] = i4 < n4 ? __ldg(reinterpret_cast<const float4 *>(norm_w) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+}
+// All threads of the CTA call this (it contains CTA barriers when norm is set).
+__device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t K, int n_it, bool norm, float norm_eps, float *red) {
+    constexpr int NT = MMVQ_THREADS;
+    const int n4 = (int)(K / 4);
+    int   *aq = (int *)p;
+    float *ad = (float *)(p + (size_t)n_it * 4096);
+    float *as = (float *)(p + (size_t)n_it * (4096 + 512));
+    int   *ag = (int *)(p + (size_t)n_it * (4096 + 1024));
+    if (norm) {
+        float ss = 0.f;
+#pragma unroll
+        for (int u = 0; u < ACT_RR; u++) ss += r.v[u].x * r.v[u].x + r.v[u].y * r.v[u].y + r.v[u].z * r.v[u].z + r.v[u].w * r.v[u].w;
+        ss = warp_sum(ss);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+        __syncthreads();
+        float t = (threadIdx.x & 31) < NT / 32 ? red[threadIdx.x & 31] : 0.f;
+        t = warp_sum(t);
+        const float nscale = rsqrtf(t / (float)K + norm_eps);
+#pragma unroll
+        for (int u = 0; u < ACT_RR; u++) {
+            r.v[u].x = r.v[u].x * nscale * r.w[u].x; r.v[u].y = r.v[u].y * nscale * r.w[u].y;
+            r.v[u].z = r.v[u].z * nscale * r.w[u].z; r.v[u].w = r.v[u].w * nscale * r.w[u].w;
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < ACT_RR; u++) {
+        const int i4 = u * NT + threadIdx.x;
+        if (u * NT >= n4) break;  // warp-uniform: the whole batch is past the end
+        const bool active = i4 < n4;
+        float d, s;
+        int sum4;
+        const int packed = quantize_q8_1_group8(r.v[u], d, s, sum4);
+        const int hi4 = __shfl_xor_sync(0xffffffffu, sum4, 4);
+        if (active) {
+            const int blk = i4 >> 3, part = i4 & 7;
+            const int slice = blk >> 2, b = blk & 3;
+            const int it = slice >> 5, lane = slice & 31;
+            const int j = b * 2 + (part >> 2);
+            aq[(((it * 8 + j) * 32 + lane) << 2) + (part & 3)] = packed;
+            if (part == 0) {
+                const int o = ((it * 32 + lane) << 2) + b;
+                ad[o] = d;
+                as[o] = s;
+                ag[o] = (sum4 & 0xffff) | (hi4 << 16);  // 16-wide integer sums (q6_K offset term)
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------ per-type slice dot
 // Each returns, for every column, the contribution of this lane's 128-weight slice.
 template <int TYPE, int NCOLS>
