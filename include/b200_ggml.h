@@ -142,7 +142,9 @@ B200_API int b200_mul_mat_vec_q_multi(int type, const b200_gemv_job *jobs, int n
 typedef struct {
     const float *norm_weight; /* f32 [K], 16-byte aligned, or NULL */
     float        norm_eps;
-    int32_t      _pad;
+    int32_t      silu_pair;   /* != 0: n_jobs == 2, N == 1, jobs[0] = gate, jobs[1] = up (same M, same X):
+                                 jobs[0].dst[m] = silu(gate[m] . x) * (up[m] . x) -- UNARY(SILU) + MUL of llm_build_ffn
+                                 (src/llama.cpp:9289-9414) folded into the epilogue; jobs[1].dst is not written */
     const float *residual[B200_GEMV_MAX_JOBS];
 } b200_gemv_fuse;
 B200_API int b200_mul_mat_vec_q_fused(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride,

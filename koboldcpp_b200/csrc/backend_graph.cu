@@ -27,6 +27,8 @@ struct Step {
     const ggml_tensor *n2;              // second node of a fused pair
     std::vector<const ggml_tensor *> group;  // STEP_GEMV members; STEP_ROPE_KV: {CPY K, CPY V}
     std::vector<const ggml_tensor *> adds;   // STEP_GEMV: per member the ADD node folded into its epilogue (or NULL)
+    const ggml_tensor *silu_mul = nullptr;   // STEP_GEMV of (gate, up): the MUL node of SILU(gate) * up folded into the epilogue
+    int gate_idx = 0;                   // ... and which member of `group` is the gate
     int slot = -1, slot2 = -1;          // CPY nodes: index into the slot table, else -1
     Step() : kind(STEP_NODE), n(nullptr), n2(nullptr) {}
 };
@@ -325,6 +327,28 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                 add_of[mm] = d;
                 done[pd] = 1;
             }
+            // R4: decode gate/up pair whose results only feed MUL(SILU(gate), up) -> the activation is computed in the epilogue,
+            // the SILU and MUL nodes disappear and the two f32 vectors are never written
+            if (s.group.size() == 2 && a->ne[1] == 1 && add_of.find(s.group[0]) == add_of.end() && add_of.find(s.group[1]) == add_of.end() &&
+                s.group[0]->src[0]->ne[1] == s.group[1]->src[0]->ne[1]) {
+                for (int gi_ = 0; gi_ < 2 && !s.silu_mul; gi_++) {
+                    const ggml_tensor *gt = s.group[gi_], *up = s.group[1 - gi_];
+                    const ggml_tensor *sn = gi.sole_user(gt);
+                    if (!sn || sn->op != GGML_OP_UNARY || sn->op_params[0] != GGML_UNARY_OP_SILU || sn->src[0] != gt) continue;
+                    const ggml_tensor *mn = gi.sole_user(sn);
+                    if (!mn || mn->op != GGML_OP_MUL || gi.sole_user(up) != mn) continue;
+                    if (!((mn->src[0] == sn && mn->src[1] == up) || (mn->src[1] == sn && mn->src[0] == up))) continue;
+                    if (!same_shape(mn, gt) || !same_shape(up, gt) || !is_contiguous(mn) || !is_contiguous(gt) || mn->type != GGML_TYPE_F32) continue;
+                    const int ps = gi.pos(sn), pm = gi.pos(mn);
+                    if (ps < 0 || pm < 0 || done[ps] || done[pm]) continue;
+                    std::vector<int> mem = {ps, pm};
+                    if (!can_gather(gi, mem, i, done)) continue;
+                    s.silu_mul = mn;
+                    s.gate_idx = gi_;
+                    done[ps] = 1;
+                    done[pm] = 1;
+                }
+            }
             s.kind = STEP_GEMV;
             auto nm = norm_mul_of.find(a->src[1]);
             s.n2 = nm == norm_mul_of.end() ? nullptr : nm->second;  // RMS_NORM node folded into the prologue
@@ -423,6 +447,17 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
                 memcpy(&fuse.norm_eps, rn->op_params, 4);
             }
             int nj = 0;
+            if (s.silu_mul) {  // jobs[0] = gate, jobs[1] = up, one output vector
+                for (int q = 0; q < 2; q++) {
+                    const ggml_tensor *m = s.group[q == 0 ? s.gate_idx : 1 - s.gate_idx];
+                    jobs[q].W = m->src[0]->data; jobs[q].X = X; jobs[q].M = m->src[0]->ne[1]; jobs[q].id_index = -1; jobs[q]._pad = 0;
+                    jobs[q].dst = (float *)s.silu_mul->data;
+                }
+                fuse.silu_pair = 1;
+                B200_CHECK_RC(b200_mul_mat_vec_q_fused(a->src[0]->type, jobs, 2, a->src[0]->nb[1], x_stride, (int64_t)(a->nb[1] / 4), a->src[0]->ne[0], 1, &fuse, x.stream));
+                x.launches++;
+                return;
+            }
             for (size_t q = 0; q < s.group.size(); q++) {
                 const ggml_tensor *m = s.group[q], *add = s.adds[q];
                 jobs[nj].W = m->src[0]->data; jobs[nj].X = X; jobs[nj].M = m->src[0]->ne[1]; jobs[nj].id_index = -1; jobs[nj]._pad = 0;

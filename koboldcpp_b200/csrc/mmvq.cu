@@ -67,8 +67,13 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
     // contiguous row range, balanced to one row: the first rows_rem CTAs take rows_q + 1 rows
     const int bid = blockIdx.x;
     const int r0 = bid * p.rows_q + (bid < p.rows_rem ? bid : p.rows_rem);
-    const int nrows = p.rows_q + (bid < p.rows_rem ? 1 : 0);
-    const int nmy = warp < nrows ? (nrows - warp + MMVQ_NW - 1) / MMVQ_NW : 0;  // rows of this warp
+    const bool pair = MULTI && NCOLS == 1 && p.silu_pair != 0;
+    // pair mode: the CTA owns `np` (gate, up) row pairs starting at pair r0; warp w streams gate row, up row, gate row, ... of the
+    // pairs w, w+NW, ...: table slot lr = w + NW * k holds the gate (k even) or up (k odd) row of pair r0 + (k >> 1) * NW + w
+    const int np = p.rows_q + (bid < p.rows_rem ? 1 : 0);
+    const int nrows = pair ? 2 * MMVQ_NW * ((np + MMVQ_NW - 1) / MMVQ_NW) : np;
+    const int nmy = pair ? 2 * ((np - warp + MMVQ_NW - 1) / MMVQ_NW)
+                         : (warp < nrows ? (nrows - warp + MMVQ_NW - 1) / MMVQ_NW : 0);  // rows of this warp
 
     if (lane == 0) {
         for (int s = 0; s < n_stage; s++) mbar_init(&my_bars[s], 1);
@@ -79,6 +84,15 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         if (p.ids != nullptr) pdl_wait();  // expert ids are written by the producer kernel
         // row table: every thread resolves a few rows (<= 16 jobs: linear scan)
         for (int lr = threadIdx.x; lr < nrows; lr += MMVQ_THREADS) {
+            if (pair) {
+                const int k = lr / MMVQ_NW, w = lr - k * MMVQ_NW, pl = (k >> 1) * MMVQ_NW + w;
+                const bool valid = pl < np;
+                const int64_t prow = (int64_t)r0 + pl;
+                rsrc[lr] = valid ? (const unsigned char *)p.jobs[k & 1].W + (size_t)prow * p.w_row_bytes : nullptr;
+                rdst[lr] = p.jobs[0].dst + prow;
+                rjob[lr] = 0;
+                continue;
+            }
             int64_t row = r0 + lr;
             int j = 0;
             while (row >= p.jobs[j].M) { row -= p.jobs[j].M; j++; }
@@ -151,6 +165,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
     for (int n = 0; n < NCOLS; n++) acc[n] = 0.f;
 
     int k = 0;
+    float gate_v = 0.f;
     for (int job = jfirst; job <= jlast; job++) {
         const float *xj = p.jobs[job].X;
         if (loaded_x != xj && nrows > 0) {
@@ -190,6 +205,13 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
                 cphase ^= (cstage == 0);
                 if (ik < nmy) issue();
             }
+            if (pair) {  // (NCOLS == 1)
+                const float v = warp_sum(acc[0]);
+                acc[0] = 0.f;
+                if ((k & 1) == 0) gate_v = v;
+                else if (lane == 0) dst[0] = gate_v / (1.0f + expf(-gate_v)) * v;  // silu_mul_kernel's expression (ops.cu)
+                continue;
+            }
 #pragma unroll
             for (int n = 0; n < NCOLS; n++) {
                 float v = warp_sum(acc[n]);
@@ -227,8 +249,9 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     if (rc) return rc;
     const size_t bar_bytes = MMVQ_BAR_BYTES;
     const size_t act_bytes = ((size_t)NCOLS * act_col_bytes(p.n_it) + 127) / 128 * 128;
-    const int64_t grid = p.total_rows < g_sm_count ? p.total_rows : g_sm_count;
-    const int64_t rows_per_cta = (p.total_rows + grid - 1) / grid;
+    const int64_t units = p.silu_pair ? p.total_rows / 2 : p.total_rows;  // rows, or (gate, up) pairs
+    const int64_t grid = units < g_sm_count ? units : g_sm_count;
+    const int64_t rows_per_cta = p.silu_pair ? 2 * MMVQ_NW * (((units + grid - 1) / grid + MMVQ_NW - 1) / MMVQ_NW) : (p.total_rows + grid - 1) / grid;
     if (MULTI && rows_per_cta > MMVQ_MAX_TAB) {
         set_error("b200_mul_mat_vec_q_multi: %lld rows exceed the per-CTA row table", (long long)p.total_rows);
         return B200_ERR_UNSUPPORTED;
@@ -260,8 +283,8 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
                                            (int)(g_smem_optin - 256)));
         attr_set = true;
     }
-    p.rows_q = (int)(p.total_rows / grid);
-    p.rows_rem = (int)(p.total_rows % grid);
+    p.rows_q = (int)(units / grid);
+    p.rows_rem = (int)(units % grid);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(MMVQ_THREADS);
@@ -334,6 +357,13 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
         p.norm_eps = fuse->norm_eps;
         if (fuse->norm_weight && ((uintptr_t)fuse->norm_weight & 15)) { set_error("b200_mul_mat_vec_q_fused: norm weight must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
         for (int j = 0; j < n_jobs; j++) p.residual[j] = fuse->residual[j];
+        if (fuse->silu_pair) {
+            if (n_jobs != 2 || N != 1 || ids || jobs[0].M != jobs[1].M || jobs[0].X != jobs[1].X || fuse->residual[0] || fuse->residual[1]) {
+                set_error("b200_mul_mat_vec_q_fused: silu_pair needs two jobs (gate, up) of equal M on the same X, N == 1, no residual");
+                return B200_ERR_INVALID;
+            }
+            p.silu_pair = 1;
+        }
     }
     int64_t total = 0;
     const bool need16 = (type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K);

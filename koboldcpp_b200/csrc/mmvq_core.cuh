@@ -29,6 +29,7 @@ struct MmvqParams {
     // residual[j] (same layout as jobs[j].dst) is added to the result of job j
     const float   *norm_w;
     float          norm_eps;
+    int            silu_pair;     // jobs[0] = gate, jobs[1] = up: rows_q / rows_rem count PAIRS; dst = silu(gate . x) * (up . x)
     const float   *residual[B200_GEMV_MAX_JOBS];
 };
 

@@ -28,7 +28,7 @@ class GemvJob(C.Structure):
 
 
 class GemvFuse(C.Structure):
-    _fields_ = [("norm_weight", C.c_void_p), ("norm_eps", C.c_float), ("_pad", C.c_int32), ("residual", C.c_void_p * 16)]
+    _fields_ = [("norm_weight", C.c_void_p), ("norm_eps", C.c_float), ("silu_pair", C.c_int32), ("residual", C.c_void_p * 16)]
 
 
 class Tensor(C.Structure):
@@ -139,6 +139,7 @@ _OPS_SIGS = {
     "b200_op_cpy": (C.c_int, [C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p]),
     "b200_op_rope_kv_store": (C.c_int, [C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p, C.c_void_p,
                                         C.POINTER(RopeParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_op_silu_mul": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200_op_rms_norm_mul": (C.c_int, [C.POINTER(Tensor), C.c_void_p, C.c_void_p, C.POINTER(Tensor), C.c_float, C.c_void_p]),
 }
 

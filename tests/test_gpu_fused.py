@@ -52,6 +52,40 @@ def test_gemv_with_norm_prologue_and_residual(t, K, M, N):
     assert np.array_equal(got, got2)
 
 
+@pytest.mark.parametrize("t", [Q4_K, Q6_K])
+@pytest.mark.parametrize("K,M,norm", [(4096, 11008, True), (2048, 37, False), (4096, 148 * 16 + 5, True), (8192, 3584, False)])
+def test_gemv_gate_up_pair_with_silu_epilogue(t, K, M, norm):
+    """silu_pair: dst = silu(gate . x) * (up . x) must equal the two-job launch followed by b200_op_silu_mul bit for bit
+    (same dot products, same expression), for row counts that leave partial pair groups on the last CTAs."""
+    L = lib()
+    rng = np.random.default_rng(K + M + t)
+    wg, wu = random_blocks(rng, t, M, K), random_blocks(rng, t, M, K)
+    x = rng.standard_normal((1, K)).astype(np.float32) * 2.0
+    nw = (1.0 + 0.2 * rng.standard_normal(K)).astype(np.float32)
+    dg, du, dx, dnw = dev(wg), dev(wu), dev(x), dev(nw)
+    og, ou, oref, ofused = (H.DeviceBuffer(4 * M + 256, zero=True) for _ in range(4))
+    jobs = (GemvJob * 2)()
+    for j, (w, o) in enumerate(((dg, og), (du, ou))):
+        jobs[j].W, jobs[j].X, jobs[j].dst, jobs[j].M, jobs[j].id_index = w.ptr, dx.ptr, o.ptr, M, -1
+    fuse = GemvFuse()
+    if norm:
+        fuse.norm_weight, fuse.norm_eps = dnw.ptr, 1e-5
+    check(L.b200_mul_mat_vec_q_fused(t, jobs, 2, row_size(t, K), K, M, K, 1, C.byref(fuse), None))
+    check(L.b200_op_silu_mul(og.ptr, ou.ptr, None, oref.ptr, M, None))
+    exp = oref.to_numpy(np.float32, (M,))
+    jobs[0].dst = ofused.ptr
+    jobs[1].dst = ofused.ptr
+    fuse.silu_pair = 1
+    check(L.b200_mul_mat_vec_q_fused(t, jobs, 2, row_size(t, K), K, M, K, 1, C.byref(fuse), None))
+    got = ofused.to_numpy(np.float32, (M,))
+    assert np.array_equal(got, exp), float(np.abs(got - exp).max())
+    # and against the oracle's exact q8_1 dot (no norm: the activation quantisation is then bit-identical)
+    if not norm:
+        g, u = O.mul_mat_q8_1(t, wg, x, K, M)[0].astype(np.float64), O.mul_mat_q8_1(t, wu, x, K, M)[0].astype(np.float64)
+        ref = g / (1.0 + np.exp(-g)) * u
+        assert np.abs(got - ref).max() <= 1e-4 * np.abs(ref).max()
+
+
 @pytest.mark.parametrize("kv_type", [F16, Q8_0])
 @pytest.mark.parametrize("D,NH,HK,T", [(128, 32, 32, 1), (128, 32, 8, 3), (64, 32, 4, 5)])
 def test_rope_kv_store_equals_separate_nodes(kv_type, D, NH, HK, T):
