@@ -15,6 +15,8 @@
 //     quantize_row_q8_0) and dp4a; softmax state and the V accumulator stay in fp32 registers;
 //   * the number of splits is chosen so that #CTAs is a near-multiple of 2 x SM count; the last CTA to finish a
 //     (kv-head, column tile) merges the splits itself (ticket counter), so there is no combine launch.
+#include <cstdlib>
+
 #include "b200_common.cuh"
 
 namespace b200 {
@@ -424,6 +426,21 @@ static FaPlan fa_plan(const b200_fattn_args *a) {
     pl.C = n_cols >= 8 ? 8 : n_cols >= 4 ? 4 : n_cols >= 2 ? 2 : 1;
     if (n_cols == 3) pl.C = 4;
     if (n_cols > 4 && n_cols < 8) pl.C = 8;
+    // Few kv-heads and a short cache (GQA decode, or 1-2 kv-heads per rank under tensor parallelism): even FA_MAX_SPLITS splits
+    // leave SMs idle and every CTA carries all the q-heads of the group.  Such a launch is latency-bound, not HBM-bound, so spread
+    // the q-heads over more CTAs (smaller C, more column tiles); the extra K/V reads hit L2.  Measured on B200 @ n_kv = 4096:
+    // 64/8 heads 26.3 -> 21.4 us (C 8 -> 4), 32/4 22.8 -> 16.4 (C 2), 8/1 22.6 -> 10.6 (C 1); at 32k rows it loses, hence the
+    // tiles-per-warp bound.
+    {
+        const int n_tiles0 = (int)((a->n_kv + FA_TP - 1) / FA_TP);
+        const int slots0 = 2 * fa_sm_count();
+        while (pl.C > 1 && n_tiles0 <= 4 * FA_MAX_SPLITS * FA_NW &&
+               ((n_cols + pl.C - 1) / pl.C) * a->n_head_kv * FA_MAX_SPLITS < slots0) pl.C /= 2;
+    }
+    if (const char *e = getenv("B200_FA_C")) {  // developer override (tools/bench_kernels.py)
+        const int c = atoi(e);
+        if ((c == 1 || c == 2 || c == 4 || c == 8) && c < pl.C) pl.C = c;
+    }
     pl.n_ct = (int)((n_cols + pl.C - 1) / pl.C);
     const int n_tiles = (int)((a->n_kv + FA_TP - 1) / FA_TP);
     const int64_t pairs = (int64_t)pl.n_ct * a->n_head_kv;
