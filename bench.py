@@ -409,7 +409,10 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
         kvbytes = LL.kv_bytes_per_token(shape, N_CTX, F16)
         tok_s = world * steps / (res_ms / 1e3)
         e2e_tok_s = world * steps / (e2e_ms / 1e3)
-        mask_bytes = 4 * N_CTX * 32
+        # per step: token id + position + ONE mask element (the cell that becomes visible); the decoder re-sends the whole
+        # 4 * n_kv * 32-byte mask only when the position does not follow the previous one, i.e. when pos() wraps (every `span` steps)
+        wraps = sum(1 for i in range(steps) if pos(warmup + i) != pos(warmup + i - 1) + 1)
+        mask_bytes = 4 + (4 * N_CTX * 32 * wraps) // steps
         line = {
             "metric": METRIC, "value": tok_s, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": res_ms / steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 dot (dp4a) / f32 accumulate; f16 KV",

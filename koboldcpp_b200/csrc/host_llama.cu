@@ -4,6 +4,7 @@
 // constructors below fill struct ggml_tensor the way the ggml_* builders do (ggml.c: ggml_new_tensor_impl :3790-3870,
 // ggml_view_impl :6130-6190, ggml_permute :6300-6350, ggml_rope_impl :6920-6975, ggml_flash_attn_ext :7130-7180, ...).
 // No compute happens in this file.
+#include <chrono>
 #include <cmath>
 #include <deque>
 #include <map>
@@ -243,8 +244,22 @@ struct b200_llama {
     Bump bump;
     size_t region_inputs = 0, region_half = 0;  // layout of the compute buffer: [inputs | half A | half B | tail]
     ggml_tensor inp_tokens, inp_pos, inp_mask, inp_out_ids;
-    std::vector<float> mask_host;
-    std::vector<int32_t> pos_host, out_ids_host;
+    // pinned staging of the per-call inputs: [tokens | positions | out ids | mask], reused every call behind `in_ev`
+    unsigned char *pin = nullptr;
+    size_t pin_bytes = 0;
+    cudaEvent_t in_ev = nullptr;   // recorded behind the input copies of the last call
+    bool in_ev_pending = false;
+    // what the device-side KQ mask currently holds (single-token decode only moves one element per call)
+    // the graph of the previous call, reusable when only the KV write position moved (single-token decode): per layer the two
+    // destination views of the cache stores and the CPY nodes that alias them
+    struct KvStore { ggml_tensor *view, *cpy; char *base; size_t row; };
+    std::vector<KvStore> kv_stores;
+    int32_t g_n_tokens = 0, g_n_outputs = 0;
+    int64_t g_n_kv = -1;
+    double t_build = 0, t_inputs = 0, t_compute = 0, t_sync = 0;  // host seconds per phase (B200_LLAMA_TIMING=1 prints them at free)
+    int64_t t_calls = 0;
+    int64_t mk_n_kv = -1, mk_rows = -1;
+    int32_t mk_n_tokens = 0, mk_n_past = -1;
     Arena arena;
     ggml_cgraph graph;
     std::vector<ggml_tensor *> graph_nodes;
@@ -346,6 +361,13 @@ extern "C" void b200_llama_free(b200_llama *m) {
         delete b;  // ggml_backend_buffer_free: iface.free_buffer(buffer); delete buffer  (ggml-backend.cpp:95-104)
     }
     if (m->be) m->be->iface.free(m->be);
+    if (getenv("B200_LLAMA_TIMING") && m->t_calls > 0) {
+        const double k = 1e6 / (double)m->t_calls;
+        fprintf(stderr, "b200_llama host time per decode call (us, %lld calls): build_graph %.1f  inputs %.1f  graph_compute %.1f  synchronize %.1f\n",
+                (long long)m->t_calls, m->t_build * k, m->t_inputs * k, m->t_compute * k, m->t_sync * k);
+    }
+    if (m->pin) cudaFreeHost(m->pin);
+    if (m->in_ev) cudaEventDestroy(m->in_ev);
     delete m;
 }
 
@@ -514,6 +536,23 @@ int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outpu
     if (n_kv > hp.n_ctx) n_kv = hp.n_ctx;
     const size_t in_end = m->region_inputs, a0 = in_end, b0 = a0 + m->region_half, t0 = b0 + m->region_half;
 
+    // Same token count, same n_kv, same outputs as the graph we still hold: every node is identical except the destination of the
+    // 2 * n_layer cache stores, which moves with kv_head.  Patch those views instead of rebuilding ~900 nodes (the backend keys its
+    // captured CUDA graph on everything BUT those destinations, so it replays the same executable either way).
+    if (m->graph.n_nodes > 0 && m->g_n_tokens == n_tokens && m->g_n_kv == n_kv && m->g_n_outputs == n_outputs && !m->kv_stores.empty()) {
+        for (const b200_llama::KvStore &ks : m->kv_stores) {
+            const size_t offs = ks.row * (size_t)kv_head;
+            ks.view->data = ks.base + offs;
+            ks.view->view_offs = offs;
+            memcpy(ks.view->op_params, &offs, sizeof(offs));
+            ks.cpy->data = ks.view->data;
+            ks.cpy->view_offs = offs;
+        }
+        return B200_OK;
+    }
+    m->kv_stores.clear();
+    m->g_n_tokens = 0;
+
     m->arena.reset();
     Builder b;
     b.arena = &m->arena;
@@ -559,9 +598,13 @@ int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outpu
         b.expand(Qcur); b.expand(Kcur); b.expand(Vcur);
         ggml_tensor *kc = m->k_l[(size_t)il], *vc = m->v_l[(size_t)il];
         ggml_tensor *k_view = b.view_1d(kc, (int64_t)n_tokens * n_embd_gqa, row_size(kc->type, n_embd_gqa) * (size_t)kv_head);
-        b.expand(b.cpy(Kcur, k_view));
+        ggml_tensor *k_cpy = b.cpy(Kcur, k_view);
+        b.expand(k_cpy);
         ggml_tensor *v_view = b.view_1d(vc, (int64_t)n_tokens * n_embd_gqa, row_size(vc->type, n_embd_gqa) * (size_t)kv_head);
-        b.expand(b.cpy(Vcur, v_view));
+        ggml_tensor *v_cpy = b.cpy(Vcur, v_view);
+        b.expand(v_cpy);
+        m->kv_stores.push_back({k_view, k_cpy, (char *)kc->data, row_size(kc->type, n_embd_gqa)});
+        m->kv_stores.push_back({v_view, v_cpy, (char *)vc->data, row_size(vc->type, n_embd_gqa)});
         // llm_build_kqv (flash-attention branch)
         ggml_tensor *q = b.permute(Qcur, 0, 2, 1, 3);
         ggml_tensor *k = b.view_3d(kc, D, n_kv, n_head_kv, row_size(kc->type, n_embd_gqa), row_size(kc->type, D), 0);
@@ -631,6 +674,9 @@ int build_graph(b200_llama *m, int32_t n_tokens, int32_t n_past, int32_t n_outpu
     m->graph.size = (int)m->graph_nodes.size();
     m->graph.n_nodes = (int)m->graph_nodes.size();
     m->graph.nodes = m->graph_nodes.data();
+    m->g_n_tokens = n_tokens;
+    m->g_n_kv = n_kv;
+    m->g_n_outputs = n_outputs;
     return B200_OK;
 }
 
@@ -640,31 +686,66 @@ int enqueue_decode(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32
     LL_REQUIRE(n_past >= 0 && n_past + n_tokens <= m->hp.n_ctx, B200_ERR_INVALID, "b200_llama_decode: context overflow");
     for (int i = 0; i < n_tokens; i++) LL_REQUIRE(tokens[i] >= 0 && tokens[i] < m->hp.n_vocab, B200_ERR_INVALID, "b200_llama_decode: token id out of range");
     const int32_t n_outputs = logits_all ? n_tokens : 1;
+    const auto tp0 = std::chrono::steady_clock::now();
     const int rc = build_graph(m, n_tokens, n_past, n_outputs);
     if (rc != B200_OK) return rc;
+    const auto tp1 = std::chrono::steady_clock::now();
     ggml_backend_t be = m->be;
     // llama_set_inputs (:16587-16720): tokens, positions, causal mask (-inf above the diagonal and on padding rows), out ids
     const int64_t n_kv = m->graph_nodes.empty() ? 0 : ((int64_t)(n_past + n_tokens) + KV_PAD - 1) / KV_PAD * KV_PAD > m->hp.n_ctx
                                                           ? m->hp.n_ctx : ((int64_t)(n_past + n_tokens) + KV_PAD - 1) / KV_PAD * KV_PAD;
     const int64_t mask_rows = ((int64_t)n_tokens + GGML_KQ_MASK_PAD - 1) / GGML_KQ_MASK_PAD * GGML_KQ_MASK_PAD;
-    m->pos_host.resize((size_t)n_tokens);
-    for (int i = 0; i < n_tokens; i++) m->pos_host[(size_t)i] = n_past + i;
-    m->mask_host.assign((size_t)(n_kv * mask_rows), -INFINITY);
-    for (int j = 0; j < n_tokens; j++) {
-        float *row = m->mask_host.data() + (size_t)j * (size_t)n_kv;
-        const int64_t lim = (int64_t)n_past + j;
-        for (int64_t i = 0; i <= lim && i < n_kv; i++) row[i] = 0.0f;
+    // Staging is pinned (a pageable source makes the driver stage and serialise the copy) and reused: wait until the copies of
+    // the previous call have left it.
+    const size_t mask_floats = (size_t)(n_kv * mask_rows);
+    const size_t off_pos = 4 * (size_t)m->max_batch, off_ids = 2 * off_pos, off_mask = (off_ids + 64 + 255) / 256 * 256;
+    const size_t pin_need = off_mask + 4 * (size_t)m->hp.n_ctx * (size_t)((m->max_batch + GGML_KQ_MASK_PAD - 1) / GGML_KQ_MASK_PAD * GGML_KQ_MASK_PAD);
+    if (m->pin_bytes < pin_need) {
+        if (m->in_ev_pending) { cudaEventSynchronize(m->in_ev); m->in_ev_pending = false; }
+        if (m->pin) cudaFreeHost(m->pin);
+        m->pin = nullptr;
+        m->pin_bytes = 0;
+        LL_REQUIRE(cudaHostAlloc((void **)&m->pin, pin_need, cudaHostAllocDefault) == cudaSuccess, B200_ERR_NOMEM, "b200_llama_decode: cannot pin %zu bytes of input staging", pin_need);
+        m->pin_bytes = pin_need;
+        m->mk_n_kv = -1;
     }
-    be->iface.set_tensor_async(be, &m->inp_tokens, tokens, 0, 4 * (size_t)n_tokens);
-    be->iface.set_tensor_async(be, &m->inp_pos, m->pos_host.data(), 0, 4 * (size_t)n_tokens);
-    be->iface.set_tensor_async(be, &m->inp_mask, m->mask_host.data(), 0, 4 * (size_t)(n_kv * mask_rows));
+    if (!m->in_ev) LL_REQUIRE(cudaEventCreateWithFlags(&m->in_ev, cudaEventDisableTiming) == cudaSuccess, B200_ERR_CUDA, "b200_llama_decode: cudaEventCreate failed");
+    if (m->in_ev_pending) { cudaEventSynchronize(m->in_ev); m->in_ev_pending = false; }
+    int32_t *tok_pin = (int32_t *)m->pin, *pos_pin = (int32_t *)(m->pin + off_pos), *ids_pin = (int32_t *)(m->pin + off_ids);
+    float *mask_pin = (float *)(m->pin + off_mask);
+    for (int i = 0; i < n_tokens; i++) { tok_pin[i] = tokens[i]; pos_pin[i] = n_past + i; }
+    be->iface.set_tensor_async(be, &m->inp_tokens, tok_pin, 0, 4 * (size_t)n_tokens);
+    be->iface.set_tensor_async(be, &m->inp_pos, pos_pin, 0, 4 * (size_t)n_tokens);
+    // One more token behind the previous one with the same mask geometry: the device mask (which this decoder owns and nothing
+    // else writes) differs from what it holds in ONE element -- cell n_past becomes visible.  Anything else: rebuild and send all.
+    const bool one_more = n_tokens == 1 && m->mk_n_tokens == 1 && m->mk_n_kv == n_kv && m->mk_rows == mask_rows && n_past == m->mk_n_past + 1 && n_past < n_kv;
+    if (one_more) {
+        mask_pin[n_past] = 0.0f;
+        be->iface.set_tensor_async(be, &m->inp_mask, mask_pin + n_past, 4 * (size_t)n_past, 4);
+    } else {
+        for (size_t i = 0; i < mask_floats; i++) mask_pin[i] = -INFINITY;
+        for (int j = 0; j < n_tokens; j++) {
+            float *row = mask_pin + (size_t)j * (size_t)n_kv;
+            const int64_t lim = (int64_t)n_past + j;
+            for (int64_t i = 0; i <= lim && i < n_kv; i++) row[i] = 0.0f;
+        }
+        be->iface.set_tensor_async(be, &m->inp_mask, mask_pin, 0, 4 * mask_floats);
+    }
+    m->mk_n_kv = n_kv; m->mk_rows = mask_rows; m->mk_n_tokens = n_tokens; m->mk_n_past = n_past;
     if (n_outputs < n_tokens) {
-        m->out_ids_host.assign(1, n_tokens - 1);
-        be->iface.set_tensor_async(be, &m->inp_out_ids, m->out_ids_host.data(), 0, 4);
+        ids_pin[0] = n_tokens - 1;
+        be->iface.set_tensor_async(be, &m->inp_out_ids, ids_pin, 0, 4);
     }
+    if (cudaEventRecord(m->in_ev, (cudaStream_t)ggml_backend_b200_get_stream(be)) == cudaSuccess) m->in_ev_pending = true;
+    const auto tp2 = std::chrono::steady_clock::now();
     int64_t l0 = 0, l1 = 0;
     ggml_backend_b200_get_stats(&l0, nullptr, nullptr);
     const ggml_status st = be->iface.graph_compute(be, &m->graph);
+    const auto tp3 = std::chrono::steady_clock::now();
+    m->t_build += std::chrono::duration<double>(tp1 - tp0).count();
+    m->t_inputs += std::chrono::duration<double>(tp2 - tp1).count();
+    m->t_compute += std::chrono::duration<double>(tp3 - tp2).count();
+    m->t_calls++;
     ggml_backend_b200_get_stats(&l1, nullptr, nullptr);
     m->last_launches = l1 - l0;
     LL_REQUIRE(st == GGML_STATUS_SUCCESS, B200_ERR_CUDA, "b200_llama_decode: graph_compute failed (%d)", (int)st);
@@ -685,7 +766,9 @@ extern "C" int b200_llama_synchronize(b200_llama *m) {
 extern "C" int b200_llama_decode(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32_t n_past, float *logits, int32_t logits_all) {
     const int rc = enqueue_decode(m, tokens, n_tokens, n_past, logits, logits_all);
     if (rc != B200_OK) return rc;
+    const auto ts0 = std::chrono::steady_clock::now();
     m->be->iface.synchronize(m->be);
+    m->t_sync += std::chrono::duration<double>(std::chrono::steady_clock::now() - ts0).count();
     return B200_OK;
 }
 extern "C" int b200_llama_replay(b200_llama *m) {
