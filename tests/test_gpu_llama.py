@@ -147,3 +147,31 @@ def test_graph_replay_counts():
         assert b.value == 39 and c.value == 0, (a.value, b.value, c.value)
     finally:
         m.close()
+
+
+@pytest.mark.parametrize("type_kv", [F16, Q8_0])
+def test_decoder_input_shortcuts_do_not_change_results(type_kv):
+    """The host decoder reuses the previous graph (patched KV-store views) and sends ONE mask element when a single token follows
+    the previous one.  A sequence decoded that way must equal, bit for bit, the same sequence decoded by a model that is forced
+    onto the general path before every call (a 2-token call in between resets both shortcuts), and jumping back to an earlier
+    position must reproduce the logits first seen there (the mask hides the cells behind it again)."""
+    shape = SHAPES["test-dense"]
+    tensors = make_tensors(shape, 11)
+    toks = [(t * 37 + 3) % shape.n_vocab for t in range(24)]
+    fast = build(shape, tensors, 512, type_kv)
+    slow = build(shape, tensors, 512, type_kv)
+    try:
+        a, b = [], []
+        for t, tok in enumerate(toks):
+            a.append(fast.decode([tok], t).copy())
+            slow.decode([tok, tok], 300)               # different token count + far-away cells: full rebuild next call
+            b.append(slow.decode([tok], t).copy())
+        assert np.array_equal(np.concatenate(a), np.concatenate(b))
+        # rewind: position 10 again (cells 10.. still hold newer rows; the rebuilt mask must hide them)
+        again = fast.decode([toks[10]], 10).copy()
+        assert np.array_equal(again, a[10])
+        nxt = fast.decode([toks[11]], 11).copy()      # and the one-element update continues from the rewound state
+        assert np.array_equal(nxt, a[11])
+    finally:
+        fast.close()
+        slow.close()
