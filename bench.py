@@ -405,6 +405,14 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
     if rank == 0:
         peak, peak_src = peaks()
         g = gemv_leg(shape, steps, warmup)
+        # DRAM bytes per launch from the committed ncu --set full capture (measured / algorithmic ratio of the same kernels)
+        traffic, traffic_src = None, None
+        try:
+            tj = json.loads((ROOT / "profiles" / "ncu_traffic.json").read_text())
+            traffic = float(tj["gemv_dram_bytes_over_algorithmic_bytes"]) * g["alg_bytes_per_token"] / g["launches_per_token"]
+            traffic_src = "profiles/ncu_traffic.json"
+        except Exception:
+            pass
         wbytes = LL.weight_bytes_per_token(shape)
         kvbytes = LL.kv_bytes_per_token(shape, N_CTX, F16)
         tok_s = world * steps / (res_ms / 1e3)
@@ -422,7 +430,8 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
             "gpu_launches": int(st["n_kernels"]) * steps * 2,
             "launches_per_step": int(st["n_kernels"]), "graph_nodes_per_step": int(st["n_nodes"]),
             "roofline": {"bound": "hbm", "kernel": "decode GEMV family (gemv_stream_kernel), the token's launch sequence timed alone",
-                         "achieved": g["gbs"], "peak": peak, "unit": "GB/s", "frac": g["gbs"] / peak, "traffic": None, "peak_source": peak_src,
+                         "achieved": g["gbs"], "peak": peak, "unit": "GB/s", "frac": g["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "alg_bytes_per_launch": g["alg_bytes_per_token"] / g["launches_per_token"], "avg_launch_us": g["avg_launch_us"],
                          "launches_per_step": g["launches_per_token"], "share_of_step": g["ms_per_token"] / (res_ms / steps)},
             "step_roofline": {"alg_bytes_per_step": wbytes + kvbytes, "achieved": (wbytes + kvbytes) / (res_ms / steps) / 1e6, "peak": peak, "unit": "GB/s",
