@@ -429,7 +429,7 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
                     "ms_per_step": e2e_ms / steps},
             "gpu_launches": int(st["n_kernels"]) * steps * 2,
             "launches_per_step": int(st["n_kernels"]), "graph_nodes_per_step": int(st["n_nodes"]),
-            "roofline": {"bound": "hbm", "kernel": "decode GEMV family (gemv_stream_kernel), the token's launch sequence timed alone",
+            "roofline": {"bound": "hbm", "kernel": "decode GEMV family (mmvq_kernel<TYPE,1,MULTI>), the token's launch sequence timed alone",
                          "achieved": g["gbs"], "peak": peak, "unit": "GB/s", "frac": g["gbs"] / peak, "traffic": traffic, "traffic_source": traffic_src,
                          "peak_source": peak_src,
                          "alg_bytes_per_launch": g["alg_bytes_per_token"] / g["launches_per_token"], "avg_launch_us": g["avg_launch_us"],
