@@ -709,12 +709,13 @@ int enqueue_decode(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32
         m->pin_bytes = pin_need;
         m->mk_n_kv = -1;
     }
-    if (!m->in_ev) LL_REQUIRE(cudaEventCreateWithFlags(&m->in_ev, cudaEventDisableTiming) == cudaSuccess, B200_ERR_CUDA, "b200_llama_decode: cudaEventCreate failed");
     if (m->in_ev_pending) { cudaEventSynchronize(m->in_ev); m->in_ev_pending = false; }
     int32_t *tok_pin = (int32_t *)m->pin, *pos_pin = (int32_t *)(m->pin + off_pos), *ids_pin = (int32_t *)(m->pin + off_ids);
     float *mask_pin = (float *)(m->pin + off_mask);
     for (int i = 0; i < n_tokens; i++) { tok_pin[i] = tokens[i]; pos_pin[i] = n_past + i; }
     be->iface.set_tensor_async(be, &m->inp_tokens, tok_pin, 0, 4 * (size_t)n_tokens);
+    // (created here: set_tensor_async has just made the backend's device current, and an event belongs to the device it was created on)
+    if (!m->in_ev) LL_REQUIRE(cudaEventCreateWithFlags(&m->in_ev, cudaEventDisableTiming) == cudaSuccess, B200_ERR_CUDA, "b200_llama_decode: cudaEventCreate failed");
     be->iface.set_tensor_async(be, &m->inp_pos, pos_pin, 0, 4 * (size_t)n_tokens);
     // One more token behind the previous one with the same mask geometry: the device mask (which this decoder owns and nothing
     // else writes) differs from what it holds in ONE element -- cell n_past becomes visible.  Anything else: rebuild and send all.
@@ -737,6 +738,7 @@ int enqueue_decode(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32
         be->iface.set_tensor_async(be, &m->inp_out_ids, ids_pin, 0, 4);
     }
     if (cudaEventRecord(m->in_ev, (cudaStream_t)ggml_backend_b200_get_stream(be)) == cudaSuccess) m->in_ev_pending = true;
+    else { cudaGetLastError(); cudaStreamSynchronize((cudaStream_t)ggml_backend_b200_get_stream(be)); }  // no event: make the staging reusable the slow way
     const auto tp2 = std::chrono::steady_clock::now();
     int64_t l0 = 0, l1 = 0;
     ggml_backend_b200_get_stats(&l0, nullptr, nullptr);
