@@ -85,6 +85,12 @@ B200_API int b200_op_soft_max(const b200_tensor *x, const b200_tensor *mask, con
 
 /* ARGSORT of every row (ne0 <= 1024), i32 indices out; order: 0 ascending, 1 descending (ties keep index order).
  * replaces k_argsort_f32_i32, ggml-cuda/argsort.cu:11-100 */
+/* The router of llm_build_moe_ffn (src/llama.cpp:9416-9470) in one launch, replacing SOFT_MAX -> ARGSORT(desc) + VIEW(top n_used) ->
+ * GET_ROWS -> SUM_ROWS -> DIV: per token, probs = softmax(logits[n_expert]); ids[k] = index of the k-th largest prob (ties: lowest
+ * index); w_gather[k] = probs[ids[k]]; wsum = sum_k w_gather[k]; w_out[k] = w_gather[k] / wsum.  ld_* are row strides in elements;
+ * w_gather / w_out are [n_tok][n_used] contiguous (they may alias); n_expert <= 256, n_used <= 32. */
+B200_API int b200_op_moe_router(const float *logits, int64_t ld_logits, float *probs, int64_t ld_probs, int32_t *ids, int64_t ld_ids, float *w_gather,
+                                float *wsum, float *w_out, int32_t n_expert, int32_t n_used, int64_t n_tok, b200_stream_t stream);
 B200_API int b200_op_argsort(const b200_tensor *x, const b200_tensor *dst, int order, b200_stream_t stream);
 
 /* SUM_ROWS: dst[row] = sum over ne0.  replaces k_sum_rows_f32, ggml-cuda/sumrows.cu:3-30 */

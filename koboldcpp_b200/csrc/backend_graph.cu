@@ -15,11 +15,12 @@
 #include <unordered_map>
 
 #include "../../include/b200_comm.h"
+#include "../../include/b200_ggml_ops.h"
 #include "backend_exec.h"
 
 namespace b200 {
 
-enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV, STEP_AR_ADD };
+enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV, STEP_AR_ADD, STEP_MOE_ROUTER };
 
 struct Step {
     int kind;
@@ -196,6 +197,60 @@ static bool match_rope_kv(const GraphInfo &gi, int i, const std::vector<char> &d
     return true;
 }
 
+static const ggml_tensor *through_views(const ggml_tensor *t) {
+    while (t && is_view_op(t->op) && t->op != GGML_OP_NONE && t->src[0]) t = t->src[0];
+    return t;
+}
+// SOFT_MAX at position i followed (views aside) by ARGSORT(desc), GET_ROWS(probs, top-k view), SUM_ROWS, DIV: the MoE router chain of
+// llm_build_moe_ffn.  out = positions of the five compute nodes.  The argsort row is only written up to n_used entries by the fused
+// kernel, so every reader of the ARGSORT node must be a view of exactly those entries.
+static bool match_moe_router(const GraphInfo &gi, int i, const std::vector<char> &done, int out[5]) {
+    const ggml_cgraph *cg = gi.cg;
+    const ggml_tensor *sm = cg->nodes[i];
+    if (sm->op != GGML_OP_SOFT_MAX || sm->src[1] || sm->type != GGML_TYPE_F32 || !is_contiguous(sm) || !sm->src[0] || sm->src[0]->type != GGML_TYPE_F32) return false;
+    if (sm->src[0]->nb[0] != 4 || sm->ne[2] != 1 || sm->ne[3] != 1 || sm->ne[0] > 256 || !same_shape(sm, sm->src[0])) return false;
+    float scale = 0.f, max_bias = 1.f;
+    memcpy(&scale, sm->op_params, 4);
+    memcpy(&max_bias, (const float *)sm->op_params + 1, 4);
+    if (scale != 1.0f || max_bias != 0.0f) return false;
+    // the graph is in depth-first order (ggml_build_forward_expand): the expert matmuls that consume the selection usually sit
+    // between ARGSORT and the GET_ROWS / SUM_ROWS / DIV that produce the weights, so search ahead and let can_gather() decide
+    int pos[4] = {-1, -1, -1, -1};
+    const int horizon = i + 96 < cg->n_nodes ? i + 96 : cg->n_nodes;
+    for (int j = i + 1; j < horizon; j++) {
+        const ggml_tensor *t = cg->nodes[j];
+        if (done[j] || is_view_op(t->op)) continue;
+        if (pos[0] < 0 && t->op == GGML_OP_ARGSORT && through_views(t->src[0]) == sm) pos[0] = j;
+        else if (pos[0] >= 0 && pos[1] < 0 && t->op == GGML_OP_GET_ROWS && through_views(t->src[0]) == sm && through_views(t->src[1]) == cg->nodes[pos[0]]) pos[1] = j;
+        else if (pos[1] >= 0 && pos[2] < 0 && t->op == GGML_OP_SUM_ROWS && through_views(t->src[0]) == cg->nodes[pos[1]]) pos[2] = j;
+        else if (pos[2] >= 0 && pos[3] < 0 && t->op == GGML_OP_DIV && through_views(t->src[0]) == cg->nodes[pos[1]] && through_views(t->src[1]) == cg->nodes[pos[2]]) { pos[3] = j; break; }
+    }
+    if (pos[3] < 0) return false;
+    const ggml_tensor *as = cg->nodes[pos[0]], *gr = cg->nodes[pos[1]], *sr = cg->nodes[pos[2]], *dv = cg->nodes[pos[3]];
+    const int64_t n_expert = sm->ne[0], n_tok = sm->ne[1];
+    if (through_views(as->src[0]) != sm || as->op_params[0] != 1 /* GGML_SORT_ORDER_DESC */ || !is_contiguous(as) || as->ne[0] != n_expert || as->ne[1] != n_tok) return false;
+    const ggml_tensor *sel = gr->src[1], *pv = gr->src[0];
+    if (!sel || !pv || through_views(pv) != sm || through_views(sel) != as || sel->data != as->data || sel->nb[1] != as->nb[1] || sel->ne[1] != n_tok) return false;
+    const int64_t n_used = sel->ne[0];
+    if (n_used < 1 || n_used > 32 || n_used > n_expert || pv->ne[0] != 1 || pv->ne[1] != n_expert || pv->data != sm->data) return false;
+    if (gr->type != GGML_TYPE_F32 || !is_contiguous(gr) || nelements(gr) != n_used * n_tok) return false;
+    if (through_views(sr->src[0]) != gr || sr->src[0]->data != gr->data || !is_contiguous(sr) || nelements(sr) != n_tok || sr->src[0]->ne[0] != n_used) return false;
+    if (through_views(dv->src[0]) != gr || dv->src[0]->data != gr->data || through_views(dv->src[1]) != sr || !is_contiguous(dv) || dv->type != GGML_TYPE_F32) return false;
+    if (dv->ne[0] != n_used || nelements(dv) != n_used * n_tok) return false;
+    // readers of the argsort result: views of the first n_used entries of every row only (followed through further views)
+    for (int j = 0; j < cg->n_nodes; j++) {
+        const ggml_tensor *t = cg->nodes[j];
+        for (int q = 0; q < GGML_MAX_SRC; q++) {
+            const ggml_tensor *sq = t->src[q];
+            if (!sq || through_views(sq) != as) continue;
+            if (is_view_op(t->op)) continue;  // a view of it: checked where it is consumed
+            if (sq->data != as->data || sq->ne[0] != n_used || sq->nb[1] != as->nb[1] || sq->ne[1] != n_tok || sq->ne[2] != 1) return false;
+        }
+    }
+    out[0] = i; out[1] = pos[0]; out[2] = pos[1]; out[3] = pos[2]; out[4] = pos[3];
+    return true;
+}
+
 // Lower cgraph -> Steps.  `done[i]` marks nodes absorbed by a fused step.
 static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
     std::vector<Step> &steps = g->steps;
@@ -263,6 +318,18 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             continue;
         }
         if (j < n && silu_mul_pair(a, cg->nodes[j])) { s.kind = STEP_SILU_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
+
+        // R5: the MoE router chain -> one launch at the position of its SOFT_MAX (the weight nodes move up past the expert matmuls)
+        if (a->op == GGML_OP_SOFT_MAX) {
+            int m5[5];
+            if (match_moe_router(gi, i, done, m5) && can_gather(gi, std::vector<int>(m5, m5 + 5), i, done)) {
+                s.kind = STEP_MOE_ROUTER;
+                s.group = {cg->nodes[m5[1]], cg->nodes[m5[2]], cg->nodes[m5[3]], cg->nodes[m5[4]]};
+                for (int q = 1; q < 5; q++) done[m5[q]] = 1;
+                steps.push_back(s);
+                continue;
+            }
+        }
 
         // R3: a decode-size all-reduce whose only reader is ADD(sum, r) with r already computed -> the residual is added by the
         // exchange kernel itself (peer window, comm.cu); the ADD node disappears
@@ -402,6 +469,14 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
         case STEP_NODE:
             run_node(x, s.n, s.slot >= 0 ? (void *const *)(g->slots_dev + s.slot) : nullptr);
             return;
+        case STEP_MOE_ROUTER: {
+            const ggml_tensor *sm = s.n, *as = s.group[0], *gr = s.group[1], *sr = s.group[2], *dv = s.group[3];
+            B200_CHECK_RC(b200_op_moe_router((const float *)sm->src[0]->data, (int64_t)(sm->src[0]->nb[1] / 4), (float *)sm->data, (int64_t)(sm->nb[1] / 4),
+                                             (int32_t *)as->data, (int64_t)(as->nb[1] / 4), (float *)gr->data, (float *)sr->data, (float *)dv->data,
+                                             (int32_t)sm->ne[0], (int32_t)gr->src[1]->ne[0], sm->ne[1], x.stream));
+            x.launches++;
+            return;
+        }
         case STEP_AR_ADD: {
             const ggml_tensor *a = s.n, *d = s.n2;
             const ggml_tensor *r = d->src[0] == a ? d->src[1] : d->src[0];

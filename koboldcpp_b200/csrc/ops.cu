@@ -367,6 +367,75 @@ __global__ void soft_max_kernel(TD x, TD mask, int mask_f16, TD dst, float scale
     for (int i = threadIdx.x; i < n; i += blockDim.x) yr[i] = vals[i] * inv;
 }
 
+// ------------------------------------------------------------------------------------------------ MoE router (fused)
+// soft_max -> argsort(desc)[:n_used] -> get_rows -> sum_rows -> div of llm_build_moe_ffn (src/llama.cpp:9416-9470) for one token
+// per warp: the five launches of the node chain become one.  Every intermediate the graph defines is still written (probs, the
+// first n_used entries of the argsort row, the gathered weights, their sum), so readers of those tensors see what they expect.
+constexpr int ROUTER_MAX_EXPERT = 256, ROUTER_WARPS = 4;
+__global__ void __launch_bounds__(ROUTER_WARPS * 32) moe_router_kernel(const float *__restrict__ logits, int64_t ld_logits, float *__restrict__ probs,
+                                                                       int64_t ld_probs, int32_t *__restrict__ ids, int64_t ld_ids, float *__restrict__ w_gather,
+                                                                       float *__restrict__ wsum, float *__restrict__ w_out, int n_expert, int n_used,
+                                                                       int64_t n_tok) {
+    pdl_enter();
+    const int lane = threadIdx.x & 31;
+    const int64_t tok = (int64_t)blockIdx.x * ROUTER_WARPS + (threadIdx.x >> 5);
+    if (tok >= n_tok) return;
+    constexpr int U = ROUTER_MAX_EXPERT / 32;
+    float v[U];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        const int e = lane + 32 * u;
+        v[u] = e < n_expert ? logits[tok * ld_logits + e] : -INFINITY;
+        mx = fmaxf(mx, v[u]);
+    }
+    mx = warp_max(mx);
+    float s = 0.f;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        const int e = lane + 32 * u;
+        const float ev = e < n_expert ? expf(v[u] - mx) : 0.f;
+        v[u] = ev;
+        s += ev;
+    }
+    s = warp_sum(s);
+    const float inv = 1.0f / s;
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+        const int e = lane + 32 * u;
+        const float pr = v[u] * inv;
+        if (e < n_expert) probs[tok * ld_probs + e] = pr;
+        v[u] = e < n_expert ? pr : -INFINITY;
+    }
+    float mine = 0.f, tot = 0.f;  // lane k keeps the k-th selected weight
+    for (int k = 0; k < n_used; k++) {
+        float best = -INFINITY;
+        int bi = 0x7fffffff;
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (v[u] > best) { best = v[u]; bi = lane + 32 * u; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (bi == lane + 32 * u) v[u] = -INFINITY;
+        }
+        if (lane == k) mine = best;
+        if (lane == 0) {
+            ids[tok * ld_ids + k] = bi;
+            w_gather[tok * n_used + k] = best;
+        }
+        tot += best;
+    }
+    if (lane == 0) wsum[tok] = tot;
+    if (lane < n_used) w_out[tok * n_used + lane] = mine / tot;
+}
+
 // ------------------------------------------------------------------------------------------------ ARGSORT (bitonic, one CTA per row)
 __global__ void argsort_kernel(TD x, TD dst, int order, int npad) {
     extern __shared__ int idx[];
@@ -657,6 +726,17 @@ extern "C" int b200_op_soft_max(const b200_tensor *x, const b200_tensor *mask, c
     const int block = x->ne[0] >= 1024 ? 256 : 128;
     soft_max_kernel<<<(unsigned)rows, block, smem, (cudaStream_t)stream>>>(td(x), m, mf16, td(dst), scale, max_bias, m0, m1, n_head_log2);
     B200_CUDA_TRY(cudaGetLastError());
+    return B200_OK;
+}
+
+extern "C" int b200_op_moe_router(const float *logits, int64_t ld_logits, float *probs, int64_t ld_probs, int32_t *ids, int64_t ld_ids, float *w_gather,
+                                  float *wsum, float *w_out, int32_t n_expert, int32_t n_used, int64_t n_tok, b200_stream_t stream) {
+    REQUIRE(logits && probs && ids && w_gather && wsum && w_out, B200_ERR_INVALID, "b200_op_moe_router: NULL argument");
+    REQUIRE(n_expert >= 1 && n_expert <= ROUTER_MAX_EXPERT && n_used >= 1 && n_used <= 32 && n_used <= n_expert && n_tok >= 0, B200_ERR_UNSUPPORTED,
+            "b200_op_moe_router: up to %d experts, up to 32 used", ROUTER_MAX_EXPERT);
+    if (n_tok == 0) return B200_OK;
+    LAUNCH_PDL(moe_router_kernel, (unsigned)((n_tok + ROUTER_WARPS - 1) / ROUTER_WARPS), ROUTER_WARPS * 32, (cudaStream_t)stream, logits, ld_logits, probs, ld_probs, ids,
+               ld_ids, w_gather, wsum, w_out, (int)n_expert, (int)n_used, n_tok);
     return B200_OK;
 }
 

@@ -139,6 +139,8 @@ _OPS_SIGS = {
     "b200_op_cpy": (C.c_int, [C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p]),
     "b200_op_rope_kv_store": (C.c_int, [C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.POINTER(Tensor), C.c_void_p, C.c_void_p,
                                         C.POINTER(RopeParams), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200_op_moe_router": (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32,
+                                      C.c_int64, C.c_void_p]),
     "b200_op_silu_mul": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200_op_rms_norm_mul": (C.c_int, [C.POINTER(Tensor), C.c_void_p, C.c_void_p, C.POINTER(Tensor), C.c_float, C.c_void_p]),
 }

@@ -195,3 +195,26 @@ def test_decode_chain_equals_separate_launches(kv_type):
     assert close(got["qo"], qo, 3e-3) and close(got["h"], h, 3e-3) and close(got["act"], act, 5e-3) and close(got["out"], out, 5e-3)
     assert np.mean(kc.to_numpy(np.uint8, (rowb,)) != kc2.to_numpy(np.uint8, (rowb,))) < 0.05
     assert np.mean(vc.to_numpy(np.uint8, (rowb,)) != vc2.to_numpy(np.uint8, (rowb,))) < 0.05
+
+
+@pytest.mark.parametrize("n_expert,n_used,n_tok", [(8, 2, 1), (8, 2, 7), (64, 6, 3), (256, 8, 5), (5, 5, 2)])
+def test_moe_router_equals_the_node_chain(n_expert, n_used, n_tok):
+    """b200_op_moe_router against soft_max -> argsort(desc)[:k] -> gather -> sum -> div done in numpy (f32)."""
+    L = lib()
+    rng = np.random.default_rng(n_expert * 31 + n_tok)
+    logits = (rng.standard_normal((n_tok, n_expert)) * 2.0).astype(np.float32)
+    dl = dev(logits)
+    probs, ids = H.DeviceBuffer(4 * n_tok * n_expert + 256, zero=True), H.DeviceBuffer(4 * n_tok * n_expert + 256, zero=True)
+    wg, ws, wo = H.DeviceBuffer(4 * n_tok * n_used + 256), H.DeviceBuffer(4 * n_tok + 256), H.DeviceBuffer(4 * n_tok * n_used + 256)
+    check(L.b200_op_moe_router(dl.ptr, n_expert, probs.ptr, n_expert, ids.ptr, n_expert, wg.ptr, ws.ptr, wo.ptr, n_expert, n_used, n_tok, None))
+    e = np.exp(logits - logits.max(axis=1, keepdims=True))
+    p = (e / e.sum(axis=1, keepdims=True)).astype(np.float32)
+    order = np.argsort(-p, axis=1, kind="stable")[:, :n_used]
+    w = np.take_along_axis(p, order, axis=1)
+    got_p = probs.to_numpy(np.float32, (n_tok, n_expert))
+    got_ids = ids.to_numpy(np.int32, (n_tok, n_expert))[:, :n_used]
+    assert np.allclose(got_p, p, rtol=2e-6, atol=1e-9)
+    assert np.array_equal(got_ids, order)
+    assert np.array_equal(wg.to_numpy(np.float32, (n_tok, n_used)), np.take_along_axis(got_p, got_ids, axis=1))
+    assert np.allclose(ws.to_numpy(np.float32, (n_tok,)), w.sum(axis=1), rtol=1e-6)
+    assert np.allclose(wo.to_numpy(np.float32, (n_tok, n_used)), w / w.sum(axis=1, keepdims=True), rtol=1e-5)
