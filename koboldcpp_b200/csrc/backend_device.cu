@@ -6,18 +6,25 @@
 namespace b200 {
 
 bool g_use_graphs = true, g_use_fusion = true;
+bool g_dry = false;
+int g_dry_devices = 0;
 int64_t g_stat_launches = 0, g_stat_replays = 0, g_stat_captures = 0;
 
 int device_count() {
     static int n = -1;
     if (n < 0) {
         int c = 0;
+        if (const char *e = getenv("B200_DRY_RUN")) {  // host-side validation without a GPU: see backend_internal.h
+            g_dry_devices = atoi(e) > 0 ? atoi(e) : 1;
+            g_dry = true;
+            fprintf(stderr, "B200 backend: DRY RUN with %d emulated device(s): graphs are planned, nothing is computed\n", g_dry_devices);
+        }
         if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); c = 0; }
         n = c > GGML_B200_MAX_DEVICES ? GGML_B200_MAX_DEVICES : c;
         if (getenv("B200_NO_GRAPHS")) g_use_graphs = false;
         if (getenv("B200_NO_FUSION")) g_use_fusion = false;
         // programmatic dependent launch: a GEMV's weight prefetch overlaps the tail of its producer (b200_ggml.h)
-        b200_set_pdl(getenv("B200_NO_PDL") ? 0 : 1);
+        if (!g_dry) b200_set_pdl(getenv("B200_NO_PDL") ? 0 : 1);
     }
     return n;
 }

@@ -173,6 +173,13 @@ static bool match_rope_kv(const GraphInfo &gi, int i, const std::vector<char> &d
     const ggml_tensor *rq = cg->nodes[i];
     if (rq->op != GGML_OP_ROPE || (rq->op_params[2] & GGML_ROPE_TYPE_NEOX) || rq->type != GGML_TYPE_F32) return false;
     if (!is_contiguous(rq) || !is_contiguous(rq->src[0]) || rq->ne[3] != 1 || rq->ne[0] % 32) return false;
+    // the K-shift graph (build_k_shift, src/llama.cpp:10144-10192) is a chain of per-layer ROPEs over cache views / casts with CPYs
+    // back into the cache: not this pattern.  Q and K here are fresh projections, V is never a ROPE result.
+    {
+        const ggml_tensor *q0 = rq->src[0];
+        while (q0 && is_view_op(q0->op) && q0->op != GGML_OP_NONE && q0->src[0]) q0 = q0->src[0];
+        if (!q0 || is_cpy_op(q0->op) || q0->op == GGML_OP_NONE) return false;
+    }
     int rk = -1, ck = -1, cv = -1;
     const int horizon = i + 24 < cg->n_nodes ? i + 24 : cg->n_nodes;
     for (int j = i + 1; j < horizon; j++) {
@@ -190,7 +197,13 @@ static bool match_rope_kv(const GraphInfo &gi, int i, const std::vector<char> &d
         if (!is_contiguous(t) || src->type != GGML_TYPE_F32 || !is_contiguous(src)) continue;
         if (nelements(t) != nelements(cg->nodes[rk])) continue;
         if (ck < 0 && src == cg->nodes[rk]) { ck = j; continue; }
-        if (ck >= 0 && cv < 0 && t->type == cg->nodes[ck]->type && gi.pos(src) < j) { cv = j; break; }
+        if (ck >= 0 && cv < 0 && t->type == cg->nodes[ck]->type && gi.pos(src) < j) {
+            const ggml_tensor *v0 = src;
+            while (v0 && is_view_op(v0->op) && v0->op != GGML_OP_NONE && v0->src[0]) v0 = v0->src[0];
+            if (!v0 || v0->op == GGML_OP_ROPE || is_cpy_op(v0->op)) return false;
+            cv = j;
+            break;
+        }
     }
     if (rk < 0 || ck < 0 || cv < 0) return false;
     out[0] = i; out[1] = rk; out[2] = ck; out[3] = cv;
@@ -616,6 +629,41 @@ static void upload_slots(GraphExec *g, const ggml_cgraph *cg, int n_slots) {
     B200_CHECK_CUDA(cudaMemcpyAsync(g->slots_dev, g->slots_host.data(), sizeof(void *) * (size_t)n_slots, cudaMemcpyHostToDevice, g->stream));
 }
 
+// B200_DRY_RUN: plan the graph, account the launches, check that every node is one supports_op accepted, zero the outputs
+static const char *step_kind_name(int k) {
+    static const char *names[] = {"NODE", "RMS_MUL", "SILU_MUL", "GEMV", "ROPE_KV", "AR_ADD", "MOE_ROUTER"};
+    return k >= 0 && k < (int)(sizeof(names) / sizeof(names[0])) ? names[k] : "?";
+}
+static void dry_compute(GraphExec *g, const ggml_cgraph *cg) {
+    plan_steps(g, cg);
+    static const bool dump = getenv("B200_PLAN_DUMP") != nullptr;
+    for (int i = 0; i < cg->n_nodes; i++) {
+        const ggml_tensor *t = cg->nodes[i];
+        if (!op_supported(g->device, t)) {
+            fprintf(stderr, "B200 dry run: node %d (%s, op %d) reached graph_compute but supports_op rejects it\n", i, t->name, (int)t->op);
+            backend_abort("graph_compute", "unsupported node");
+        }
+        if (!is_view_op(t->op) && t->data && !(t->buffer && buft_is_b200_split(t->buffer->buft))) memset(t->data, 0, nbytes(t));
+    }
+    int64_t launches = 0;
+    for (const Step &s : g->steps) {
+        int64_t l = 1;
+        if (s.kind == STEP_NODE && s.n->op == GGML_OP_MUL_MAT && s.n->src[0] && is_quantized(s.n->src[0]->type) && s.n->src[1]->ne[1] > 8) l = 1;
+        launches += l;
+        if (dump) {
+            fprintf(stderr, "  step %-10s %-24s", step_kind_name(s.kind), s.n ? s.n->name : "");
+            for (const ggml_tensor *m : s.group) fprintf(stderr, " +%s", m->name);
+            if (s.n2) fprintf(stderr, " n2=%s", s.n2->name);
+            if (s.silu_mul) fprintf(stderr, " silu_mul=%s", s.silu_mul->name);
+            for (const ggml_tensor *ad : s.adds) if (ad) fprintf(stderr, " add=%s", ad->name);
+            fprintf(stderr, "\n");
+        }
+    }
+    if (dump) fprintf(stderr, "B200 dry run: graph of %d nodes -> %zu steps\n", cg->n_nodes, g->steps.size());
+    g_stat_launches += launches;
+    g_stat_replays++;
+}
+
 enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cg) {
     if (cg->n_nodes == 0) return GGML_STATUS_SUCCESS;
     const int n_slots = count_cpy(cg);
@@ -632,6 +680,7 @@ enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cg) {
         const ggml_tensor *w = cg->nodes[i]->src[0];
         has_split = cg->nodes[i]->op == GGML_OP_MUL_MAT && w && w->buffer && buft_is_b200_split(w->buffer->buft);
     }
+    if (g_dry) { dry_compute(g, cg); return GGML_STATUS_SUCCESS; }
     const bool use_graph = g_use_graphs && cg->n_nodes >= 16 && !has_split;
     if (!use_graph) {
         plan_steps(g, cg);

@@ -77,15 +77,21 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
                 default: return false;
             }
         }
-        case GGML_OP_ROPE:
-            return s0 && s1 && rows_contiguous_f32(s0) && rows_contiguous_f32(op) && s1->type == GGML_TYPE_I32 && (op->op_params[2] & ~GGML_ROPE_TYPE_NEOX) == 0 &&
-                   (!op->src[2] || op->src[2]->type == GGML_TYPE_F32);
+        case GGML_OP_ROPE: {
+            if (!s0 || !s1 || s1->type != GGML_TYPE_I32 || (op->op_params[2] & ~GGML_ROPE_TYPE_NEOX) != 0 || (op->src[2] && op->src[2]->type != GGML_TYPE_F32)) return false;
+            if (rows_contiguous_f32(s0) && rows_contiguous_f32(op)) return true;
+            // f16: the in-place K-shift over an f16 KV cache (src/llama.cpp:10181-10186; reference rope.cu f16 path)
+            return s0->type == GGML_TYPE_F16 && op->type == GGML_TYPE_F16 && s0->nb[0] == 2 && op->nb[0] == 2 && same_shape(s0, op) &&
+                   ((s0->nb[1] | s0->nb[2] | s0->nb[3] | op->nb[1] | op->nb[2] | op->nb[3]) & 3) == 0;
+        }
         case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
             if (!s0) return false;
             const int a = s0->type, b = op->type;
             if (a == GGML_TYPE_F32 && b == GGML_TYPE_Q8_0) return s0->nb[0] == 4 && s0->ne[0] % 32 == 0 && op->ne[0] % 32 == 0 && ((s0->nb[1] | s0->nb[2] | s0->nb[3]) & 15) == 0;
             if ((a == GGML_TYPE_F32 || a == GGML_TYPE_F16) && (b == GGML_TYPE_F32 || b == GGML_TYPE_F16)) return true;
             if (a == GGML_TYPE_I32 && b == GGML_TYPE_I32) return true;
+            // ggml_cast of a q8_0 K cache to f32 for the K-shift (src/llama.cpp:10165-10168; reference ggml-cuda.cu:3061)
+            if (a == GGML_TYPE_Q8_0 && b == GGML_TYPE_F32) return s0->nb[0] == 34 && s0->ne[0] % 32 == 0 && op->nb[0] == 4 && ((s0->nb[1] | s0->nb[2] | s0->nb[3]) & 1) == 0;
             return a == b && is_contiguous(s0) && is_contiguous(op);
         }
         case GGML_OP_GET_ROWS:

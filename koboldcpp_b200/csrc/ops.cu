@@ -181,8 +181,25 @@ __global__ void unary_kernel(int op, const float *__restrict__ x, float *__restr
 }
 
 // ------------------------------------------------------------------------------------------------ ROPE
+// T = float, or __half for the in-place K-shift over an f16 cache (build_k_shift, src/llama.cpp:10144-10192; reference rope.cu f16 path)
+template <typename T> struct RopeIO;
+template <> struct RopeIO<float> {
+    static __device__ __forceinline__ float2 ld2(const char *p) { return *(const float2 *)p; }
+    static __device__ __forceinline__ void st2(char *p, float2 v) { *(float2 *)p = v; }
+    static __device__ __forceinline__ float ld(const char *p) { return *(const float *)p; }
+    static __device__ __forceinline__ void st(char *p, float v) { *(float *)p = v; }
+};
+template <> struct RopeIO<__half> {
+    static __device__ __forceinline__ float2 ld2(const char *p) { return __half22float2(*(const __half2 *)p); }
+    static __device__ __forceinline__ void st2(char *p, float2 v) { *(__half2 *)p = __floats2half2_rn(v.x, v.y); }
+    static __device__ __forceinline__ float ld(const char *p) { return __half2float(*(const __half *)p); }
+    static __device__ __forceinline__ void st(char *p, float v) { *(__half *)p = __float2half_rn(v); }
+};
+template <typename T>
 __global__ void rope_kernel(TD x, const int32_t *__restrict__ pos, const float *__restrict__ ff, TD dst, RopeDev rp) {
     // one thread per (pair, head, token)
+    constexpr int ES = (int)sizeof(T);
+    using IO = RopeIO<T>;
     const int64_t half = x.ne[0] / 2;
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t total = half * x.ne[1] * x.ne[2] * x.ne[3];
@@ -192,7 +209,7 @@ __global__ void rope_kernel(TD x, const int32_t *__restrict__ pos, const float *
     char *ds = dst.data + i1 * dst.nb[1] + i2 * dst.nb[2] + i3 * dst.nb[3];
     const int64_t i0 = 2 * ip;
     if (i0 >= rp.n_dims) {  // pass-through tail (ggml.c:14386-14392)
-        *(float2 *)(ds + i0 * 4) = *(const float2 *)(xs + i0 * 4);
+        IO::st2(ds + i0 * ES, IO::ld2(xs + i0 * ES));
         return;
     }
     // theta = pos * theta_scale^(i0/2) / freq_factor; YaRN mix (rope_yarn, ggml.c:14223-14240)
@@ -210,12 +227,12 @@ __global__ void rope_kernel(TD x, const int32_t *__restrict__ pos, const float *
     sn *= mscale;
     cs *= mscale;
     if (!rp.neox) {
-        const float2 v = *(const float2 *)(xs + i0 * 4);
-        *(float2 *)(ds + i0 * 4) = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
+        const float2 v = IO::ld2(xs + i0 * ES);
+        IO::st2(ds + i0 * ES, make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs));
     } else {
-        const float x0 = *(const float *)(xs + ip * 4), x1 = *(const float *)(xs + (ip + rp.n_dims / 2) * 4);
-        *(float *)(ds + ip * 4) = x0 * cs - x1 * sn;
-        *(float *)(ds + (ip + rp.n_dims / 2) * 4) = x0 * sn + x1 * cs;
+        const float x0 = IO::ld(xs + ip * ES), x1 = IO::ld(xs + (ip + rp.n_dims / 2) * ES);
+        IO::st(ds + ip * ES, x0 * cs - x1 * sn);
+        IO::st(ds + (ip + rp.n_dims / 2) * ES, x0 * sn + x1 * cs);
     }
 }
 
@@ -279,6 +296,20 @@ __global__ void cpy_f32_q8_0_kernel(TD src, TD dst, int64_t nblocks, char *const
     o16[0] = (unsigned short)(q0 | (q1 << 8));
     o16[1] = (unsigned short)(q2 | (q3 << 8));
     if (part == 0) *reinterpret_cast<__half *>(out) = __float2half_rn(d);
+}
+
+// q8_0 -> f32 (ggml_cast of a quantised K cache before the K-shift RoPE, src/llama.cpp:10165-10168; reference cpy.cu q8_0->f32):
+// one thread per element of the linear element order; dequantize_row_q8_0 arithmetic (d * q, ggml-quants.c:1617-1632)
+__global__ void cpy_q8_0_f32_kernel(TD src, TD dst, int64_t n) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int64_t s0 = i % src.ne[0], s1 = (i / src.ne[0]) % src.ne[1], s2 = (i / (src.ne[0] * src.ne[1])) % src.ne[2],
+                  s3 = i / (src.ne[0] * src.ne[1] * src.ne[2]);
+    const int64_t d0 = i % dst.ne[0], d1 = (i / dst.ne[0]) % dst.ne[1], d2 = (i / (dst.ne[0] * dst.ne[1])) % dst.ne[2],
+                  d3 = i / (dst.ne[0] * dst.ne[1] * dst.ne[2]);
+    const unsigned char *b = (const unsigned char *)(src.data + (s0 >> 5) * Q8_0_BYTES + s1 * src.nb[1] + s2 * src.nb[2] + s3 * src.nb[3]);
+    const float d = h2f(*reinterpret_cast<const unsigned short *>(b));
+    *(float *)(dst.data + d0 * dst.nb[0] + d1 * dst.nb[1] + d2 * dst.nb[2] + d3 * dst.nb[3]) = __fmul_rn((float)(signed char)b[2 + (s0 & 31)], d);
 }
 
 // ------------------------------------------------------------------------------------------------ GET_ROWS
@@ -587,8 +618,11 @@ extern "C" int b200_op_unary(int op, const b200_tensor *x, const b200_tensor *ds
 extern "C" int b200_op_rope(const b200_tensor *x, const int32_t *pos, const float *freq_factors, const b200_tensor *dst,
                             const b200_rope_params *rp, b200_stream_t stream) {
     REQUIRE(x && dst && pos && rp && x->data && dst->data, B200_ERR_INVALID, "b200_op_rope: NULL argument");
-    REQUIRE(x->type == B200_TYPE_F32 && dst->type == B200_TYPE_F32 && x->nb[0] == 4 && dst->nb[0] == 4 && same_shape(x, dst), B200_ERR_UNSUPPORTED,
-            "b200_op_rope: f32 only");
+    const bool f16 = x->type == B200_TYPE_F16;
+    REQUIRE((x->type == B200_TYPE_F32 || f16) && dst->type == x->type && x->nb[0] == (f16 ? 2u : 4u) && dst->nb[0] == x->nb[0] && same_shape(x, dst),
+            B200_ERR_UNSUPPORTED, "b200_op_rope: f32 or f16, same type in and out");
+    REQUIRE(!f16 || ((((uintptr_t)x->data | (uintptr_t)dst->data | x->nb[1] | x->nb[2] | x->nb[3] | dst->nb[1] | dst->nb[2] | dst->nb[3]) & 3) == 0), B200_ERR_UNSUPPORTED,
+            "b200_op_rope: f16 rows must be 4-byte aligned");
     REQUIRE(rp->n_dims > 0 && rp->n_dims % 2 == 0 && rp->n_dims <= x->ne[0] && x->ne[0] % 2 == 0, B200_ERR_INVALID, "b200_op_rope: bad n_dims");
     REQUIRE((rp->mode & ~2) == 0, B200_ERR_UNSUPPORTED, "b200_op_rope: mode %d not supported", rp->mode);
     RopeDev d;
@@ -605,7 +639,8 @@ extern "C" int b200_op_rope(const b200_tensor *x, const int32_t *pos, const floa
     d.corr1 = end < rp->n_dims - 1 ? end : (float)(rp->n_dims - 1);
     const int64_t total = x->ne[0] / 2 * x->ne[1] * x->ne[2] * x->ne[3];
     if (total == 0) return B200_OK;
-    rope_kernel<<<grid1d(total, 256), 256, 0, (cudaStream_t)stream>>>(td(x), pos, freq_factors, td(dst), d);
+    if (f16) rope_kernel<__half><<<grid1d(total, 256), 256, 0, (cudaStream_t)stream>>>(td(x), pos, freq_factors, td(dst), d);
+    else rope_kernel<float><<<grid1d(total, 256), 256, 0, (cudaStream_t)stream>>>(td(x), pos, freq_factors, td(dst), d);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }
@@ -680,6 +715,10 @@ extern "C" int b200_op_cpy_indirect(const b200_tensor *src, const b200_tensor *d
                 B200_ERR_UNSUPPORTED, "b200_op_cpy: f32->q8_0 needs contiguous 16-byte aligned source rows of a multiple of 32 values");
         const int64_t nblk = n / 32;
         cpy_f32_q8_0_kernel<<<grid1d(nblk * 8, 256), 256, 0, st>>>(td(src), td(dst), nblk, ind);
+    } else if (s == B200_TYPE_Q8_0 && d == B200_TYPE_F32) {
+        REQUIRE(src->nb[0] == Q8_0_BYTES && src->ne[0] % 32 == 0 && dst->nb[0] == 4 && !ind && ((src->nb[1] | src->nb[2] | src->nb[3] | (uintptr_t)src->data) & 1) == 0,
+                B200_ERR_UNSUPPORTED, "b200_op_cpy: q8_0->f32 needs whole 2-byte aligned source blocks");
+        cpy_q8_0_f32_kernel<<<g, 256, 0, st>>>(td(src), td(dst), n);
     } else {
         REQUIRE(false, B200_ERR_UNSUPPORTED, "b200_op_cpy: type pair (%d -> %d) not supported", s, d);
     }
