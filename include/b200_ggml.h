@@ -61,6 +61,18 @@ B200_API const char *b200_version(void);
  * prefetch then overlaps the tail of its producer.  Off by default; the ggml backend turns it on for its graphs. */
 B200_API void b200_set_pdl(int enabled);
 
+/* Cross-kernel L2 prefetch.  Decode is a chain of dependent, HBM-bound kernels; between two of them (tail of one, launch and
+ * activation phase of the next) HBM would idle.  Weights and the KV cache do not depend on the chain, so a kernel can ask the
+ * TMA engine to pull the NEXT kernel's operands into the 126 MB L2 (cp.async.bulk.prefetch.L2, SASS UBLKPF) once it has issued
+ * its own loads.  The plan set here is consumed by the next launch of b200_mul_mat_vec_q*, b200_mul_mat_id_vec_q,
+ * b200_flash_attn_ext or b200_op_rope_kv_store on the calling thread (and cleared).  Regions: 16-byte aligned, readable,
+ * at most 4, each below 4 GiB.  Purely a performance hint: results never depend on it. */
+typedef struct {
+    const void *ptr[4];
+    uint32_t    bytes[4];
+} b200_prefetch;
+B200_API void b200_set_next_prefetch(const b200_prefetch *plan);
+
 /* ---- device plumbing (so ctypes / cgo / JNI hosts need no CUDA binding of their own) ------------
  * replaces: ggml_backend_cuda_get_device_count / cudaMalloc / cudaMemcpyAsync call sites in
  * ggml/src/ggml-cuda.cu:3262-3270, 546-560, 471-485 */
@@ -137,7 +149,7 @@ B200_API int b200_mul_mat_vec_q_multi(int type, const b200_gemv_job *jobs, int n
 /* The same launch with the neighbouring graph nodes folded in (what llm_build_norm + llm_build_lora_mm + ggml_add emit around
  * every matmul of a layer, src/llama.cpp:9254-9287, 10479-10560):
  *   norm_weight != NULL: X is replaced by RMS_NORM(X, norm_eps) * norm_weight while it is quantised (X rows of K floats; the
- *                        normalised activations are never written to memory);
+ *                        normalised activations are only written when norm_out / norm_mul_out ask for them);
  *   residual[j] != NULL: dst_j = W_j . X + residual[j]   (same layout as dst_j; may alias it). */
 typedef struct {
     const float *norm_weight; /* f32 [K], 16-byte aligned, or NULL */
@@ -146,78 +158,19 @@ typedef struct {
                                  jobs[0].dst[m] = silu(gate[m] . x) * (up[m] . x) -- UNARY(SILU) + MUL of llm_build_ffn
                                  (src/llama.cpp:9289-9414) folded into the epilogue; jobs[1].dst is not written */
     const float *residual[B200_GEMV_MAX_JOBS];
+    /* The folded nodes remain graph nodes: another split of ggml_backend_sched may read them (the reference backend never
+     * elides a node's output).  Each of these is optional (NULL = do not store) and costs one extra store per value:
+     *   raw_dst[j]:   with residual[j]: the un-added product W_j . X (the MUL_MAT node), same layout as dst_j;
+     *   norm_out / norm_mul_out: with norm_weight: RMS_NORM(X) and RMS_NORM(X) * norm_weight, N rows of K floats
+     *                 (row stride K), stored by one CTA of the launch;
+     *   gate_out / up_out / silu_out: with silu_pair: gate . x, up . x and silu(gate . x), M floats each.
+     * A destination that aliases a later one in this list (ggml-alloc in-place reuse) must be passed as NULL. */
+    float       *raw_dst[B200_GEMV_MAX_JOBS];
+    float       *norm_out, *norm_mul_out;
+    float       *gate_out, *up_out, *silu_out;
 } b200_gemv_fuse;
 B200_API int b200_mul_mat_vec_q_fused(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes, int64_t x_stride,
                                       int64_t dst_stride, int64_t K, int64_t N, const b200_gemv_fuse *fuse, b200_stream_t stream);
-
-/* ---- decode chain: the dependent GEMVs of a layer (and the small ops between them) in ONE persistent launch ---------------
- * replaces: the per-node launch sequence of ggml_backend_cuda_graph_compute for batch-1 decode (ggml-cuda.cu:2508-2823), i.e.
- * quantize_q8_1 + mul_mat_vec_q per matmul plus rms_norm / add / silu / mul / rope / cpy launches between them.
- * One CTA per SM stays resident for the whole chain; phases are separated by grid barriers, and because weights do not depend
- * on activations every warp keeps its TMA weight ring filling ACROSS phase boundaries, so HBM streaming does not stop while
- * activations are exchanged.  N = 1 (one token).  Phases run in order:
- *   B200_CHAIN_GEMV:  dst_j = W_j . x (+ residual_j);  x = X, or RMS_NORM(X, eps) * norm_weight when norm_weight != NULL;
- *                     jobs may mix weight types.  silu_pair != 0: jobs[0] = gate, jobs[1] = up (same M):
- *                     jobs[0].dst[m] = silu(gate[m] . x) * (up[m] . x)   (UNARY(SILU) + MUL of llm_build_ffn folded in);
- *                     M of every job must be even: a warp streams two rows at a time and shares the activation registers;
- *                     sumsq_out != NULL: every CTA stores the sum of squares of the jobs[0] outputs it produced at
- *                     sumsq_out[blockIdx.x] (b200_decode_chain_sumsq_slots() floats, no initialisation needed);
- *                     sumsq_in != NULL (with norm_weight): sum(X^2) is taken from those partial sums of the producing phase
- *                     instead of a second pass over X;
- *   B200_CHAIN_ROPE_KV: the b200_op_rope_kv_store work (include/b200_ggml_ops.h) for T = 1;
- *   B200_CHAIN_ATTN:  FLASH_ATTN_EXT for one query token (N = 1): the (kv-head, 16-row tile) space is cut into one contiguous
- *                     range per CTA, K/V rows go straight from HBM to registers, the last CTA of a kv-head merges its partial
- *                     results (ticket).  Same layouts and semantics as b200_flash_attn_ext below. */
-enum { B200_CHAIN_GEMV = 0, B200_CHAIN_ROPE_KV = 1, B200_CHAIN_ATTN = 2 };
-#define B200_CHAIN_MAX_PHASES 12 /* b200_decode_chain: the program travels as kernel parameters */
-#define B200_CHAIN_MAX_JOBS 4
-typedef struct {
-    const void  *W;
-    float       *dst;
-    const float *residual; /* or NULL */
-    size_t       w_row_bytes;
-    int32_t      M, type;
-} b200_chain_job;
-typedef struct {
-    int32_t kind, n_jobs, K, silu_pair;
-    float   norm_eps;
-    int32_t _pad;
-    const float *X, *norm_weight;
-    float       *sumsq_out;
-    const float *sumsq_in;
-    union {
-        b200_chain_job jobs[B200_CHAIN_MAX_JOBS];
-        struct { /* ROPE_KV: q [D, H], k [D, HK], v [D*HK] f32 contiguous; cache rows at *k_slot / *v_slot (or k_cache / v_cache) */
-            const float *q, *k, *v;
-            float *q_out, *k_out;
-            void *k_cache, *v_cache;
-            void *const *k_slot, *const *v_slot;
-            const int32_t *pos;
-            const float *freq_factors;
-            int32_t D, H, HK, kv_type;
-            int32_t n_dims, mode, n_ctx_orig;
-            float freq_base, freq_scale, ext_factor, attn_factor, beta_fast, beta_slow;
-        } rope;
-        struct { /* ATTN: q f32 [D, H] contiguous; k/v [D, n_kv, HK] cache views (byte strides); mask f16 [n_kv] or NULL; dst f32 [D, H] */
-            const float *q;
-            const void *k, *v, *mask;
-            float *dst;
-            void *workspace; /* b200_decode_chain_attn_workspace_bytes(); its first 4*HK bytes are zero between launches */
-            size_t k_nb1, k_nb2, v_nb1, v_nb2;
-            int32_t D, H, HK, n_kv, kv_type;
-            float scale, max_bias, logit_softcap;
-        } attn;
-    } u;
-} b200_chain_phase;
-/* barrier: 4 bytes of device memory that are ZERO when the kernel starts (the kernel leaves them zero again). */
-B200_API int b200_decode_chain(const b200_chain_phase *phases, int n_phases, unsigned *barrier, b200_stream_t stream);
-/* Long programs (a whole token): compile the phases on the host into a blob of b200_decode_chain_program_bytes() bytes,
- * copy the blob to device memory (any way the caller likes), and launch it from there. */
-B200_API size_t b200_decode_chain_program_bytes(const b200_chain_phase *phases, int n_phases);
-B200_API int b200_decode_chain_compile(const b200_chain_phase *phases, int n_phases, void *program_host);
-B200_API int b200_decode_chain_run(const void *program_dev, const void *geometry /* first 16 bytes of the host blob */, unsigned *barrier, b200_stream_t stream);
-B200_API int b200_decode_chain_sumsq_slots(void);
-B200_API size_t b200_decode_chain_attn_workspace_bytes(int32_t D, int32_t H, int32_t HK);
 
 /* ---- (a9) MUL_MAT_ID (expert GEMV), ids read on the device ------------------------------------------
  * replaces: ggml_cuda_mul_mat_id incl. its cudaMemcpyAsync(ids)+cudaStreamSynchronize and the
@@ -231,6 +184,19 @@ B200_API int b200_mul_mat_id_vec_q(int type, const void *as, size_t w_row_bytes,
                                    const int32_t *ids, int64_t ids_stride, const float *b, int64_t b_stride_row, int64_t b_stride_tok,
                                    float *dst, int64_t dst_stride_row, int64_t dst_stride_tok,
                                    int64_t K, int64_t M, int64_t n_used, int64_t n_b_rows, int64_t T, b200_stream_t stream);
+
+/* MUL_MAT_ID for batches (prompt processing of a mixture-of-experts model), same tensor layout as b200_mul_mat_id_vec_q:
+ * replaces the batch branch of ggml_cuda_mul_mat_id (ggml/src/ggml-cuda.cu:2066-2139: ids -> host + stream sync, then per expert
+ * k_copy_src1_to_contiguous / mul_mat / k_copy_dst_from_contiguous, :1954-2001).  The (token, slot) pairs are grouped by expert
+ * ON THE DEVICE (count, prefix sum, sorted row lists, tile table -- no host synchronisation, CUDA-graph capturable), the selected
+ * activation rows are gathered as bf16, and ONE grouped tcgen05 launch computes every expert's tile list and scatters the f32
+ * results to dst.  K must be a multiple of 256, n_expert <= 256, n_used * T <= 65535.  Rows whose id is outside [0, n_expert)
+ * are skipped.  workspace: b200_mul_mat_id_q_workspace_bytes() bytes, 256-byte aligned. */
+B200_API size_t b200_mul_mat_id_q_workspace_bytes(int type, int64_t K, int64_t M, int64_t n_used, int64_t T, int32_t n_expert);
+B200_API int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, size_t expert_bytes, int32_t n_expert,
+                               const int32_t *ids, int64_t ids_stride, const float *b, int64_t b_stride_row, int64_t b_stride_tok,
+                               float *dst, int64_t dst_stride_row, int64_t dst_stride_tok, int64_t K, int64_t M, int64_t n_used,
+                               int64_t n_b_rows, int64_t T, void *workspace, size_t workspace_bytes, b200_stream_t stream);
 
 /* ---- (a7) prefill GEMM on tcgen05: dst[n][m] = sum_k W[m][k] * X[n][k], any N ------------------------
  * replaces: ggml_cuda_op_mul_mat_q + mul_mat_q<type,...> + stream-k fixup + quantize_mmq_q8_1 and the cuBLAS

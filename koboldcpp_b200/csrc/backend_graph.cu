@@ -12,7 +12,9 @@
 //             moving KV-cache write position does not invalidate the graph.
 //   * replay: cudaGraphLaunch.
 // There is no CPU fallback: a node supports_op said no to never reaches this file, and anything else aborts like the reference.
+#include <algorithm>
 #include <unordered_map>
+#include <unordered_set>
 
 #include "../../include/b200_comm.h"
 #include "../../include/b200_ggml_ops.h"
@@ -31,7 +33,9 @@ struct Step {
     const ggml_tensor *silu_mul = nullptr;   // STEP_GEMV of (gate, up): the MUL node of SILU(gate) * up folded into the epilogue
     int gate_idx = 0;                   // ... and which member of `group` is the gate
     int slot = -1, slot2 = -1;          // CPY nodes: index into the slot table, else -1
-    Step() : kind(STEP_NODE), n(nullptr), n2(nullptr) {}
+    bool store_norm = false, store_norm_mul = false;  // STEP_GEMV with a folded norm: this launch also stores the RMS_NORM / MUL values
+    b200_prefetch pf;                   // operands of the next streaming step(s), pulled into L2 by this step's kernel
+    Step() : kind(STEP_NODE), n(nullptr), n2(nullptr) { memset(&pf, 0, sizeof(pf)); }
 };
 
 struct CachedGraph {
@@ -265,7 +269,13 @@ static bool match_moe_router(const GraphInfo &gi, int i, const std::vector<char>
 }
 
 // Lower cgraph -> Steps.  `done[i]` marks nodes absorbed by a fused step.
+static void plan_prefetch(std::vector<Step> &steps);
+static void plan_steps_inner(GraphExec *g, const ggml_cgraph *cg);
 static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
+    plan_steps_inner(g, cg);
+    plan_prefetch(g->steps);
+}
+static void plan_steps_inner(GraphExec *g, const ggml_cgraph *cg) {
     std::vector<Step> &steps = g->steps;
     steps.clear();
     const int n = cg->n_nodes;
@@ -288,6 +298,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
     std::unordered_map<const ggml_tensor *, const ggml_tensor *> norm_mul_of;  // activation tensor (MUL node) -> its RMS_NORM node
     std::unordered_map<const ggml_tensor *, const ggml_tensor *> add_of;       // MUL_MAT node -> the ADD node folded into it
     std::unordered_map<int, Step> deferred;                                    // position -> step to emit there
+    std::unordered_set<const ggml_tensor *> norm_stored;                       // folded activations whose values a GEMV step already stores
 
     for (int i = 0; i < n; i++) {
         auto df = deferred.find(i);
@@ -322,6 +333,9 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                 }
                 if (readers == gi.uses(b)) break;
             }
+            // the folded nodes' values are still stored (by the first GEMV): they must not land on the bytes the GEMVs read
+            if (ranges_overlap(a->data, nbytes(a), a->src[0]->data, nbytes(a->src[0])) || ranges_overlap(b->data, nbytes(b), a->src[0]->data, nbytes(a->src[0])) ||
+                (((uintptr_t)a->data | (uintptr_t)b->data) & 15) || !is_contiguous(b)) all_gemv = false;
             if (all_gemv && readers == gi.uses(b)) {
                 norm_mul_of[b] = a;
                 done[j] = 1;
@@ -421,7 +435,9 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                     if (!same_shape(mn, gt) || !same_shape(up, gt) || !is_contiguous(mn) || !is_contiguous(gt) || mn->type != GGML_TYPE_F32) continue;
                     const int ps = gi.pos(sn), pm = gi.pos(mn);
                     if (ps < 0 || pm < 0 || done[ps] || done[pm]) continue;
-                    std::vector<int> mem = {ps, pm};
+                    // the two matmuls are part of the fused kernel: ggml-alloc usually computes SILU in place over the gate result
+                    std::vector<int> mem = {gi.pos(gt), gi.pos(up), ps, pm};
+                    std::sort(mem.begin(), mem.end());
                     if (!can_gather(gi, mem, i, done)) continue;
                     s.silu_mul = mn;
                     s.gate_idx = gi_;
@@ -432,6 +448,17 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             s.kind = STEP_GEMV;
             auto nm = norm_mul_of.find(a->src[1]);
             s.n2 = nm == norm_mul_of.end() ? nullptr : nm->second;  // RMS_NORM node folded into the prologue
+            if (s.n2 && norm_stored.insert(a->src[1]).second) {
+                // first reader: it also stores the MUL value, and the RMS_NORM value unless its bytes were legitimately reused
+                // between the MUL node and this position (it has no reader left then) or alias the MUL output (in-place)
+                s.store_norm_mul = true;
+                s.store_norm = s.n2->data != a->src[1]->data;
+                for (int k2 = gi.pos(a->src[1]) + 1; k2 < i && s.store_norm; k2++) {
+                    const ggml_tensor *t = cg->nodes[k2];
+                    if (!is_view_op(t->op) && t->data && ranges_overlap(t->data, nbytes(t), s.n2->data, nbytes(s.n2))) s.store_norm = false;
+                }
+                if (ranges_overlap(s.n2->data, nbytes(s.n2), a->src[1]->data, nbytes(a->src[1]))) s.store_norm = false;
+            }
             for (const ggml_tensor *mm : s.group) {
                 auto ad = add_of.find(mm);
                 s.adds.push_back(ad == add_of.end() ? nullptr : ad->second);
@@ -440,6 +467,64 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             continue;
         }
         steps.push_back(s);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ cross-kernel L2 prefetch
+// Every step that streams weights / KV rows is a prefetch TARGET (its operand byte ranges) and, if its kernel can carry a plan, an
+// ISSUER for the next target: the issuing kernel asks the TMA engine to pull those ranges into L2 after its own loads are out, so
+// HBM does not idle through kernel tails, launch gaps and activation prologues (include/b200_ggml.h: b200_set_next_prefetch).
+static bool quant_mm_node(const ggml_tensor *t) {
+    return t->op == GGML_OP_MUL_MAT && t->src[0] && is_quantized(t->src[0]->type) && !(t->src[0]->buffer && buft_is_b200_split(t->src[0]->buffer->buft));
+}
+static bool step_issues_prefetch(const Step &s) {
+    if (s.kind == STEP_GEMV || s.kind == STEP_ROPE_KV) return true;
+    if (s.kind != STEP_NODE) return false;
+    if (quant_mm_node(s.n)) return s.n->src[1]->ne[1] <= 8;
+    return s.n->op == GGML_OP_MUL_MAT_ID ? s.n->src[2]->ne[0] * s.n->src[2]->ne[1] <= B200_GEMV_MAX_JOBS : s.n->op == GGML_OP_FLASH_ATTN_EXT;
+}
+struct PfRegion { const char *p; size_t n; size_t taken; };
+static void step_regions(const Step &s, std::vector<PfRegion> &out) {
+    out.clear();
+    auto add = [&](const void *p, size_t n) { if (p && n >= 4096) out.push_back(PfRegion{(const char *)p, n, 0}); };
+    if (s.kind == STEP_GEMV) { for (const ggml_tensor *m : s.group) add(m->src[0]->data, nbytes(m->src[0])); return; }
+    if (s.kind != STEP_NODE) return;
+    if (quant_mm_node(s.n)) { add(s.n->src[0]->data, nbytes(s.n->src[0])); return; }
+    if (s.n->op == GGML_OP_FLASH_ATTN_EXT) {
+        for (int q = 1; q <= 2; q++) {
+            const ggml_tensor *kv = s.n->src[q];
+            // [D, n_kv, n_head_kv] view of a cache whose row holds all heads (nb2 < nb1): the rows form one contiguous range
+            const size_t n = kv->nb[2] < kv->nb[1] ? (size_t)kv->ne[1] * kv->nb[1] : nbytes(kv);
+            add(kv->data, n);
+        }
+    }
+}
+static void plan_prefetch(std::vector<Step> &steps) {
+    static const size_t budget_mb = getenv("B200_PF_MB") ? (size_t)atoi(getenv("B200_PF_MB")) : 40;
+    const size_t n = steps.size();
+    if (budget_mb == 0 || n < 2) return;
+    std::vector<std::vector<PfRegion>> regs(n);
+    for (size_t i = 0; i < n; i++) step_regions(steps[i], regs[i]);
+    for (size_t i = 0; i < n; i++) {
+        if (!step_issues_prefetch(steps[i])) continue;
+        // the next target (cyclic: the first kernels of the next token are fed by the last kernels of this one)
+        size_t t = i;
+        for (size_t d = 1; d < n; d++) { const size_t c = (i + d) % n; if (!regs[c].empty()) { t = c; break; } }
+        if (t == i) continue;
+        size_t budget = budget_mb << 20;
+        int slot = 0;
+        for (PfRegion &r : regs[t]) {
+            if (slot >= 4 || budget == 0) break;
+            const size_t left = r.n - r.taken;
+            if (left == 0) continue;
+            size_t take = left < budget ? left : budget;
+            if (take > 0xfffffff0u) take = 0xfffffff0u;
+            steps[i].pf.ptr[slot] = r.p + r.taken;
+            steps[i].pf.bytes[slot] = (uint32_t)take;
+            r.taken += take;
+            budget -= take;
+            slot++;
+        }
     }
 }
 
@@ -478,6 +563,7 @@ static uint64_t graph_key(const ggml_cgraph *cg) {
 
 // ------------------------------------------------------------------------------------------------ execution
 static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
+    if (s.pf.bytes[0] && step_issues_prefetch(s)) b200_set_next_prefetch(&s.pf);
     switch (s.kind) {
         case STEP_NODE:
             run_node(x, s.n, s.slot >= 0 ? (void *const *)(g->slots_dev + s.slot) : nullptr);
@@ -542,6 +628,21 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
                     jobs[q].dst = (float *)s.silu_mul->data;
                 }
                 fuse.silu_pair = 1;
+                {   // the matmul / SILU nodes keep their values unless ggml-alloc placed a later node of the group on the same bytes
+                    const ggml_tensor *gt = s.group[s.gate_idx], *up = s.group[1 - s.gate_idx], *mn = s.silu_mul;
+                    const ggml_tensor *sn = mn->src[0] == up ? mn->src[1] : mn->src[0];
+                    auto clash = [&](const ggml_tensor *t, std::initializer_list<const ggml_tensor *> later) {
+                        for (const ggml_tensor *o : later) if (ranges_overlap(t->data, nbytes(t), o->data, nbytes(o))) return true;
+                        return false;
+                    };
+                    fuse.gate_out = clash(gt, {up, sn, mn}) ? nullptr : (float *)gt->data;
+                    fuse.up_out = clash(up, {sn, mn}) ? nullptr : (float *)up->data;
+                    fuse.silu_out = clash(sn, {mn}) ? nullptr : (float *)sn->data;
+                }
+                if (s.n2) {
+                    fuse.norm_out = s.store_norm ? (float *)s.n2->data : nullptr;
+                    fuse.norm_mul_out = s.store_norm_mul ? (float *)act->data : nullptr;
+                }
                 B200_CHECK_RC(b200_mul_mat_vec_q_fused(a->src[0]->type, jobs, 2, a->src[0]->nb[1], x_stride, (int64_t)(a->nb[1] / 4), a->src[0]->ne[0], 1, &fuse, x.stream));
                 x.launches++;
                 return;
@@ -553,10 +654,15 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
                     const ggml_tensor *r = add->src[0] == m ? add->src[1] : add->src[0];
                     jobs[nj].dst = (float *)add->data;
                     fuse.residual[nj] = (const float *)r->data;
+                    fuse.raw_dst[nj] = ranges_overlap(m->data, nbytes(m), add->data, nbytes(add)) ? nullptr : (float *)m->data;
                 } else {
                     jobs[nj].dst = (float *)m->data;
                 }
                 nj++;
+            }
+            if (s.n2) {
+                fuse.norm_out = s.store_norm ? (float *)s.n2->data : nullptr;
+                fuse.norm_mul_out = s.store_norm_mul ? (float *)act->data : nullptr;
             }
             B200_CHECK_RC(b200_mul_mat_vec_q_fused(a->src[0]->type, jobs, nj, a->src[0]->nb[1], x_stride, (int64_t)(a->nb[1] / 4), a->src[0]->ne[0], act->ne[1],
                                                    &fuse, x.stream));
@@ -583,7 +689,7 @@ static void ensure_workspaces(GraphExec *g, const ggml_cgraph *cg, int n_slots) 
     for (int i = 0; i < cg->n_nodes; i++) {
         const ggml_tensor *t = cg->nodes[i];
         if (t->op == GGML_OP_FLASH_ATTN_EXT) { const size_t b = node_fa_workspace(t); if (b > fa) fa = b; }
-        if (t->op == GGML_OP_MUL_MAT) { const size_t b = node_scratch_bytes(t); if (b > sc) sc = b; }
+        if (t->op == GGML_OP_MUL_MAT || t->op == GGML_OP_MUL_MAT_ID) { const size_t b = node_scratch_bytes(t); if (b > sc) sc = b; }
     }
     // growing a workspace moves it: every captured graph has the old pointer baked in
     if (fa > g->fa_ws_bytes) {
@@ -656,6 +762,10 @@ static void dry_compute(GraphExec *g, const ggml_cgraph *cg) {
             if (s.n2) fprintf(stderr, " n2=%s", s.n2->name);
             if (s.silu_mul) fprintf(stderr, " silu_mul=%s", s.silu_mul->name);
             for (const ggml_tensor *ad : s.adds) if (ad) fprintf(stderr, " add=%s", ad->name);
+            size_t pfb = 0;
+            for (int q = 0; q < 4; q++) pfb += s.pf.bytes[q];
+            if (pfb) fprintf(stderr, " prefetch=%.1fMB", pfb / 1048576.0);
+            if (s.store_norm_mul) fprintf(stderr, " stores_norm%s", s.store_norm ? "+rms" : "");
             fprintf(stderr, "\n");
         }
     }

@@ -49,7 +49,10 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
             if (s1->nb[0] != 4 || ((s1->nb[1] | s1->nb[2]) & 15) || op->nb[0] != 4 || ids->nb[0] != 4 || (ids->nb[1] & 3)) return false;
             if (s0->ne[3] != 1 || s1->ne[3] != 1) return false;
             if ((s0->type == GGML_TYPE_Q4_K || s0->type == GGML_TYPE_Q5_K) && ((s0->nb[1] | s0->nb[2]) & 15)) return false;
-            return ids->ne[0] * ids->ne[1] <= B200_GEMV_MAX_JOBS;  // decode regime (T * n_used <= 16)
+            if (ids->ne[0] * ids->ne[1] <= B200_GEMV_MAX_JOBS) return true;  // decode regime (T * n_used <= 16): expert GEMV
+            // batches: device-side group-by-expert + one grouped tensor-core launch (b200_mul_mat_id_q)
+            return s0->ne[0] % 256 == 0 && s0->ne[2] <= 256 && ids->ne[0] * ids->ne[1] <= 65535 && ids->ne[2] == 1 && s1->ne[2] == ids->ne[1] &&
+                   (s1->ne[1] == 1 || s1->ne[1] == ids->ne[0]);
         }
         case GGML_OP_FLASH_ATTN_EXT: {
             const ggml_tensor *k = op->src[1], *v = op->src[2], *m = op->src[3];
@@ -233,6 +236,15 @@ static void run_mul_mat(ExecCtx &x, const ggml_tensor *n) {
 static void run_mul_mat_id(ExecCtx &x, const ggml_tensor *n) {
     const ggml_tensor *as = n->src[0], *b = n->src[1], *ids = n->src[2];
     // as [K, M, n_expert]; b [K, n_b_rows, T]; ids [n_used, T]; dst [M, n_used, T]   (ggml.c:5693-5729)
+    if (ids->ne[0] * ids->ne[1] > B200_GEMV_MAX_JOBS) {
+        const size_t need = b200_mul_mat_id_q_workspace_bytes(as->type, as->ne[0], as->ne[1], ids->ne[0], ids->ne[1], (int32_t)as->ne[2]);
+        if (need > x.scratch_bytes) backend_abort("mul_mat_id workspace", "workspace smaller than planned");
+        B200_CHECK_RC(b200_mul_mat_id_q(as->type, as->data, as->nb[1], as->nb[2], (int32_t)as->ne[2], (const int32_t *)ids->data, (int64_t)(ids->nb[1] / 4),
+                                        (const float *)b->data, (int64_t)(b->nb[1] / 4), (int64_t)(b->nb[2] / 4), (float *)n->data, (int64_t)(n->nb[1] / 4),
+                                        (int64_t)(n->nb[2] / 4), as->ne[0], as->ne[1], ids->ne[0], b->ne[1], ids->ne[1], x.scratch, x.scratch_bytes, x.stream));
+        x.launches += 3;
+        return;
+    }
     B200_CHECK_RC(b200_mul_mat_id_vec_q(as->type, as->data, as->nb[1], as->nb[2], (int32_t)as->ne[2], (const int32_t *)ids->data, (int64_t)(ids->nb[1] / 4),
                                         (const float *)b->data, (int64_t)(b->nb[1] / 4), (int64_t)(b->nb[2] / 4), (float *)n->data, (int64_t)(n->nb[1] / 4),
                                         (int64_t)(n->nb[2] / 4), as->ne[0], as->ne[1], ids->ne[0], b->ne[1], ids->ne[1], x.stream));
@@ -270,6 +282,8 @@ size_t node_fa_workspace(const ggml_tensor *n) {
 }
 
 size_t node_scratch_bytes(const ggml_tensor *n) {
+    if (n->op == GGML_OP_MUL_MAT_ID && n->src[0] && n->src[2] && n->src[2]->ne[0] * n->src[2]->ne[1] > B200_GEMV_MAX_JOBS)
+        return b200_mul_mat_id_q_workspace_bytes(n->src[0]->type, n->src[0]->ne[0], n->src[0]->ne[1], n->src[2]->ne[0], n->src[2]->ne[1], (int32_t)n->src[0]->ne[2]);
     if (n->op != GGML_OP_MUL_MAT || !n->src[0] || !n->src[1] || !is_quantized(n->src[0]->type) || n->src[1]->ne[1] <= 8) return 0;
     return b200_mul_mat_q_workspace_bytes(n->src[0]->type, n->src[0]->ne[0], n->src[0]->ne[1], n->src[1]->ne[1]);
 }

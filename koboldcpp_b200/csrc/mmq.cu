@@ -247,6 +247,11 @@ struct MmqParams {
     const __nv_bfloat16 *Xb;  // [n_pad][K]
     float *dst;
     int64_t dst_stride, K, M, N;
+    // grouped mode (MUL_MAT_ID batches, b200_mul_mat_id_q): blockIdx.y indexes a device-built tile table {n_tiles, (expert, first
+    // sorted row, end row) ...}; W advances by expert_bytes per expert; sorted row i is stored at dst[row_dst[i] + m]
+    const int *tile_tab;
+    const int *row_dst;
+    size_t expert_bytes;
 };
 
 template <int TYPE, int BN>
@@ -476,17 +481,26 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const void *tmap, int c0,
 
 struct alignas(64) TmapBytes { unsigned char b[128]; };  // CUtensorMap without pulling <cuda.h> into device code
 
-template <int TYPE, int BN>
+template <int TYPE, int BN, bool GROUPED = false>
 __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_constant__ TmapBytes tmB, const __grid_constant__ MmqParams p) {
     constexpr int A_BYTES = MQ_BM * MQ_BK * 2, B_BYTES = BN * MQ_BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
     constexpr int G256 = group256_bytes(TYPE);
+    int64_t n0 = (int64_t)blockIdx.y * BN, n_end = p.N;
+    const unsigned char *Wbase = p.W;
+    if constexpr (GROUPED) {  // uniform over the CTA: tiles past the table's end have nothing to do
+        if ((int)blockIdx.y >= __ldg(p.tile_tab)) return;
+        const int *te = p.tile_tab + 1 + 3 * blockIdx.y;
+        Wbase += (size_t)__ldg(te) * p.expert_bytes;
+        n0 = __ldg(te + 1);
+        n_end = __ldg(te + 2);
+    }
     extern __shared__ unsigned char smem_raw[];
     unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) unsigned long long full_bar[MQ2_STAGES], empty_bar[MQ2_STAGES], tmem_full_bar;
     __shared__ unsigned tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
-    const int64_t m0 = (int64_t)blockIdx.x * MQ_BM, n0 = (int64_t)blockIdx.y * BN;
+    const int64_t m0 = (int64_t)blockIdx.x * MQ_BM;
     const int nsb = (int)(p.K / 256), nkb = nsb * 4;
 
     if (tid == 0) {
@@ -503,7 +517,7 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
     if (warp < 4) {
         const int64_t m = m0 + tid;
         const bool row_ok = m < p.M;
-        const unsigned char *wrow = p.W + (size_t)(row_ok ? m : 0) * p.w_row_bytes;
+        const unsigned char *wrow = Wbase + (size_t)(row_ok ? m : 0) * p.w_row_bytes;
         const unsigned a_off = (unsigned)((tid >> 3) * 1024 + (tid & 7) * 128);
         // software pipeline: the raw bytes of group sb+1 are in flight (registers) while group sb is unpacked
         constexpr int NW = group256_words(TYPE);
@@ -576,7 +590,11 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
 #pragma unroll
                 for (int j = 0; j < 32; j++) {
                     const int64_t n = n0 + c0 + j;
-                    if (n < p.N) drow[n * p.dst_stride] = v[j];
+                    if constexpr (GROUPED) {
+                        if (n < n_end) drow[(int64_t)__ldg(p.row_dst + n)] = v[j];  // scatter: sorted row -> (token, slot)
+                    } else {
+                        if (n < n_end) drow[n * p.dst_stride] = v[j];
+                    }
                 }
             }
         }
@@ -649,15 +667,15 @@ static EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-template <int TYPE, int BN>
-static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st) {
+template <int TYPE, int BN, bool GROUPED = false>
+static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st, unsigned grid_y = 0) {
     constexpr size_t smem = (size_t)MQ2_STAGES * (MQ_BM * MQ_BK * 2 + BN * MQ_BK * 2) + 1024;
     static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
     int cur_dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&cur_dev));
     bool &attr_set = attr_set_dev[cur_dev & 15];
     if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc2_kernel<TYPE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmq_tc2_kernel<TYPE, BN, GROUPED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
     EncodeTiledFn enc = encode_tiled_fn();
@@ -670,8 +688,8 @@ static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st) {
     // CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 = 9, INTERLEAVE_NONE = 0, SWIZZLE_128B = 3, L2_PROMOTION_L2_256B = 3, FLOAT_OOB_FILL_NONE = 0
     const int rc = enc(&tm, 9, 2, (void *)p.Xb, gdim, gstr, box, estr, 0, 3, 3, 0);
     if (rc != 0) { set_error("b200_mul_mat_q: cuTensorMapEncodeTiled failed (%d)", rc); return B200_ERR_CUDA; }
-    dim3 grid((unsigned)((p.M + MQ_BM - 1) / MQ_BM), (unsigned)((p.N + BN - 1) / BN));
-    mmq_tc2_kernel<TYPE, BN><<<grid, MQ2_THREADS, smem, st>>>(tm, p);
+    dim3 grid((unsigned)((p.M + MQ_BM - 1) / MQ_BM), GROUPED ? grid_y : (unsigned)((p.N + BN - 1) / BN));
+    mmq_tc2_kernel<TYPE, BN, GROUPED><<<grid, MQ2_THREADS, smem, st>>>(tm, p);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }
@@ -692,6 +710,85 @@ static int mmq_dispatch_bn(const MmqParams &p, cudaStream_t st) {
         case 64: return mmq_launch<TYPE, 64>(p, st);
         case 128: return mmq_launch<TYPE, 128>(p, st);
         default: return mmq_launch<TYPE, 256>(p, st);
+    }
+}
+
+
+// ================================================================ (a9) MUL_MAT_ID for batches: group by expert on the device
+// Replaces the batch branch of ggml_cuda_mul_mat_id (/root/reference/ggml/src/ggml-cuda.cu:2066-2139: ids copied to the host +
+// stream sync, then per expert k_copy_src1_to_contiguous -> mul_mat -> k_copy_dst_from_contiguous, :1954-2001).  Here nothing
+// leaves the device: one small kernel counts the (token, slot) pairs per expert, prefix-sums them, writes the sorted row lists and
+// the tile table; a gather pass converts the selected activation rows to bf16 in sorted order; ONE grouped tensor-core launch
+// walks the tile table (every tile belongs to one expert) and scatters its f32 results straight to dst[(token, slot)].
+constexpr int MID_MAX_EXPERTS = 256;
+struct MidTables {      // int offsets into the table area of the workspace
+    int *tile_tab;      // 1 + 3 * max_tiles
+    int *row_src;       // n_rows: float offset of the activation row of sorted row i
+    int *row_dst;       // n_rows: float offset of dst row of sorted row i
+};
+__global__ void __launch_bounds__(1024, 1) mid_group_kernel(const int32_t *__restrict__ ids, int64_t ids_stride, int n_used, int T, int n_expert, int n_b_rows,
+                                                            int64_t b_stride_row, int64_t b_stride_tok, int64_t d_stride_row, int64_t d_stride_tok, int BN,
+                                                            MidTables t) {
+    __shared__ int count[MID_MAX_EXPERTS], off[MID_MAX_EXPERTS + 1], cursor[MID_MAX_EXPERTS];
+    for (int e = threadIdx.x; e < n_expert; e += blockDim.x) { count[e] = 0; cursor[e] = 0; }
+    __syncthreads();
+    const int n = n_used * T;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int e = ids[(int64_t)(i / n_used) * ids_stride + i % n_used];
+        if (e >= 0 && e < n_expert) atomicAdd(&count[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int acc = 0, nt = 0;
+        for (int e = 0; e < n_expert; e++) {
+            off[e] = acc;
+            for (int r0 = acc; r0 < acc + count[e]; r0 += BN) {
+                t.tile_tab[1 + 3 * nt] = e;
+                t.tile_tab[2 + 3 * nt] = r0;
+                t.tile_tab[3 + 3 * nt] = acc + count[e];
+                nt++;
+            }
+            acc += count[e];
+        }
+        off[n_expert] = acc;
+        t.tile_tab[0] = nt;
+    }
+    __syncthreads();
+    // rows of invalid expert ids are left out (their dst rows stay untouched; the reference asserts on them); the slots behind
+    // the last valid row are given a harmless source so the gather pass needs no count
+    for (int i = off[n_expert] + threadIdx.x; i < n; i += blockDim.x) { t.row_src[i] = 0; t.row_dst[i] = 0; }
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int tok = i / n_used, s = i % n_used;
+        const int e = ids[(int64_t)tok * ids_stride + s];
+        if (e < 0 || e >= n_expert) continue;
+        const int pos = off[e] + atomicAdd(&cursor[e], 1);
+        t.row_src[pos] = (int)(tok * b_stride_tok + (s % n_b_rows) * b_stride_row);
+        t.row_dst[pos] = (int)(tok * d_stride_tok + s * d_stride_row);
+    }
+}
+// gather + convert: sorted row i <- bf16(b[row_src[i]]), K values
+__global__ void mid_gather_bf16_kernel(const float *__restrict__ b, const int *__restrict__ row_src, int64_t K, __nv_bfloat16 *__restrict__ out) {
+    const int64_t i4 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n = blockIdx.y;
+    if (i4 * 4 >= K) return;
+    const float4 v = __ldg(reinterpret_cast<const float4 *>(b + (int64_t)__ldg(row_src + n)) + i4);
+    uint2 pk;
+    pk.x = pack_bf16(v.x, v.y);
+    pk.y = pack_bf16(v.z, v.w);
+    *reinterpret_cast<uint2 *>(out + n * K + i4 * 4) = pk;
+}
+
+static int64_t mid_bn(int64_t n_rows, int n_expert) { return mmq_bn((n_rows + n_expert - 1) / n_expert); }
+static int64_t mid_max_tiles(int64_t n_rows, int n_expert) { return (n_rows + mid_bn(n_rows, n_expert) - 1) / mid_bn(n_rows, n_expert) + n_expert; }
+static size_t mid_xb_bytes(int64_t n_rows, int64_t K) { return ((size_t)n_rows * (size_t)K * 2 + 255) / 256 * 256; }
+
+template <int TYPE>
+static int mid_dispatch_bn(const MmqParams &p, int64_t bn, int64_t n_rows, unsigned grid_y, cudaStream_t st) {
+    switch (bn) {
+        case 32: return mmq2_launch<TYPE, 32, true>(p, n_rows, st, grid_y);
+        case 64: return mmq2_launch<TYPE, 64, true>(p, n_rows, st, grid_y);
+        case 128: return mmq2_launch<TYPE, 128, true>(p, n_rows, st, grid_y);
+        default: return mmq2_launch<TYPE, 256, true>(p, n_rows, st, grid_y);
     }
 }
 
@@ -737,12 +834,76 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
     B200_CUDA_TRY(cudaGetLastError());
     MmqParams p;
     p.W = (const unsigned char *)W; p.w_row_bytes = w_row_bytes; p.Xb = xb; p.dst = dst; p.dst_stride = dst_stride; p.K = K; p.M = M; p.N = N;
+    p.tile_tab = nullptr; p.row_dst = nullptr; p.expert_bytes = 0;
     switch (type) {
         case B200_TYPE_Q4_0: return mmq_dispatch_bn<B200_TYPE_Q4_0>(p, st);
         case B200_TYPE_Q8_0: return mmq_dispatch_bn<B200_TYPE_Q8_0>(p, st);
         case B200_TYPE_Q4_K: return mmq_dispatch_bn<B200_TYPE_Q4_K>(p, st);
         case B200_TYPE_Q5_K: return mmq_dispatch_bn<B200_TYPE_Q5_K>(p, st);
         case B200_TYPE_Q6_K: return mmq_dispatch_bn<B200_TYPE_Q6_K>(p, st);
+    }
+    return B200_ERR_UNSUPPORTED;
+}
+
+extern "C" size_t b200_mul_mat_id_q_workspace_bytes(int type, int64_t K, int64_t M, int64_t n_used, int64_t T, int32_t n_expert) {
+    (void)type; (void)M;
+    const int64_t n_rows = n_used * T;
+    if (K <= 0 || n_rows <= 0 || n_expert <= 0) return 0;
+    return mid_xb_bytes(n_rows, K) + sizeof(int) * (size_t)(1 + 3 * mid_max_tiles(n_rows, n_expert) + 2 * n_rows) + 256;
+}
+
+extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, size_t expert_bytes, int32_t n_expert, const int32_t *ids,
+                                 int64_t ids_stride, const float *b, int64_t b_stride_row, int64_t b_stride_tok, float *dst, int64_t dst_stride_row,
+                                 int64_t dst_stride_tok, int64_t K, int64_t M, int64_t n_used, int64_t n_b_rows, int64_t T, void *workspace,
+                                 size_t workspace_bytes, b200_stream_t stream) {
+    if (!as || !ids || !b || !dst) { set_error("b200_mul_mat_id_q: NULL argument"); return B200_ERR_INVALID; }
+    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
+        set_error("b200_mul_mat_id_q: unsupported weight type %d", type);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (K <= 0 || K % 256 || M < 0 || T < 0 || n_used < 1 || n_b_rows < 1 || n_expert < 1 || n_expert > MID_MAX_EXPERTS) {
+        set_error("b200_mul_mat_id_q: bad shape (K must be a multiple of 256, at most %d experts)", MID_MAX_EXPERTS);
+        return K % 256 ? B200_ERR_UNSUPPORTED : B200_ERR_INVALID;
+    }
+    if (M == 0 || T == 0) return B200_OK;
+    const int bv = type_block_values(type);
+    const size_t row_bytes = (size_t)(K / bv) * type_block_bytes(type);
+    if (w_row_bytes < row_bytes || ((w_row_bytes | expert_bytes | (uintptr_t)as) & 1)) { set_error("b200_mul_mat_id_q: weight stride/alignment"); return B200_ERR_INVALID; }
+    if ((type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K) && ((w_row_bytes | expert_bytes | (uintptr_t)as) & 15)) {
+        set_error("b200_mul_mat_id_q: q4_K/q5_K rows must be 16-byte aligned");
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (((uintptr_t)b & 15) || ((b_stride_row | b_stride_tok) & 3)) { set_error("b200_mul_mat_id_q: b rows must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
+    const int64_t n_rows = n_used * T;
+    const int64_t span_b = (T - 1) * b_stride_tok + (n_b_rows - 1) * b_stride_row, span_d = (T - 1) * dst_stride_tok + (n_used - 1) * dst_stride_row;
+    if (n_rows > 65535 || span_b > 0x7fffffff || span_d > 0x7fffffff) { set_error("b200_mul_mat_id_q: batch too large"); return B200_ERR_UNSUPPORTED; }
+    const size_t need = b200_mul_mat_id_q_workspace_bytes(type, K, M, n_used, T, n_expert);
+    if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 255)) {
+        set_error("b200_mul_mat_id_q: workspace of %zu bytes (256-byte aligned) required, %zu given", need, workspace_bytes);
+        return B200_ERR_INVALID;
+    }
+    const cudaStream_t st = (cudaStream_t)stream;
+    const int64_t bn = mid_bn(n_rows, n_expert), max_tiles = mid_max_tiles(n_rows, n_expert);
+    __nv_bfloat16 *xb = (__nv_bfloat16 *)workspace;
+    MidTables t;
+    t.tile_tab = (int *)((unsigned char *)workspace + mid_xb_bytes(n_rows, K));
+    t.row_src = t.tile_tab + 1 + 3 * max_tiles;
+    t.row_dst = t.row_src + n_rows;
+    mid_group_kernel<<<1, 1024, 0, st>>>(ids, ids_stride, (int)n_used, (int)T, (int)n_expert, (int)n_b_rows, b_stride_row, b_stride_tok, dst_stride_row,
+                                         dst_stride_tok, (int)bn, t);
+    B200_CUDA_TRY(cudaGetLastError());
+    dim3 g1((unsigned)((K / 4 + 255) / 256), (unsigned)n_rows);
+    mid_gather_bf16_kernel<<<g1, 256, 0, st>>>(b, t.row_src, K, xb);
+    B200_CUDA_TRY(cudaGetLastError());
+    MmqParams p;
+    p.W = (const unsigned char *)as; p.w_row_bytes = w_row_bytes; p.Xb = xb; p.dst = dst; p.dst_stride = 0; p.K = K; p.M = M; p.N = n_rows;
+    p.tile_tab = t.tile_tab; p.row_dst = t.row_dst; p.expert_bytes = expert_bytes;
+    switch (type) {
+        case B200_TYPE_Q4_0: return mid_dispatch_bn<B200_TYPE_Q4_0>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q8_0: return mid_dispatch_bn<B200_TYPE_Q8_0>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q4_K: return mid_dispatch_bn<B200_TYPE_Q4_K>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q5_K: return mid_dispatch_bn<B200_TYPE_Q5_K>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q6_K: return mid_dispatch_bn<B200_TYPE_Q6_K>(p, bn, n_rows, (unsigned)max_tiles, st);
     }
     return B200_ERR_UNSUPPORTED;
 }

@@ -147,6 +147,16 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         act_issue(aregs, p.jobs[jfirst].X, p.norm_w, p.K);
     }
     for (int s = 0; s < n_stage && ik < nmy; s++) issue();
+    // Once this warp has nothing left to request for itself, its elected lane pulls a share of the NEXT kernel's operands into L2:
+    // the requests queue behind our own, so HBM keeps streaming through our tail, the launch gap and the consumer's prologue.
+    bool pf_done = false;
+    auto maybe_prefetch = [&]() {
+        if (!pf_done && ik >= nmy) {
+            if (lane == 0) l2_prefetch_issue(p.pf, (unsigned)(bid * MMVQ_NW + warp), (unsigned)(gridDim.x * MMVQ_NW));
+            pf_done = true;
+        }
+    };
+    maybe_prefetch();
     TRACE(2);
 
     // ---- the ring fill above is independent of the producer kernel's output
@@ -170,8 +180,10 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         const float *xj = p.jobs[job].X;
         if (loaded_x != xj && nrows > 0) {
             if (loaded_x != nullptr) __syncthreads();  // everyone is done with the previous activations
-            if (acts_first && loaded_x == nullptr) act_finish(aregs, act_base, p.K, n_it, p.norm_w != nullptr, p.norm_eps, red);
-            else load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red);
+            // the RMS_NORM / MUL nodes folded into this prologue keep their values: the first CTA stores them once
+            float *n_out = bid == 0 && loaded_x == nullptr ? p.norm_out : nullptr, *nm_out = bid == 0 && loaded_x == nullptr ? p.norm_mul_out : nullptr;
+            if (acts_first && loaded_x == nullptr) act_finish(aregs, act_base, p.K, n_it, p.norm_w != nullptr, p.norm_eps, red, n_out, nm_out);
+            else load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red, n_out, nm_out);
             __syncthreads();
             loaded_x = xj;
             TRACE(4);
@@ -179,17 +191,19 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         for (; k < nmy; k++) {
             const int lr = warp + k * MMVQ_NW;
             uintptr_t src;
-            float *dst;
+            float *dst, *raw;
             const float *res;
             if constexpr (MULTI) {
                 if (rjob[lr] != job) break;
                 src = (uintptr_t)rsrc[lr];
                 dst = rdst[lr];
                 res = p.residual[job] ? p.residual[job] + (dst - p.jobs[job].dst) : nullptr;
+                raw = p.raw_dst[job] ? p.raw_dst[job] + (dst - p.jobs[job].dst) : nullptr;
             } else {
                 src = (uintptr_t)w0 + (size_t)(r0 + lr) * p.w_row_bytes;
                 dst = p.jobs[0].dst + (r0 + lr);
                 res = p.residual[0] ? p.residual[0] + (r0 + lr) : nullptr;
+                raw = p.raw_dst[0] ? p.raw_dst[0] + (r0 + lr) : nullptr;
             }
             for (int it = 0; it < n_it; it++) {
                 mbar_wait(&my_bars[cstage], cphase);
@@ -204,19 +218,30 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
                 cstage = cstage + 1 == n_stage ? 0 : cstage + 1;
                 cphase ^= (cstage == 0);
                 if (ik < nmy) issue();
+                maybe_prefetch();
             }
             if (pair) {  // (NCOLS == 1)
                 const float v = warp_sum(acc[0]);
                 acc[0] = 0.f;
                 if ((k & 1) == 0) gate_v = v;
-                else if (lane == 0) dst[0] = gate_v / (1.0f + expf(-gate_v)) * v;  // silu_mul_kernel's expression (ops.cu)
+                else if (lane == 0) {
+                    const int64_t row = dst - p.jobs[0].dst;
+                    const float sg = gate_v / (1.0f + expf(-gate_v));  // silu_mul_kernel's expression (ops.cu)
+                    if (p.gate_out) p.gate_out[row] = gate_v;
+                    if (p.up_out) p.up_out[row] = v;
+                    if (p.silu_out) p.silu_out[row] = sg;
+                    dst[0] = sg * v;
+                }
                 continue;
             }
 #pragma unroll
             for (int n = 0; n < NCOLS; n++) {
                 float v = warp_sum(acc[n]);
                 if (MULTI && src == 0) v = __int_as_float(0x7fc00000);
-                if (lane == 0) dst[(int64_t)n * p.dst_stride] = res ? v + res[(int64_t)n * p.dst_stride] : v;
+                if (lane == 0) {
+                    if (raw) raw[(int64_t)n * p.dst_stride] = v;
+                    dst[(int64_t)n * p.dst_stride] = res ? v + res[(int64_t)n * p.dst_stride] : v;
+                }
                 acc[n] = 0.f;
             }
             if (k == 0) TRACE(6);
@@ -356,13 +381,19 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
         p.norm_w = fuse->norm_weight;
         p.norm_eps = fuse->norm_eps;
         if (fuse->norm_weight && ((uintptr_t)fuse->norm_weight & 15)) { set_error("b200_mul_mat_vec_q_fused: norm weight must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
-        for (int j = 0; j < n_jobs; j++) p.residual[j] = fuse->residual[j];
+        for (int j = 0; j < n_jobs; j++) { p.residual[j] = fuse->residual[j]; p.raw_dst[j] = fuse->residual[j] ? fuse->raw_dst[j] : nullptr; }
+        if (fuse->norm_weight) {
+            p.norm_out = fuse->norm_out;
+            p.norm_mul_out = fuse->norm_mul_out;
+            if (((uintptr_t)p.norm_out | (uintptr_t)p.norm_mul_out) & 15) { set_error("b200_mul_mat_vec_q_fused: norm_out / norm_mul_out must be 16-byte aligned"); return B200_ERR_UNSUPPORTED; }
+        }
         if (fuse->silu_pair) {
             if (n_jobs != 2 || N != 1 || ids || jobs[0].M != jobs[1].M || jobs[0].X != jobs[1].X || fuse->residual[0] || fuse->residual[1]) {
                 set_error("b200_mul_mat_vec_q_fused: silu_pair needs two jobs (gate, up) of equal M on the same X, N == 1, no residual");
                 return B200_ERR_INVALID;
             }
             p.silu_pair = 1;
+            p.gate_out = fuse->gate_out; p.up_out = fuse->up_out; p.silu_out = fuse->silu_out;
         }
     }
     int64_t total = 0;
@@ -379,6 +410,7 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
     }
     if ((w_row_bytes & 1) || (expert_bytes & 1)) { set_error("b200_mul_mat_vec_q: odd strides"); return B200_ERR_UNSUPPORTED; }
     p.total_rows = total;
+    p.pf = take_prefetch();
     if (total == 0) return B200_OK;
     if (total > 0x7fffffff) { set_error("b200_mul_mat_vec_q: too many rows"); return B200_ERR_UNSUPPORTED; }
     const bool pdl = g_mmvq_pdl;

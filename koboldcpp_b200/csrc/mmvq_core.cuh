@@ -31,6 +31,11 @@ struct MmvqParams {
     float          norm_eps;
     int            silu_pair;     // jobs[0] = gate, jobs[1] = up: rows_q / rows_rem count PAIRS; dst = silu(gate . x) * (up . x)
     const float   *residual[B200_GEMV_MAX_JOBS];
+    // the folded nodes' own values (b200_gemv_fuse: never elide a graph node's output); NULL = not wanted
+    float         *raw_dst[B200_GEMV_MAX_JOBS];
+    float         *norm_out, *norm_mul_out;
+    float         *gate_out, *up_out, *silu_out;
+    PrefetchPlan   pf;            // operands of the NEXT kernel, pulled into L2 once this CTA has issued its own loads
 };
 
 template <int TYPE>
@@ -86,7 +91,8 @@ __device__ __forceinline__ float rms_scale(const float *__restrict__ xs, int64_t
 // value quantised is (x * nscale) * w, the order of the RMS_NORM -> MUL node pair.  All threads of the CTA call this.
 template <int NT = MMVQ_THREADS>
 __device__ __forceinline__ void quantize_activation_row(unsigned char *p, const float *__restrict__ x, int64_t K, int n_it,
-                                                        const float *__restrict__ norm_w, float nscale) {
+                                                        const float *__restrict__ norm_w, float nscale,
+                                                        float *__restrict__ norm_out = nullptr, float *__restrict__ norm_mul_out = nullptr) {
     const int n4 = (int)(K / 4);
     int   *aq = (int *)p;
     float *ad = (float *)(p + (size_t)n_it * 4096);
@@ -102,8 +108,10 @@ __device__ __forceinline__ void quantize_activation_row(unsigned char *p, const 
             v[u] = i4 < n4 ? __ldcg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
             if (norm_w != nullptr && i4 < n4) {
                 const float4 ww = __ldg(reinterpret_cast<const float4 *>(norm_w) + i4);
-                v[u].x = v[u].x * nscale * ww.x; v[u].y = v[u].y * nscale * ww.y;
-                v[u].z = v[u].z * nscale * ww.z; v[u].w = v[u].w * nscale * ww.w;
+                v[u].x = v[u].x * nscale; v[u].y = v[u].y * nscale; v[u].z = v[u].z * nscale; v[u].w = v[u].w * nscale;
+                if (norm_out) reinterpret_cast<float4 *>(norm_out)[i4] = v[u];
+                v[u].x = v[u].x * ww.x; v[u].y = v[u].y * ww.y; v[u].z = v[u].z * ww.z; v[u].w = v[u].w * ww.w;
+                if (norm_mul_out) reinterpret_cast<float4 *>(norm_mul_out)[i4] = v[u];
             }
         }
 #pragma unroll
@@ -135,11 +143,13 @@ __device__ __forceinline__ void quantize_activation_row(unsigned char *p, const 
 // Quantise X[n][0..K) (f32, global) into the CTA's shared activation store.  All threads of the CTA call this.
 template <int NCOLS>
 __device__ void load_activations(unsigned char *act_base, const float *__restrict__ X, int64_t x_stride, int64_t K, int n_it,
-                                 const float *__restrict__ norm_w, float norm_eps, float *red) {
+                                 const float *__restrict__ norm_w, float norm_eps, float *red, float *norm_out = nullptr,
+                                 float *norm_mul_out = nullptr) {
     for (int n = 0; n < NCOLS; n++) {
         const float *x = X + (int64_t)n * x_stride;
         const float nscale = norm_w != nullptr ? rms_scale(x, K, norm_eps, red) : 1.0f;
-        quantize_activation_row(act_base + (size_t)n * act_col_bytes(n_it), x, K, n_it, norm_w, nscale);
+        quantize_activation_row(act_base + (size_t)n * act_col_bytes(n_it), x, K, n_it, norm_w, nscale,
+                                norm_out ? norm_out + (int64_t)n * K : nullptr, norm_mul_out ? norm_mul_out + (int64_t)n * K : nullptr);
     }
 }
 
@@ -171,7 +181,8 @@ __device__ __forceinline__ void act_issue(ActRegs &r, const float *__restrict__ 
     }
 }
 // All threads of the CTA call this (it contains CTA barriers when norm is set).
-__device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t K, int n_it, bool norm, float norm_eps, float *red) {
+__device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t K, int n_it, bool norm, float norm_eps, float *red,
+                                           float *__restrict__ norm_out = nullptr, float *__restrict__ norm_mul_out = nullptr) {
     constexpr int NT = MMVQ_THREADS;
     const int n4 = (int)(K / 4);
     int   *aq = (int *)p;
@@ -190,8 +201,11 @@ __device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t
         const float nscale = rsqrtf(t / (float)K + norm_eps);
 #pragma unroll
         for (int u = 0; u < ACT_RR; u++) {
-            r.v[u].x = r.v[u].x * nscale * r.w[u].x; r.v[u].y = r.v[u].y * nscale * r.w[u].y;
-            r.v[u].z = r.v[u].z * nscale * r.w[u].z; r.v[u].w = r.v[u].w * nscale * r.w[u].w;
+            const int i4 = u * NT + threadIdx.x;
+            r.v[u].x = r.v[u].x * nscale; r.v[u].y = r.v[u].y * nscale; r.v[u].z = r.v[u].z * nscale; r.v[u].w = r.v[u].w * nscale;
+            if (norm_out && i4 < n4) reinterpret_cast<float4 *>(norm_out)[i4] = r.v[u];
+            r.v[u].x = r.v[u].x * r.w[u].x; r.v[u].y = r.v[u].y * r.w[u].y; r.v[u].z = r.v[u].z * r.w[u].z; r.v[u].w = r.v[u].w * r.w[u].w;
+            if (norm_mul_out && i4 < n4) reinterpret_cast<float4 *>(norm_mul_out)[i4] = r.v[u];
         }
     }
 #pragma unroll

@@ -134,6 +134,24 @@ def mul_mat_id_vec_q(t: int, w: np.ndarray, ids: np.ndarray, b: np.ndarray, K: i
     return dd.to_numpy(np.float32, (T, n_used, M))
 
 
+def mul_mat_id_q(t: int, w: np.ndarray, ids: np.ndarray, b: np.ndarray, K: int, M: int, n_expert: int) -> np.ndarray:
+    """Batched MUL_MAT_ID on the tensor cores (b200_mul_mat_id_q); same layouts as mul_mat_id_vec_q.  dst is pre-filled with NaN so
+    that rows the kernel must not touch (invalid expert ids) can be told apart."""
+    require_gpu()
+    ids = np.ascontiguousarray(ids, dtype=np.int32)
+    T, n_used = ids.shape
+    b = np.ascontiguousarray(b, dtype=np.float32).reshape(T, -1, K)
+    nbr = b.shape[1]
+    rs = row_size(t, K)
+    dw, di, db = DeviceBuffer.from_numpy(np.ascontiguousarray(w, dtype=np.uint8), pad=16), DeviceBuffer.from_numpy(ids), DeviceBuffer.from_numpy(b)
+    dd = DeviceBuffer.from_numpy(np.full((T, n_used, M), np.nan, dtype=np.float32))
+    ws_bytes = lib().b200_mul_mat_id_q_workspace_bytes(t, K, M, n_used, T, n_expert)
+    ws = DeviceBuffer(ws_bytes + 256)
+    check(lib().b200_mul_mat_id_q(t, dw.ptr, rs, rs * M, n_expert, di.ptr, n_used, db.ptr, K, nbr * K, dd.ptr, M, n_used * M, K, M, n_used, nbr, T,
+                                  ws.ptr, ws_bytes, None), "b200_mul_mat_id_q")
+    return dd.to_numpy(np.float32, (T, n_used, M))
+
+
 def flash_attn_ext(q: np.ndarray, k: np.ndarray, v: np.ndarray, mask: np.ndarray | None, type_kv: int, scale: float,
                    max_bias: float = 0.0, softcap: float = 0.0) -> np.ndarray:
     """q f32 [n_head, N, D]; k, v packed rows uint8 [n_head_kv, n_kv, row_bytes]; mask f16 [N_pad, n_kv] -> f32 [N, n_head, D]."""

@@ -28,7 +28,14 @@ class GemvJob(C.Structure):
 
 
 class GemvFuse(C.Structure):
-    _fields_ = [("norm_weight", C.c_void_p), ("norm_eps", C.c_float), ("silu_pair", C.c_int32), ("residual", C.c_void_p * 16)]
+    _fields_ = [("norm_weight", C.c_void_p), ("norm_eps", C.c_float), ("silu_pair", C.c_int32), ("residual", C.c_void_p * 16),
+                ("raw_dst", C.c_void_p * 16), ("norm_out", C.c_void_p), ("norm_mul_out", C.c_void_p), ("gate_out", C.c_void_p), ("up_out", C.c_void_p),
+                ("silu_out", C.c_void_p)]
+
+
+class Prefetch(C.Structure):
+    """b200_prefetch (include/b200_ggml.h)."""
+    _fields_ = [("ptr", C.c_void_p * 4), ("bytes", C.c_uint32 * 4)]
 
 
 class Tensor(C.Structure):
@@ -48,35 +55,6 @@ class RopeParams(C.Structure):
                 ("ext_factor", C.c_float), ("attn_factor", C.c_float), ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
 
 
-class ChainJob(C.Structure):
-    _fields_ = [("W", C.c_void_p), ("dst", C.c_void_p), ("residual", C.c_void_p), ("w_row_bytes", C.c_size_t), ("M", C.c_int32), ("type", C.c_int32)]
-
-
-class ChainRope(C.Structure):
-    _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("q_out", C.c_void_p), ("k_out", C.c_void_p), ("k_cache", C.c_void_p),
-                ("v_cache", C.c_void_p), ("k_slot", C.c_void_p), ("v_slot", C.c_void_p), ("pos", C.c_void_p), ("freq_factors", C.c_void_p),
-                ("D", C.c_int32), ("H", C.c_int32), ("HK", C.c_int32), ("kv_type", C.c_int32), ("n_dims", C.c_int32), ("mode", C.c_int32),
-                ("n_ctx_orig", C.c_int32), ("freq_base", C.c_float), ("freq_scale", C.c_float), ("ext_factor", C.c_float), ("attn_factor", C.c_float),
-                ("beta_fast", C.c_float), ("beta_slow", C.c_float)]
-
-
-class ChainAttn(C.Structure):
-    _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("mask", C.c_void_p), ("dst", C.c_void_p), ("workspace", C.c_void_p),
-                ("k_nb1", C.c_size_t), ("k_nb2", C.c_size_t), ("v_nb1", C.c_size_t), ("v_nb2", C.c_size_t),
-                ("D", C.c_int32), ("H", C.c_int32), ("HK", C.c_int32), ("n_kv", C.c_int32), ("kv_type", C.c_int32),
-                ("scale", C.c_float), ("max_bias", C.c_float), ("logit_softcap", C.c_float)]
-
-
-class ChainU(C.Union):
-    _fields_ = [("jobs", ChainJob * 4), ("rope", ChainRope), ("attn", ChainAttn)]
-
-
-class ChainPhase(C.Structure):
-    """b200_chain_phase (include/b200_ggml.h)."""
-    _fields_ = [("kind", C.c_int32), ("n_jobs", C.c_int32), ("K", C.c_int32), ("silu_pair", C.c_int32), ("norm_eps", C.c_float), ("_pad", C.c_int32),
-                ("X", C.c_void_p), ("norm_weight", C.c_void_p), ("sumsq_out", C.c_void_p), ("sumsq_in", C.c_void_p), ("u", ChainU)]
-
-
 class FattnArgs(C.Structure):
     _fields_ = [("q", C.c_void_p), ("k", C.c_void_p), ("v", C.c_void_p), ("mask", C.c_void_p), ("dst", C.c_void_p),
                 ("D", C.c_int64), ("N", C.c_int64), ("n_head", C.c_int64), ("n_head_kv", C.c_int64), ("n_kv", C.c_int64),
@@ -91,6 +69,7 @@ _SIGS = {
     "b200_last_error": (C.c_char_p, []),
     "b200_version": (C.c_char_p, []),
     "b200_set_pdl": (None, [C.c_int]),
+    "b200_set_next_prefetch": (None, [C.POINTER(Prefetch)]),
     "b200_device_count": (C.c_int, []),
     "b200_set_device": (C.c_int, [C.c_int]),
     "b200_device_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
@@ -119,14 +98,11 @@ _SIGS = {
     "b200_mul_mat_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
     "b200_mul_mat_vec_q_multi": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_int32, C.c_void_p]),
     "b200_mul_mat_vec_q_fused": (C.c_int, [C.c_int, C.POINTER(GemvJob), C.c_int, C.c_size_t, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.POINTER(GemvFuse), C.c_void_p]),
-    "b200_decode_chain": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
-    "b200_decode_chain_program_bytes": (C.c_size_t, [C.c_void_p, C.c_int]),
-    "b200_decode_chain_compile": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p]),
-    "b200_decode_chain_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "b200_decode_chain_sumsq_slots": (C.c_int, []),
-    "b200_decode_chain_attn_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32, C.c_int32]),
     "b200_mul_mat_id_vec_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
                                         C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p]),
+    "b200_mul_mat_id_q_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int32]),
+    "b200_mul_mat_id_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64,
+                                    C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200_mul_mat_q_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int64, C.c_int64, C.c_int64]),
     "b200_mul_mat_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200_flash_attn_workspace_bytes": (C.c_size_t, [C.POINTER(FattnArgs)]),

@@ -123,78 +123,122 @@ def test_rope_kv_store_equals_separate_nodes(kv_type, D, NH, HK, T):
     assert np.array_equal(outs[1][3].reshape(-1), np.asarray(exp_v).view(np.uint8).reshape(-1))
 
 
-@pytest.mark.parametrize("kv_type", [F16, Q8_0])
-def test_decode_chain_equals_separate_launches(kv_type):
-    """b200_decode_chain: [QKV GEMV with RMS-norm prologue (mixed types) -> ROPE+KV store -> GEMV + residual -> gate/up GEMV
-    with the SiLU*up epilogue -> GEMV + residual] in ONE persistent launch against the same steps run one by one."""
-    from koboldcpp_b200.lib import ChainPhase, Q5_K
+def test_folded_nodes_keep_their_values():
+    """The graph executor folds RMS_NORM->MUL into the GEMV prologue, ADD into its epilogue and SILU*up into the pair epilogue.
+    The folded nodes are still graph nodes another ggml_backend_sched split may read: with the optional outputs of
+    b200_gemv_fuse the launch must store exactly what the unfused kernels would have stored."""
     L = lib()
-    rng = np.random.default_rng(99)
-    E, NH, HK, D, FF = 1024, 8, 4, 128, 2816
-    kvw = HK * D
-    eps = 1e-5
-    x = rng.standard_normal(E).astype(np.float32) * 2
-    nw1 = (1 + 0.1 * rng.standard_normal(E)).astype(np.float32)
-    nw2 = (1 + 0.1 * rng.standard_normal(E)).astype(np.float32)
-    wq, wk, wv = random_blocks(rng, Q4_K, E, E), random_blocks(rng, Q4_K, kvw, E), random_blocks(rng, Q6_K, kvw, E)
-    wo, wg, wu, wd = random_blocks(rng, Q5_K, E, E), random_blocks(rng, Q4_K, FF, E), random_blocks(rng, Q4_K, FF, E), random_blocks(rng, Q6_K, E, FF)
-    pos = np.array([77], dtype=np.int32)
-    d = {k: dev(v) for k, v in dict(x=x, nw1=nw1, nw2=nw2, wq=wq, wk=wk, wv=wv, wo=wo, wg=wg, wu=wu, wd=wd, pos=pos).items()}
-    rowb = row_size(kv_type, kvw)
-    bufs = {k: H.DeviceBuffer(4 * n + 256, zero=True) for k, n in dict(q=E, k=kvw, v=kvw, qo=E, ko=kvw, h=E, act=FF, out=E).items()}
-    kc, vc, bar = H.DeviceBuffer(rowb + 256, zero=True), H.DeviceBuffer(rowb + 256, zero=True), H.DeviceBuffer(256, zero=True)
+    K, M = 4096, 1000
+    rng = np.random.default_rng(5)
+    t = Q4_K
+    wg, wu = random_blocks(rng, t, M, K), random_blocks(rng, t, M, K)
+    x = rng.standard_normal((1, K)).astype(np.float32) * 2.0
+    nw = (1.0 + 0.2 * rng.standard_normal(K)).astype(np.float32)
+    res = rng.standard_normal((1, M)).astype(np.float32)
+    dg, du, dx, dnw, dres = dev(wg), dev(wu), dev(x), dev(nw), dev(res)
+    # unfused reference on the device: rms_norm_mul kernel (stores both values), plain GEMVs, silu_mul kernel
+    nrm, nrm_mul = H.DeviceBuffer(4 * K + 256, zero=True), H.DeviceBuffer(4 * K + 256, zero=True)
+    tx, tdst = Tensor.contiguous(dx.ptr, F32, (K, 1)), Tensor.contiguous(nrm_mul.ptr, F32, (K, 1))
+    check(L.b200_op_rms_norm_mul(tx, dnw.ptr, nrm.ptr, tdst, 1e-5, None))
+    og, ou, osilu, opar = (H.DeviceBuffer(4 * M + 256, zero=True) for _ in range(4))
+    check(L.b200_mul_mat_vec_q(t, dg.ptr, row_size(t, K), nrm_mul.ptr, K, og.ptr, M, K, M, 1, None))
+    check(L.b200_mul_mat_vec_q(t, du.ptr, row_size(t, K), nrm_mul.ptr, K, ou.ptr, M, K, M, 1, None))
+    check(L.b200_op_silu_mul(og.ptr, ou.ptr, osilu.ptr, opar.ptr, M, None))
+    # fused pair launch with every node value requested
+    f_nrm, f_nrm_mul = H.DeviceBuffer(4 * K + 256, zero=True), H.DeviceBuffer(4 * K + 256, zero=True)
+    fg, fu, fsilu, fpar = (H.DeviceBuffer(4 * M + 256, zero=True) for _ in range(4))
+    jobs = (GemvJob * 2)()
+    for j, w in enumerate((dg, du)):
+        jobs[j].W, jobs[j].X, jobs[j].dst, jobs[j].M, jobs[j].id_index = w.ptr, dx.ptr, fpar.ptr, M, -1
+    fuse = GemvFuse()
+    fuse.norm_weight, fuse.norm_eps, fuse.silu_pair = dnw.ptr, 1e-5, 1
+    fuse.norm_out, fuse.norm_mul_out, fuse.gate_out, fuse.up_out, fuse.silu_out = f_nrm.ptr, f_nrm_mul.ptr, fg.ptr, fu.ptr, fsilu.ptr
+    check(L.b200_mul_mat_vec_q_fused(t, jobs, 2, row_size(t, K), K, M, K, 1, C.byref(fuse), None))
+    a_n, b_n = nrm.to_numpy(np.float32, (K,)), f_nrm.to_numpy(np.float32, (K,))
+    # the norm scale comes from two different f32 reduction trees (row kernel vs GEMV prologue): compare to f32 rounding
+    assert np.abs(a_n - b_n).max() <= 4e-7 * np.abs(a_n).max()
+    assert np.abs(nrm_mul.to_numpy(np.float32, (K,)) - f_nrm_mul.to_numpy(np.float32, (K,))).max() <= 4e-7 * np.abs(a_n).max() * 2
+    for ref, got in ((og, fg), (ou, fu), (osilu, fsilu), (opar, fpar)):
+        r, g = ref.to_numpy(np.float32, (M,)), got.to_numpy(np.float32, (M,))
+        assert np.abs(r - g).max() <= 2e-3 * np.abs(r).max()
+    # the stored gate / up / silu values are exactly the ones the final product was built from
+    g, u, sg, par = (b_.to_numpy(np.float32, (M,)) for b_ in (fg, fu, fsilu, fpar))
+    assert np.array_equal(sg * u, par)
+    # residual epilogue with the raw product kept
+    raw, out = H.DeviceBuffer(4 * M + 256, zero=True), H.DeviceBuffer(4 * M + 256, zero=True)
+    job = (GemvJob * 1)()
+    job[0].W, job[0].X, job[0].dst, job[0].M, job[0].id_index = dg.ptr, dx.ptr, out.ptr, M, -1
+    fuse2 = GemvFuse()
+    fuse2.residual[0] = dres.ptr
+    fuse2.raw_dst[0] = raw.ptr
+    check(L.b200_mul_mat_vec_q_fused(t, job, 1, row_size(t, K), K, M, K, 1, C.byref(fuse2), None))
+    plain = H.DeviceBuffer(4 * M + 256, zero=True)
+    check(L.b200_mul_mat_vec_q(t, dg.ptr, row_size(t, K), dx.ptr, K, plain.ptr, M, K, M, 1, None))
+    r = raw.to_numpy(np.float32, (M,))
+    assert np.array_equal(r, plain.to_numpy(np.float32, (M,)))
+    assert np.array_equal(out.to_numpy(np.float32, (M,)), r + res[0])
 
-    def gemv_phase(X, K, jobs, norm=None, pair=0):
-        ph = ChainPhase()
-        ph.kind, ph.n_jobs, ph.K, ph.silu_pair, ph.norm_eps = 0, len(jobs), K, pair, eps
-        ph.X, ph.norm_weight = X, norm
-        for i, (W, dst, res, M, t) in enumerate(jobs):
-            j = ph.u.jobs[i]
-            j.W, j.dst, j.residual, j.w_row_bytes, j.M, j.type = W, dst, res, row_size(t, K), M, t
-        return ph
 
-    ph = (ChainPhase * 5)()
-    ph[0] = gemv_phase(d["x"].ptr, E, [(d["wq"].ptr, bufs["q"].ptr, None, E, Q4_K), (d["wk"].ptr, bufs["k"].ptr, None, kvw, Q4_K), (d["wv"].ptr, bufs["v"].ptr, None, kvw, Q6_K)], d["nw1"].ptr)
-    r = ph[1]
-    r.kind = 1
-    rr = r.u.rope
-    rr.q, rr.k, rr.v, rr.q_out, rr.k_out = bufs["q"].ptr, bufs["k"].ptr, bufs["v"].ptr, bufs["qo"].ptr, bufs["ko"].ptr
-    rr.k_cache, rr.v_cache, rr.pos = kc.ptr, vc.ptr, d["pos"].ptr
-    rr.D, rr.H, rr.HK, rr.kv_type, rr.n_dims, rr.mode, rr.n_ctx_orig = D, NH, HK, kv_type, D, 0, 4096
-    rr.freq_base, rr.freq_scale, rr.ext_factor, rr.attn_factor, rr.beta_fast, rr.beta_slow = 10000.0, 1.0, 0.0, 1.0, 32.0, 1.0
-    # (the attention itself is a separate launch in the backend; here the roped q simply feeds the next GEMV)
-    ph[2] = gemv_phase(bufs["qo"].ptr, E, [(d["wo"].ptr, bufs["h"].ptr, d["x"].ptr, E, Q5_K)])
-    ph[3] = gemv_phase(bufs["h"].ptr, E, [(d["wg"].ptr, bufs["act"].ptr, None, FF, Q4_K), (d["wu"].ptr, bufs["act"].ptr, None, FF, Q4_K)], d["nw2"].ptr, pair=1)
-    ph[4] = gemv_phase(bufs["act"].ptr, FF, [(d["wd"].ptr, bufs["out"].ptr, bufs["h"].ptr, E, Q6_K)])
-    for _ in range(3):  # the barrier word must come back to zero: run it several times
-        check(L.b200_decode_chain(ph, 5, bar.ptr, None))
-    got = {k: b.to_numpy(np.float32, (n,)) for k, (b, n) in dict(qo=(bufs["qo"], E), h=(bufs["h"], E), act=(bufs["act"], FF), out=(bufs["out"], E)).items()}
-    assert bar.to_numpy(np.uint32, (1,))[0] == 0
+def test_l2_prefetch_plan_is_only_a_hint():
+    """b200_set_next_prefetch: the next GEMV / attention / rope_kv launch carries the plan; results are bit-identical with and
+    without it, for aligned, unaligned and tiny regions, and the plan is consumed by exactly one launch."""
+    from koboldcpp_b200.lib import Prefetch
+    L = lib()
+    K, M = 4096, 2000
+    rng = np.random.default_rng(11)
+    w = random_blocks(rng, Q6_K, M, K)
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    dw, dx = dev(w), dev(x)
+    other = H.DeviceBuffer(8 << 20, zero=True)
+    outs = []
+    for plan in (None, [(other.ptr, 8 << 20)], [(other.ptr + 6, 1 << 20), (other.ptr + (4 << 20), 100), (dw.ptr, w.nbytes)]):
+        if plan is not None:
+            pf = Prefetch()
+            for i, (ptr, n) in enumerate(plan):
+                pf.ptr[i], pf.bytes[i] = ptr, n
+            L.b200_set_next_prefetch(C.byref(pf))
+        o = H.DeviceBuffer(4 * M + 256, zero=True)
+        check(L.b200_mul_mat_vec_q(Q6_K, dw.ptr, row_size(Q6_K, K), dx.ptr, K, o.ptr, M, K, M, 1, None))
+        check(L.b200_device_synchronize())
+        outs.append(o.to_numpy(np.float32, (M,)))
+    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
 
-    # the same steps with the single-purpose entry points
-    def norm(v, w):
-        return ((v * np.float32(1.0 / np.sqrt((v.astype(np.float64) ** 2).mean() + eps))) * w).astype(np.float32)
-    xn = norm(x, nw1)
-    q, k, v = (H.mul_mat_vec_q(t, w, xn[None], E, m)[0] for t, w, m in ((Q4_K, wq, E), (Q4_K, wk, kvw), (Q6_K, wv, kvw)))
-    rp = RopeParams(D, 0, 4096, 10000.0, 1.0, 0.0, 1.0, 32.0, 1.0)
-    dq, dk, dv = dev(q), dev(k), dev(v)
-    dqo, dko = H.DeviceBuffer(4 * E + 256), H.DeviceBuffer(4 * kvw + 256)
-    kc2, vc2 = H.DeviceBuffer(rowb + 256, zero=True), H.DeviceBuffer(rowb + 256, zero=True)
-    check(L.b200_op_rope_kv_store(Tensor.contiguous(dq.ptr, F32, (D, NH, 1)), Tensor.contiguous(dqo.ptr, F32, (D, NH, 1)), Tensor.contiguous(dk.ptr, F32, (D, HK, 1)),
-                                  Tensor.contiguous(dko.ptr, F32, (D, HK, 1)), Tensor.contiguous(dv.ptr, F32, (D * HK, 1)), d["pos"].ptr, None, C.byref(rp), kv_type,
-                                  kc2.ptr, vc2.ptr, None, None, None))
-    qo = dqo.to_numpy(np.float32, (E,))
-    h = H.mul_mat_vec_q(Q5_K, wo, qo[None], E, E)[0] + x
-    hn = norm(h, nw2)
-    gg, uu = H.mul_mat_vec_q(Q4_K, wg, hn[None], E, FF)[0], H.mul_mat_vec_q(Q4_K, wu, hn[None], E, FF)[0]
-    act = (gg / (1 + np.exp(-gg.astype(np.float64)))).astype(np.float32) * uu
-    out = H.mul_mat_vec_q(Q6_K, wd, act[None], FF, E)[0] + h
 
-    def close(a, b, tol):
-        return float(np.abs(a - b).max() / (np.abs(b).max() + 1e-30)) < tol
-    assert close(got["qo"], qo, 3e-3) and close(got["h"], h, 3e-3) and close(got["act"], act, 5e-3) and close(got["out"], out, 5e-3)
-    assert np.mean(kc.to_numpy(np.uint8, (rowb,)) != kc2.to_numpy(np.uint8, (rowb,))) < 0.05
-    assert np.mean(vc.to_numpy(np.uint8, (rowb,)) != vc2.to_numpy(np.uint8, (rowb,))) < 0.05
+@pytest.mark.parametrize("neox", [0, 2])
+def test_rope_f16_in_place_k_shift(neox):
+    """ROPE over an f16 cache view in place (build_k_shift, src/llama.cpp:10181-10186): equals the f32 kernel on the
+    f16-rounded input, rounded once to f16."""
+    L = lib()
+    D, HK, T = 128, 4, 37
+    rng = np.random.default_rng(3)
+    k16 = rng.standard_normal((T, HK, D)).astype(np.float16)
+    shift = rng.integers(-20, 20, size=T).astype(np.int32)
+    rp = RopeParams(D, neox, 4096, 10000.0, 1.0, 0.0, 1.0, 32.0, 1.0)
+    dk16, dpos = dev(k16), dev(shift)
+    t16 = Tensor.contiguous(dk16.ptr, F16, (D, HK, T))
+    check(L.b200_op_rope(t16, dpos.ptr, None, t16, C.byref(rp), None))
+    got = dk16.to_numpy(np.float16, k16.shape)
+    k32 = k16.astype(np.float32)
+    d32, o32 = dev(k32), H.DeviceBuffer(k32.nbytes + 256, zero=True)
+    check(L.b200_op_rope(Tensor.contiguous(d32.ptr, F32, (D, HK, T)), dpos.ptr, None, Tensor.contiguous(o32.ptr, F32, (D, HK, T)), C.byref(rp), None))
+    exp = o32.to_numpy(np.float32, k32.shape).astype(np.float16)
+    assert np.array_equal(got, exp)
+
+
+def test_cpy_q8_0_to_f32_is_the_reference_dequantisation():
+    """ggml_cast(q8_0 K cache -> f32) of the K-shift graph (src/llama.cpp:10165-10168): bit-exact dequantize_row_q8_0."""
+    L = lib()
+    D, HK, T = 128, 4, 19
+    rng = np.random.default_rng(4)
+    x = rng.standard_normal((T, HK * D)).astype(np.float32)
+    q = np.asarray(O.quantize_rows(Q8_0, x)).view(np.uint8).reshape(T, -1)
+    dq, out = dev(q), H.DeviceBuffer(x.nbytes + 256, zero=True)
+    src = Tensor.contiguous(dq.ptr, Q8_0, (D, HK, T))
+    dst = Tensor.contiguous(out.ptr, F32, (D, HK, T))
+    check(L.b200_op_cpy(src, dst, None))
+    got = out.to_numpy(np.float32, x.shape)
+    exp = np.stack([O.dequantize(Q8_0, r, HK * D) for r in q])
+    assert np.array_equal(got, exp)
 
 
 @pytest.mark.parametrize("n_expert,n_used,n_tok", [(8, 2, 1), (8, 2, 7), (64, 6, 3), (256, 8, 5), (5, 5, 2)])
