@@ -10,7 +10,10 @@ Legs (all printed in ONE JSON line by rank 0):
              position, KQ mask), graph_compute, D2H of the logits (pinned), host argmax feeds the next token (greedy).
   roofline   the decode GEMV family: the token's GEMV launch sequence (same types, shapes and order, rotating weight sets
              larger than L2) timed alone with CUDA events; achieved = algorithmic bytes / time against the measured HBM peak.
-  cpu_baseline  the reference's own CPU backend (oracle/_ref) timed on this box's host cores on a bounded sample.
+  e2e_llamacpp  the same metric with the REFERENCE's unmodified llama.cpp as the host: llama_decode under ggml_backend_sched with
+             libkcpp_b200.so attached by ggml_backend_register, on a GGUF file of the workload (tools/make_gguf.py).
+  cpu_baseline  the reference's own llama.cpp + CPU backend (oracle/_ref) decoding the same GGUF on this box's host cores
+             (bounded sample: 16 tokens at n_kv = 4096).
   tp_70b     auxiliary: BASELINE.json configs[4], ONE Llama-3-70B-shaped Q4_K_M model sharded over all N ranks (strong scaling,
              NCCL all-reduce / all-gather in the captured graph); at N = 1 the same model on one GPU, so 1 -> N speed-up is
              the ratio of the tp_70b values of two runs.
@@ -93,16 +96,88 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# ------------------------------------------------------------------------------------------------ llama.cpp-level legs
+# The reference's own, unmodified llama.cpp (oracle/_ref/libllama_ref*.so + llama_harness, compiled from /root/reference by
+# oracle/Makefile; the binaries travel to the GPU box) decodes the SAME GGUF file: on its CPU backend (reference arm,
+# cpu_baseline) and with libkcpp_b200.so attached through ggml_backend_register (e2e_llamacpp).
+def _cpu_flags() -> set:
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("flags"):
+                return set(line.split(":", 1)[1].split())
+    except OSError:
+        pass
+    return set()
+
+
+def harness_path():
+    ref = ROOT / "oracle" / "_ref"
+    if {"avx512f", "avx512bw", "avx512vl", "avx512dq", "avx512_vnni"} <= _cpu_flags() and (ref / "llama_harness_avx512").exists():
+        return ref / "llama_harness_avx512", "avx512-vnni build"
+    return (ref / "llama_harness"), "avx2 build"
+
+
+def host_threads() -> int:
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def bench_gguf(shape) -> Path:
+    """The workload as a GGUF file (gguf-py writer, tools/make_gguf.py): the configuration's shapes and llama_tensor_get_type mix
+    with random-init quantised blocks (throughput runs need no trained or even reference-quantised values)."""
+    d = Path(os.environ.get("B200_GGUF_CACHE", "/tmp/b200_gguf"))
+    d.mkdir(parents=True, exist_ok=True)
+    out = d / f"bench_{shape.name}.gguf"
+    if not out.exists():
+        sys.path.insert(0, str(ROOT / "tools"))
+        import make_gguf
+        tmp = out.with_suffix(".tmp")
+        make_gguf.build(shape, tmp, None, seed=1234, replicate_layers=True)
+        tmp.rename(out)
+    return out
+
+
+def run_harness(model: Path, backend: str, extra: list, timeout: float = 900.0) -> dict:
+    exe, build = harness_path()
+    if not exe.exists():
+        raise FileNotFoundError(f"{exe} missing (built by oracle/Makefile where /root/reference exists)")
+    cmd = [str(exe), "--model", str(model), "--quiet", "--n-ctx", str(N_CTX)] + [str(x) for x in extra]
+    if backend == "b200":
+        cmd += ["--backend-lib", str(ROOT / "koboldcpp_b200" / "libkcpp_b200.so")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)
+    if r.returncode != 0:
+        raise RuntimeError(f"llama_harness rc={r.returncode}: {r.stderr[-600:]}")
+    j = json.loads(r.stdout.strip().splitlines()[-1])
+    j["build"] = build
+    return j
+
+
+def llamacpp_cpu_decode(shape, n_gen: int, n_warm: int) -> dict:
+    """tg at n_kv = 4096 through llama_decode on the reference CPU backend with all host threads.  The KV cache is brought to
+    N_PREFILLED occupied cells by the harness (--kv-fill: the prompt's rows repeated through the reference's own session-state
+    format) instead of a 3968-token CPU prompt (~15 tok/s: minutes); the timed decode steps are the real thing."""
+    thr = host_threads()
+    j = run_harness(bench_gguf(shape), "cpu", ["--n-prompt", 32, "--kv-fill", N_PREFILLED, "--n-gen", n_gen, "--n-warm", n_warm, "--threads", thr])
+    return {"tok_s": j["tg_tok_s"], "ms_per_token": 1e3 / j["tg_tok_s"], "cores": j["threads"],
+            "sample": f"reference llama.cpp + ggml CPU backend ({j['build']}), llama_decode on the same GGUF, {j['n_gen']} greedy tokens timed after {n_warm} warm-up "
+                      f"at n_kv={N_CTX} (KV filled to {N_PREFILLED} cells via llama_state_set_data), {j['threads']} threads"}
+
+
 def reference_arm(args, rank: int) -> int:
-    """The reference's own CPU implementation of the path on this box's host cores (see tests/cpu_baseline.py)."""
+    """The reference's own CPU implementation of the path on this box's host cores: its llama.cpp + ggml CPU backend."""
     if rank != 0:
         return 0
-    sys.path.insert(0, str(ROOT / "tests"))
-    import cpu_baseline as B
     from koboldcpp_b200.llama import SHAPES
     shape = SHAPES[WORKLOAD]
-    budget = min(150.0, max(10.0, 1.0 * (args.steps + args.warmup)))
-    r = B.time_decode(shape, N_CTX, budget_s=budget)
+    try:
+        r = llamacpp_cpu_decode(shape, max(4, min(args.steps, 160)), max(1, min(args.warmup, 8)))
+    except Exception as ex:  # the harness is prebuilt in oracle/_ref; fall back to the per-layer sample of the same backend
+        sys.path.insert(0, str(ROOT / "tests"))
+        import cpu_baseline as B
+        r = B.time_decode(shape, N_CTX, budget_s=min(150.0, max(10.0, 1.0 * (args.steps + args.warmup))))
+        r["sample"] += f" [llama.cpp harness unavailable: {ex}]"
     line = {"impl": "reference", "metric": METRIC, "value": r["tok_s"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": r["ms_per_token"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 dot / f32 accumulate",
             "data": "synthetic", "config": config_dict(shape),
@@ -442,14 +517,28 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
         }
         if tp70 is not None:
             line["tp_70b"] = tp70
+        if world == 1 and not args.no_llamacpp:
+            # the same metric through the REFERENCE's host code: unmodified llama.cpp + ggml_backend_sched drive libkcpp_b200.so
+            # (Route 2 attach), host token ids in, host logits out, greedy; real 3968-token prompt in 512-token batches first
+            try:
+                j = run_harness(bench_gguf(shape), "b200", ["--n-prompt", N_PREFILLED, "--n-gen", min(steps, N_CTX - N_PREFILLED - 8), "--n-warm", 3, "--n-batch", PP_BATCH, "--n-ubatch", PP_BATCH])
+                line["e2e_llamacpp"] = {"value": j["tg_tok_s"], "unit": UNIT, "pp_tokens_per_s": j["pp_tok_s"], "n_prompt": j["n_prompt"], "n_gen": j["n_gen"],
+                                        "host": "reference llama.cpp (llama_decode, ggml_backend_sched) with the B200 backend attached by ggml_backend_register",
+                                        "h2d_bytes_per_step": 4 + 4 + 4 * N_CTX * 32 + 4, "d2h_bytes_per_step": 4 * shape.n_vocab}
+            except Exception as ex:
+                line["e2e_llamacpp"] = {"value": None, "unit": UNIT, "error": f"{type(ex).__name__}: {ex}"[:300]}
         if world == 1 and not args.no_cpu:
             try:
-                sys.path.insert(0, str(ROOT / "tests"))
-                import cpu_baseline as B
-                r = B.time_decode(shape, N_CTX, budget_s=args.cpu_budget)
+                r = llamacpp_cpu_decode(shape, 16, 2)
                 line["cpu_baseline"] = {"value": r["tok_s"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"]}
-            except Exception as ex:  # the checker library is prebuilt in oracle/_ref; its absence must not hide the GPU numbers
-                line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
+            except Exception as ex:
+                try:  # per-layer sample of the same compiled reference backend
+                    sys.path.insert(0, str(ROOT / "tests"))
+                    import cpu_baseline as B
+                    r = B.time_decode(shape, N_CTX, budget_s=args.cpu_budget)
+                    line["cpu_baseline"] = {"value": r["tok_s"], "unit": UNIT, "cores": r["cores"], "kind": "reference", "sample": r["sample"] + f" [llama.cpp harness unavailable: {ex}]"[:200]}
+                except Exception as ex2:  # the checker library is prebuilt in oracle/_ref; its absence must not hide the GPU numbers
+                    line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex2}"}
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
@@ -464,6 +553,7 @@ def main() -> int:
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-llamacpp", action="store_true", help="skip the e2e_llamacpp leg (reference llama.cpp driving the B200 backend)")
     ap.add_argument("--cpu-budget", type=float, default=18.0)
     ap.add_argument("--no-tp70", action="store_true", default=bool(os.environ.get("B200_BENCH_NO_TP70")),
                     help="skip the auxiliary 70B tensor-parallel leg (BASELINE.json configs[4])")

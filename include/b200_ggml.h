@@ -61,18 +61,6 @@ B200_API const char *b200_version(void);
  * prefetch then overlaps the tail of its producer.  Off by default; the ggml backend turns it on for its graphs. */
 B200_API void b200_set_pdl(int enabled);
 
-/* Cross-kernel L2 prefetch.  Decode is a chain of dependent, HBM-bound kernels; between two of them (tail of one, launch and
- * activation phase of the next) HBM would idle.  Weights and the KV cache do not depend on the chain, so a kernel can ask the
- * TMA engine to pull the NEXT kernel's operands into the 126 MB L2 (cp.async.bulk.prefetch.L2, SASS UBLKPF) once it has issued
- * its own loads.  The plan set here is consumed by the next launch of b200_mul_mat_vec_q*, b200_mul_mat_id_vec_q,
- * b200_flash_attn_ext or b200_op_rope_kv_store on the calling thread (and cleared).  Regions: 16-byte aligned, readable,
- * at most 4, each below 4 GiB.  Purely a performance hint: results never depend on it. */
-typedef struct {
-    const void *ptr[4];
-    uint32_t    bytes[4];
-} b200_prefetch;
-B200_API void b200_set_next_prefetch(const b200_prefetch *plan);
-
 /* ---- device plumbing (so ctypes / cgo / JNI hosts need no CUDA binding of their own) ------------
  * replaces: ggml_backend_cuda_get_device_count / cudaMalloc / cudaMemcpyAsync call sites in
  * ggml/src/ggml-cuda.cu:3262-3270, 546-560, 471-485 */

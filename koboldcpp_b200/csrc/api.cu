@@ -17,13 +17,6 @@ void set_error(const char *fmt, ...) {
     va_end(ap);
 }
 
-static thread_local PrefetchPlan g_next_pf = {};
-PrefetchPlan take_prefetch() {
-    PrefetchPlan p = g_next_pf;
-    g_next_pf = PrefetchPlan{};
-    return p;
-}
-
 int cuda_fail(cudaError_t e, const char *what) {
     set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
     return B200_ERR_CUDA;
@@ -38,23 +31,6 @@ extern "C" {
 const char *b200_last_error(void) { return g_err; }
 const char *b200_version(void) { return "koboldcpp_b200 0.1 (sm_100a)"; }
 void b200_set_pdl(int enabled) { g_mmvq_pdl = enabled != 0; }
-void b200_set_next_prefetch(const b200_prefetch *plan) {
-    PrefetchPlan p = {};
-    if (plan) {
-        for (int i = 0; i < 4; i++) {
-            // 16-byte granularity: round the start up and the length down (a hint may be shortened, never widened)
-            uintptr_t a = (uintptr_t)plan->ptr[i];
-            uint64_t n = plan->bytes[i];
-            if (!a || n < 32) continue;
-            const uintptr_t a16 = (a + 15) & ~(uintptr_t)15;
-            n -= (a16 - a);
-            n &= ~(uint64_t)15;
-            p.ptr[i] = (const unsigned char *)a16;
-            p.bytes[i] = (unsigned)n;
-        }
-    }
-    g_next_pf = p;
-}
 
 int b200_device_count(void) {
     int n = 0;

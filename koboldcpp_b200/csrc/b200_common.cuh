@@ -129,33 +129,6 @@ __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.p
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
-// ---------------------------------------------------------------- cross-kernel L2 prefetch (include/b200_ggml.h: b200_set_next_prefetch)
-// The plan travels as kernel parameters; `worker` of `n_workers` (one elected lane per warp, or one thread per CTA) issues its
-// share of 8 KB chunks with cp.async.bulk.prefetch.L2 (SASS UBLKPF.L2): fire and forget, no shared memory, no completion.
-struct PrefetchPlan {
-    const unsigned char *ptr[4];
-    unsigned             bytes[4];
-};
-template <unsigned CH = 8192>
-__device__ __forceinline__ void l2_prefetch_issue(const PrefetchPlan &pf, unsigned worker, unsigned n_workers) {
-#pragma unroll
-    for (int r = 0; r < 4; r++) {
-        const unsigned n = pf.bytes[r];
-        if (n == 0) continue;
-        const unsigned nch = (n + CH - 1) / CH;
-        // rotate the starting worker per region so that short regions do not all land on the first workers
-        unsigned c = worker + n_workers - (unsigned)(r * 977u) % n_workers;
-        c = c >= n_workers ? c - n_workers : c;
-        for (; c < nch; c += n_workers) {
-            const unsigned off = c * CH;
-            const unsigned len = n - off < CH ? n - off : CH;
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pf.ptr[r] + off), "r"(len) : "memory");
-        }
-    }
-}
-// host side: the plan for the next launch on this thread (b200_set_next_prefetch), consumed and cleared by take_prefetch()
-PrefetchPlan take_prefetch();
-
 // ---------------------------------------------------------------- cp.async (LDGSTS)
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");

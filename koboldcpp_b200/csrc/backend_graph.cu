@@ -34,8 +34,7 @@ struct Step {
     int gate_idx = 0;                   // ... and which member of `group` is the gate
     int slot = -1, slot2 = -1;          // CPY nodes: index into the slot table, else -1
     bool store_norm = false, store_norm_mul = false;  // STEP_GEMV with a folded norm: this launch also stores the RMS_NORM / MUL values
-    b200_prefetch pf;                   // operands of the next streaming step(s), pulled into L2 by this step's kernel
-    Step() : kind(STEP_NODE), n(nullptr), n2(nullptr) { memset(&pf, 0, sizeof(pf)); }
+    Step() : kind(STEP_NODE), n(nullptr), n2(nullptr) {}
 };
 
 struct CachedGraph {
@@ -269,13 +268,7 @@ static bool match_moe_router(const GraphInfo &gi, int i, const std::vector<char>
 }
 
 // Lower cgraph -> Steps.  `done[i]` marks nodes absorbed by a fused step.
-static void plan_prefetch(std::vector<Step> &steps);
-static void plan_steps_inner(GraphExec *g, const ggml_cgraph *cg);
 static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
-    plan_steps_inner(g, cg);
-    plan_prefetch(g->steps);
-}
-static void plan_steps_inner(GraphExec *g, const ggml_cgraph *cg) {
     std::vector<Step> &steps = g->steps;
     steps.clear();
     const int n = cg->n_nodes;
@@ -470,64 +463,6 @@ static void plan_steps_inner(GraphExec *g, const ggml_cgraph *cg) {
     }
 }
 
-// ------------------------------------------------------------------------------------------------ cross-kernel L2 prefetch
-// Every step that streams weights / KV rows is a prefetch TARGET (its operand byte ranges) and, if its kernel can carry a plan, an
-// ISSUER for the next target: the issuing kernel asks the TMA engine to pull those ranges into L2 after its own loads are out, so
-// HBM does not idle through kernel tails, launch gaps and activation prologues (include/b200_ggml.h: b200_set_next_prefetch).
-static bool quant_mm_node(const ggml_tensor *t) {
-    return t->op == GGML_OP_MUL_MAT && t->src[0] && is_quantized(t->src[0]->type) && !(t->src[0]->buffer && buft_is_b200_split(t->src[0]->buffer->buft));
-}
-static bool step_issues_prefetch(const Step &s) {
-    if (s.kind == STEP_GEMV || s.kind == STEP_ROPE_KV) return true;
-    if (s.kind != STEP_NODE) return false;
-    if (quant_mm_node(s.n)) return s.n->src[1]->ne[1] <= 8;
-    return s.n->op == GGML_OP_MUL_MAT_ID ? s.n->src[2]->ne[0] * s.n->src[2]->ne[1] <= B200_GEMV_MAX_JOBS : s.n->op == GGML_OP_FLASH_ATTN_EXT;
-}
-struct PfRegion { const char *p; size_t n; size_t taken; };
-static void step_regions(const Step &s, std::vector<PfRegion> &out) {
-    out.clear();
-    auto add = [&](const void *p, size_t n) { if (p && n >= 4096) out.push_back(PfRegion{(const char *)p, n, 0}); };
-    if (s.kind == STEP_GEMV) { for (const ggml_tensor *m : s.group) add(m->src[0]->data, nbytes(m->src[0])); return; }
-    if (s.kind != STEP_NODE) return;
-    if (quant_mm_node(s.n)) { add(s.n->src[0]->data, nbytes(s.n->src[0])); return; }
-    if (s.n->op == GGML_OP_FLASH_ATTN_EXT) {
-        for (int q = 1; q <= 2; q++) {
-            const ggml_tensor *kv = s.n->src[q];
-            // [D, n_kv, n_head_kv] view of a cache whose row holds all heads (nb2 < nb1): the rows form one contiguous range
-            const size_t n = kv->nb[2] < kv->nb[1] ? (size_t)kv->ne[1] * kv->nb[1] : nbytes(kv);
-            add(kv->data, n);
-        }
-    }
-}
-static void plan_prefetch(std::vector<Step> &steps) {
-    static const size_t budget_mb = getenv("B200_PF_MB") ? (size_t)atoi(getenv("B200_PF_MB")) : 40;
-    const size_t n = steps.size();
-    if (budget_mb == 0 || n < 2) return;
-    std::vector<std::vector<PfRegion>> regs(n);
-    for (size_t i = 0; i < n; i++) step_regions(steps[i], regs[i]);
-    for (size_t i = 0; i < n; i++) {
-        if (!step_issues_prefetch(steps[i])) continue;
-        // the next target (cyclic: the first kernels of the next token are fed by the last kernels of this one)
-        size_t t = i;
-        for (size_t d = 1; d < n; d++) { const size_t c = (i + d) % n; if (!regs[c].empty()) { t = c; break; } }
-        if (t == i) continue;
-        size_t budget = budget_mb << 20;
-        int slot = 0;
-        for (PfRegion &r : regs[t]) {
-            if (slot >= 4 || budget == 0) break;
-            const size_t left = r.n - r.taken;
-            if (left == 0) continue;
-            size_t take = left < budget ? left : budget;
-            if (take > 0xfffffff0u) take = 0xfffffff0u;
-            steps[i].pf.ptr[slot] = r.p + r.taken;
-            steps[i].pf.bytes[slot] = (uint32_t)take;
-            r.taken += take;
-            budget -= take;
-            slot++;
-        }
-    }
-}
-
 // ------------------------------------------------------------------------------------------------ graph key
 static inline void mix(uint64_t &h, uint64_t v) {
     h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
@@ -563,7 +498,6 @@ static uint64_t graph_key(const ggml_cgraph *cg) {
 
 // ------------------------------------------------------------------------------------------------ execution
 static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
-    if (s.pf.bytes[0] && step_issues_prefetch(s)) b200_set_next_prefetch(&s.pf);
     switch (s.kind) {
         case STEP_NODE:
             run_node(x, s.n, s.slot >= 0 ? (void *const *)(g->slots_dev + s.slot) : nullptr);
@@ -762,9 +696,6 @@ static void dry_compute(GraphExec *g, const ggml_cgraph *cg) {
             if (s.n2) fprintf(stderr, " n2=%s", s.n2->name);
             if (s.silu_mul) fprintf(stderr, " silu_mul=%s", s.silu_mul->name);
             for (const ggml_tensor *ad : s.adds) if (ad) fprintf(stderr, " add=%s", ad->name);
-            size_t pfb = 0;
-            for (int q = 0; q < 4; q++) pfb += s.pf.bytes[q];
-            if (pfb) fprintf(stderr, " prefetch=%.1fMB", pfb / 1048576.0);
             if (s.store_norm_mul) fprintf(stderr, " stores_norm%s", s.store_norm ? "+rms" : "");
             fprintf(stderr, "\n");
         }

@@ -39,7 +39,6 @@ struct FaParams {
     size_t q_nb1, q_nb2, k_nb1, k_nb2, v_nb1, v_nb2, mask_nb1;
     float  scale, max_bias, softcap, m0, m1;
     int    n_head_log2;
-    PrefetchPlan pf;   // operands of the next kernel (b200_set_next_prefetch)
 };
 
 template <int TYPE, int D>
@@ -151,18 +150,6 @@ __global__ void __launch_bounds__(FA_NW * 32, 2) fattn_kernel(const __grid_const
     };
 #pragma unroll
     for (int s = 0; s < FA_NBUF - 1; s++) issue();
-    // when this warp has requested its last tile, its elected lane pulls a share of the next kernel's operands into L2
-    bool pf_done = false;
-    auto maybe_prefetch = [&]() {
-        if (!pf_done && t_issue >= t_end) {
-            if (lane == 0) {
-                const unsigned cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-                l2_prefetch_issue(p.pf, cta * FA_NW + warp, gridDim.x * gridDim.y * gridDim.z * FA_NW);
-            }
-            pf_done = true;
-        }
-    };
-    maybe_prefetch();
 
     // ---- Q for this lane: 8 dims x C columns (f16 path: f32 pre-scaled; q8_0 path: int8 + per-32 scale)
     float qf[C][8];
@@ -220,7 +207,6 @@ __global__ void __launch_bounds__(FA_NW * 32, 2) fattn_kernel(const __grid_const
     int cbuf = 0;
     for (int t = t_begin + warp; t < t_end; t += FA_NW) {
         issue();
-        maybe_prefetch();
         cp_async_wait<FA_NBUF - 1>();
         __syncwarp();
         const unsigned char *kt = my_tiles + (size_t)cbuf * 2 * G::TILE_BYTES;
@@ -579,7 +565,6 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     while (p.n_head_log2 * 2 <= p.n_head) p.n_head_log2 *= 2;
     p.m0 = powf(2.0f, -(a->max_bias) / p.n_head_log2);
     p.m1 = powf(2.0f, -(a->max_bias / 2.0f) / p.n_head_log2);
-    p.pf = take_prefetch();
     const cudaStream_t st = (cudaStream_t)stream;
     const bool pdl = g_mmvq_pdl;
     if (a->type_k == B200_TYPE_F16) {

@@ -147,16 +147,6 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
         act_issue(aregs, p.jobs[jfirst].X, p.norm_w, p.K);
     }
     for (int s = 0; s < n_stage && ik < nmy; s++) issue();
-    // Once this warp has nothing left to request for itself, its elected lane pulls a share of the NEXT kernel's operands into L2:
-    // the requests queue behind our own, so HBM keeps streaming through our tail, the launch gap and the consumer's prologue.
-    bool pf_done = false;
-    auto maybe_prefetch = [&]() {
-        if (!pf_done && ik >= nmy) {
-            if (lane == 0) l2_prefetch_issue(p.pf, (unsigned)(bid * MMVQ_NW + warp), (unsigned)(gridDim.x * MMVQ_NW));
-            pf_done = true;
-        }
-    };
-    maybe_prefetch();
     TRACE(2);
 
     // ---- the ring fill above is independent of the producer kernel's output
@@ -218,7 +208,6 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
                 cstage = cstage + 1 == n_stage ? 0 : cstage + 1;
                 cphase ^= (cstage == 0);
                 if (ik < nmy) issue();
-                maybe_prefetch();
             }
             if (pair) {  // (NCOLS == 1)
                 const float v = warp_sum(acc[0]);
@@ -410,7 +399,6 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
     }
     if ((w_row_bytes & 1) || (expert_bytes & 1)) { set_error("b200_mul_mat_vec_q: odd strides"); return B200_ERR_UNSUPPORTED; }
     p.total_rows = total;
-    p.pf = take_prefetch();
     if (total == 0) return B200_OK;
     if (total > 0x7fffffff) { set_error("b200_mul_mat_vec_q: too many rows"); return B200_ERR_UNSUPPORTED; }
     const bool pdl = g_mmvq_pdl;

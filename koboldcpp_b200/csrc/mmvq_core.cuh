@@ -35,7 +35,6 @@ struct MmvqParams {
     float         *raw_dst[B200_GEMV_MAX_JOBS];
     float         *norm_out, *norm_mul_out;
     float         *gate_out, *up_out, *silu_out;
-    PrefetchPlan   pf;            // operands of the NEXT kernel, pulled into L2 once this CTA has issued its own loads
 };
 
 template <int TYPE>

@@ -236,9 +236,7 @@ __global__ void rope_kernel(TD x, const int32_t *__restrict__ pos, const float *
     }
 }
 
-__global__ void rope_kv_store_kernel(RopeKvDev a, const int32_t *__restrict__ pos, const float *__restrict__ ff, RopeDev rp, PrefetchPlan pf) {
-    // the next kernel (attention) streams the KV cache: start pulling it into L2 before waiting for our own inputs
-    if ((threadIdx.x & 31) == 0) l2_prefetch_issue<32768>(pf, blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), gridDim.x * (blockDim.x >> 5));
+__global__ void rope_kv_store_kernel(RopeKvDev a, const int32_t *__restrict__ pos, const float *__restrict__ ff, RopeDev rp) {
     pdl_enter();
     rope_kv_store_item(a, pos, ff, rp, (int64_t)blockIdx.x * blockDim.x + threadIdx.x);
 }
@@ -685,8 +683,7 @@ extern "C" int b200_op_rope_kv_store(const b200_tensor *q, const b200_tensor *q_
     if (nq + nk == 0) return B200_OK;
     const int64_t total = (nq + 31) / 32 * 32 + 2 * ((nk + 31) / 32 * 32);
     const RopeDev rd = rope_dev(rp);
-    const PrefetchPlan pf = take_prefetch();
-    LAUNCH_PDL(rope_kv_store_kernel, grid1d(total, 256), 256, (cudaStream_t)stream, a, pos, freq_factors, rd, pf);
+    LAUNCH_PDL(rope_kv_store_kernel, grid1d(total, 256), 256, (cudaStream_t)stream, a, pos, freq_factors, rd);
     return B200_OK;
 }
 

@@ -33,11 +33,6 @@ class GemvFuse(C.Structure):
                 ("silu_out", C.c_void_p)]
 
 
-class Prefetch(C.Structure):
-    """b200_prefetch (include/b200_ggml.h)."""
-    _fields_ = [("ptr", C.c_void_p * 4), ("bytes", C.c_uint32 * 4)]
-
-
 class Tensor(C.Structure):
     """b200_tensor (include/b200_ggml_ops.h): ggml-style element counts and byte strides."""
     _fields_ = [("data", C.c_void_p), ("type", C.c_int32), ("_pad", C.c_int32), ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4)]
@@ -69,7 +64,6 @@ _SIGS = {
     "b200_last_error": (C.c_char_p, []),
     "b200_version": (C.c_char_p, []),
     "b200_set_pdl": (None, [C.c_int]),
-    "b200_set_next_prefetch": (None, [C.POINTER(Prefetch)]),
     "b200_device_count": (C.c_int, []),
     "b200_set_device": (C.c_int, [C.c_int]),
     "b200_device_info": (C.c_int, [C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

@@ -29,7 +29,7 @@ static double now_s() { return std::chrono::duration<double>(std::chrono::steady
 
 struct Args {
     std::string model, backend_lib, logits_out, state_save, state_load, split_mode = "none", type_kv = "f16";
-    int ngl = 999, n_prompt = 128, n_gen = 128, n_ctx = 0, threads = 0, fa = 1, n_batch = 512, n_ubatch = 512, main_gpu = 0, shift_at = -1, shift_by = 0;
+    int ngl = 999, n_prompt = 128, n_gen = 128, n_ctx = 0, threads = 0, fa = 1, n_batch = 512, n_ubatch = 512, main_gpu = 0, shift_at = -1, shift_by = 0, n_warm = 0, kv_fill = 0;
     bool quiet = false;
 };
 
@@ -61,6 +61,8 @@ int main(int argc, char **argv) {
         else if (k == "--state-load") a.state_load = val();
         else if (k == "--shift-at") a.shift_at = atoi(val());   // after this many generated tokens: drop `shift-by` oldest cells + K-shift
         else if (k == "--shift-by") a.shift_by = atoi(val());
+        else if (k == "--n-warm") a.n_warm = atoi(val());      // untimed decode steps in front of the n_gen timed ones
+        else if (k == "--kv-fill") a.kv_fill = atoi(val());    // after the prompt: replicate its KV rows so that kv_fill cells are occupied
         else if (k == "--quiet") a.quiet = true;
         else { fprintf(stderr, "unknown argument %s\n", k.c_str()); return 2; }
     }
@@ -92,7 +94,7 @@ int main(int argc, char **argv) {
     const double t_load = now_s() - t_load0;
 
     llama_context_params cp = llama_context_default_params();
-    cp.n_ctx = a.n_ctx > 0 ? a.n_ctx : (uint32_t)(a.n_prompt + a.n_gen + 8);
+    cp.n_ctx = a.n_ctx > 0 ? a.n_ctx : (uint32_t)(std::max(a.n_prompt, a.kv_fill) + a.n_gen + a.n_warm + 8);
     cp.n_batch = a.n_batch;
     cp.n_ubatch = a.n_ubatch;
     if (a.threads > 0) { cp.n_threads = a.threads; cp.n_threads_batch = a.threads; }
@@ -172,10 +174,50 @@ int main(int argc, char **argv) {
         }
     }
 
-    // tg: n_gen single-token decodes (the first generated token came from the prompt logits)
-    const double t1 = now_s();
+    if (a.kv_fill > n_past) {
+        // "KV pre-filled to N cells"  without computing an N-token prompt on the CPU: take the session state
+        // the reference itself serialises (llama_state_get_data, src/llama.cpp:20825-20845: arch, output ids, logits, embeddings, then
+        // cell_count, per-cell {pos, n_seq_id, seq_ids}, v_trans, n_layer, per layer {type, row size, rows} for K and for V), repeat
+        // the prompt's cell rows cyclically up to N cells with positions 0..N-1, and hand it back through llama_state_set_data.
+        std::vector<uint8_t> st(llama_state_get_size(ctx));
+        const size_t got = llama_state_get_data(ctx, st.data(), st.size());
+        size_t off = 0;
+        auto rd32 = [&](size_t o) { uint32_t v; memcpy(&v, st.data() + o, 4); return v; };
+        auto rd64 = [&](size_t o) { uint64_t v; memcpy(&v, st.data() + o, 8); return v; };
+        off += 4 + rd32(off);                         // arch string
+        off += 4 + 4 * (size_t)rd32(off);             // output ids
+        off += 8 + 4 * (size_t)rd64(off);             // logits
+        off += 8 + 4 * (size_t)rd64(off);             // embeddings
+        const size_t hdr_end = off;
+        const uint32_t n0 = rd32(off); off += 4;
+        if ((int)n0 != n_past || got < off) { fprintf(stderr, "--kv-fill: unexpected state layout (cells %u, n_past %d)\n", n0, n_past); return 10; }
+        for (uint32_t i = 0; i < n0; i++) { const uint32_t ns = rd32(off + 4); off += 8 + 4 * (size_t)ns; }
+        const uint32_t v_trans = rd32(off), n_layer = rd32(off + 4); off += 8;
+        if (v_trans) { fprintf(stderr, "--kv-fill needs flash attention (non-transposed V cache)\n"); return 10; }
+        std::vector<uint8_t> out(st.begin(), st.begin() + hdr_end);
+        auto put = [&](const void *p, size_t n) { const uint8_t *b = (const uint8_t *)p; out.insert(out.end(), b, b + n); };
+        const uint32_t N = (uint32_t)a.kv_fill;
+        put(&N, 4);
+        for (uint32_t i = 0; i < N; i++) { const int32_t pos = (int32_t)i; const uint32_t ns = 1; const int32_t sid = 0; put(&pos, 4); put(&ns, 4); put(&sid, 4); }
+        put(&v_trans, 4); put(&n_layer, 4);
+        for (int kv = 0; kv < 2; kv++) {
+            for (uint32_t il = 0; il < n_layer; il++) {
+                const uint64_t row = rd64(off + 4);
+                put(st.data() + off, 12);
+                off += 12;
+                for (uint32_t i = 0; i < N; i++) put(st.data() + off + (size_t)(i % n0) * row, row);
+                off += (size_t)n0 * row;
+            }
+        }
+        if (llama_state_set_data(ctx, out.data(), out.size()) == 0) { fprintf(stderr, "--kv-fill: llama_state_set_data failed\n"); return 10; }
+        n_past = a.kv_fill;
+    }
+
+    // tg: n_gen single-token decodes (the first generated token came from the prompt logits); n_warm untimed ones in front
+    double t1 = now_s();
     int n_dec = 0;
-    for (int g = 0; g < a.n_gen; g++) {
+    for (int g = -a.n_warm; g < a.n_gen; g++) {
+        if (g == 0) { llama_synchronize(ctx); t1 = now_s(); n_dec = 0; }
         if (a.shift_at >= 0 && g == a.shift_at && a.shift_by > 0) {
             // koboldcpp ContextShift: drop the oldest cells, slide the rest (llama_kv_cache_seq_rm + seq_add -> K-shift graph,
             // src/llama.cpp:16530 build_k_shift) -- gpttype_adapter.cpp PurgeMissingTokens / context shifting

