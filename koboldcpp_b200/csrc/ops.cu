@@ -300,9 +300,10 @@ __global__ void cpy_f32_q8_0_kernel(TD src, TD dst, int64_t nblocks, char *const
 
 // q8_0 -> f32 (ggml_cast of a quantised K cache before the K-shift RoPE, src/llama.cpp:10165-10168; reference cpy.cu q8_0->f32):
 // one thread per element of the linear element order; dequantize_row_q8_0 arithmetic (d * q, ggml-quants.c:1617-1632)
-__global__ void cpy_q8_0_f32_kernel(TD src, TD dst, int64_t n) {
+__global__ void cpy_q8_0_f32_kernel(TD src, TD dst, int64_t n, char *const *ind) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (ind) dst.data = *ind;
     const int64_t s0 = i % src.ne[0], s1 = (i / src.ne[0]) % src.ne[1], s2 = (i / (src.ne[0] * src.ne[1])) % src.ne[2],
                   s3 = i / (src.ne[0] * src.ne[1] * src.ne[2]);
     const int64_t d0 = i % dst.ne[0], d1 = (i / dst.ne[0]) % dst.ne[1], d2 = (i / (dst.ne[0] * dst.ne[1])) % dst.ne[2],
@@ -716,9 +717,9 @@ extern "C" int b200_op_cpy_indirect(const b200_tensor *src, const b200_tensor *d
         const int64_t nblk = n / 32;
         cpy_f32_q8_0_kernel<<<grid1d(nblk * 8, 256), 256, 0, st>>>(td(src), td(dst), nblk, ind);
     } else if (s == B200_TYPE_Q8_0 && d == B200_TYPE_F32) {
-        REQUIRE(src->nb[0] == Q8_0_BYTES && src->ne[0] % 32 == 0 && dst->nb[0] == 4 && !ind && ((src->nb[1] | src->nb[2] | src->nb[3] | (uintptr_t)src->data) & 1) == 0,
+        REQUIRE(src->nb[0] == Q8_0_BYTES && src->ne[0] % 32 == 0 && dst->nb[0] == 4 && ((src->nb[1] | src->nb[2] | src->nb[3] | (uintptr_t)src->data) & 1) == 0,
                 B200_ERR_UNSUPPORTED, "b200_op_cpy: q8_0->f32 needs whole 2-byte aligned source blocks");
-        cpy_q8_0_f32_kernel<<<g, 256, 0, st>>>(td(src), td(dst), n);
+        cpy_q8_0_f32_kernel<<<g, 256, 0, st>>>(td(src), td(dst), n, ind);
     } else {
         REQUIRE(false, B200_ERR_UNSUPPORTED, "b200_op_cpy: type pair (%d -> %d) not supported", s, d);
     }
