@@ -22,6 +22,7 @@
 #include "b200_common.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 
 #include "mmvq_core.cuh"
 
@@ -36,11 +37,17 @@ namespace b200 {
 constexpr int MMVQ_MAX_TAB = 1024;  // rows per CTA in MULTI mode (17 bytes each)
 
 #ifdef B200_MMVQ_TRACE
-__device__ unsigned long long g_mmvq_trace[148 * 8];
+// developer timeline: [launch slot][CTA][stamp]; the slot (p.dbg >> 8) is a per-launch counter set by the host, so a captured
+// graph keeps one slot per launch and the whole chain can be read back after a replay (tools/trace_mmvq.py)
+constexpr int TRACE_SLOTS = 256;
+__device__ unsigned long long g_mmvq_trace[TRACE_SLOTS * 148 * 8];
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-#define TRACE(i) do { if (threadIdx.x == 0 && blockIdx.x < 148) g_mmvq_trace[blockIdx.x * 8 + (i)] = gtime(); } while (0)
+#define TRACE(i) do { if (threadIdx.x == 0 && blockIdx.x < 148) g_mmvq_trace[((size_t)(p.dbg >> 8) * 148 + blockIdx.x) * 8 + (i)] = gtime(); } while (0)
+static int g_trace_slot = 0;
+#define TRACE_SLOT(p) do { (p).dbg |= (g_trace_slot++ % TRACE_SLOTS) << 8; } while (0)
 #else
 #define TRACE(i) do {} while (0)
+#define TRACE_SLOT(p) do {} while (0)
 #endif
 
 template <int TYPE, int NCOLS, bool MULTI>
@@ -142,11 +149,15 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
     // when the producer's CTA there has retired, so little overlap is lost.
     const bool acts_first = NCOLS == 1 && p.K <= ACT_RR_MAX && nrows > 0;
     ActRegs aregs;
+    // p.prefill stages of the ring are filled BEFORE the wait for the producer kernel (weights do not depend on it)
+    int s_fill = 0;
+    if (!MULTI || p.ids == nullptr)
+        for (; s_fill < p.prefill && s_fill < n_stage && ik < nmy; s_fill++) issue();
     if (acts_first) {
         pdl_wait();
-        act_issue(aregs, p.jobs[jfirst].X, p.norm_w, p.K);
+        if (!(p.dbg & 1)) act_issue(aregs, p.jobs[jfirst].X, p.norm_w, p.K);
     }
-    for (int s = 0; s < n_stage && ik < nmy; s++) issue();
+    for (; s_fill < n_stage && ik < nmy; s_fill++) issue();
     TRACE(2);
 
     // ---- the ring fill above is independent of the producer kernel's output
@@ -172,7 +183,8 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
             if (loaded_x != nullptr) __syncthreads();  // everyone is done with the previous activations
             // the RMS_NORM / MUL nodes folded into this prologue keep their values: the first CTA stores them once
             float *n_out = bid == 0 && loaded_x == nullptr ? p.norm_out : nullptr, *nm_out = bid == 0 && loaded_x == nullptr ? p.norm_mul_out : nullptr;
-            if (acts_first && loaded_x == nullptr) act_finish(aregs, act_base, p.K, n_it, p.norm_w != nullptr, p.norm_eps, red, n_out, nm_out);
+            if (p.dbg & 1) {}
+            else if (acts_first && loaded_x == nullptr) act_finish(aregs, act_base, p.K, n_it, p.norm_w != nullptr, p.norm_eps, red, n_out, nm_out);
             else load_activations<NCOLS>(act_base, xj, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red, n_out, nm_out);
             __syncthreads();
             loaded_x = xj;
@@ -199,7 +211,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
                 mbar_wait(&my_bars[cstage], cphase);
                 if (k == 0 && it == 0) TRACE(5);
                 const int nblk = it == n_it - 1 ? last_nblk : 4;
-                if ((!MULTI || src != 0) && nblk > 0) {
+                if ((!MULTI || src != 0) && nblk > 0 && !(p.dbg & 2)) {
                     const unsigned mis = ALIGNED16 ? 0u : (unsigned)((src + (size_t)it * G::SEG_BYTES) & 15);
                     SliceDot<TYPE, NCOLS>::run(my_ring + (size_t)cstage * G::STAGE_BYTES + mis, lane, it, act_base, n_it, nblk, acc);
                 }
@@ -239,6 +251,10 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
     __syncthreads();
     TRACE(7);
 }
+
+}  // namespace b200
+#include "mmvq_pair.cuh"
+namespace b200 {
 
 // ------------------------------------------------------------------------------------------------ host side
 static int g_sm_count = 0;
@@ -287,6 +303,11 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     if ((int64_t)ns > steps) ns = (size_t)(steps < 2 ? 2 : steps);
     if (ns > (size_t)MMVQ_MAX_STAGE) ns = MMVQ_MAX_STAGE;
     p.n_stage = (int)ns;
+    static const int prefill_pct = getenv("B200_MMVQ_PREFILL") ? atoi(getenv("B200_MMVQ_PREFILL")) : 0;
+    p.prefill = pdl ? (int)(ns * prefill_pct / 100) : 0;
+    static const int dbg = getenv("B200_MMVQ_DBG") ? atoi(getenv("B200_MMVQ_DBG")) : 0;
+    p.dbg = dbg;
+    TRACE_SLOT(p);
     const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * G::STAGE_BYTES + tab_bytes;
     static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
     int cur_dev = 0;
@@ -313,9 +334,79 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     return B200_OK;
 }
 
+// decode form: two rows per warp step (mmvq_pair.cuh)
+template <int TYPE, bool MULTI>
+static int launch_mmvq_pair(MmvqParams &p, cudaStream_t st, bool pdl) {
+    using G = Geo<TYPE>;
+    int rc = device_props();
+    if (rc) return rc;
+    const size_t bar_bytes = MMVQ_BAR_BYTES;
+    const size_t act_bytes = ((size_t)act_col_bytes(p.n_it) + 127) / 128 * 128;
+    const size_t stage2 = 2 * (size_t)G::STAGE_BYTES;
+    const int64_t units = p.silu_pair ? p.total_rows / 2 : p.total_rows;  // rows, or (gate, up) pairs
+    const int64_t grid = units < g_sm_count ? units : g_sm_count;
+    const int64_t units_per_cta = (units + grid - 1) / grid;
+    const int64_t rows_per_cta = p.silu_pair ? 2 * MMVQ_NW * ((units_per_cta + MMVQ_NW - 1) / MMVQ_NW) : units_per_cta;
+    if (MULTI && rows_per_cta > MMVQ_MAX_TAB) {
+        set_error("b200_mul_mat_vec_q_multi: %lld rows exceed the per-CTA row table", (long long)p.total_rows);
+        return B200_ERR_UNSUPPORTED;
+    }
+    p.tab_rows = MULTI ? (int)((rows_per_cta + 63) / 64 * 64) : 0;
+    const size_t tab_bytes = MULTI ? (size_t)17 * p.tab_rows + 64 : 0;
+    const size_t min_need = bar_bytes + act_bytes + 2 * (size_t)MMVQ_NW * stage2 + tab_bytes + 256;
+    const size_t cap = g_smem_optin;
+    if (min_need > cap) return -1000;  // caller falls back to the one-row-per-step kernel
+    const size_t budget = cap - 256 - tab_bytes;
+    size_t ns = (budget - bar_bytes - act_bytes) / ((size_t)MMVQ_NW * stage2);
+    // no point in more stages than a warp has steps
+    const int64_t rows_per_warp = (rows_per_cta + MMVQ_NW - 1) / MMVQ_NW;
+    const int64_t steps = (rows_per_warp + 1) / 2 * p.n_it;
+    if ((int64_t)ns > steps) ns = (size_t)(steps < 2 ? 2 : steps);
+    if (ns > (size_t)MMVQ_MAX_STAGE) ns = MMVQ_MAX_STAGE;
+    p.n_stage = (int)ns;
+    static const int prefill_pct = getenv("B200_MMVQ_PREFILL") ? atoi(getenv("B200_MMVQ_PREFILL")) : 0;
+    p.prefill = pdl ? (int)(ns * prefill_pct / 100) : 0;
+    static const int dbg = getenv("B200_MMVQ_DBG") ? atoi(getenv("B200_MMVQ_DBG")) : 0;
+    p.dbg = dbg;
+    TRACE_SLOT(p);
+    const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * stage2 + tab_bytes;
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(mmvq_pair_kernel<TYPE, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)(g_smem_optin - 256)));
+        attr_set = true;
+    }
+    p.rows_q = (int)(units / grid);
+    p.rows_rem = (int)(units % grid);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid);
+    cfg.blockDim = dim3(MMVQ_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, mmvq_pair_kernel<TYPE, MULTI>, p));
+    return B200_OK;
+}
+
 template <int TYPE>
 static int dispatch_cols(MmvqParams &p, int N, cudaStream_t st, bool pdl) {
     const bool multi = p.n_jobs > 1 || p.ids != nullptr;
+    static const bool no_pair = getenv("B200_MMVQ_NO_PAIR") != nullptr;
+    if (N == 1 && !no_pair) {
+        bool same_x = true;
+        for (int j = 1; j < p.n_jobs; j++) same_x = same_x && p.jobs[j].X == p.jobs[0].X;
+        if (same_x) {
+            const int rc = multi ? launch_mmvq_pair<TYPE, true>(p, st, pdl) : launch_mmvq_pair<TYPE, false>(p, st, pdl);
+            if (rc != -1000) return rc;
+        }
+    }
     if (multi) {  // fused / expert launches are decode-only: 1..4 columns
         switch (N) {
             case 1: return launch_mmvq<TYPE, 1, true>(p, st, pdl);
@@ -419,7 +510,8 @@ using namespace b200;
 
 #ifdef B200_MMVQ_TRACE
 extern "C" __attribute__((visibility("default"))) int b200_mmvq_trace(unsigned long long *out) {
-    B200_CUDA_TRY(cudaMemcpyFromSymbol(out, g_mmvq_trace, sizeof(unsigned long long) * 148 * 8));
+    B200_CUDA_TRY(cudaMemcpyFromSymbol(out, g_mmvq_trace, sizeof(unsigned long long) * TRACE_SLOTS * 148 * 8));
+    g_trace_slot = 0;
     return B200_OK;
 }
 #endif

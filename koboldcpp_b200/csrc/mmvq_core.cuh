@@ -14,6 +14,8 @@ struct MmvqParams {
     b200_gemv_job  jobs[B200_GEMV_MAX_JOBS];
     int            n_jobs;
     int            n_stage;
+    int            dbg;
+    int            prefill;       // ring stages filled before griddepcontrol.wait
     int            n_it;          // ceil(K / 4096): steps per row
     int            n_expert;
     int            rows_q, rows_rem;   // rows per CTA = rows_q (+1 for the first rows_rem CTAs)
@@ -487,6 +489,220 @@ struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
                     const float d8 = reinterpret_cast<const float *>(a.d)[o], s8 = reinterpret_cast<const float *>(a.s)[o];
                     acc[n] += d * (d8 * (float)s - 8.0f * s8);  // sum (v-8)*u*d8 = d8*sum(v*u) - 8*s8  (vecdotq.cuh:23-42)
                 }
+            }
+        }
+    }
+};
+
+// ------------------------------------------------------------------------------------------------ row dots on preloaded activations
+// One column (decode), several weight rows per step: the lane's 128 activations of step `it` are loaded into registers ONCE
+// (LaneActs) and contracted with the same 128-weight slice of every row of the step.  Same arithmetic, in the same order, as
+// SliceDot<TYPE, 1>: results are bit-identical.
+struct LaneActs {
+    int4   u[8];   // 8 x 16 int8
+    float4 d8;     // q8_1 d of the 4 blocks
+    float4 s8;     // q8_1 s of the 4 blocks      (types with an offset/min term)
+    int4   g;      // 16-wide integer sums          (q6_K)
+};
+template <int TYPE>
+__device__ __forceinline__ void lane_acts_load(LaneActs &A, unsigned char *act_base, int n_it, int it, int lane) {
+    const ActView a = act_view(act_base, n_it, 0);
+#pragma unroll
+    for (int j = 0; j < 8; j++) A.u[j] = a.q[((it * 8 + j) * 32) + lane];
+    A.d8 = a.d[it * 32 + lane];
+    if constexpr (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K || TYPE == B200_TYPE_Q4_0) A.s8 = a.s[it * 32 + lane];
+    if constexpr (TYPE == B200_TYPE_Q6_K) A.g = a.g[it * 32 + lane];
+}
+
+template <int TYPE>
+struct RowDot;
+
+template <>
+struct RowDot<B200_TYPE_Q4_K> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int /*nblk*/, float &acc) {
+        const unsigned char *b = seg + (lane >> 1) * Q4_K_BYTES;
+        const int h = lane & 1;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(b);
+        const float d = h2f((unsigned short)(hdr.x & 0xffff)), dmin = h2f((unsigned short)(hdr.x >> 16));
+        unsigned scw, mnw;
+        if (h == 0) {
+            scw = hdr.y & 0x3f3f3f3fu;
+            mnw = hdr.z & 0x3f3f3f3fu;
+        } else {
+            scw = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+            mnw = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+        }
+        const uint4 *qp = reinterpret_cast<const uint4 *>(b + 16 + 64 * h);
+        unsigned v[16];
+        *reinterpret_cast<uint4 *>(v + 0)  = qp[0];
+        *reinterpret_cast<uint4 *>(v + 4)  = qp[1];
+        *reinterpret_cast<uint4 *>(v + 8)  = qp[2];
+        *reinterpret_cast<uint4 *>(v + 12) = qp[3];
+        int sumi[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int cc = 0; cc < 2; cc++) {
+#pragma unroll
+            for (int hq = 0; hq < 2; hq++) {
+                const int4 ulo = A.u[(2 * cc) * 2 + hq];
+                const int4 uhi = A.u[(2 * cc + 1) * 2 + hq];
+                const unsigned *w = v + 8 * cc + 4 * hq;
+                sumi[2 * cc]     = dp4a((int)(w[0] & 0x0f0f0f0fu), ulo.x, sumi[2 * cc]);
+                sumi[2 * cc]     = dp4a((int)(w[1] & 0x0f0f0f0fu), ulo.y, sumi[2 * cc]);
+                sumi[2 * cc]     = dp4a((int)(w[2] & 0x0f0f0f0fu), ulo.z, sumi[2 * cc]);
+                sumi[2 * cc]     = dp4a((int)(w[3] & 0x0f0f0f0fu), ulo.w, sumi[2 * cc]);
+                sumi[2 * cc + 1] = dp4a_u(w[0] & 0xf0f0f0f0u, uhi.x, sumi[2 * cc + 1]);
+                sumi[2 * cc + 1] = dp4a_u(w[1] & 0xf0f0f0f0u, uhi.y, sumi[2 * cc + 1]);
+                sumi[2 * cc + 1] = dp4a_u(w[2] & 0xf0f0f0f0u, uhi.z, sumi[2 * cc + 1]);
+                sumi[2 * cc + 1] = dp4a_u(w[3] & 0xf0f0f0f0u, uhi.w, sumi[2 * cc + 1]);
+            }
+        }
+        sumi[1] >>= 4;
+        sumi[3] >>= 4;
+        const float4 d8 = A.d8, s8 = A.s8;
+        const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
+                         d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
+        const float sm = s8.x * (float)(mnw & 0xff) + s8.y * (float)((mnw >> 8) & 0xff) + s8.z * (float)((mnw >> 16) & 0xff) +
+                         s8.w * (float)(mnw >> 24);
+        acc += d * sd - dmin * sm;
+    }
+};
+
+template <>
+struct RowDot<B200_TYPE_Q5_K> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int /*nblk*/, float &acc) {
+        const unsigned char *b = seg + (lane >> 1) * Q5_K_BYTES;
+        const int h = lane & 1;
+        const uint4 hdr = *reinterpret_cast<const uint4 *>(b);
+        const float d = h2f((unsigned short)(hdr.x & 0xffff)), dmin = h2f((unsigned short)(hdr.x >> 16));
+        unsigned scw, mnw;
+        if (h == 0) {
+            scw = hdr.y & 0x3f3f3f3fu;
+            mnw = hdr.z & 0x3f3f3f3fu;
+        } else {
+            scw = (hdr.w & 0x0f0f0f0fu) | ((hdr.y >> 2) & 0x30303030u);
+            mnw = ((hdr.w >> 4) & 0x0f0f0f0fu) | ((hdr.z >> 2) & 0x30303030u);
+        }
+        unsigned qh[8], v[16];
+        *reinterpret_cast<uint4 *>(qh + 0) = *reinterpret_cast<const uint4 *>(b + 16);
+        *reinterpret_cast<uint4 *>(qh + 4) = *reinterpret_cast<const uint4 *>(b + 32);
+        const uint4 *qp = reinterpret_cast<const uint4 *>(b + 48 + 64 * h);
+        *reinterpret_cast<uint4 *>(v + 0)  = qp[0];
+        *reinterpret_cast<uint4 *>(v + 4)  = qp[1];
+        *reinterpret_cast<uint4 *>(v + 8)  = qp[2];
+        *reinterpret_cast<uint4 *>(v + 12) = qp[3];
+        int sumi[4] = {0, 0, 0, 0};
+#pragma unroll
+        for (int cc = 0; cc < 2; cc++) {
+#pragma unroll
+            for (int hq = 0; hq < 2; hq++) {
+                const int4 ulo = A.u[(2 * cc) * 2 + hq];
+                const int4 uhi = A.u[(2 * cc + 1) * 2 + hq];
+                const int ul[4] = {ulo.x, ulo.y, ulo.z, ulo.w}, uh[4] = {uhi.x, uhi.y, uhi.z, uhi.w};
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const unsigned w = v[8 * cc + 4 * hq + i], hb = qh[4 * hq + i] >> (4 * h + 2 * cc);
+                    sumi[2 * cc]     = dp4a((int)((w & 0x0f0f0f0fu) | ((hb << 4) & 0x10101010u)), ul[i], sumi[2 * cc]);
+                    sumi[2 * cc + 1] = dp4a((int)(((w >> 4) & 0x0f0f0f0fu) | ((hb << 3) & 0x10101010u)), uh[i], sumi[2 * cc + 1]);
+                }
+            }
+        }
+        const float4 d8 = A.d8, s8 = A.s8;
+        const float sd = d8.x * (float)(sumi[0] * (int)(scw & 0xff)) + d8.y * (float)(sumi[1] * (int)((scw >> 8) & 0xff)) +
+                         d8.z * (float)(sumi[2] * (int)((scw >> 16) & 0xff)) + d8.w * (float)(sumi[3] * (int)(scw >> 24));
+        const float sm = s8.x * (float)(mnw & 0xff) + s8.y * (float)((mnw >> 8) & 0xff) + s8.z * (float)((mnw >> 16) & 0xff) +
+                         s8.w * (float)(mnw >> 24);
+        acc += d * sd - dmin * sm;
+    }
+};
+
+template <>
+struct RowDot<B200_TYPE_Q6_K> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int /*nblk*/, float &acc) {
+        const unsigned char *b = seg + (lane >> 1) * Q6_K_BYTES;
+        const int h = lane & 1;
+        unsigned ql[16], qh[8], scw[2];
+        lds_words<16>(b + 64 * h, ql);
+        lds_words<8>(b + 128 + 32 * h, qh);
+        lds_words<2>(b + 192 + 8 * h, scw);
+        const float d = h2f(*reinterpret_cast<const unsigned short *>(b + 208));
+        const signed char *sc = reinterpret_cast<const signed char *>(scw);
+        const float d8v[4] = {A.d8.x, A.d8.y, A.d8.z, A.d8.w};
+        const int gv[4] = {A.g.x, A.g.y, A.g.z, A.g.w};
+        float sd = 0.f;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const int4 u0 = A.u[r * 2 + 0], u1 = A.u[r * 2 + 1];
+            const int ua[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+            int s0 = 0, s1 = 0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const unsigned l = r & 1 ? ql[8 + i] : ql[i], hb = qh[i];
+                unsigned q;  // row-group r (= q8_1 block r of this slice), word i (ggml-quants.c:2990-2999)
+                if (r == 0)      q = (l & 0x0f0f0f0fu) | ((hb << 4) & 0x30303030u);
+                else if (r == 1) q = (l & 0x0f0f0f0fu) | ((hb << 2) & 0x30303030u);
+                else if (r == 2) q = ((l >> 4) & 0x0f0f0f0fu) | (hb & 0x30303030u);
+                else             q = ((l >> 4) & 0x0f0f0f0fu) | ((hb >> 2) & 0x30303030u);
+                if (i < 4) s0 = dp4a((int)q, ua[i], s0);
+                else       s1 = dp4a((int)q, ua[i], s1);
+            }
+            s0 -= 32 * (int)(short)(gv[r] & 0xffff);
+            s1 -= 32 * (gv[r] >> 16);
+            sd += d8v[r] * (float)(s0 * (int)sc[2 * r] + s1 * (int)sc[2 * r + 1]);
+        }
+        acc += d * sd;
+    }
+};
+
+template <>
+struct RowDot<B200_TYPE_Q8_0> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int nblk, float &acc) {
+        const unsigned char *b = seg + lane * (4 * Q8_0_BYTES);
+        const float d8v[4] = {A.d8.x, A.d8.y, A.d8.z, A.d8.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+                const unsigned char *bk = b + k * Q8_0_BYTES;
+                const float d = h2f(*reinterpret_cast<const unsigned short *>(bk));
+                unsigned w[8];
+                lds_words<8>(bk + 2, w);
+                const int4 u0 = A.u[k * 2 + 0], u1 = A.u[k * 2 + 1];
+                int s = dp4a((int)w[0], u0.x, 0);
+                s = dp4a((int)w[1], u0.y, s);
+                s = dp4a((int)w[2], u0.z, s);
+                s = dp4a((int)w[3], u0.w, s);
+                s = dp4a((int)w[4], u1.x, s);
+                s = dp4a((int)w[5], u1.y, s);
+                s = dp4a((int)w[6], u1.z, s);
+                s = dp4a((int)w[7], u1.w, s);
+                acc += d * d8v[k] * (float)s;
+            }
+        }
+    }
+};
+
+template <>
+struct RowDot<B200_TYPE_Q4_0> {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int nblk, float &acc) {
+        const unsigned char *b = seg + lane * (4 * Q4_0_BYTES);
+        const float d8v[4] = {A.d8.x, A.d8.y, A.d8.z, A.d8.w}, s8v[4] = {A.s8.x, A.s8.y, A.s8.z, A.s8.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+                const unsigned char *bk = b + k * Q4_0_BYTES;
+                const float d = h2f(*reinterpret_cast<const unsigned short *>(bk));
+                unsigned w[4];
+                lds_words<4>(bk + 2, w);
+                const int4 u0 = A.u[k * 2 + 0], u1 = A.u[k * 2 + 1];
+                int s = dp4a((int)(w[0] & 0x0f0f0f0fu), u0.x, 0);
+                s = dp4a((int)(w[1] & 0x0f0f0f0fu), u0.y, s);
+                s = dp4a((int)(w[2] & 0x0f0f0f0fu), u0.z, s);
+                s = dp4a((int)(w[3] & 0x0f0f0f0fu), u0.w, s);
+                int sh = dp4a_u(w[0] & 0xf0f0f0f0u, u1.x, 0);
+                sh = dp4a_u(w[1] & 0xf0f0f0f0u, u1.y, sh);
+                sh = dp4a_u(w[2] & 0xf0f0f0f0u, u1.z, sh);
+                sh = dp4a_u(w[3] & 0xf0f0f0f0u, u1.w, sh);
+                s += sh >> 4;
+                acc += d * (d8v[k] * (float)s - 8.0f * s8v[k]);
             }
         }
     }
