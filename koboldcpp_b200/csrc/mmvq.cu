@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq_kernel(const __grid_cons
 }
 
 }  // namespace b200
-#include "mmvq_pair.cuh"
+#include "mmvq3.cuh"
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -334,49 +334,49 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
     return B200_OK;
 }
 
-// decode form: two rows per warp step (mmvq_pair.cuh)
+// decode form, lean skeleton (mmvq3.cuh)
 template <int TYPE, bool MULTI>
-static int launch_mmvq_pair(MmvqParams &p, cudaStream_t st, bool pdl) {
-    using G = Geo<TYPE>;
+static int launch_mmvq3(MmvqParams &p, cudaStream_t st, bool pdl) {
+    using G3 = Geo3<TYPE>;
     int rc = device_props();
     if (rc) return rc;
+    if (p.n_it > 8) return -1000;  // K > 32768: fewer than two warps per slice; the one-row kernel handles it
+    const bool nit1 = p.n_it == 1;
+    const int grp = MMVQ_NW / p.n_it, n_ring = nit1 ? MMVQ_NW : grp * p.n_it;  // warps per K-slice, warps that stream
     const size_t bar_bytes = MMVQ_BAR_BYTES;
     const size_t act_bytes = ((size_t)act_col_bytes(p.n_it) + 127) / 128 * 128;
-    const size_t stage2 = 2 * (size_t)G::STAGE_BYTES;
     const int64_t units = p.silu_pair ? p.total_rows / 2 : p.total_rows;  // rows, or (gate, up) pairs
     const int64_t grid = units < g_sm_count ? units : g_sm_count;
     const int64_t units_per_cta = (units + grid - 1) / grid;
-    const int64_t rows_per_cta = p.silu_pair ? 2 * MMVQ_NW * ((units_per_cta + MMVQ_NW - 1) / MMVQ_NW) : units_per_cta;
-    if (MULTI && rows_per_cta > MMVQ_MAX_TAB) {
-        set_error("b200_mul_mat_vec_q_multi: %lld rows exceed the per-CTA row table", (long long)p.total_rows);
-        return B200_ERR_UNSUPPORTED;
-    }
-    p.tab_rows = MULTI ? (int)((rows_per_cta + 63) / 64 * 64) : 0;
-    const size_t tab_bytes = MULTI ? (size_t)17 * p.tab_rows + 64 : 0;
-    const size_t min_need = bar_bytes + act_bytes + 2 * (size_t)MMVQ_NW * stage2 + tab_bytes + 256;
-    const size_t cap = g_smem_optin;
-    if (min_need > cap) return -1000;  // caller falls back to the one-row-per-step kernel
-    const size_t budget = cap - 256 - tab_bytes;
-    size_t ns = (budget - bar_bytes - act_bytes) / ((size_t)MMVQ_NW * stage2);
-    // no point in more stages than a warp has steps
-    const int64_t rows_per_warp = (rows_per_cta + MMVQ_NW - 1) / MMVQ_NW;
-    const int64_t steps = (rows_per_warp + 1) / 2 * p.n_it;
-    if ((int64_t)ns > steps) ns = (size_t)(steps < 2 ? 2 : steps);
+    const int64_t part_rows = nit1 ? 0 : (p.silu_pair ? 2 : 1) * units_per_cta;
+    const size_t part_bytes = (size_t)part_rows * p.n_it * 4;
+    const size_t cap = g_smem_optin - 256;
+    if (bar_bytes + act_bytes + part_bytes + 2 * (size_t)n_ring * G3::STAGE2 > cap) return -1000;  // caller falls back to the one-row kernel
+    size_t ns = (cap - bar_bytes - act_bytes - part_bytes) / ((size_t)n_ring * G3::STAGE2);
+    // no point in more stages than a warp has pairs
+    const int64_t per_warp = (units_per_cta + grp - 1) / grp;
+    const int64_t steps = p.silu_pair ? per_warp : (per_warp + 1) / 2;
+    if ((int64_t)ns > steps) ns = (size_t)(steps < 1 ? 1 : steps);
     if (ns > (size_t)MMVQ_MAX_STAGE) ns = MMVQ_MAX_STAGE;
     p.n_stage = (int)ns;
-    static const int prefill_pct = getenv("B200_MMVQ_PREFILL") ? atoi(getenv("B200_MMVQ_PREFILL")) : 0;
-    p.prefill = pdl ? (int)(ns * prefill_pct / 100) : 0;
-    static const int dbg = getenv("B200_MMVQ_DBG") ? atoi(getenv("B200_MMVQ_DBG")) : 0;
+    p.grp = grp;
+    p.part_rows = (int)part_rows;
+    // row segments per warp that go out before griddepcontrol.wait: the activation loads queue behind them on the SM's ingest
+    // path, so small launches (whose critical path is the activation phase) send one, large ones two (measured,
+    // profiles/r02_gemv_prefill_sweep.log)
+    static const int prefill = getenv("B200_MMVQ_PREFILL") ? atoi(getenv("B200_MMVQ_PREFILL")) : -1;
+    p.prefill = !pdl ? 0 : prefill >= 0 ? prefill : (nit1 && steps >= 2 ? 2 : 1);
+    static const int dbg = getenv("B200_MMVQ_DBG") ? atoi(getenv("B200_MMVQ_DBG")) : 0;  // developer knobs: 1 no activation phase, 2 no dot
     p.dbg = dbg;
     TRACE_SLOT(p);
-    const size_t smem = bar_bytes + act_bytes + ns * MMVQ_NW * stage2 + tab_bytes;
-    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    const size_t smem = bar_bytes + act_bytes + ns * n_ring * G3::STAGE2 + part_bytes;
+    auto kern = nit1 ? mmvq3_kernel<TYPE, MULTI, true> : mmvq3_kernel<TYPE, MULTI, false>;
+    static bool attr_set_dev[16][2] = {};  // cudaFuncSetAttribute is per device
     int cur_dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&cur_dev));
-    bool &attr_set = attr_set_dev[cur_dev & 15];
+    bool &attr_set = attr_set_dev[cur_dev & 15][nit1 ? 1 : 0];
     if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(mmvq_pair_kernel<TYPE, MULTI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)(g_smem_optin - 256)));
+        B200_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap));
         attr_set = true;
     }
     p.rows_q = (int)(units / grid);
@@ -391,19 +391,19 @@ static int launch_mmvq_pair(MmvqParams &p, cudaStream_t st, bool pdl) {
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
     cfg.numAttrs = pdl ? 1 : 0;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, mmvq_pair_kernel<TYPE, MULTI>, p));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, p));
     return B200_OK;
 }
 
 template <int TYPE>
 static int dispatch_cols(MmvqParams &p, int N, cudaStream_t st, bool pdl) {
     const bool multi = p.n_jobs > 1 || p.ids != nullptr;
-    static const bool no_pair = getenv("B200_MMVQ_NO_PAIR") != nullptr;
+    static const bool no_pair = getenv("B200_MMVQ_NO_MMVQ3") != nullptr;
     if (N == 1 && !no_pair) {
         bool same_x = true;
         for (int j = 1; j < p.n_jobs; j++) same_x = same_x && p.jobs[j].X == p.jobs[0].X;
         if (same_x) {
-            const int rc = multi ? launch_mmvq_pair<TYPE, true>(p, st, pdl) : launch_mmvq_pair<TYPE, false>(p, st, pdl);
+            const int rc = multi ? launch_mmvq3<TYPE, true>(p, st, pdl) : launch_mmvq3<TYPE, false>(p, st, pdl);
             if (rc != -1000) return rc;
         }
     }

@@ -20,6 +20,7 @@ struct MmvqParams {
     int            n_expert;
     int            rows_q, rows_rem;   // rows per CTA = rows_q (+1 for the first rows_rem CTAs)
     int            tab_rows;           // MULTI: capacity of the per-CTA row table
+    int            grp, part_rows;     // mmvq3 (K > 4096): warps per K-slice, rows of the per-slice partial-sum table
     int64_t        K;
     int64_t        total_rows;
     size_t         w_row_bytes;   // row stride
@@ -156,33 +157,73 @@ __device__ void load_activations(unsigned char *act_base, const float *__restric
 
 // Register-resident, two-phase variant for one column (decode): act_issue() puts every load of the row (and of the norm weights)
 // in flight and returns; act_finish() computes the RMS statistics from the registers, quantises and stores.  The GEMV issues the
-// activation loads BEFORE it fills its weight ring: an SM ingests ~64 B/clk, so a load issued behind 190 KB of bulk copies waits
-// ~1.5 us for its turn (measured with tools/trace_mmvq.py), while issued in front of them it returns in one L2 round trip and the
-// quantisation overlaps the arrival of the weights.
+// activation loads BEFORE it fills (most of) its weight ring: an SM ingests ~64 B/clk, so a load issued behind 190 KB of bulk
+// copies waits ~1.5 us for its turn (measured with tools/trace_mmvq.py), while issued in front of them it returns in one L2 round
+// trip and the quantisation overlaps the arrival of the weights.
+// A thread owns 8 consecutive values (two float4), four lanes one q8_1 block: the per-block work (two IEEE divisions, the
+// reductions, the fp16 roundings) is paid once per 8 values -- the quantisation is replicated in every CTA and sits on the critical
+// path of every launch (1.4 us of a 3.9 us 4096 x 4096 launch when a thread owned 4 values, profiles/r02_gemv_trace_timeline.log).
 constexpr int ACT_RR     = 8;                               // float4 per thread
 constexpr int ACT_RR_MAX = ACT_RR * 4 * MMVQ_THREADS;       // 16384 values
-struct ActRegs {
-    float4 v[ACT_RR];
-    float4 w[ACT_RR];
+template <int RR>
+struct ActRegsT {
+    float4 v[RR];
+    float4 w[RR];
 };
-__device__ __forceinline__ void act_issue(ActRegs &r, const float *__restrict__ x, const float *__restrict__ norm_w, int64_t K) {
+using ActRegs = ActRegsT<ACT_RR>;
+// RR float4 per thread (even): RR * 4 * MMVQ_THREADS >= K (the decode kernel instantiates RR = 2 for K <= 4096)
+template <int RR>
+__device__ __forceinline__ void act_issue(ActRegsT<RR> &r, const float *__restrict__ x, const float *__restrict__ norm_w, int64_t K) {
+    static_assert(RR % 2 == 0, "a thread owns pairs of float4");
     constexpr int NT = MMVQ_THREADS;
-    const int n4 = (int)(K / 4);
+    const int n4 = (int)(K / 4);  // K is a multiple of 32
 #pragma unroll
-    for (int u = 0; u < ACT_RR; u++) {
-        const int i4 = u * NT + threadIdx.x;
-        r.v[u] = i4 < n4 ? __ldcg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int u = 0; u < RR / 2; u++) {
+        const int i4 = 2 * (u * NT + threadIdx.x);
+        if (2 * u * NT < n4) {  // warp-uniform: skip whole batches past the end
+            r.v[2 * u]     = i4 < n4 ? __ldcg(reinterpret_cast<const float4 *>(x) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            r.v[2 * u + 1] = i4 < n4 ? __ldcg(reinterpret_cast<const float4 *>(x) + i4 + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+            r.v[2 * u] = r.v[2 * u + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
     }
     if (norm_w != nullptr) {
 #pragma unroll
-        for (int u = 0; u < ACT_RR; u++) {
-            const int i4 = u * NT + threadIdx.x;
-            r.w[u] = i4 < n4 ? __ldg(reinterpret_cast<const float4 *>(norm_w) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int u = 0; u < RR / 2; u++) {
+            const int i4 = 2 * (u * NT + threadIdx.x);
+            if (2 * u * NT < n4) {
+                r.w[2 * u]     = i4 < n4 ? __ldg(reinterpret_cast<const float4 *>(norm_w) + i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                r.w[2 * u + 1] = i4 < n4 ? __ldg(reinterpret_cast<const float4 *>(norm_w) + i4 + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
         }
     }
 }
+// q8_1 quantisation of one 32-value block held by 4 consecutive lanes (8 values each): same arithmetic as quantize_q8_1_group8
+// (quantize_row_q8_1_ref, ggml-quants.c:1160-1193).  lo / hi: the lane's 8 quantised values; sum16: sum of q over this lane's
+// half of the block (16 values).
+__device__ __forceinline__ void quantize_q8_1_group4(const float4 a, const float4 b, int &lo, int &hi, float &d16, float &s16, int &sum16) {
+    float amax = fmaxf(fmaxf(fmaxf(fabsf(a.x), fabsf(a.y)), fmaxf(fabsf(a.z), fabsf(a.w))),
+                       fmaxf(fmaxf(fabsf(b.x), fabsf(b.y)), fmaxf(fabsf(b.z), fabsf(b.w))));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+    amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+    const float d  = __fdiv_rn(amax, 127.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    const int q0 = (int)roundf(__fmul_rn(a.x, id)), q1 = (int)roundf(__fmul_rn(a.y, id));
+    const int q2 = (int)roundf(__fmul_rn(a.z, id)), q3 = (int)roundf(__fmul_rn(a.w, id));
+    const int q4 = (int)roundf(__fmul_rn(b.x, id)), q5 = (int)roundf(__fmul_rn(b.y, id));
+    const int q6 = (int)roundf(__fmul_rn(b.z, id)), q7 = (int)roundf(__fmul_rn(b.w, id));
+    int s = (q0 + q1 + q2 + q3) + (q4 + q5 + q6 + q7);
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    sum16 = s;
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    d16 = __half2float(__float2half_rn(d));
+    s16 = __half2float(__float2half_rn(__fmul_rn((float)s, d)));
+    lo = (q0 & 0xff) | ((q1 & 0xff) << 8) | ((q2 & 0xff) << 16) | (int)((unsigned)q3 << 24);
+    hi = (q4 & 0xff) | ((q5 & 0xff) << 8) | ((q6 & 0xff) << 16) | (int)((unsigned)q7 << 24);
+}
 // All threads of the CTA call this (it contains CTA barriers when norm is set).
-__device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t K, int n_it, bool norm, float norm_eps, float *red,
+template <int RR>
+__device__ __forceinline__ void act_finish(ActRegsT<RR> &r, unsigned char *p, int64_t K, int n_it, bool norm, float norm_eps, float *red,
                                            float *__restrict__ norm_out = nullptr, float *__restrict__ norm_mul_out = nullptr) {
     constexpr int NT = MMVQ_THREADS;
     const int n4 = (int)(K / 4);
@@ -193,7 +234,7 @@ __device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t
     if (norm) {
         float ss = 0.f;
 #pragma unroll
-        for (int u = 0; u < ACT_RR; u++) ss += r.v[u].x * r.v[u].x + r.v[u].y * r.v[u].y + r.v[u].z * r.v[u].z + r.v[u].w * r.v[u].w;
+        for (int u = 0; u < RR; u++) ss += r.v[u].x * r.v[u].x + r.v[u].y * r.v[u].y + r.v[u].z * r.v[u].z + r.v[u].w * r.v[u].w;
         ss = warp_sum(ss);
         if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
         __syncthreads();
@@ -201,8 +242,9 @@ __device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t
         t = warp_sum(t);
         const float nscale = rsqrtf(t / (float)K + norm_eps);
 #pragma unroll
-        for (int u = 0; u < ACT_RR; u++) {
-            const int i4 = u * NT + threadIdx.x;
+        for (int u = 0; u < RR; u++) {
+            const int i4 = 2 * ((u >> 1) * NT + threadIdx.x) + (u & 1);
+            if ((u & ~1) * NT >= n4) break;  // warp-uniform
             r.v[u].x = r.v[u].x * nscale; r.v[u].y = r.v[u].y * nscale; r.v[u].z = r.v[u].z * nscale; r.v[u].w = r.v[u].w * nscale;
             if (norm_out && i4 < n4) reinterpret_cast<float4 *>(norm_out)[i4] = r.v[u];
             r.v[u].x = r.v[u].x * r.w[u].x; r.v[u].y = r.v[u].y * r.w[u].y; r.v[u].z = r.v[u].z * r.w[u].z; r.v[u].w = r.v[u].w * r.w[u].w;
@@ -210,25 +252,25 @@ __device__ __forceinline__ void act_finish(ActRegs &r, unsigned char *p, int64_t
         }
     }
 #pragma unroll
-    for (int u = 0; u < ACT_RR; u++) {
-        const int i4 = u * NT + threadIdx.x;
-        if (u * NT >= n4) break;  // warp-uniform: the whole batch is past the end
-        const bool active = i4 < n4;
+    for (int u = 0; u < RR / 2; u++) {
+        const int i8 = u * NT + threadIdx.x;  // 8-value group
+        if (2 * u * NT >= n4) break;          // warp-uniform: the whole batch is past the end
+        const bool active = 2 * i8 < n4;
         float d, s;
-        int sum4;
-        const int packed = quantize_q8_1_group8(r.v[u], d, s, sum4);
-        const int hi4 = __shfl_xor_sync(0xffffffffu, sum4, 4);
+        int lo, hi, sum16;
+        quantize_q8_1_group4(r.v[2 * u], r.v[2 * u + 1], lo, hi, d, s, sum16);
+        const int hi16 = __shfl_xor_sync(0xffffffffu, sum16, 2);
         if (active) {
-            const int blk = i4 >> 3, part = i4 & 7;
-            const int slice = blk >> 2, b = blk & 3;
+            const int blk = i8 >> 2, part = i8 & 3;   // q8_1 block, quarter of the block
+            const int slice = blk >> 2, b = blk & 3;  // 128-value slice (one lane's share of a step), block inside it
             const int it = slice >> 5, lane = slice & 31;
-            const int j = b * 2 + (part >> 2);
-            aq[(((it * 8 + j) * 32 + lane) << 2) + (part & 3)] = packed;
+            const int j = b * 2 + (part >> 1);        // int4 inside the slice
+            *reinterpret_cast<int2 *>(&aq[(((it * 8 + j) * 32 + lane) << 2) + 2 * (part & 1)]) = make_int2(lo, hi);
             if (part == 0) {
                 const int o = ((it * 32 + lane) << 2) + b;
                 ad[o] = d;
                 as[o] = s;
-                ag[o] = (sum4 & 0xffff) | (hi4 << 16);  // 16-wide integer sums (q6_K offset term)
+                ag[o] = (sum16 & 0xffff) | (hi16 << 16);  // 16-wide integer sums (q6_K offset term)
             }
         }
     }

@@ -44,7 +44,7 @@ L.check(lib.b200_mmvq_trace(out.ctypes.data))
 tr = out.reshape(256, 148, 8)[:N].astype(np.int64)
 grid = min(148, M)
 tr = tr[:, :grid, :]
-names = ["start", "prologue", "issued", "pdl_wait", "acts", "first_data", "first_row", "end"]
+names = ["start", "prefilled", "pdl_wait", "issued", "acts", "first_data", "first_row", "end"]
 ends = tr[:, :, 7].max(axis=1)
 print(f"type {t} K {K} M {M} {'hot' if hot else 'cold'}: launch period {np.median(np.diff(ends[8:])):.0f} ns; ns relative to the END of the previous launch")
 print(f"  {'stamp':10s} {'min':>7s} {'median':>7s} {'max':>7s}   (median over launches 8..{N - 1} of the per-launch min / median / max over CTAs)")
