@@ -36,6 +36,9 @@ struct FaParams {
     int    D, N, n_head, n_head_kv, n_kv, gqa;
     int    n_cols;     // N * gqa query columns per kv-head
     int    n_splits, tiles_per_split;
+    int    cols_per_cta;  // fattn_mma_kernel: query columns per CTA (<= 16, runtime)
+    int    trace_slot;    // developer timeline (B200_FA_TRACE builds)
+    int    cluster_merge; // fattn_mma_kernel: the n_splits CTAs of a (kv-head, column tile) are one cluster and merge through DSMEM
     size_t q_nb1, q_nb2, k_nb1, k_nb2, v_nb1, v_nb2, mask_nb1;
     float  scale, max_bias, softcap, m0, m1;
     int    n_head_log2;
@@ -402,8 +405,26 @@ __global__ void __launch_bounds__(FA_NW * 32, 2) fattn_kernel(const __grid_const
     }
 }
 
+#ifdef B200_FA_TRACE
+// developer timeline: [launch slot][CTA][stamp] (globaltimer ns), read back by tools/trace_fattn.py
+constexpr int FA_TRACE_SLOTS = 64, FA_TRACE_CTAS = 320;
+__device__ unsigned long long g_fa_trace[FA_TRACE_SLOTS * FA_TRACE_CTAS * 8];
+__device__ __forceinline__ unsigned long long fa_gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define FTRACE(i) do { if (threadIdx.x == 0) { const int cta__ = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z); \
+    if (cta__ < FA_TRACE_CTAS) g_fa_trace[((size_t)p.trace_slot * FA_TRACE_CTAS + cta__) * 8 + (i)] = fa_gtime(); } } while (0)
+static int g_fa_trace_slot = 0;
+#define FTRACE_SLOT(p) do { (p).trace_slot = g_fa_trace_slot++ % FA_TRACE_SLOTS; } while (0)
+#else
+#define FTRACE(i) do {} while (0)
+#define FTRACE_SLOT(p) do {} while (0)
+#endif
+}  // namespace b200
+#include "fattn_mma.cuh"
+namespace b200 {
+
 // ------------------------------------------------------------------------------------------------ host side
 struct FaPlan {
+    bool cluster;  // tensor-core kernel: splits merged through distributed shared memory
     int C, n_ct, n_splits, tiles_per_split;
     size_t part_bytes, ticket_bytes;
 };
@@ -420,9 +441,56 @@ static int fa_sm_count() {
     return sm;
 }
 
+static bool fa_use_mma(const b200_fattn_args *a) {
+    static const bool off = getenv("B200_FA_NO_MMA") != nullptr;  // developer switch: the scalar kernel
+    return !off && a->type_k == B200_TYPE_F16;
+}
+
 static FaPlan fa_plan(const b200_fattn_args *a) {
     FaPlan pl;
     const int64_t n_cols = a->N * (a->n_head / a->n_head_kv);
+    if (fa_use_mma(a)) {
+        // tensor-core kernel: a CTA costs the same for 1..16 columns, so a column tile is as wide as it can be
+        pl.C = (int)(n_cols < FM_MAXC ? n_cols : FM_MAXC);
+        pl.n_ct = (int)((n_cols + pl.C - 1) / pl.C);
+        const int n_tiles = (int)((a->n_kv + FM_TP - 1) / FM_TP);
+        const int64_t pairs = (int64_t)pl.n_ct * a->n_head_kv;
+        const int slots = 2 * fa_sm_count();
+        int best = 1;
+        int64_t best_cost = -1;
+        for (int s = 1; s <= FA_MAX_SPLITS; s++) {
+            const int tps = (n_tiles + s - 1) / s;
+            if (s > 1 && tps < 2 * FM_NW) break;
+            if ((int64_t)(s - 1) * tps >= n_tiles) continue;  // would leave an empty split
+            const int64_t waves = (pairs * s + slots - 1) / slots;
+            const int64_t cost = waves * tps;
+            if (best_cost < 0 || cost * 100 < best_cost * 97) { best = s; best_cost = cost; }
+        }
+        // up to 8 splits merge on chip (one thread-block cluster per (kv-head, column tile)); more splits go through global
+        // memory, which costs ~6 us more: take the best split count <= 8 unless the unrestricted one is much shorter
+        static const bool no_cluster = getenv("B200_FA_NO_CLUSTER") != nullptr;
+        if (best > FM_MAX_CLUSTER && !no_cluster) {
+            int best8 = 1;
+            int64_t cost8 = -1;
+            for (int s = 1; s <= FM_MAX_CLUSTER; s++) {
+                const int tps = (n_tiles + s - 1) / s;
+                if (s > 1 && tps < 2 * FM_NW) break;
+                if ((int64_t)(s - 1) * tps >= n_tiles) continue;
+                const int64_t waves = (pairs * s + slots - 1) / slots;
+                const int64_t cost = waves * tps;
+                if (cost8 < 0 || cost * 100 < cost8 * 97) { best8 = s; cost8 = cost; }
+            }
+            // HBM-bound, a CTA streams a (K, V) tile in ~0.37 us (8 KB at 1/296 of 6.5 TB/s): 16 tiles ~ the 6 us saved
+            if (cost8 - best_cost < 16) best = best8;
+        }
+        pl.n_splits = best;
+        pl.cluster = best > 1 && best <= FM_MAX_CLUSTER && !no_cluster;
+        pl.tiles_per_split = (n_tiles + best - 1) / best;
+        pl.ticket_bytes = ((size_t)pairs * sizeof(int) + 255) / 256 * 256;
+        pl.part_bytes = best > 1 && !pl.cluster ? (size_t)pairs * best * pl.C * (a->D + FA_RS_PAD) * sizeof(float) : 0;
+        return pl;
+    }
+    pl.cluster = false;
     pl.C = n_cols >= 8 ? 8 : n_cols >= 4 ? 4 : n_cols >= 2 ? 2 : 1;
     if (n_cols == 3) pl.C = 4;
     if (n_cols > 4 && n_cols < 8) pl.C = 8;
@@ -493,6 +561,43 @@ static int fa_launch(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool 
     return B200_OK;
 }
 
+template <int D>
+static int fa_launch_mma(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
+    using G = MmaGeo<D>;
+    const size_t smem = (size_t)FM_NW * FM_NBUF * 2 * G::TILE_BYTES;  // >= the merge buffers ((FM_NW + 1) * 16 * (D + 4) + 128 floats)
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_mma_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl.n_splits, (unsigned)p.n_head_kv, (unsigned)pl.n_ct);
+    cfg.blockDim = dim3(FM_NW * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    if (pdl) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    if (pl.cluster) {
+        at[na].id = cudaLaunchAttributeClusterDimension;
+        at[na].val.clusterDim.x = (unsigned)pl.n_splits;
+        at[na].val.clusterDim.y = 1;
+        at[na].val.clusterDim.z = 1;
+        na++;
+    }
+    cfg.attrs = at;
+    cfg.numAttrs = na;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fattn_mma_kernel<D>, p));
+    return B200_OK;
+}
+
 template <int TYPE, int D>
 static int fa_dispatch_c(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
     switch (pl.C) {
@@ -528,6 +633,14 @@ static int fa_check(const b200_fattn_args *a) {
 
 using namespace b200;
 
+#ifdef B200_FA_TRACE
+extern "C" __attribute__((visibility("default"))) int b200_fattn_trace(unsigned long long *out) {
+    B200_CUDA_TRY(cudaMemcpyFromSymbol(out, g_fa_trace, sizeof(unsigned long long) * FA_TRACE_SLOTS * FA_TRACE_CTAS * 8));
+    g_fa_trace_slot = 0;
+    return B200_OK;
+}
+#endif
+
 extern "C" size_t b200_flash_attn_workspace_bytes(const b200_fattn_args *a) {
     if (fa_check(a) != B200_OK) return 0;
     const FaPlan pl = fa_plan(a);
@@ -558,6 +671,9 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     p.gqa = (int)(a->n_head / a->n_head_kv);
     p.n_cols = p.N * p.gqa;
     p.n_splits = pl.n_splits; p.tiles_per_split = pl.tiles_per_split;
+    p.cols_per_cta = pl.C;
+    p.cluster_merge = pl.cluster ? 1 : 0;
+    FTRACE_SLOT(p);
     p.q_nb1 = a->q_nb1; p.q_nb2 = a->q_nb2; p.k_nb1 = a->k_nb1; p.k_nb2 = a->k_nb2; p.v_nb1 = a->v_nb1; p.v_nb2 = a->v_nb2;
     p.mask_nb1 = a->mask_nb1;
     p.scale = a->scale; p.max_bias = a->max_bias; p.softcap = a->logit_softcap;
@@ -567,6 +683,10 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     p.m1 = powf(2.0f, -(a->max_bias / 2.0f) / p.n_head_log2);
     const cudaStream_t st = (cudaStream_t)stream;
     const bool pdl = g_mmvq_pdl;
+    if (fa_use_mma(a)) {
+        if (((uintptr_t)a->q | a->q_nb1 | a->q_nb2) & 7) { set_error("b200_flash_attn_ext: Q must be 8-byte aligned"); return B200_ERR_UNSUPPORTED; }
+        return a->D == 128 ? fa_launch_mma<128>(p, pl, st, pdl) : fa_launch_mma<64>(p, pl, st, pdl);
+    }
     if (a->type_k == B200_TYPE_F16) {
         return a->D == 128 ? fa_dispatch_c<B200_TYPE_F16, 128>(p, pl, st, pdl) : fa_dispatch_c<B200_TYPE_F16, 64>(p, pl, st, pdl);
     }

@@ -9,3 +9,8 @@ nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler
 objs=$(ls build/obj/*.o | grep -v '/mmvq.o')
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o build/libtrace.so $objs build/trace/mmvq.o -lcuda
 echo built build/libtrace.so
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC,-fvisibility=hidden -I include --expt-relaxed-constexpr \
+  -DB200_FA_TRACE -x cu -c koboldcpp_b200/csrc/fattn.cu -o build/trace/fattn.o
+objs=$(ls build/obj/*.o | grep -v '/mmvq.o' | grep -v '/fattn.o')
+nvcc -gencode arch=compute_100a,code=sm_100a -shared -o build/libtrace.so $objs build/trace/mmvq.o build/trace/fattn.o -lcuda
+echo built build/libtrace.so with the attention timeline
