@@ -397,6 +397,14 @@ def product_arm(args, rank: int, world: int, local_rank: int) -> int:
         dist_.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         dist = dist_
     check(L.b200_set_device(local_rank), "set_device")
+    if os.environ.get("B200_BENCH_ONLY_TP70"):  # developer shortcut: the sharded 70B leg alone (not a round bench line)
+        tp70 = tp_leg(rank, world, local_rank, dist, min(args.steps, 32), 3)
+        if rank == 0:
+            print(json.dumps({"tp_70b_only": tp70}))
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
     shape = LL.SHAPES[WORKLOAD]
     steps, warmup = args.steps, max(3, args.warmup)
     t_setup = time.time()

@@ -68,6 +68,20 @@ __device__ __forceinline__ unsigned lds_word_unaligned(const unsigned char *base
     return __funnelshift_r(w[0], w[1], sh);  // sh == 0 -> w[0]
 }
 
+// consecutive 32-bit words from a shared-memory byte run that is only 2-byte aligned
+template <int NW>
+__device__ __forceinline__ void lds_words(const unsigned char *p, unsigned (&out)[NW]) {
+    const unsigned *w = reinterpret_cast<const unsigned *>((uintptr_t)p & ~(uintptr_t)3);
+    const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
+    unsigned prev = w[0];
+#pragma unroll
+    for (int i = 0; i < NW; i++) {
+        const unsigned nxt = w[i + 1];  // one word of over-read at most: stages carry 16 bytes of slack
+        out[i] = __funnelshift_r(prev, nxt, sh);
+        prev = nxt;
+    }
+}
+
 // ---------------------------------------------------------------- q8_1 quantisation of one 32-value block
 // held by 8 consecutive lanes (4 values each).  Arithmetic of quantize_row_q8_1_ref (ggml-quants.c:1160-1193):
 //   d = amax/127, id = d ? 1/d : 0, q = roundf(x*id), y.d = fp16(d), y.s = fp16(sum(q)*d)

@@ -443,7 +443,14 @@ static int fa_sm_count() {
 
 static bool fa_use_mma(const b200_fattn_args *a) {
     static const bool off = getenv("B200_FA_NO_MMA") != nullptr;  // developer switch: the scalar kernel
-    return !off && a->type_k == B200_TYPE_F16;
+    if (off) return false;
+    // q8_0 cache: the tile is dequantised to f16 in shared memory first (~2 instructions per value); that pays as soon as several
+    // query columns share it (GQA group, prompt batch): 32/8 heads @ 32k 67 -> 54 us, but one column per kv-head 28 -> 31 us
+    if (a->type_k == B200_TYPE_Q8_0) return a->N * (a->n_head / a->n_head_kv) >= 2;
+    // a tiny cache with one or two kv-heads (a rank's share under 8-way tensor parallelism: 8 q-heads on 1 kv-head, 2 MB) is
+    // pure latency: the scalar kernel spreads the q-heads over 8x more CTAs and finishes in 10.6 us against 12.6 us here
+    if (a->N == 1 && a->n_head / a->n_head_kv <= 8 && (int64_t)a->n_head_kv * a->n_kv * a->D * 4 < (6 << 20)) return false;
+    return a->type_k == B200_TYPE_F16;
 }
 
 static FaPlan fa_plan(const b200_fattn_args *a) {
@@ -466,25 +473,27 @@ static FaPlan fa_plan(const b200_fattn_args *a) {
             const int64_t cost = waves * tps;
             if (best_cost < 0 || cost * 100 < best_cost * 97) { best = s; best_cost = cost; }
         }
-        // up to 8 splits merge on chip (one thread-block cluster per (kv-head, column tile)); more splits go through global
-        // memory, which costs ~6 us more: take the best split count <= 8 unless the unrestricted one is much shorter
+        // 2, 4, 8 or 16 splits merge on chip (one thread-block cluster per (kv-head, column tile); other sizes pack badly into
+        // the GPCs: 9-CTA clusters ran 32 heads @ 4k in 32.8 us instead of 18.6); more splits go through global memory, which costs
+        // ~6 us more: take the best cluster size unless the unrestricted split count is much shorter
         static const bool no_cluster = getenv("B200_FA_NO_CLUSTER") != nullptr;
-        if (best > FM_MAX_CLUSTER && !no_cluster) {
-            int best8 = 1;
-            int64_t cost8 = -1;
-            for (int s = 1; s <= FM_MAX_CLUSTER; s++) {
+        if (best > 1 && !no_cluster) {
+            int bestc = 0;
+            int64_t costc = -1;
+            for (int s = 2; s <= FM_MAX_CLUSTER; s *= 2) {
                 const int tps = (n_tiles + s - 1) / s;
-                if (s > 1 && tps < 2 * FM_NW) break;
+                if (tps < 2 * FM_NW) break;
                 if ((int64_t)(s - 1) * tps >= n_tiles) continue;
+                if (s == 16 && pairs * s > slots) continue;  // 16-CTA clusters only when all of them are resident at once
                 const int64_t waves = (pairs * s + slots - 1) / slots;
                 const int64_t cost = waves * tps;
-                if (cost8 < 0 || cost * 100 < cost8 * 97) { best8 = s; cost8 = cost; }
+                if (costc < 0 || cost * 100 < costc * 97) { bestc = s; costc = cost; }
             }
             // HBM-bound, a CTA streams a (K, V) tile in ~0.37 us (8 KB at 1/296 of 6.5 TB/s): 16 tiles ~ the 6 us saved
-            if (cost8 - best_cost < 16) best = best8;
+            if (bestc > 0 && costc - best_cost < 16) best = bestc;
         }
         pl.n_splits = best;
-        pl.cluster = best > 1 && best <= FM_MAX_CLUSTER && !no_cluster;
+        pl.cluster = best > 1 && best <= FM_MAX_CLUSTER && (best & (best - 1)) == 0 && !no_cluster;
         pl.tiles_per_split = (n_tiles + best - 1) / best;
         pl.ticket_bytes = ((size_t)pairs * sizeof(int) + 255) / 256 * 256;
         pl.part_bytes = best > 1 && !pl.cluster ? (size_t)pairs * best * pl.C * (a->D + FA_RS_PAD) * sizeof(float) : 0;
@@ -561,16 +570,19 @@ static int fa_launch(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool 
     return B200_OK;
 }
 
-template <int D>
+template <int TYPE, int D>
 static int fa_launch_mma(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
-    using G = MmaGeo<D>;
-    const size_t smem = (size_t)FM_NW * FM_NBUF * 2 * G::TILE_BYTES;  // >= the merge buffers ((FM_NW + 1) * 16 * (D + 4) + 128 floats)
+    using G = MmaGeo<TYPE, D>;
+    size_t smem = (size_t)FM_NW * G::WARP_BYTES;
+    const size_t merge = ((size_t)(FM_NW + 1) * FM_MAXC * (D + FA_RS_PAD) + 2 * FM_MAXC * FM_MAX_CLUSTER + 2 * FM_MAXC * FA_MAX_SPLITS) * sizeof(float);
+    if (merge > smem) smem = merge;
     static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
     int cur_dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&cur_dev));
     bool &attr_set = attr_set_dev[cur_dev & 15];
     if (!attr_set) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_mma_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_mma_kernel<TYPE, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_mma_kernel<TYPE, D>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         attr_set = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -594,7 +606,7 @@ static int fa_launch_mma(const FaParams &p, const FaPlan &pl, cudaStream_t st, b
     }
     cfg.attrs = at;
     cfg.numAttrs = na;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fattn_mma_kernel<D>, p));
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fattn_mma_kernel<TYPE, D>, p));
     return B200_OK;
 }
 
@@ -685,7 +697,8 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     const bool pdl = g_mmvq_pdl;
     if (fa_use_mma(a)) {
         if (((uintptr_t)a->q | a->q_nb1 | a->q_nb2) & 7) { set_error("b200_flash_attn_ext: Q must be 8-byte aligned"); return B200_ERR_UNSUPPORTED; }
-        return a->D == 128 ? fa_launch_mma<128>(p, pl, st, pdl) : fa_launch_mma<64>(p, pl, st, pdl);
+        if (a->type_k == B200_TYPE_Q8_0) return a->D == 128 ? fa_launch_mma<B200_TYPE_Q8_0, 128>(p, pl, st, pdl) : fa_launch_mma<B200_TYPE_Q8_0, 64>(p, pl, st, pdl);
+        return a->D == 128 ? fa_launch_mma<B200_TYPE_F16, 128>(p, pl, st, pdl) : fa_launch_mma<B200_TYPE_F16, 64>(p, pl, st, pdl);
     }
     if (a->type_k == B200_TYPE_F16) {
         return a->D == 128 ? fa_dispatch_c<B200_TYPE_F16, 128>(p, pl, st, pdl) : fa_dispatch_c<B200_TYPE_F16, 64>(p, pl, st, pdl);

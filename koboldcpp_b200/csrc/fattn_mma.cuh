@@ -21,13 +21,21 @@ constexpr int FM_NW   = 4;    // warps per CTA
 constexpr int FM_NBUF = 3;    // tiles in the per-warp ring
 constexpr int FM_TP   = 16;   // KV rows per tile
 constexpr int FM_MAXC = 16;   // query columns per CTA
-constexpr int FM_MAX_CLUSTER = 8;  // splits merged on chip (portable cluster size)
+constexpr int FM_MAX_CLUSTER = 16;  // splits merged on chip (cluster sizes above 8 are "non-portable": B200 schedules them)
 
-template <int D>
+template <int TYPE, int D>
 struct MmaGeo {
-    static constexpr int ROW_BYTES  = D * 2;
+    static constexpr bool Q8        = TYPE == B200_TYPE_Q8_0;
+    static constexpr int ROW_BYTES  = D * 2;           // f16 tile (what ldmatrix reads)
     static constexpr int ROW_STRIDE = ROW_BYTES + 16;  // ldmatrix: 8 rows x 16 bytes must hit 8 different bank groups
     static constexpr int TILE_BYTES = FM_TP * ROW_STRIDE;
+    // q8_0 cache: the ring holds raw rows (D/32 blocks of 34 bytes, 8- or 4-byte aligned); a warp dequantises the tile it is
+    // about to use into ONE f16 tile pair of its own
+    static constexpr int RAW_ROW    = D / 32 * Q8_0_BYTES;
+    static constexpr int RAW_STRIDE = (RAW_ROW + 15) / 16 * 16 + 8;
+    static constexpr int RAW_TILE   = (FM_TP * RAW_STRIDE + 16 + 127) / 128 * 128;
+    static constexpr int RING_TILE  = Q8 ? RAW_TILE : TILE_BYTES;                                  // one K or V tile in the ring
+    static constexpr int WARP_BYTES = FM_NBUF * 2 * RING_TILE + (Q8 ? 2 * TILE_BYTES : 0);         // ring (+ f16 scratch pair)
 };
 
 __device__ __forceinline__ void ldsm_x4(unsigned addr, unsigned &r0, unsigned &r1, unsigned &r2, unsigned &r3) {
@@ -63,7 +71,7 @@ __device__ __forceinline__ float ld_cluster_f32(const float *local, unsigned ran
 // copy rows [row0, row0+16) of one head (f16, D values) into a padded tile; rows >= n_kv are zero-filled
 template <int D>
 __device__ __forceinline__ void mma_load_tile(unsigned char *dst, const unsigned char *base, size_t nb1, int row0, int n_kv, int lane) {
-    using G = MmaGeo<D>;
+    using G = MmaGeo<B200_TYPE_F16, D>;
     constexpr int CPR = G::ROW_BYTES / 16;       // 16-byte chunks per row
     constexpr int RPP = 32 / CPR;                // rows per pass of the warp
     const int c = lane % CPR, r0 = lane / CPR;
@@ -78,9 +86,65 @@ __device__ __forceinline__ void mma_load_tile(unsigned char *dst, const unsigned
     }
 }
 
+// q8_0: copy raw rows [row0, row0+16) of one head; rows >= n_kv are zero-filled (d = 0, q = 0: dequantises to zeros)
 template <int D>
+__device__ __forceinline__ void mma_load_tile_q8(unsigned char *dst, const unsigned char *base, size_t nb1, int row0, int n_kv, int lane) {
+    using G = MmaGeo<B200_TYPE_Q8_0, D>;
+    constexpr int CH = G::RAW_ROW % 8 == 0 ? 8 : 4;  // D = 128: 136 = 17 x 8; D = 64: 68 = 17 x 4
+    constexpr int CPR = G::RAW_ROW / CH;
+    for (int i = lane; i < FM_TP * CPR; i += 32) {
+        const int r = i / CPR, c = i - r * CPR;
+        unsigned char *d = dst + r * G::RAW_STRIDE + c * CH;
+        if (row0 + r < n_kv) {
+            if constexpr (CH == 8) cp_async8(d, base + (size_t)(row0 + r) * nb1 + c * CH);
+            else cp_async4(d, base + (size_t)(row0 + r) * nb1 + c * CH);
+        } else {
+            if constexpr (CH == 8) *reinterpret_cast<uint2 *>(d) = make_uint2(0, 0);
+            else *reinterpret_cast<unsigned *>(d) = 0u;
+        }
+    }
+}
+// four int8 (one word) -> two half2 (exact): (s ^ 0x80) is u = s + 128; 0x6400 | u is the half 1024 + u; minus 1152
+__device__ __forceinline__ void i8x4_to_h2x2(unsigned w, __half2 &lo, __half2 &hi) {
+    const unsigned u = w ^ 0x80808080u;
+    const unsigned a = __byte_perm(u, 0x64646464u, 0x4140), b = __byte_perm(u, 0x64646464u, 0x4342);
+    const __half2 off = __floats2half2_rn(1152.0f, 1152.0f);
+    lo = __hsub2(*reinterpret_cast<const __half2 *>(&a), off);
+    hi = __hsub2(*reinterpret_cast<const __half2 *>(&b), off);
+}
+// dequantise one raw q8_0 tile (16 rows x D/32 blocks) into an f16 tile: value = fp16(d * q) (one f16 rounding, 2^-11 relative)
+template <int D>
+__device__ __forceinline__ void mma_dequant_tile_q8(unsigned char *dst, const unsigned char *raw, int lane) {
+    using G = MmaGeo<B200_TYPE_Q8_0, D>;
+    constexpr int NB = D / 32;
+#pragma unroll
+    for (int i = 0; i < FM_TP * NB / 32; i++) {
+        const int idx = lane + 32 * i;
+        const int r = idx / NB, b = idx - r * NB;
+        const unsigned char *src = raw + r * G::RAW_STRIDE + b * Q8_0_BYTES;  // 2-byte aligned: d, then 32 int8
+        const __half dh = *reinterpret_cast<const __half *>(src);
+        const __half2 d2 = __half2half2(dh);
+        unsigned w[8];
+        lds_words<8>(src + 2, w);
+        uint4 out[4];
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            __half2 lo, hi;
+            i8x4_to_h2x2(w[k], lo, hi);
+            lo = __hmul2(lo, d2);
+            hi = __hmul2(hi, d2);
+            reinterpret_cast<__half2 *>(out)[2 * k] = lo;
+            reinterpret_cast<__half2 *>(out)[2 * k + 1] = hi;
+        }
+        uint4 *o = reinterpret_cast<uint4 *>(dst + r * G::ROW_STRIDE + b * 64);
+        o[0] = out[0]; o[1] = out[1]; o[2] = out[2]; o[3] = out[3];
+    }
+}
+
+template <int TYPE, int D>
 __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_constant__ FaParams p) {
-    using G = MmaGeo<D>;
+    using G = MmaGeo<TYPE, D>;
+    constexpr bool Q8 = G::Q8;
     constexpr int KS = D / 16;  // k-steps of the K.Q contraction == 16-dim blocks of the P.V output
     constexpr int RS = D + FA_RS_PAD;
 
@@ -92,7 +156,8 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     const int col0 = ct * C;
     const int ncol = min(C, p.n_cols - col0);
 
-    unsigned char *my_tiles = smem + (size_t)warp * FM_NBUF * 2 * G::TILE_BYTES;
+    unsigned char *my_tiles = smem + (size_t)warp * G::WARP_BYTES;
+    unsigned char *my_f16   = my_tiles + FM_NBUF * 2 * G::RING_TILE;  // q8_0: the dequantised (K, V) pair of the current tile
     const int n_tiles = (p.n_kv + FM_TP - 1) / FM_TP;
     const int t_begin = split * p.tiles_per_split;
     const int t_end   = min(n_tiles, t_begin + p.tiles_per_split);
@@ -131,13 +196,49 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         }
     }
 
+    // ---- batches (prompt processing): KV tiles whose mask is -inf for every column of this CTA (the causal upper triangle, the
+    // cells of other sequences) are neither loaded nor computed.  Bit i of `skip`: the i-th tile of this warp, t = t_begin + warp
+    // + 4 i; lane i checks tile i (two passes cover 64 tiles per warp; later tiles are simply processed).
+    unsigned long long skip = 0;
+    if (p.N > 1 && p.mask != nullptr) {
+        const bool al16 = (((uintptr_t)p.mask | p.mask_nb1) & 15) == 0;
+#pragma unroll 1
+        for (int pass = 0; pass < 2; pass++) {
+            const int tt = t_begin + warp + FM_NW * (pass * 32 + lane);
+            bool masked = false;
+            if (tt < t_end) {
+                masked = true;
+                const int key = tt * FM_TP;
+                for (int c = 0; c < ncol; c++) {
+                    const unsigned char *mr = p.mask + (size_t)((col0 + c) / p.gqa) * p.mask_nb1 + 2 * (size_t)key;
+                    if (al16 && key + FM_TP <= p.n_kv) {
+                        const uint4 u0 = __ldg(reinterpret_cast<const uint4 *>(mr)), u1 = __ldg(reinterpret_cast<const uint4 *>(mr) + 1);
+                        masked = masked && (u0.x & u0.y & u0.z & u0.w & u1.x & u1.y & u1.z & u1.w) == 0xfc00fc00u &&
+                                 (u0.x | u0.y | u0.z | u0.w | u1.x | u1.y | u1.z | u1.w) == 0xfc00fc00u;
+                    } else {
+                        for (int e = 0; e < FM_TP; e++)
+                            if (key + e < p.n_kv) masked = masked && *reinterpret_cast<const unsigned short *>(mr + 2 * e) == 0xfc00;
+                    }
+                }
+            }
+            skip |= (unsigned long long)__ballot_sync(0xffffffffu, masked) << (32 * pass);
+        }
+    }
+
     int t_issue = t_begin + warp;
-    int ibuf = 0;
+    int ibuf = 0, n_issued = 0;
     auto issue = [&]() {
-        if (t_issue < t_end) {
-            unsigned char *kb = my_tiles + (size_t)ibuf * 2 * G::TILE_BYTES;
-            mma_load_tile<D>(kb, kbase, p.k_nb1, t_issue * FM_TP, p.n_kv, lane);
-            mma_load_tile<D>(kb + G::TILE_BYTES, vbase, p.v_nb1, t_issue * FM_TP, p.n_kv, lane);
+        const bool sk = n_issued < 64 && ((skip >> n_issued) & 1ull) != 0;
+        n_issued++;
+        if (t_issue < t_end && !sk) {
+            unsigned char *kb = my_tiles + (size_t)ibuf * 2 * G::RING_TILE;
+            if constexpr (Q8) {
+                mma_load_tile_q8<D>(kb, kbase, p.k_nb1, t_issue * FM_TP, p.n_kv, lane);
+                mma_load_tile_q8<D>(kb + G::RING_TILE, vbase, p.v_nb1, t_issue * FM_TP, p.n_kv, lane);
+            } else {
+                mma_load_tile<D>(kb, kbase, p.k_nb1, t_issue * FM_TP, p.n_kv, lane);
+                mma_load_tile<D>(kb + G::RING_TILE, vbase, p.v_nb1, t_issue * FM_TP, p.n_kv, lane);
+            }
         }
         cp_async_commit();  // always commit (possibly empty) so the group accounting stays uniform
         t_issue += FM_NW;
@@ -172,14 +273,30 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     const unsigned k_off = (unsigned)(((mi >> 1) * 8 + mr) * G::ROW_STRIDE + (mi & 1) * 16);  // K: keys (mi>>1)*8.., dims (mi&1)*8..
     const unsigned v_off = (unsigned)(((mi & 1) * 8 + mr) * G::ROW_STRIDE + (mi >> 1) * 16);  // V: keys (mi&1)*8.., dims (mi>>1)*8..
 
-    int cbuf = 0;
+    int cbuf = 0, n_done = 0;
     for (int t = t_begin + warp; t < t_end; t += FM_NW) {
         issue();
         cp_async_wait<FM_NBUF - 1>();
         __syncwarp();
         if (t == t_begin) FTRACE(3);
-        const unsigned kt = smem_u32(my_tiles + (size_t)cbuf * 2 * G::TILE_BYTES);
-        const unsigned vt = kt + G::TILE_BYTES;
+        const bool sk = n_done < 64 && ((skip >> n_done) & 1ull) != 0;
+        n_done++;
+        if (sk) {  // every score of the tile is -inf: p = 0, nothing changes
+            cbuf = cbuf + 1 == FM_NBUF ? 0 : cbuf + 1;
+            continue;
+        }
+        unsigned kt, vt;
+        if constexpr (Q8) {
+            const unsigned char *rk = my_tiles + (size_t)cbuf * 2 * G::RING_TILE;
+            mma_dequant_tile_q8<D>(my_f16, rk, lane);
+            mma_dequant_tile_q8<D>(my_f16 + G::TILE_BYTES, rk + G::RING_TILE, lane);
+            __syncwarp();
+            kt = smem_u32(my_f16);
+            vt = kt + G::TILE_BYTES;
+        } else {
+            kt = smem_u32(my_tiles + (size_t)cbuf * 2 * G::RING_TILE);
+            vt = kt + G::TILE_BYTES;
+        }
 
         float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
@@ -308,28 +425,35 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         cluster_sync_all();
         FTRACE(5);
         const int ns = p.n_splits;
-        // phase 1: the (M, L) pairs of every split and column into local shared memory, as normalised weights
+        // phase 1: the (M, L) pairs of every split and column into local shared memory, as normalised weights (remote loads in
+        // independent batches of 8)
         float *wts = cpart + (size_t)C * RS;  // [C][FM_MAX_CLUSTER]: exp(M_s - M) / L
         if ((int)threadIdx.x < ncol) {
             const int c = threadIdx.x;
             const float *row = cpart + (size_t)c * RS;
-            float ms[FM_MAX_CLUSTER], ls[FM_MAX_CLUSTER];
-#pragma unroll
-            for (int s2 = 0; s2 < FM_MAX_CLUSTER; s2++) {
-                ms[s2] = s2 < ns ? ld_cluster_f32(row + D, s2) : -INFINITY;
-                ls[s2] = s2 < ns ? ld_cluster_f32(row + D + 1, s2) : 0.f;
-            }
+            float *w = wts + c * FM_MAX_CLUSTER;
             float M = -INFINITY;
+            for (int s0 = 0; s0 < ns; s0 += 8) {
+                float ms[8], ls[8];
 #pragma unroll
-            for (int s2 = 0; s2 < FM_MAX_CLUSTER; s2++) M = fmaxf(M, ms[s2]);
-            float L = 0.f;
+                for (int k = 0; k < 8; k++) {
+                    ms[k] = s0 + k < ns ? ld_cluster_f32(row + D, s0 + k) : -INFINITY;
+                    ls[k] = s0 + k < ns ? ld_cluster_f32(row + D + 1, s0 + k) : 0.f;
+                }
 #pragma unroll
-            for (int s2 = 0; s2 < FM_MAX_CLUSTER; s2++) {
-                ms[s2] = ms[s2] == -INFINITY ? 0.f : __expf(ms[s2] - M);
-                L += ms[s2] * ls[s2];
+                for (int k = 0; k < 8; k++) {
+                    M = fmaxf(M, ms[k]);
+                    if (s0 + k < ns) { w[s0 + k] = ms[k]; w[FM_MAX_CLUSTER * FM_MAXC + s0 + k] = ls[k]; }  // (second table behind the first)
+                }
             }
-#pragma unroll
-            for (int s2 = 0; s2 < FM_MAX_CLUSTER; s2++) wts[c * FM_MAX_CLUSTER + s2] = ms[s2] / L;
+            float L = 0.f;
+            for (int s2 = 0; s2 < ns; s2++) {
+                const float f = w[s2] == -INFINITY ? 0.f : __expf(w[s2] - M);
+                L += f * w[FM_MAX_CLUSTER * FM_MAXC + s2];
+                w[s2] = f;
+            }
+            const float inv = 1.0f / L;
+            for (int s2 = 0; s2 < ns; s2++) w[s2] *= inv;
         }
         __syncthreads();
         // phase 2: this CTA's slice of the head dims, ns independent remote loads per value
@@ -338,12 +462,14 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         for (int idx = threadIdx.x; idx < ncol * nd; idx += FM_NW * 32) {
             const int c = idx / nd, d = d_lo + idx % nd;
             const float *src = cpart + (size_t)c * RS + d;
-            float v[FM_MAX_CLUSTER];
-#pragma unroll
-            for (int s2 = 0; s2 < FM_MAX_CLUSTER; s2++) v[s2] = s2 < ns ? ld_cluster_f32(src, s2) : 0.f;
             float a = 0.f;
+            for (int s0 = 0; s0 < ns; s0 += 8) {
+                float v[8];
 #pragma unroll
-            for (int s2 = 0; s2 < FM_MAX_CLUSTER; s2++) a += wts[c * FM_MAX_CLUSTER + s2] * v[s2];
+                for (int k = 0; k < 8; k++) v[k] = s0 + k < ns ? ld_cluster_f32(src, s0 + k) : 0.f;
+#pragma unroll
+                for (int k = 0; k < 8; k++) a += (s0 + k < ns ? wts[c * FM_MAX_CLUSTER + s0 + k] : 0.f) * v[k];
+            }
             const int col = col0 + c, n = col / p.gqa, h = hk * p.gqa + col % p.gqa;
             p.dst[((size_t)n * p.n_head + h) * D + d] = a;
         }

@@ -399,20 +399,6 @@ struct SliceDot<B200_TYPE_Q5_K, NCOLS> {
     }
 };
 
-// consecutive 32-bit words from a shared-memory byte run that is only 2-byte aligned
-template <int NW>
-__device__ __forceinline__ void lds_words(const unsigned char *p, unsigned (&out)[NW]) {
-    const unsigned *w = reinterpret_cast<const unsigned *>((uintptr_t)p & ~(uintptr_t)3);
-    const unsigned sh = ((unsigned)(uintptr_t)p & 3u) * 8u;
-    unsigned prev = w[0];
-#pragma unroll
-    for (int i = 0; i < NW; i++) {
-        const unsigned nxt = w[i + 1];  // one word of over-read at most: stages carry 16 bytes of slack
-        out[i] = __funnelshift_r(prev, nxt, sh);
-        prev = nxt;
-    }
-}
-
 // ---- Q6_K: u8 ql[128], u8 qh[64], i8 scales[16], half d  (ggml-common.h:321-327); 210 bytes => 2-byte aligned
 template <int NCOLS>
 struct SliceDot<B200_TYPE_Q6_K, NCOLS> {

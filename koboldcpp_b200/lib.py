@@ -2,6 +2,7 @@
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 PKG = Path(__file__).resolve().parent
@@ -124,7 +125,7 @@ def load(path: Path | None = None):
     global _lib
     if _lib is not None:
         return _lib
-    p = Path(path) if path else LIB_PATH
+    p = Path(path) if path else Path(os.environ.get("B200_LIB", LIB_PATH))  # B200_LIB: developer A/B of two builds
     if not p.exists():
         raise B200Error(f"{p} not found: build it with `python -m koboldcpp_b200.build` (nvcc, sm_100a)")
     L = C.CDLL(str(p))

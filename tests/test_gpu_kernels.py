@@ -284,6 +284,38 @@ def test_flash_attn_shapes(H, tkv, cfg):
         assert err <= TOL_FA[tkv], err
 
 
+@pytest.mark.parametrize("cfg", [
+    # (n_head, n_head_kv, D, n_kv, N, n_past): a prompt batch at the front of the cache and one behind 1536 cached cells
+    (40, 40, 128, 512, 512, 0),      # C3: Llama-2-13B pp512
+    (16, 4, 128, 2048, 512, 1536),   # GQA 4, second batch of a long prompt
+    (8, 8, 64, 320, 300, 20),        # D = 64, ragged sizes
+    (8, 2, 128, 1024, 250, 256),     # cells behind the batch that no query sees
+])
+def test_flash_attn_prefill_causal(H, cfg):
+    """a12: prompt batches through the tensor-core kernel.  Causal mask as llama.cpp builds it (src/llama.cpp:16866-16930): query i
+    sees cells [0, n_past + i]; the KV tiles above the diagonal are skipped by the kernel, so the result must not depend on
+    what those cells hold (they are filled with NaN-producing garbage here)."""
+    nh, nhkv, D, nkv, N, n_past = cfg
+    rng = np.random.default_rng(sum(cfg))
+    q = rng.standard_normal((nh, N, D)).astype(np.float32)
+    kf, vf = rng.standard_normal((nhkv, nkv, D)), rng.standard_normal((nhkv, nkv, D))
+    npad = (N + 31) // 32 * 32
+    mask = np.full((npad, nkv), -np.inf, dtype=np.float16)
+    for i in range(N):
+        mask[i, :min(nkv, n_past + i + 1)] = 0
+    f64 = O.flash_attn_f64(q, O.pack_kv(R.F16, kf), O.pack_kv(R.F16, vf), mask, R.F16, 1.0 / np.sqrt(D))
+    got = H.flash_attn_ext(q, O.pack_kv(R.F16, kf), O.pack_kv(R.F16, vf), mask, R.F16, 1.0 / np.sqrt(D))
+    assert np.isfinite(got).all()
+    assert np.abs(got - f64).max() <= TOL_FA[R.F16], float(np.abs(got - f64).max())
+    # whole 16-cell tiles no query of the batch can see: poison them (inf * 0 = NaN if a masked tile were multiplied in)
+    hidden = (n_past + N + 15) // 16 * 16
+    if hidden < nkv:
+        kf[:, hidden:] = 6e4
+        vf[:, hidden:] = np.inf
+        got2 = H.flash_attn_ext(q, O.pack_kv(R.F16, kf), O.pack_kv(R.F16, vf), mask, R.F16, 1.0 / np.sqrt(D))
+        assert np.isfinite(got2).all() and np.array_equal(got2, got)
+
+
 def test_flash_attn_no_mask_and_fully_masked_prefix(H):
     rng = np.random.default_rng(21)
     nh, nhkv, D, nkv = 4, 4, 128, 300
