@@ -42,6 +42,7 @@ struct CachedGraph {
     int64_t launches = 0;  // kernels inside one replay
     int n_slots = 0;
     uint64_t last_used = 0;
+    uint64_t check = 0;    // second, independent hash of the graph: compared on every cache hit
 };
 
 struct GraphExec {
@@ -464,18 +465,25 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
 }
 
 // ------------------------------------------------------------------------------------------------ graph key
-static inline void mix(uint64_t &h, uint64_t v) {
-    h ^= v + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2);
-    h *= 0xff51afd7ed558ccdull;
-    h ^= h >> 32;
+// Two independent 64-bit hashes over the same words: the first is the cache key, the second is stored with the entry and compared
+// on every hit, so that replaying another graph's kernels and pointers needs a simultaneous collision of both (2^-128).
+struct KeyHash {
+    uint64_t a, b;
+};
+static inline void mix(KeyHash &h, uint64_t v) {
+    h.a ^= v + 0x9e3779b97f4a7c15ull + (h.a << 6) + (h.a >> 2);
+    h.a *= 0xff51afd7ed558ccdull;
+    h.a ^= h.a >> 32;
+    h.b = (h.b ^ v) * 0x100000001b3ull;  // FNV-1a step on 64-bit words ...
+    h.b ^= h.b >> 29;                     // ... with an extra fold (word-sized inputs)
 }
-static void hash_tensor(uint64_t &h, const ggml_tensor *t, bool with_data) {
+static void hash_tensor(KeyHash &h, const ggml_tensor *t, bool with_data) {
     mix(h, (uint64_t)t->type | ((uint64_t)t->op << 32));
     for (int i = 0; i < 4; i++) { mix(h, (uint64_t)t->ne[i]); mix(h, (uint64_t)t->nb[i]); }
     if (with_data) mix(h, (uint64_t)(uintptr_t)t->data);
 }
-static uint64_t graph_key(const ggml_cgraph *cg) {
-    uint64_t h = 0x243f6a8885a308d3ull;
+static KeyHash graph_key(const ggml_cgraph *cg) {
+    KeyHash h = {0x243f6a8885a308d3ull, 0xcbf29ce484222325ull};
     mix(h, (uint64_t)cg->n_nodes);
     mix(h, (uint64_t)g_use_fusion);
     mix(h, (uint64_t)b200_comm_peer_ready());
@@ -729,9 +737,16 @@ enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cg) {
         g_stat_launches += x.launches;
         return GGML_STATUS_SUCCESS;
     }
-    const uint64_t key = graph_key(cg);
+    const KeyHash kh = graph_key(cg);
+    const uint64_t key = kh.a;
     g->tick++;
     auto it = g->cache.find(key);
+    if (it != g->cache.end() && it->second.check != kh.b) {  // same key, different graph: drop the entry and capture afresh
+        B200_CHECK_CUDA(cudaStreamSynchronize(g->stream));
+        cudaGraphExecDestroy(it->second.exec);
+        g->cache.erase(it);
+        it = g->cache.end();
+    }
     if (it == g->cache.end()) {
         if (g->cache.size() >= 24) {  // prefill with ever-changing batch sizes must not leak executables: evict the oldest
             auto old = g->cache.begin();
@@ -750,6 +765,7 @@ enum ggml_status graph_exec_compute(GraphExec *g, ggml_cgraph *cg) {
         B200_CHECK_CUDA(cudaGraphDestroy(graph));
         c.launches = x.launches;
         c.n_slots = n_slots;
+        c.check = kh.b;
         it = g->cache.emplace(key, c).first;
         g_stat_captures++;
     }

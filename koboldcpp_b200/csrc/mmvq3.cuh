@@ -161,6 +161,14 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
         float *n_out = bid == 0 ? p.norm_out : nullptr, *nm_out = bid == 0 ? p.norm_mul_out : nullptr;
         if (p.dbg & 1) {}
         else if (acts_first) act_finish(aregs, act_base, p.K, n_it, p.norm_w != nullptr, p.norm_eps, red, n_out, nm_out);
+        else if (p.norm_w == nullptr) {
+            // a row above ACT_RR_MAX values (Llama-3-70B ffn_down: K = 28672) goes through the registers in chunks
+            for (int64_t k0 = 0; k0 < p.K; k0 += ACT_RR_MAX) {
+                const int64_t kc = p.K - k0 < ACT_RR_MAX ? p.K - k0 : ACT_RR_MAX;
+                act_issue(aregs, p.jobs[0].X + k0, nullptr, kc);
+                act_finish(aregs, act_base, kc, n_it, false, 0.f, red, nullptr, nullptr, (int)(k0 / 4096));
+            }
+        }
         else load_activations<1>(act_base, p.jobs[0].X, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red, n_out, nm_out);
         __syncthreads();
         if (active) lane_acts_load<TYPE>(A, act_base, n_it, wit, lane);  // once per kernel

@@ -223,14 +223,16 @@ __device__ __forceinline__ void quantize_q8_1_group4(const float4 a, const float
 }
 // All threads of the CTA call this (it contains CTA barriers when norm is set).
 template <int RR>
+// it0: the registers hold the values [4096 it0, 4096 it0 + K) of a longer row of n_it steps (rows above ACT_RR_MAX values are
+// quantised in chunks; not with norm, whose statistic needs the whole row first).
 __device__ __forceinline__ void act_finish(ActRegsT<RR> &r, unsigned char *p, int64_t K, int n_it, bool norm, float norm_eps, float *red,
-                                           float *__restrict__ norm_out = nullptr, float *__restrict__ norm_mul_out = nullptr) {
+                                           float *__restrict__ norm_out = nullptr, float *__restrict__ norm_mul_out = nullptr, int it0 = 0) {
     constexpr int NT = MMVQ_THREADS;
     const int n4 = (int)(K / 4);
-    int   *aq = (int *)p;
-    float *ad = (float *)(p + (size_t)n_it * 4096);
-    float *as = (float *)(p + (size_t)n_it * (4096 + 512));
-    int   *ag = (int *)(p + (size_t)n_it * (4096 + 1024));
+    int   *aq = (int *)p + (size_t)it0 * 1024;
+    float *ad = (float *)(p + (size_t)n_it * 4096) + (size_t)it0 * 128;
+    float *as = (float *)(p + (size_t)n_it * (4096 + 512)) + (size_t)it0 * 128;
+    int   *ag = (int *)(p + (size_t)n_it * (4096 + 1024)) + (size_t)it0 * 128;
     if (norm) {
         float ss = 0.f;
 #pragma unroll

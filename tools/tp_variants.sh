@@ -1,0 +1,9 @@
+#!/bin/bash
+# Developer A/B of the 70B tensor-parallel leg under kernel switches (N ranks = $1)
+N=${1:-2}
+run() { echo "== $*"; env "$@" B200_BENCH_ONLY_TP70=1 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus $N --steps 20 --warmup 3 2>/dev/null | grep tp_70b | python -c "import sys,json; d=json.loads(sys.stdin.read())['tp_70b_only']; print(d['value'], d['ms_per_step'], d['e2e']['value'], d['pp512_tokens_per_s'])"; }
+run X=1
+run B200_MMVQ_NO_MMVQ3=1
+run B200_FA_NO_MMA=1
+run B200_MMVQ_PREFILL=0
+run B200_LIB=$PWD/build/old/libkcpp_b200_old.so
