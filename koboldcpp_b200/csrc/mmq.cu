@@ -252,6 +252,9 @@ struct MmqParams {
     const int *tile_tab;
     const int *row_dst;
     size_t expert_bytes;
+    // split-K (mmq_tc2_kernel, not grouped): blockIdx.z owns a contiguous share of the 256-value groups and ADDS its tile into a
+    // zeroed dst (red.global.add.f32).  Only 1 or 2: the sum of two partials does not depend on their arrival order.
+    int ksplit;
 };
 
 template <int TYPE, int BN>
@@ -501,7 +504,11 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
     const int64_t m0 = (int64_t)blockIdx.x * MQ_BM;
-    const int nsb = (int)(p.K / 256), nkb = nsb * 4;
+    const int nsb_all = (int)(p.K / 256);
+    // split-K: this CTA's 256-value groups [sb0, sb0 + nsb)
+    const int ksplit = GROUPED ? 1 : p.ksplit;
+    const int sb0 = (int)(((int64_t)blockIdx.z * nsb_all) / ksplit);
+    const int nsb = (int)(((int64_t)(blockIdx.z + 1) * nsb_all) / ksplit) - sb0, nkb = nsb * 4;
 
     if (tid == 0) {
         for (int s = 0; s < MQ2_STAGES; s++) { mbar_init(&full_bar[s], MQ_PRODUCERS + 1); mbar_init(&empty_bar[s], 1); }
@@ -567,10 +574,10 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
             fence_proxy_async_smem();
             mbar_arrive(&full_bar[s]);
         };
-        fetch(cur, 0);
+        fetch(cur, sb0);
 #pragma unroll 1
         for (int sb = 0; sb < nsb; sb++) {
-            if (sb + 1 < nsb) fetch(nxt, sb + 1);
+            if (sb + 1 < nsb) fetch(nxt, sb0 + sb + 1);
             unsigned o[32];
             DequantR<TYPE, 0>::run(cur, o); publish(sb * 4 + 0, o);
             DequantR<TYPE, 1>::run(cur, o); publish(sb * 4 + 1, o);
@@ -593,7 +600,10 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
                     if constexpr (GROUPED) {
                         if (n < n_end) drow[(int64_t)__ldg(p.row_dst + n)] = v[j];  // scatter: sorted row -> (token, slot)
                     } else {
-                        if (n < n_end) drow[n * p.dst_stride] = v[j];
+                        if (n < n_end) {
+                            if (ksplit > 1) atomicAdd(drow + n * p.dst_stride, v[j]);  // (result unused: RED.ADD.F32)
+                            else drow[n * p.dst_stride] = v[j];
+                        }
                     }
                 }
             }
@@ -623,7 +633,7 @@ __global__ void __launch_bounds__(MQ2_THREADS, 1) mmq_tc2_kernel(const __grid_co
                 const int s = kb % MQ2_STAGES;
                 mbar_wait(&empty_bar[s], ((unsigned)(kb / MQ2_STAGES) & 1u) ^ 1u);
                 mbar_expect_tx(&full_bar[s], (unsigned)B_BYTES);
-                tma_load_2d(smem + (size_t)s * STAGE_BYTES + A_BYTES, &tmB, kb * MQ_BK, (int)n0, &full_bar[s]);
+                tma_load_2d(smem + (size_t)s * STAGE_BYTES + A_BYTES, &tmB, (sb0 * 4 + kb) * MQ_BK, (int)n0, &full_bar[s]);
             }
         }
     }
@@ -689,7 +699,20 @@ static int mmq2_launch(const MmqParams &p, int64_t n_pad, cudaStream_t st, unsig
     const int rc = enc(&tm, 9, 2, (void *)p.Xb, gdim, gstr, box, estr, 0, 3, 3, 0);
     if (rc != 0) { set_error("b200_mul_mat_q: cuTensorMapEncodeTiled failed (%d)", rc); return B200_ERR_CUDA; }
     dim3 grid((unsigned)((p.M + MQ_BM - 1) / MQ_BM), GROUPED ? grid_y : (unsigned)((p.N + BN - 1) / BN));
-    mmq_tc2_kernel<TYPE, BN, GROUPED><<<grid, MQ2_THREADS, smem, st>>>(tm, p);
+    MmqParams q = p;
+    q.ksplit = 1;
+    if constexpr (!GROUPED) {
+        // fewer tiles than half the SMs (M = 4096 x N = 512: 64 CTAs, every one bound by its own 128 dequantising threads): two
+        // CTAs share a tile's K range and add into a zeroed dst.  Two partials only: the sum is independent of the arrival order.
+        static const bool no_split = getenv("B200_MMQ_NO_SPLITK") != nullptr;
+        if (!no_split && (int64_t)grid.x * grid.y * 2 <= 148 && p.K >= 2048) {
+            q.ksplit = 2;
+            grid.z = 2;
+            if (p.dst_stride == p.M) B200_CUDA_TRY(cudaMemsetAsync(p.dst, 0, (size_t)p.M * p.N * sizeof(float), st));
+            else B200_CUDA_TRY(cudaMemset2DAsync(p.dst, (size_t)p.dst_stride * sizeof(float), 0, (size_t)p.M * sizeof(float), (size_t)p.N, st));
+        }
+    }
+    mmq_tc2_kernel<TYPE, BN, GROUPED><<<grid, MQ2_THREADS, smem, st>>>(tm, q);
     B200_CUDA_TRY(cudaGetLastError());
     return B200_OK;
 }

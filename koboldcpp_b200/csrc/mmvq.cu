@@ -348,6 +348,8 @@ static int launch_mmvq3(MmvqParams &p, cudaStream_t st, bool pdl) {
     const int64_t units = p.silu_pair ? p.total_rows / 2 : p.total_rows;  // rows, or (gate, up) pairs
     const int64_t grid = units < g_sm_count ? units : g_sm_count;
     const int64_t units_per_cta = (units + grid - 1) / grid;
+    static const int onerow_below = getenv("B200_MMVQ_ONEROW_BELOW") ? atoi(getenv("B200_MMVQ_ONEROW_BELOW")) : 0;  // developer knob
+    if (units_per_cta <= onerow_below) return -1000;
     const int64_t part_rows = nit1 ? 0 : (p.silu_pair ? 2 : 1) * units_per_cta;
     const size_t part_bytes = (size_t)part_rows * p.n_it * 4;
     const size_t cap = g_smem_optin - 256;

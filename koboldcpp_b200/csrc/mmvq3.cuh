@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
     __shared__ float red[MMVQ_NW];
 
     TRACE(0);
-    pdl_trigger();  // one CTA per SM: a dependent CTA can only become resident when this one retires
+    if (!(p.dbg & 4)) pdl_trigger();  // one CTA per SM: a dependent CTA can only become resident when this one retires
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = lane >> 4;  // lanes 0-15 work for row A of a pair, lanes 16-31 for row B
     const int n_stage = p.n_stage, n_it = NIT1 ? 1 : p.n_it;
@@ -138,6 +138,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
     TRACE(2);
     if (acts_first && !(p.dbg & 1)) act_issue(aregs, p.jobs[0].X, p.norm_w, p.K);
     if (filler && 2 * fs + h >= p.prefill) issue_unit(fs, fs);
+    if (p.dbg & 4) pdl_trigger();  // developer knob: late trigger
     TRACE(3);
     // K-sliced form: the residual of output row threadIdx.x travels from now until the epilogue
     float eres = 0.f;
