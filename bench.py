@@ -196,26 +196,29 @@ def config_dict(shape) -> dict:
 # ------------------------------------------------------------------------------------------------ GEMV roofline leg
 def gemv_launch_plan(shape):
     """The decode GEMV launches of one token as graph_compute issues them (backend_graph.cu: siblings reading the same
-    activation and sharing a weight type are one multi-job launch).  Returns per layer a list of (type, K, [M, ...])."""
+    activation are one multi-job launch; two K-quant weight types may share it).  Returns per layer a list of
+    (K, [(type, M), ...])."""
     from koboldcpp_b200.llama import tensor_shape, tensor_types
     types = tensor_types(shape)
+    kq = {12, 13, 14}
     layers = []
     for il in range(shape.n_layer):
         p = f"blk.{il}."
         launches = []
         for group in (["attn_q.weight", "attn_k.weight", "attn_v.weight"], ["attn_output.weight"], ["ffn_gate.weight", "ffn_up.weight"], ["ffn_down.weight"]):
-            by_type: dict[int, list[int]] = {}
-            order = []
-            for leaf in group:
-                ty = types[p + leaf]
-                if ty not in by_type:
-                    order.append(ty)
-                by_type.setdefault(ty, []).append(tensor_shape(shape, p + leaf)[1])
             K = tensor_shape(shape, p + group[0])[0]
-            for ty in order:
-                launches.append((ty, K, by_type[ty]))
+            members = [(types[p + leaf], tensor_shape(shape, p + leaf)[1]) for leaf in group]
+            tys = []
+            for ty, _ in members:
+                if ty not in tys:
+                    tys.append(ty)
+            if len(tys) == 1 or (len(tys) == 2 and set(tys) <= kq):
+                launches.append((K, members))
+            else:
+                for ty in tys:
+                    launches.append((K, [(t, M) for (t, M) in members if t == ty]))
         layers.append(launches)
-    head = (types["output.weight"], shape.n_embd, [shape.n_vocab])
+    head = (shape.n_embd, [(types["output.weight"], shape.n_vocab)])
     return layers, head
 
 
@@ -227,16 +230,15 @@ def gemv_leg(shape, steps: int, warmup: int) -> dict:
     layers, head = gemv_launch_plan(shape)
     n_sets = 4
     rng = np.random.default_rng(0)
-    kinds = sorted({(ty, K, tuple(Ms)) for lay in layers for (ty, K, Ms) in lay} | {(head[0], head[1], tuple(head[2]))})
+    kinds = sorted({(K, tuple(mem)) for lay in layers for (K, mem) in lay} | {(head[0], tuple(head[1]))})
     pool = {}
-    for (ty, K, Ms) in kinds:
-        rs = row_size(ty, K)
+    for (K, mem) in kinds:
         sets = []
-        for _ in range(1 if (ty, K, list(Ms)) == (head[0], head[1], list(head[2])) else n_sets):
-            sets.append([H.DeviceBuffer.from_numpy(rng.integers(0, 256, size=rs * M, dtype=np.uint8), pad=256) for M in Ms])
-        pool[(ty, K, Ms)] = sets
-    kmax = max(k for _, k, _ in kinds)
-    mmax = max(sum(Ms) for _, _, Ms in kinds)
+        for _ in range(1 if (K, list(mem)) == (head[0], list(head[1])) else n_sets):
+            sets.append([H.DeviceBuffer.from_numpy(rng.integers(0, 256, size=row_size(ty, K) * M, dtype=np.uint8), pad=256) for (ty, M) in mem])
+        pool[(K, mem)] = sets
+    kmax = max(k for k, _ in kinds)
+    mmax = max(sum(M for _, M in mem) for _, mem in kinds)
     x = H.DeviceBuffer.from_numpy(rng.standard_normal(kmax).astype(np.float32))
     y = H.DeviceBuffer(4 * mmax + 256)
     st = C.c_void_p()
@@ -250,20 +252,22 @@ def gemv_leg(shape, steps: int, warmup: int) -> dict:
         alg_bytes = 0
         n_launch = 0
         seq = [(il, l) for il, lay in enumerate(layers) for l in lay] + [(0, head)]
-        for il, (ty, K, Ms) in seq:
-            sets = pool[(ty, K, tuple(Ms))]
+        for il, (K, mem) in seq:
+            sets = pool[(K, tuple(mem))]
             bufs = sets[il % len(sets)]
-            rs = row_size(ty, K)
-            if len(Ms) == 1:
-                check(L.b200_mul_mat_vec_q(ty, bufs[0].ptr, rs, x.ptr, K, y.ptr, Ms[0], K, Ms[0], 1, st))
+            ty0 = mem[0][0]
+            rs = row_size(ty0, K)
+            if len(mem) == 1:
+                check(L.b200_mul_mat_vec_q(ty0, bufs[0].ptr, rs, x.ptr, K, y.ptr, mem[0][1], K, mem[0][1], 1, st))
             else:
-                jobs = (GemvJob * len(Ms))()
+                jobs = (GemvJob * len(mem))()
                 off = 0
-                for j, M in enumerate(Ms):
+                for j, (ty, M) in enumerate(mem):
                     jobs[j].W = bufs[j].ptr; jobs[j].X = x.ptr; jobs[j].dst = y.ptr + 4 * off; jobs[j].M = M; jobs[j].id_index = -1
+                    jobs[j]._pad = ty if ty != ty0 else 0
                     off += M
-                check(L.b200_mul_mat_vec_q_multi(ty, jobs, len(Ms), rs, K, sum(Ms), K, 1, None, 0, 0, st))
-            alg_bytes += sum(rs * M + 4 * M for M in Ms) + 4 * K
+                check(L.b200_mul_mat_vec_q_multi(ty0, jobs, len(mem), rs, K, off, K, 1, None, 0, 0, st))
+            alg_bytes += sum(row_size(ty, K) * M + 4 * M for (ty, M) in mem) + 4 * K
             n_launch += 1
 
     check(L.b200_graph_begin_capture(st))

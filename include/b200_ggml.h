@@ -127,7 +127,8 @@ typedef struct {
     float         *dst;
     int64_t        M;
     int32_t        id_index; /* index into ids[] or -1 */
-    int32_t        _pad;
+    int32_t        _pad;     /* 0, or the weight type of THIS job when it differs from the launch's `type` (decode only: N == 1, one X,
+                                contiguous rows; Q4_K+Q6_K, Q5_K+Q6_K, Q4_K+Q5_K: attn_q/attn_k + attn_v of the *_K_M mixes in one launch) */
 } b200_gemv_job;
 #define B200_GEMV_MAX_JOBS 16
 B200_API int b200_mul_mat_vec_q_multi(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_bytes,

@@ -22,6 +22,10 @@
 
 namespace b200 {
 
+// mixed-type sibling GEMVs in one launch (developer switch B200_NO_MIXED_TYPES)
+static const bool g_mixed_types = getenv("B200_NO_MIXED_TYPES") == nullptr;
+static inline bool rows_are_contiguous(const ggml_tensor *w) { return w->nb[1] == row_size(w->type, w->ne[0]); }
+
 enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV, STEP_AR_ADD, STEP_MOE_ROUTER };
 
 struct Step {
@@ -394,7 +398,20 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             for (int j2 = i + 1; j2 < horizon && s.group.size() < B200_GEMV_MAX_JOBS; j2++) {
                 const ggml_tensor *b = cg->nodes[j2];
                 if (done[j2] || !mul_mat_fusable(b)) continue;
-                if (b->src[1] != a->src[1] || b->src[0]->type != a->src[0]->type || b->src[0]->nb[1] != a->src[0]->nb[1] || (a->ne[1] > 1 && b->nb[1] != a->nb[1])) continue;
+                if (b->src[1] != a->src[1] || (a->ne[1] > 1 && b->nb[1] != a->nb[1])) continue;
+                if (b->src[0]->type != a->src[0]->type) {
+                    // decode: a sibling of a second weight type shares the launch (attn_q / attn_k Q4_K + attn_v Q6_K of the *_K_M
+                    // mixes), b200_gemv_job.type2: contiguous rows, one of the supported pairs, at most two types per launch
+                    if (!g_mixed_types || a->ne[1] != 1 || b->src[0]->ne[0] != a->src[0]->ne[0]) continue;
+                    auto kq = [](const ggml_tensor *w) { return w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q5_K || w->type == GGML_TYPE_Q6_K; };
+                    if (!kq(a->src[0]) || !kq(b->src[0])) continue;
+                    bool ok = rows_are_contiguous(b->src[0]);
+                    for (const ggml_tensor *mm : s.group) {
+                        ok = ok && rows_are_contiguous(mm->src[0]);
+                        ok = ok && (mm->src[0]->type == a->src[0]->type || mm->src[0]->type == b->src[0]->type);
+                    }
+                    if (!ok) continue;
+                } else if (b->src[0]->nb[1] != a->src[0]->nb[1]) continue;
                 std::vector<int> mem = {i, j2};
                 if (!can_gather(gi, mem, i, done)) continue;
                 s.group.push_back(b);
@@ -418,7 +435,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             // R4: decode gate/up pair whose results only feed MUL(SILU(gate), up) -> the activation is computed in the epilogue,
             // the SILU and MUL nodes disappear and the two f32 vectors are never written
             if (s.group.size() == 2 && a->ne[1] == 1 && add_of.find(s.group[0]) == add_of.end() && add_of.find(s.group[1]) == add_of.end() &&
-                s.group[0]->src[0]->ne[1] == s.group[1]->src[0]->ne[1]) {
+                s.group[0]->src[0]->ne[1] == s.group[1]->src[0]->ne[1] && s.group[0]->src[0]->type == s.group[1]->src[0]->type) {
                 for (int gi_ = 0; gi_ < 2 && !s.silu_mul; gi_++) {
                     const ggml_tensor *gt = s.group[gi_], *up = s.group[1 - gi_];
                     const ggml_tensor *sn = gi.sole_user(gt);
@@ -591,7 +608,8 @@ static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
             }
             for (size_t q = 0; q < s.group.size(); q++) {
                 const ggml_tensor *m = s.group[q], *add = s.adds[q];
-                jobs[nj].W = m->src[0]->data; jobs[nj].X = X; jobs[nj].M = m->src[0]->ne[1]; jobs[nj].id_index = -1; jobs[nj]._pad = 0;
+                jobs[nj].W = m->src[0]->data; jobs[nj].X = X; jobs[nj].M = m->src[0]->ne[1]; jobs[nj].id_index = -1;
+                jobs[nj]._pad = m->src[0]->type != a->src[0]->type ? (int32_t)m->src[0]->type : 0;  // a member of the second weight type
                 if (add) {
                     const ggml_tensor *r = add->src[0] == m ? add->src[1] : add->src[0];
                     jobs[nj].dst = (float *)add->data;

@@ -9,6 +9,7 @@
 
 #include "../../include/b200_comm.h"
 #include "b200_common.cuh"
+#include <cstdlib>
 
 namespace b200 {
 
@@ -286,6 +287,14 @@ extern "C" int b200_all_reduce_sum_add_f32(const float *src, const float *residu
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(PW_THREADS);
     cfg.stream = (cudaStream_t)stream;
+    // developer knob: dynamic shared memory the exchange kernel asks for (it uses none): large values keep its CTAs from sharing an
+    // SM with the CTAs of the GEMVs around it
+    static const int ar_smem = getenv("B200_AR_SMEM") ? atoi(getenv("B200_AR_SMEM")) : 0;
+    if (ar_smem > 0) {
+        static bool attr_set = false;
+        if (!attr_set) { B200_CUDA_TRY(cudaFuncSetAttribute(all_reduce_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ar_smem)); attr_set = true; }
+        cfg.dynamicSmemBytes = (size_t)ar_smem;
+    }
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;

@@ -335,9 +335,9 @@ static int launch_mmvq(MmvqParams &p, cudaStream_t st, bool pdl) {
 }
 
 // decode form, lean skeleton (mmvq3.cuh)
-template <int TYPE, bool MULTI>
+template <int TYPE, bool MULTI, int TYPE2 = TYPE>
 static int launch_mmvq3(MmvqParams &p, cudaStream_t st, bool pdl) {
-    using G3 = Geo3<TYPE>;
+    using G3 = Geo3Pair<TYPE, TYPE2>;  // a stage holds a row segment of either type
     int rc = device_props();
     if (rc) return rc;
     if (p.n_it > 8) return -1000;  // K > 32768: fewer than two warps per slice; the one-row kernel handles it
@@ -372,8 +372,8 @@ static int launch_mmvq3(MmvqParams &p, cudaStream_t st, bool pdl) {
     p.dbg = dbg;
     TRACE_SLOT(p);
     const size_t smem = bar_bytes + act_bytes + ns * n_ring * G3::STAGE2 + part_bytes;
-    auto kern = nit1 ? mmvq3_kernel<TYPE, MULTI, true> : mmvq3_kernel<TYPE, MULTI, false>;
-    static bool attr_set_dev[16][2] = {};  // cudaFuncSetAttribute is per device
+    auto kern = nit1 ? mmvq3_kernel<TYPE, TYPE2, MULTI, true> : mmvq3_kernel<TYPE, TYPE2, MULTI, false>;
+    static bool attr_set_dev[16][2] = {};  // cudaFuncSetAttribute is per device (one table per template instantiation)
     int cur_dev = 0;
     B200_CUDA_TRY(cudaGetDevice(&cur_dev));
     bool &attr_set = attr_set_dev[cur_dev & 15][nit1 ? 1 : 0];
@@ -495,6 +495,35 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
     if (total == 0) return B200_OK;
     if (total > 0x7fffffff) { set_error("b200_mul_mat_vec_q: too many rows"); return B200_ERR_UNSUPPORTED; }
     const bool pdl = g_mmvq_pdl;
+    // jobs of a second weight type (b200_gemv_job.type2): the mixed-type form of the decode kernel
+    int type2 = 0;
+    unsigned mask = 0;
+    for (int j = 0; j < n_jobs; j++) {
+        const int tj = jobs[j]._pad;
+        if (tj == 0 || tj == type) continue;
+        if (type2 != 0 && tj != type2) { set_error("b200_mul_mat_vec_q_multi: at most two weight types per launch"); return B200_ERR_UNSUPPORTED; }
+        type2 = tj;
+        mask |= 1u << j;
+    }
+    if (type2 != 0) {
+        bool same_x = true;
+        for (int j = 1; j < n_jobs; j++) same_x = same_x && jobs[j].X == jobs[0].X;
+        if (N != 1 || ids != nullptr || p.silu_pair || !same_x || K % 256) { set_error("b200_mul_mat_vec_q_multi: two weight types need N == 1, one X, no expert ids"); return B200_ERR_UNSUPPORTED; }
+        int ta = type, tb = type2;
+        if (ta > tb) { const int t = ta; ta = tb; tb = t; mask = ~mask & ((1u << n_jobs) - 1u); }  // canonical order: TYPE < TYPE2
+        const size_t rb_a = (size_t)(K / 256) * type_block_bytes(ta), rb_b = (size_t)(K / 256) * type_block_bytes(tb);
+        if (ta != type && w_row_bytes != row_bytes) { set_error("b200_mul_mat_vec_q_multi: mixed-type launches need contiguous rows"); return B200_ERR_UNSUPPORTED; }
+        p.w_row_bytes = ta == type ? w_row_bytes : rb_a;
+        p.row_bytes = (unsigned)rb_a;
+        p.row_bytes2 = (unsigned)rb_b;
+        p.t2_mask = mask;
+        int rc = -1000;
+        if (ta == B200_TYPE_Q4_K && tb == B200_TYPE_Q6_K) rc = launch_mmvq3<B200_TYPE_Q4_K, true, B200_TYPE_Q6_K>(p, st, pdl);
+        else if (ta == B200_TYPE_Q5_K && tb == B200_TYPE_Q6_K) rc = launch_mmvq3<B200_TYPE_Q5_K, true, B200_TYPE_Q6_K>(p, st, pdl);
+        else if (ta == B200_TYPE_Q4_K && tb == B200_TYPE_Q5_K) rc = launch_mmvq3<B200_TYPE_Q4_K, true, B200_TYPE_Q5_K>(p, st, pdl);
+        if (rc == -1000) { set_error("b200_mul_mat_vec_q_multi: weight types %d + %d cannot share a launch", ta, tb); return B200_ERR_UNSUPPORTED; }
+        return rc;
+    }
     switch (type) {
         case B200_TYPE_Q4_0: return dispatch_cols<B200_TYPE_Q4_0>(p, (int)N, st, pdl);
         case B200_TYPE_Q8_0: return dispatch_cols<B200_TYPE_Q8_0>(p, (int)N, st, pdl);

@@ -35,17 +35,44 @@ struct Geo3 {
     static constexpr int  STAGE2    = 2 * STAGE;
 };
 
+template <int TYPE, int TYPE2>
+struct Geo3Pair {
+    static constexpr int STAGE2 = Geo3<TYPE>::STAGE2 > Geo3<TYPE2>::STAGE2 ? Geo3<TYPE>::STAGE2 : Geo3<TYPE2>::STAGE2;
+};
+
 struct RowRef {
     const unsigned char *src;  // first byte of the weight row; NULL: no such row, or an expert id out of range
     float               *dst;  // NULL: no such row
     int                  job;
+    int                  t2;   // mixed-type launch: the row belongs to a job of the second weight type
 };
 
-template <int TYPE, bool MULTI, bool NIT1>
+// every field a row dot of either type may read
+template <int TYPE, int TYPE2>
+__device__ __forceinline__ void lane_acts_load2(LaneActs &A, unsigned char *act_base, int n_it, int it, int lane) {
+    if constexpr (TYPE == TYPE2) {
+        lane_acts_load<TYPE>(A, act_base, n_it, it, lane);
+    } else {
+        const ActView a = act_view(act_base, n_it, 0);
+#pragma unroll
+        for (int j = 0; j < 8; j++) A.u[j] = a.q[((it * 8 + j) * 32) + lane];
+        A.d8 = a.d[it * 32 + lane];
+        A.s8 = a.s[it * 32 + lane];
+        A.g = a.g[it * 32 + lane];
+    }
+}
+
+// TYPE2 != TYPE: a multi-job launch whose jobs are of two weight types (attn_q / attn_k Q4_K + attn_v Q6_K of the *_K_M mixes): bit j
+// of p.t2_mask says job j is TYPE2; its rows are contiguous (row stride = row size).
+template <int TYPE, int TYPE2, bool MULTI, bool NIT1>
 __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_constant__ MmvqParams p) {
     using G3 = Geo3<TYPE>;
-    constexpr bool ALIGNED16 = G3::ALIGNED16;
-    constexpr int SEG = G3::SEG, STAGE = G3::STAGE, STAGE2 = G3::STAGE2;
+    using G3b = Geo3<TYPE2>;
+    constexpr bool MIXED = TYPE != TYPE2;
+    static_assert(!MIXED || MULTI, "two weight types need a multi-job launch");
+    constexpr bool ALIGNED16 = G3::ALIGNED16 && G3b::ALIGNED16;
+    constexpr int SEG = G3::SEG, SEGb = G3b::SEG;
+    constexpr int STAGE = G3::STAGE > G3b::STAGE ? G3::STAGE : G3b::STAGE, STAGE2 = 2 * STAGE;
     extern __shared__ __align__(128) unsigned char smem[];
     __shared__ float red[MMVQ_NW];
 
@@ -80,7 +107,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
 
     // local row lr of the CTA (silu: output lr, hh = 0 gate / 1 up)
     auto resolve_row = [&](int lr, int hh) -> RowRef {
-        RowRef r = {nullptr, nullptr, 0};
+        RowRef r = {nullptr, nullptr, 0, 0};
         if (lr >= np) return r;
         int64_t row = (int64_t)r0 + lr;
         if (silu) {
@@ -99,7 +126,8 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
                 w = (e >= 0 && e < p.n_expert) ? w + (size_t)e * p.expert_bytes : nullptr;
             }
         }
-        r.src = w != nullptr ? w + (size_t)row * p.w_row_bytes : nullptr;
+        if constexpr (MIXED) r.t2 = (int)((p.t2_mask >> jb) & 1u);
+        r.src = w != nullptr ? w + (size_t)row * (MIXED && r.t2 ? (size_t)p.row_bytes2 : p.w_row_bytes) : nullptr;
         r.dst = p.jobs[jb].dst + row;
         r.job = jb;
         return r;
@@ -107,15 +135,17 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
     // this lane's row (half h) of pair j
     auto resolve = [&](int j) -> RowRef { return silu ? resolve_row(wg + g * j, h) : resolve_row(wg + 2 * g * j + g * h, 0); };
     const unsigned seg_bytes = wit == n_it - 1 ? p.row_bytes - (unsigned)(n_it - 1) * SEG : (unsigned)SEG;
+    const unsigned seg_bytes2 = wit == n_it - 1 ? p.row_bytes2 - (unsigned)(n_it - 1) * SEGb : (unsigned)SEGb;
     // this lane copies the warp's segment of its row of pair j into stage s (or just arrives when there is nothing to copy)
     auto issue_unit = [&](int j, int s) {
         const RowRef r = resolve(j);
         unsigned long long *bar = &my_bars[s];
         if (r.src != nullptr) {
-            const unsigned char *src = r.src + (size_t)wit * SEG;
+            const bool b2 = MIXED && r.t2;
+            const unsigned char *src = r.src + (size_t)wit * (b2 ? SEGb : SEG);
             // aligned-down source, length rounded up to 16: the slack lands in the stage's head / tail padding
             const unsigned mis = ALIGNED16 ? 0u : (unsigned)((uintptr_t)src & 15);
-            const unsigned len = (mis + seg_bytes + 15u) & ~15u;
+            const unsigned len = (mis + (b2 ? seg_bytes2 : seg_bytes) + 15u) & ~15u;
             mbar_expect_tx(bar, len);
             bulk_g2s(my_ring + (size_t)s * STAGE2 + h * STAGE, src - mis, len, bar);
         } else {
@@ -172,7 +202,7 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
         }
         else load_activations<1>(act_base, p.jobs[0].X, p.x_stride, p.K, n_it, p.norm_w, p.norm_eps, red, n_out, nm_out);
         __syncthreads();
-        if (active) lane_acts_load<TYPE>(A, act_base, n_it, wit, lane);  // once per kernel
+        if (active) lane_acts_load2<TYPE, TYPE2>(A, act_base, n_it, wit, lane);  // once per kernel
         TRACE(4);
     }
 
@@ -203,14 +233,30 @@ __global__ void __launch_bounds__(MMVQ_THREADS, 1) mmvq3_kernel(const __grid_con
         mbar_wait(&my_bars[cstage], cphase);
         if (j == 0) TRACE(5);
         const unsigned char *st = my_ring + (size_t)cstage * STAGE2;
+        unsigned tmask = 0;  // mixed-type launch: which of the two rows are of the second type (all lanes vote: nblk is per lane)
+        if constexpr (MIXED) tmask = __ballot_sync(0xffffffffu, r.t2 != 0);
         if (nblk > 0 && !(p.dbg & 2)) {
-            if (vA && vB) {
-                RowDot<TYPE>::run(st + misA, lane, A, nblk, accA);
-                RowDot<TYPE>::run(st + STAGE + misB, lane, A, nblk, accB);
-            } else if (vA) {
-                RowDot<TYPE>::run(st + misA, lane, A, nblk, accA);
-            } else if (vB) {
-                RowDot<TYPE>::run(st + STAGE + misB, lane, A, nblk, accB);
+            if constexpr (!MIXED) {
+                if (vA && vB) {
+                    RowDot<TYPE>::run(st + misA, lane, A, nblk, accA);
+                    RowDot<TYPE>::run(st + STAGE + misB, lane, A, nblk, accB);
+                } else if (vA) {
+                    RowDot<TYPE>::run(st + misA, lane, A, nblk, accA);
+                } else if (vB) {
+                    RowDot<TYPE>::run(st + STAGE + misB, lane, A, nblk, accB);
+                }
+            } else {
+                const bool tA = (tmask & 1u) != 0, tB = (tmask & 0x10000u) != 0;
+                if (vA && vB && !tA && !tB) {
+                    RowDot<TYPE>::run(st + misA, lane, A, nblk, accA);
+                    RowDot<TYPE>::run(st + STAGE + misB, lane, A, nblk, accB);
+                } else if (vA && vB && tA && tB) {
+                    RowDot<TYPE2>::run(st + misA, lane, A, nblk, accA);
+                    RowDot<TYPE2>::run(st + STAGE + misB, lane, A, nblk, accB);
+                } else {  // a pair across the boundary of the two types, or half a pair
+                    if (vA) { if (tA) RowDot<TYPE2>::run(st + misA, lane, A, nblk, accA); else RowDot<TYPE>::run(st + misA, lane, A, nblk, accA); }
+                    if (vB) { if (tB) RowDot<TYPE2>::run(st + STAGE + misB, lane, A, nblk, accB); else RowDot<TYPE>::run(st + STAGE + misB, lane, A, nblk, accB); }
+                }
             }
         }
         __syncwarp();

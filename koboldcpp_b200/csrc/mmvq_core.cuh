@@ -21,6 +21,8 @@ struct MmvqParams {
     int            rows_q, rows_rem;   // rows per CTA = rows_q (+1 for the first rows_rem CTAs)
     int            tab_rows;           // MULTI: capacity of the per-CTA row table
     int            grp, part_rows;     // mmvq3 (K > 4096): warps per K-slice, rows of the per-slice partial-sum table
+    unsigned       t2_mask;            // mmvq3 mixed-type launch: bit j = job j is of the second weight type
+    unsigned       row_bytes2;         //   ... whose rows are row_bytes2 long and contiguous
     int64_t        K;
     int64_t        total_rows;
     size_t         w_row_bytes;   // row stride

@@ -94,8 +94,9 @@ def mul_mat_vec_q(t: int, w: np.ndarray, x: np.ndarray, K: int, M: int) -> np.nd
     return dd.to_numpy(np.float32, (N, M))
 
 
-def mul_mat_vec_q_multi(t: int, ws: list[np.ndarray], x: np.ndarray, K: int) -> list[np.ndarray]:
-    """Several weight matrices against the same activations in one launch (fused Q/K/V, gate/up)."""
+def mul_mat_vec_q_multi(t: int, ws: list[np.ndarray], x: np.ndarray, K: int, types: list[int] | None = None) -> list[np.ndarray]:
+    """Several weight matrices against the same activations in one launch (fused Q/K/V, gate/up).  types: per-matrix weight type
+    when the launch mixes two K-quant types (b200_gemv_job.type2); t is then the type of ws[0]."""
     require_gpu()
     x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, K)
     N = x.shape[0]
@@ -108,6 +109,7 @@ def mul_mat_vec_q_multi(t: int, ws: list[np.ndarray], x: np.ndarray, K: int) -> 
     off = 0
     for i, (dw, M) in enumerate(zip(dws, Ms)):
         jobs[i].W, jobs[i].X, jobs[i].dst, jobs[i].M, jobs[i].id_index = dw.ptr, dx.ptr, dd.ptr + 4 * off, M, -1
+        jobs[i]._pad = types[i] if types is not None and types[i] != t else 0
         off += M
     tot = sum(Ms)
     check(lib().b200_mul_mat_vec_q_multi(t, jobs, len(ws), row_size(t, K), K, tot, K, N, None, 0, 0, None), "b200_mul_mat_vec_q_multi")

@@ -186,6 +186,26 @@ def test_gemv_multi_matches_single(H):
             assert np.array_equal(bits(f), bits(single))
 
 
+@pytest.mark.parametrize("K", (4096, 8192, 2048))
+@pytest.mark.parametrize("pair", ((R.Q4_K, R.Q6_K), (R.Q6_K, R.Q4_K), (R.Q5_K, R.Q6_K), (R.Q4_K, R.Q5_K)), ids=lambda p: f"{NAME[p[0]]}+{NAME[p[1]]}")
+def test_gemv_two_weight_types_in_one_launch(H, pair, K):
+    """attn_q / attn_k + attn_v of the *_K_M mixes share one decode launch: every row must come out bit-identical to the
+    single-type launch of its matrix (row counts chosen so that pairs straddle the type boundary and CTAs end half full)."""
+    rng = np.random.default_rng(K + pair[0] * 16 + pair[1])
+    ta, tb = pair
+    Ms, ts = (1000, 137, 515), (ta, ta, tb)
+    ws = [random_blocks(t, M, K, rng) for t, M in zip(ts, Ms)]
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    fused = H.mul_mat_vec_q_multi(ta, ws, x, K, types=list(ts))
+    for w, t, f in zip(ws, ts, fused):
+        single = H.mul_mat_vec_q(t, w, x, K, w.shape[0])
+        assert np.array_equal(bits(f), bits(single)), NAME[t]
+    # the second type first
+    fused = H.mul_mat_vec_q_multi(tb, ws[::-1], x, K, types=list(ts[::-1]))
+    for w, t, f in zip(ws[::-1], ts[::-1], fused):
+        assert np.array_equal(bits(f), bits(H.mul_mat_vec_q(t, w, x, K, w.shape[0]))), NAME[t]
+
+
 def test_gemv_bad_arguments(H):
     import koboldcpp_b200.lib as L
     w = np.zeros((4, 144), np.uint8)
