@@ -287,12 +287,19 @@ extern "C" int b200_all_reduce_sum_add_f32(const float *src, const float *residu
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(PW_THREADS);
     cfg.stream = (cudaStream_t)stream;
-    // developer knob: dynamic shared memory the exchange kernel asks for (it uses none): large values keep its CTAs from sharing an
-    // SM with the CTAs of the GEMVs around it
-    static const int ar_smem = getenv("B200_AR_SMEM") ? atoi(getenv("B200_AR_SMEM")) : 0;
+    // The exchange kernel uses no shared memory but ASKS for 150 KB: its CTAs then never share an SM with a CTA of the GEMVs around
+    // it.  Under programmatic dependent launch its 16 small CTAs otherwise become resident next to the (register-lean) decode GEMV
+    // CTAs and poll for their peers' data there while the next GEMV's prologue runs on the same SM: Llama-3-70B over 8 GPUs 186 ->
+    // 241 tok/s (profiles/r02_tp70_variants_n8.log).  B200_AR_SMEM overrides (0: none).
+    static const int ar_smem = getenv("B200_AR_SMEM") ? atoi(getenv("B200_AR_SMEM")) : 150000;
     if (ar_smem > 0) {
-        static bool attr_set = false;
-        if (!attr_set) { B200_CUDA_TRY(cudaFuncSetAttribute(all_reduce_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ar_smem)); attr_set = true; }
+        static bool attr_set_dev[16] = {};
+        int cur_dev = 0;
+        B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+        if (!attr_set_dev[cur_dev & 15]) {
+            B200_CUDA_TRY(cudaFuncSetAttribute(all_reduce_push_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ar_smem));
+            attr_set_dev[cur_dev & 15] = true;
+        }
         cfg.dynamicSmemBytes = (size_t)ar_smem;
     }
     cudaLaunchAttribute at[1];

@@ -38,6 +38,7 @@ struct FaParams {
     int    n_splits, tiles_per_split;
     int    cols_per_cta;  // fattn_mma_kernel: query columns per CTA (<= 16, runtime)
     int    trace_slot;    // developer timeline (B200_FA_TRACE builds)
+    int    dyn_tiles;     // fattn_mma_kernel, decode inside a cluster: KV tiles handed out dynamically to the warps of the cluster
     int    cluster_merge; // fattn_mma_kernel: the n_splits CTAs of a (kv-head, column tile) are one cluster and merge through DSMEM
     size_t q_nb1, q_nb2, k_nb1, k_nb2, v_nb1, v_nb2, mask_nb1;
     float  scale, max_bias, softcap, m0, m1;
@@ -685,6 +686,11 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     p.n_splits = pl.n_splits; p.tiles_per_split = pl.tiles_per_split;
     p.cols_per_cta = pl.C;
     p.cluster_merge = pl.cluster ? 1 : 0;
+    // dynamic tile hand-out inside the cluster: measured SLOWER (7B @ 4k: 18.7 -> 20.1 us; the CTAs' finish times close up from
+    // 4.3 to 2.6 us but 32 warps fetching from one shared-memory counter of CTA 0 every iteration delay everybody), so it is
+    // opt-in (B200_FA_DYN=1) until the hand-out is chunked
+    static const bool use_dyn = getenv("B200_FA_DYN") != nullptr;
+    p.dyn_tiles = pl.cluster && a->N == 1 && use_dyn ? 1 : 0;
     FTRACE_SLOT(p);
     p.q_nb1 = a->q_nb1; p.q_nb2 = a->q_nb2; p.k_nb1 = a->k_nb1; p.k_nb2 = a->k_nb2; p.v_nb1 = a->v_nb1; p.v_nb2 = a->v_nb2;
     p.mask_nb1 = a->mask_nb1;

@@ -58,6 +58,15 @@ __device__ __forceinline__ unsigned pack_h2(float lo, float hi) {
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// fetch-and-increment of a counter in the shared memory of CTA `rank` of the cluster
+__device__ __forceinline__ unsigned atom_inc_cluster(unsigned *local, unsigned rank) {
+    unsigned ra, v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(smem_u32(local)), "r"(rank));
+    asm volatile("atom.shared::cluster.add.u32 %0, [%1], 1;" : "=r"(v) : "r"(ra) : "memory");
+    return v;
+}
 __device__ __forceinline__ float ld_cluster_f32(const float *local, unsigned rank) {
     unsigned ra;
     float v;
@@ -225,27 +234,42 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         }
     }
 
-    int t_issue = t_begin + warp;
+    // ---- decode inside a cluster, opt-in (p.dyn_tiles): the KV tiles of the (kv-head, column tile) are handed out DYNAMICALLY
+    // to the warps of all its CTAs (a counter in the shared memory of CTA 0, fetched one iteration ahead): with fixed ranges the
+    // CTAs of a launch finish up to 4 us apart (they do not get equal shares of the HBM bandwidth) and the merge waits for the
+    // last one (profiles/r02_fattn_trace_timeline.log).  Not the default: see fattn.cu.
+    const bool dyn = p.dyn_tiles != 0;
+    __shared__ unsigned tile_ctr;
+    const int nwt = FM_NW * p.n_splits;  // warps of the cluster
+    if (dyn) {
+        if (threadIdx.x == 0) tile_ctr = (unsigned)(nwt * (FM_NBUF - 1));  // the first FM_NBUF - 1 tiles of every warp are fixed
+        cluster_arrive();  // (waited for just before the first fetch)
+    }
+    const int t_lo = dyn ? 0 : t_begin, t_hi = dyn ? n_tiles : t_end;
+    const int t_first = dyn ? split * FM_NW + warp : t_begin + warp, t_step = dyn ? nwt : FM_NW;
+
     int ibuf = 0, n_issued = 0;
-    auto issue = [&]() {
+    auto issue = [&](int tt) {
         const bool sk = n_issued < 64 && ((skip >> n_issued) & 1ull) != 0;
         n_issued++;
-        if (t_issue < t_end && !sk) {
+        if (tt < t_hi && !sk) {
             unsigned char *kb = my_tiles + (size_t)ibuf * 2 * G::RING_TILE;
             if constexpr (Q8) {
-                mma_load_tile_q8<D>(kb, kbase, p.k_nb1, t_issue * FM_TP, p.n_kv, lane);
-                mma_load_tile_q8<D>(kb + G::RING_TILE, vbase, p.v_nb1, t_issue * FM_TP, p.n_kv, lane);
+                mma_load_tile_q8<D>(kb, kbase, p.k_nb1, tt * FM_TP, p.n_kv, lane);
+                mma_load_tile_q8<D>(kb + G::RING_TILE, vbase, p.v_nb1, tt * FM_TP, p.n_kv, lane);
             } else {
-                mma_load_tile<D>(kb, kbase, p.k_nb1, t_issue * FM_TP, p.n_kv, lane);
-                mma_load_tile<D>(kb + G::RING_TILE, vbase, p.v_nb1, t_issue * FM_TP, p.n_kv, lane);
+                mma_load_tile<D>(kb, kbase, p.k_nb1, tt * FM_TP, p.n_kv, lane);
+                mma_load_tile<D>(kb + G::RING_TILE, vbase, p.v_nb1, tt * FM_TP, p.n_kv, lane);
             }
         }
         cp_async_commit();  // always commit (possibly empty) so the group accounting stays uniform
-        t_issue += FM_NW;
         ibuf = ibuf + 1 == FM_NBUF ? 0 : ibuf + 1;
     };
-#pragma unroll
-    for (int s = 0; s < FM_NBUF - 1; s++) issue();
+    static_assert(FM_NBUF == 3, "the tile FIFO below holds FM_NBUF - 1 = 2 entries");
+    int f0 = t_first, f1 = t_first + t_step;  // tiles in flight, oldest first
+    issue(f0);
+    issue(f1);
+    (void)t_lo;
 
     // Q as f16 A fragments (the reference rounds Q to f16, ggml.c:15788)
     unsigned qa[KS][4];
@@ -274,11 +298,27 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     const unsigned v_off = (unsigned)(((mi & 1) * 8 + mr) * G::ROW_STRIDE + (mi >> 1) * 16);  // V: keys (mi&1)*8.., dims (mi>>1)*8..
 
     int cbuf = 0, n_done = 0;
-    for (int t = t_begin + warp; t < t_end; t += FM_NW) {
-        issue();
+    unsigned grabbed = 0;  // dynamic mode: the tile fetched during the previous iteration (lane 0)
+    if (dyn) {
+        cluster_wait();  // tile_ctr of CTA 0 is initialised
+        if (lane == 0) grabbed = atom_inc_cluster(&tile_ctr, 0);
+    }
+    for (;;) {
+        int tnew;
+        if (dyn) {
+            tnew = (int)__shfl_sync(0xffffffffu, grabbed, 0);
+            if (lane == 0 && tnew < t_hi) grabbed = atom_inc_cluster(&tile_ctr, 0);  // for the next iteration: its latency hides here
+        } else {
+            tnew = f1 + t_step;
+        }
+        const int t = f0;
+        if (t >= t_hi) break;  // tile numbers only grow: nothing is left for this warp
+        issue(tnew);
+        f0 = f1;
+        f1 = tnew;
         cp_async_wait<FM_NBUF - 1>();
         __syncwarp();
-        if (t == t_begin) FTRACE(3);
+        if (n_done == 0 && warp == 0) FTRACE(3);
         const bool sk = n_done < 64 && ((skip >> n_done) & 1ull) != 0;
         n_done++;
         if (sk) {  // every score of the tile is -inf: p = 0, nothing changes
