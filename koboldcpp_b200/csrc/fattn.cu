@@ -425,6 +425,7 @@ namespace b200 {
 
 // ------------------------------------------------------------------------------------------------ host side
 struct FaPlan {
+    bool prefill;  // tensor-core kernel, prompt form: 64 columns per CTA, tiles shared by its warps, no splits
     bool cluster;  // tensor-core kernel: splits merged through distributed shared memory
     int C, n_ct, n_splits, tiles_per_split;
     size_t part_bytes, ticket_bytes;
@@ -457,6 +458,20 @@ static bool fa_use_mma(const b200_fattn_args *a) {
 static FaPlan fa_plan(const b200_fattn_args *a) {
     FaPlan pl;
     const int64_t n_cols = a->N * (a->n_head / a->n_head_kv);
+    pl.prefill = false;
+    static const bool no_prefill = getenv("B200_FA_NO_PREFILL") != nullptr;  // developer switch
+    if (fa_use_mma(a) && a->type_k == B200_TYPE_F16 && n_cols > 2 * FM_MAXC && !no_prefill) {
+        // prompt batch: 64 columns per CTA, every warp 16 of them over the whole KV range
+        pl.prefill = true;
+        pl.cluster = false;
+        pl.C = FP_COLS;
+        pl.n_ct = (int)((n_cols + FP_COLS - 1) / FP_COLS);
+        pl.n_splits = 1;
+        pl.tiles_per_split = (int)((a->n_kv + FM_TP - 1) / FM_TP);
+        pl.ticket_bytes = 256;
+        pl.part_bytes = 0;
+        return pl;
+    }
     if (fa_use_mma(a)) {
         // tensor-core kernel: a CTA costs the same for 1..16 columns, so a column tile is as wide as it can be
         pl.C = (int)(n_cols < FM_MAXC ? n_cols : FM_MAXC);
@@ -611,6 +626,32 @@ static int fa_launch_mma(const FaParams &p, const FaPlan &pl, cudaStream_t st, b
     return B200_OK;
 }
 
+template <int D>
+static int fa_launch_prefill(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
+    using G = MmaGeo<B200_TYPE_F16, D>;
+    const size_t smem = (size_t)FP_NBUF * 2 * G::TILE_BYTES;
+    static bool attr_set_dev[16] = {};  // cudaFuncSetAttribute is per device
+    int cur_dev = 0;
+    B200_CUDA_TRY(cudaGetDevice(&cur_dev));
+    bool &attr_set = attr_set_dev[cur_dev & 15];
+    if (!attr_set) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(fattn_mma_prefill_kernel<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)pl.n_ct, (unsigned)p.n_head_kv, 1);
+    cfg.blockDim = dim3(FM_NW * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fattn_mma_prefill_kernel<D>, p));
+    return B200_OK;
+}
+
 template <int TYPE, int D>
 static int fa_dispatch_c(const FaParams &p, const FaPlan &pl, cudaStream_t st, bool pdl) {
     switch (pl.C) {
@@ -701,6 +742,10 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     p.m1 = powf(2.0f, -(a->max_bias / 2.0f) / p.n_head_log2);
     const cudaStream_t st = (cudaStream_t)stream;
     const bool pdl = g_mmvq_pdl;
+    if (pl.prefill) {
+        if (((uintptr_t)a->q | a->q_nb1 | a->q_nb2) & 7) { set_error("b200_flash_attn_ext: Q must be 8-byte aligned"); return B200_ERR_UNSUPPORTED; }
+        return a->D == 128 ? fa_launch_prefill<128>(p, pl, st, pdl) : fa_launch_prefill<64>(p, pl, st, pdl);
+    }
     if (fa_use_mma(a)) {
         if (((uintptr_t)a->q | a->q_nb1 | a->q_nb2) & 7) { set_error("b200_flash_attn_ext: Q must be 8-byte aligned"); return B200_ERR_UNSUPPORTED; }
         if (a->type_k == B200_TYPE_Q8_0) return a->D == 128 ? fa_launch_mma<B200_TYPE_Q8_0, 128>(p, pl, st, pdl) : fa_launch_mma<B200_TYPE_Q8_0, 64>(p, pl, st, pdl);

@@ -150,6 +150,83 @@ __device__ __forceinline__ void mma_dequant_tile_q8(unsigned char *dst, const un
     }
 }
 
+// One (16 keys x K, V) tile against the warp's 16 query columns: S = Q.K^T on the tensor cores, online softmax on the accumulator
+// fragments, O += P.V.  kt / vt: shared addresses of the f16 tiles; t: tile number (keys 16 t ..).
+template <int D>
+__device__ __forceinline__ void mma_tile_step(unsigned kt, unsigned vt, int t, const unsigned (&qa)[D / 16][4], float (&m)[2], float (&l)[2],
+                                              float (&o)[D / 8][4], const unsigned char *const (&mrow)[2], const float (&slope)[2], float scale,
+                                              float softcap, int n_kv, bool mask_al4, unsigned k_off, unsigned v_off, int t4) {
+    constexpr int KS = D / 16;
+    constexpr float LOG2E = 1.4426950408889634f;
+    float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+        unsigned b0, b1, b2, b3;
+        ldsm_x4(kt + k_off + ks * 32, b0, b1, b2, b3);
+        mma_f16(s[0], qa[ks], b0, b1);  // keys 0-7
+        mma_f16(s[1], qa[ks], b2, b3);  // keys 8-15
+    }
+    // s[nb][2 hh + e]: column g + 8 hh, key 16 t + 8 nb + 2 t4 + e
+    const int key0 = t * FM_TP + 2 * t4;
+    float tmax[2];
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+#pragma unroll
+        for (int nb = 0; nb < 2; nb++) {
+            const int key = key0 + 8 * nb;
+            float s0 = s[nb][2 * hh] * scale, s1 = s[nb][2 * hh + 1] * scale;
+            if (softcap != 0.0f) { s0 = softcap * tanhf(s0); s1 = softcap * tanhf(s1); }
+            if (mrow[hh] != nullptr && key < n_kv) {
+                float2 mf;
+                if (mask_al4) {  // (an odd n_kv reads one half past the row: it is masked out below; buffers carry a tail)
+                    mf = __half22float2(*reinterpret_cast<const __half2 *>(mrow[hh] + 2 * (size_t)key));
+                } else {
+                    mf.x = __half2float(*reinterpret_cast<const __half *>(mrow[hh] + 2 * (size_t)key));
+                    mf.y = key + 1 < n_kv ? __half2float(*reinterpret_cast<const __half *>(mrow[hh] + 2 * (size_t)key + 2)) : 0.f;
+                }
+                s0 += slope[hh] * mf.x;
+                s1 += slope[hh] * mf.y;
+            }
+            s[nb][2 * hh]     = key < n_kv ? s0 : -INFINITY;
+            s[nb][2 * hh + 1] = key + 1 < n_kv ? s1 : -INFINITY;
+        }
+        float mx = fmaxf(fmaxf(s[0][2 * hh], s[0][2 * hh + 1]), fmaxf(s[1][2 * hh], s[1][2 * hh + 1]));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        tmax[hh] = mx;
+    }
+    unsigned pa[4];
+    float alpha[2];
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+        const float mn = fmaxf(m[hh], tmax[hh]);
+        const float mb = mn == -INFINITY ? 0.f : mn * LOG2E;
+        alpha[hh] = mn == -INFINITY ? 1.0f : exp2f(m[hh] * LOG2E - mb);
+        const float p0 = exp2f(s[0][2 * hh] * LOG2E - mb), p1 = exp2f(s[0][2 * hh + 1] * LOG2E - mb);
+        const float p2 = exp2f(s[1][2 * hh] * LOG2E - mb), p3 = exp2f(s[1][2 * hh + 1] * LOG2E - mb);
+        const float q0 = mn == -INFINITY ? 0.f : p0, q1 = mn == -INFINITY ? 0.f : p1;
+        const float q2 = mn == -INFINITY ? 0.f : p2, q3 = mn == -INFINITY ? 0.f : p3;
+        l[hh] = l[hh] * alpha[hh] + ((q0 + q1) + (q2 + q3));
+        m[hh] = mn;
+        pa[hh]     = pack_h2(q0, q1);  // a0 / a1: row g (+8), keys 2 t4, 2 t4 + 1
+        pa[2 + hh] = pack_h2(q2, q3);  // a2 / a3: keys 8 + 2 t4, ...
+    }
+    if (__any_sync(0xffffffffu, alpha[0] != 1.0f || alpha[1] != 1.0f)) {
+#pragma unroll
+        for (int i = 0; i < 2 * KS; i++) {
+            o[i][0] *= alpha[0]; o[i][1] *= alpha[0];
+            o[i][2] *= alpha[1]; o[i][3] *= alpha[1];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < KS; j++) {
+        unsigned b0, b1, b2, b3;
+        ldsm_x4_t(vt + v_off + j * 32, b0, b1, b2, b3);
+        mma_f16(o[2 * j], pa, b0, b1);      // dims 16 j .. 16 j + 7
+        mma_f16(o[2 * j + 1], pa, b2, b3);  // dims 16 j + 8 .. 16 j + 15
+    }
+}
+
 template <int TYPE, int D>
 __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_constant__ FaParams p) {
     using G = MmaGeo<TYPE, D>;
@@ -208,14 +285,21 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     // ---- batches (prompt processing): KV tiles whose mask is -inf for every column of this CTA (the causal upper triangle, the
     // cells of other sequences) are neither loaded nor computed.  Bit i of `skip`: the i-th tile of this warp, t = t_begin + warp
     // + 4 i; lane i checks tile i (two passes cover 64 tiles per warp; later tiles are simply processed).
+    // tile walk of this warp: t_first, t_first + t_step, ... < t_hi.  Splits that are one cluster interleave their tiles (warp w of
+    // CTA s takes tiles 4 s + w + 4 n_splits k): every CTA sweeps the whole KV range at the same pace, so differences between
+    // regions of the cache (DRAM page / channel luck) do not make one CTA finish late; otherwise a split owns a contiguous range
+    const bool inter = p.cluster_merge != 0;
+    const int nwt = FM_NW * p.n_splits;  // warps of the cluster
+    const int t_hi = inter ? n_tiles : t_end;
+    const int t_first = inter ? split * FM_NW + warp : t_begin + warp, t_step = inter ? nwt : FM_NW;
     unsigned long long skip = 0;
     if (p.N > 1 && p.mask != nullptr) {
         const bool al16 = (((uintptr_t)p.mask | p.mask_nb1) & 15) == 0;
 #pragma unroll 1
         for (int pass = 0; pass < 2; pass++) {
-            const int tt = t_begin + warp + FM_NW * (pass * 32 + lane);
+            const int tt = t_first + t_step * (pass * 32 + lane);
             bool masked = false;
-            if (tt < t_end) {
+            if (tt < t_hi) {
                 masked = true;
                 const int key = tt * FM_TP;
                 for (int c = 0; c < ncol; c++) {
@@ -240,13 +324,10 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     // last one (profiles/r02_fattn_trace_timeline.log).  Not the default: see fattn.cu.
     const bool dyn = p.dyn_tiles != 0;
     __shared__ unsigned tile_ctr;
-    const int nwt = FM_NW * p.n_splits;  // warps of the cluster
     if (dyn) {
         if (threadIdx.x == 0) tile_ctr = (unsigned)(nwt * (FM_NBUF - 1));  // the first FM_NBUF - 1 tiles of every warp are fixed
         cluster_arrive();  // (waited for just before the first fetch)
     }
-    const int t_lo = dyn ? 0 : t_begin, t_hi = dyn ? n_tiles : t_end;
-    const int t_first = dyn ? split * FM_NW + warp : t_begin + warp, t_step = dyn ? nwt : FM_NW;
 
     int ibuf = 0, n_issued = 0;
     auto issue = [&](int tt) {
@@ -269,7 +350,6 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     int f0 = t_first, f1 = t_first + t_step;  // tiles in flight, oldest first
     issue(f0);
     issue(f1);
-    (void)t_lo;
 
     // Q as f16 A fragments (the reference rounds Q to f16, ggml.c:15788)
     unsigned qa[KS][4];
@@ -285,8 +365,6 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
     const bool mask_al4 = (((uintptr_t)p.mask | p.mask_nb1) & 3) == 0;
     float scale = p.scale;
     if (p.softcap != 0.0f) scale /= p.softcap;
-    constexpr float LOG2E = 1.4426950408889634f;
-
     float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};  // l: this lane's share (its 4 keys of every tile)
     float o[2 * KS][4];
 #pragma unroll
@@ -338,73 +416,7 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
             vt = kt + G::TILE_BYTES;
         }
 
-        float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
-#pragma unroll
-        for (int ks = 0; ks < KS; ks++) {
-            unsigned b0, b1, b2, b3;
-            ldsm_x4(kt + k_off + ks * 32, b0, b1, b2, b3);
-            mma_f16(s[0], qa[ks], b0, b1);  // keys 0-7
-            mma_f16(s[1], qa[ks], b2, b3);  // keys 8-15
-        }
-        // s[nb][2 hh + e]: column g + 8 hh, key 16 t + 8 nb + 2 t4 + e
-        const int key0 = t * FM_TP + 2 * t4;
-        float tmax[2];
-#pragma unroll
-        for (int hh = 0; hh < 2; hh++) {
-#pragma unroll
-            for (int nb = 0; nb < 2; nb++) {
-                const int key = key0 + 8 * nb;
-                float s0 = s[nb][2 * hh] * scale, s1 = s[nb][2 * hh + 1] * scale;
-                if (p.softcap != 0.0f) { s0 = p.softcap * tanhf(s0); s1 = p.softcap * tanhf(s1); }
-                if (mrow[hh] != nullptr && key < p.n_kv) {
-                    float2 mf;
-                    if (mask_al4) {  // (an odd n_kv reads one half past the row: it is masked out below; buffers carry a tail)
-                        mf = __half22float2(*reinterpret_cast<const __half2 *>(mrow[hh] + 2 * (size_t)key));
-                    } else {
-                        mf.x = __half2float(*reinterpret_cast<const __half *>(mrow[hh] + 2 * (size_t)key));
-                        mf.y = key + 1 < p.n_kv ? __half2float(*reinterpret_cast<const __half *>(mrow[hh] + 2 * (size_t)key + 2)) : 0.f;
-                    }
-                    s0 += slope[hh] * mf.x;
-                    s1 += slope[hh] * mf.y;
-                }
-                s[nb][2 * hh]     = key < p.n_kv ? s0 : -INFINITY;
-                s[nb][2 * hh + 1] = key + 1 < p.n_kv ? s1 : -INFINITY;
-            }
-            float mx = fmaxf(fmaxf(s[0][2 * hh], s[0][2 * hh + 1]), fmaxf(s[1][2 * hh], s[1][2 * hh + 1]));
-            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-            tmax[hh] = mx;
-        }
-        unsigned pa[4];
-        float alpha[2];
-#pragma unroll
-        for (int hh = 0; hh < 2; hh++) {
-            const float mn = fmaxf(m[hh], tmax[hh]);
-            const float mb = mn == -INFINITY ? 0.f : mn * LOG2E;
-            alpha[hh] = mn == -INFINITY ? 1.0f : exp2f(m[hh] * LOG2E - mb);
-            const float p0 = exp2f(s[0][2 * hh] * LOG2E - mb), p1 = exp2f(s[0][2 * hh + 1] * LOG2E - mb);
-            const float p2 = exp2f(s[1][2 * hh] * LOG2E - mb), p3 = exp2f(s[1][2 * hh + 1] * LOG2E - mb);
-            const float q0 = mn == -INFINITY ? 0.f : p0, q1 = mn == -INFINITY ? 0.f : p1;
-            const float q2 = mn == -INFINITY ? 0.f : p2, q3 = mn == -INFINITY ? 0.f : p3;
-            l[hh] = l[hh] * alpha[hh] + ((q0 + q1) + (q2 + q3));
-            m[hh] = mn;
-            pa[hh]     = pack_h2(q0, q1);  // a0 / a1: row g (+8), keys 2 t4, 2 t4 + 1
-            pa[2 + hh] = pack_h2(q2, q3);  // a2 / a3: keys 8 + 2 t4, ...
-        }
-        if (__any_sync(0xffffffffu, alpha[0] != 1.0f || alpha[1] != 1.0f)) {
-#pragma unroll
-            for (int i = 0; i < 2 * KS; i++) {
-                o[i][0] *= alpha[0]; o[i][1] *= alpha[0];
-                o[i][2] *= alpha[1]; o[i][3] *= alpha[1];
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < KS; j++) {
-            unsigned b0, b1, b2, b3;
-            ldsm_x4_t(vt + v_off + j * 32, b0, b1, b2, b3);
-            mma_f16(o[2 * j], pa, b0, b1);      // dims 16 j .. 16 j + 7
-            mma_f16(o[2 * j + 1], pa, b2, b3);  // dims 16 j + 8 .. 16 j + 15
-        }
+        mma_tile_step<D>(kt, vt, t, qa, m, l, o, mrow, slope, scale, p.softcap, p.n_kv, mask_al4, k_off, v_off, t4);
         __syncwarp();  // all lanes are done with this buffer before it is refilled two iterations from now
         cbuf = cbuf + 1 == FM_NBUF ? 0 : cbuf + 1;
     }
@@ -573,6 +585,155 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         *reinterpret_cast<float4 *>(p.dst + ((size_t)n * p.n_head + h) * D + 4 * d4) = make_float4(a.x / L, a.y / L, a.z / L, a.w / L);
     }
     FTRACE(7);
+}
+
+// ------------------------------------------------------------------------------------------------ prompt batches (a12)
+// Flash-prefill form of the same arithmetic: a CTA serves 64 query columns of one kv-head (each of its 4 warps owns 16 of them for
+// the whole KV range -- no cross-warp merge, no splits) and the 4 warps SHARE every (K, V) tile: one CTA-wide cp.async ring, one
+// __syncthreads per tile.  The decode kernel above gives every warp its own tiles instead (right for 1..16 columns); run on a
+// 512-token batch it launched 1024 CTAs whose 4 warps saw ~4 tiles each and spent their time in prologue and merge (7B pp512:
+// 165 us per layer, 27 % of the step: profiles/r02_launches_pp512_7b.txt).  Causal structure: tile i is skipped by a warp when the
+// mask is -inf for all its 16 columns, and not even loaded when that holds for all 64 (the skip words cover the LAST 64 tiles of
+// the range: that is where the upper triangle lives).
+constexpr int FP_NBUF = 4;   // stages of the CTA ring
+constexpr int FP_COLS = 64;  // query columns per CTA
+
+template <int D>
+__global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_prefill_kernel(const __grid_constant__ FaParams p) {
+    using G = MmaGeo<B200_TYPE_F16, D>;
+    constexpr int KS = D / 16;
+    extern __shared__ __align__(128) unsigned char smem[];
+    __shared__ unsigned long long skip_w[FM_NW];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t4 = lane & 3;
+    const int hk = blockIdx.y, ct = blockIdx.x;
+    const int col0 = ct * FP_COLS + warp * FM_MAXC;        // this warp's 16 columns
+    const int ncol = max(0, min(FM_MAXC, p.n_cols - col0));
+    const int n_tiles = (p.n_kv + FM_TP - 1) / FM_TP;
+    const unsigned char *kbase = p.k + (size_t)hk * p.k_nb2;
+    const unsigned char *vbase = p.v + (size_t)hk * p.v_nb2;
+
+    pdl_wait();
+    pdl_trigger();
+
+    // ---- Q fragments, mask rows, slopes of this warp's columns
+    unsigned qa[KS][4];
+    float slope[2];
+    const unsigned char *mrow[2];
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+        const int c = g + 8 * hh;
+        const bool ok = c < ncol;
+        const int col = ok ? col0 + c : 0;
+        const int n = col / p.gqa, h = hk * p.gqa + col % p.gqa;
+        slope[hh] = 1.0f;
+        if (p.max_bias > 0.0f) slope[hh] = h < p.n_head_log2 ? powf(p.m0, (float)(h + 1)) : powf(p.m1, (float)(2 * (h - p.n_head_log2) + 1));
+        mrow[hh] = p.mask != nullptr ? p.mask + (size_t)n * p.mask_nb1 : nullptr;
+        const float *qrow = reinterpret_cast<const float *>(p.q + (size_t)n * p.q_nb1 + (size_t)h * p.q_nb2);
+#pragma unroll
+        for (int s = 0; s < KS; s++) {
+            float2 lo = make_float2(0.f, 0.f), hi = make_float2(0.f, 0.f);
+            if (ok) {
+                lo = __ldcg(reinterpret_cast<const float2 *>(qrow + 16 * s + 2 * t4));
+                hi = __ldcg(reinterpret_cast<const float2 *>(qrow + 16 * s + 8 + 2 * t4));
+            }
+            qa[s][hh] = pack_h2(lo.x, lo.y);
+            qa[s][2 + hh] = pack_h2(hi.x, hi.y);
+        }
+    }
+    // ---- skip words: bit i <-> tile t_skip0 + i is masked for all columns of this warp (lane i checks tile i)
+    const int t_skip0 = n_tiles > 64 ? n_tiles - 64 : 0;
+    unsigned long long skip = 0;
+    if (p.mask != nullptr) {
+        const bool al16 = (((uintptr_t)p.mask | p.mask_nb1) & 15) == 0;
+#pragma unroll 1
+        for (int pass = 0; pass < 2; pass++) {
+            const int tt = t_skip0 + pass * 32 + lane;
+            bool masked = false;
+            if (tt < n_tiles) {
+                masked = true;
+                const int key = tt * FM_TP;
+                for (int c = 0; c < ncol; c++) {
+                    const unsigned char *mr = p.mask + (size_t)((col0 + c) / p.gqa) * p.mask_nb1 + 2 * (size_t)key;
+                    if (al16 && key + FM_TP <= p.n_kv) {
+                        const uint4 u0 = __ldg(reinterpret_cast<const uint4 *>(mr)), u1 = __ldg(reinterpret_cast<const uint4 *>(mr) + 1);
+                        masked = masked && (u0.x & u0.y & u0.z & u0.w & u1.x & u1.y & u1.z & u1.w) == 0xfc00fc00u &&
+                                 (u0.x | u0.y | u0.z | u0.w | u1.x | u1.y | u1.z | u1.w) == 0xfc00fc00u;
+                    } else {
+                        for (int e = 0; e < FM_TP; e++)
+                            if (key + e < p.n_kv) masked = masked && *reinterpret_cast<const unsigned short *>(mr + 2 * e) == 0xfc00;
+                    }
+                }
+            }
+            skip |= (unsigned long long)__ballot_sync(0xffffffffu, masked) << (32 * pass);
+        }
+    }
+    if (ncol == 0) skip = ~0ull;  // a warp without columns never needs a tile
+    if (lane == 0) skip_w[warp] = skip;
+    __syncthreads();
+    const unsigned long long skip_cta = skip_w[0] & skip_w[1] & skip_w[2] & skip_w[3];
+    auto is_skipped = [&](unsigned long long w, int tt) { return tt >= t_skip0 && ((w >> (tt - t_skip0)) & 1ull) != 0; };
+    // a warp without columns must still not read tiles before t_skip0: give it nothing to do
+    const bool idle = ncol == 0;
+
+    // ---- CTA ring: stage = (K tile, V tile); 128 threads copy a tile pair (2 x 16 rows x D/8 chunks of 16 bytes)
+    constexpr int CPR = G::ROW_BYTES / 16;
+    constexpr int CHUNKS = 2 * FM_TP * CPR;
+    auto load_stage = [&](int tt, int st) {
+        if (tt < n_tiles && !is_skipped(skip_cta, tt)) {
+            unsigned char *base = smem + (size_t)st * 2 * G::TILE_BYTES;
+#pragma unroll
+            for (int i = threadIdx.x; i < CHUNKS; i += FM_NW * 32) {
+                const int kv = i / (FM_TP * CPR), j = i - kv * (FM_TP * CPR), r = j / CPR, c = j - r * CPR;
+                const int row = tt * FM_TP + r;
+                unsigned char *d = base + kv * G::TILE_BYTES + r * G::ROW_STRIDE + c * 16;
+                if (row < p.n_kv) cp_async16(d, (kv ? vbase + (size_t)row * p.v_nb1 : kbase + (size_t)row * p.k_nb1) + c * 16);
+                else *reinterpret_cast<uint4 *>(d) = make_uint4(0, 0, 0, 0);
+            }
+        }
+        cp_async_commit();
+    };
+#pragma unroll
+    for (int st = 0; st < FP_NBUF - 1; st++) load_stage(st, st);
+
+    const bool mask_al4 = (((uintptr_t)p.mask | p.mask_nb1) & 3) == 0;
+    float scale = p.scale;
+    if (p.softcap != 0.0f) scale /= p.softcap;
+    float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};
+    float o[2 * KS][4];
+#pragma unroll
+    for (int i = 0; i < 2 * KS; i++) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    const int mi = lane >> 3, mr = lane & 7;
+    const unsigned k_off = (unsigned)(((mi >> 1) * 8 + mr) * G::ROW_STRIDE + (mi & 1) * 16);
+    const unsigned v_off = (unsigned)(((mi & 1) * 8 + mr) * G::ROW_STRIDE + (mi >> 1) * 16);
+
+    for (int t = 0; t < n_tiles; t++) {
+        cp_async_wait<FP_NBUF - 2>();   // tile t has landed (this thread's copies) ...
+        __syncthreads();                // ... everybody's; and everybody is done with tile t - 1, whose stage is refilled now
+        load_stage(t + FP_NBUF - 1, (t + FP_NBUF - 1) % FP_NBUF);
+        if (idle || is_skipped(skip, t)) continue;
+        const unsigned kt = smem_u32(smem + (size_t)(t % FP_NBUF) * 2 * G::TILE_BYTES), vt = kt + G::TILE_BYTES;
+        mma_tile_step<D>(kt, vt, t, qa, m, l, o, mrow, slope, scale, p.softcap, p.n_kv, mask_al4, k_off, v_off, t4);
+    }
+    cp_async_wait<0>();
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+        l[hh] += __shfl_xor_sync(0xffffffffu, l[hh], 1);
+        l[hh] += __shfl_xor_sync(0xffffffffu, l[hh], 2);
+    }
+#pragma unroll
+    for (int hh = 0; hh < 2; hh++) {
+        const int c = g + 8 * hh;
+        if (c < ncol) {
+            const int col = col0 + c, n = col / p.gqa, h = hk * p.gqa + col % p.gqa;
+            float *orow = p.dst + ((size_t)n * p.n_head + h) * D;
+            const float inv = 1.0f / l[hh];
+#pragma unroll
+            for (int i = 0; i < 2 * KS; i++)
+                *reinterpret_cast<float2 *>(orow + 8 * i + 2 * t4) = make_float2(o[i][2 * hh] * inv, o[i][2 * hh + 1] * inv);
+        }
+    }
 }
 
 }  // namespace b200
