@@ -200,7 +200,7 @@ def gemv_launch_plan(shape):
     (K, [(type, M), ...])."""
     from koboldcpp_b200.llama import tensor_shape, tensor_types
     types = tensor_types(shape)
-    kq = {12, 13, 14}
+    kq = {12, 13, 14} if os.environ.get("B200_MIXED_TYPES") else set()  # the planner's opt-in rule (backend_graph.cu: g_mixed_types)
     layers = []
     for il in range(shape.n_layer):
         p = f"blk.{il}."

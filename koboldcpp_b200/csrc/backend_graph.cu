@@ -22,8 +22,11 @@
 
 namespace b200 {
 
-// mixed-type sibling GEMVs in one launch (developer switch B200_NO_MIXED_TYPES)
-static const bool g_mixed_types = getenv("B200_NO_MIXED_TYPES") == nullptr;
+// Sibling GEMVs of two K-quant weight types in one launch (attn_q / attn_k Q4_K + attn_v Q6_K): built and bit-exact
+// (tests/test_gpu_kernels.py::test_gemv_two_weight_types_in_one_launch), but measured neutral on the 7B step (211 -> 195 launches,
+// 507.8 -> 504.9 tok/s: the merged launch needs the larger Q6_K stage, so 2 ring stages instead of 3, and under PDL the saved
+// launch boundary was mostly hidden already) and it lowers the GEMV family's bytes/s; therefore opt-in (B200_MIXED_TYPES=1).
+static const bool g_mixed_types = getenv("B200_MIXED_TYPES") != nullptr;
 static inline bool rows_are_contiguous(const ggml_tensor *w) { return w->nb[1] == row_size(w->type, w->ne[0]); }
 
 enum StepKind { STEP_NODE, STEP_RMS_MUL, STEP_SILU_MUL, STEP_GEMV, STEP_ROPE_KV, STEP_AR_ADD, STEP_MOE_ROUTER };
