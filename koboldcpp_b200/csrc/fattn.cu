@@ -512,7 +512,8 @@ static FaPlan fa_plan(const b200_fattn_args *a) {
         pl.cluster = best > 1 && best <= FM_MAX_CLUSTER && (best & (best - 1)) == 0 && !no_cluster;
         pl.tiles_per_split = (n_tiles + best - 1) / best;
         pl.ticket_bytes = ((size_t)pairs * sizeof(int) + 255) / 256 * 256;
-        pl.part_bytes = best > 1 && !pl.cluster ? (size_t)pairs * best * pl.C * (a->D + FA_RS_PAD) * sizeof(float) : 0;
+        // (the global-memory partials are sized for cluster launches too: if the device cannot place a cluster the launch falls back)
+        pl.part_bytes = best > 1 ? (size_t)pairs * best * pl.C * (a->D + FA_RS_PAD) * sizeof(float) : 0;
         return pl;
     }
     pl.cluster = false;
@@ -622,7 +623,17 @@ static int fa_launch_mma(const FaParams &p, const FaPlan &pl, cudaStream_t st, b
     }
     cfg.attrs = at;
     cfg.numAttrs = na;
-    B200_CUDA_TRY(cudaLaunchKernelEx(&cfg, fattn_mma_kernel<TYPE, D>, p));
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fattn_mma_kernel<TYPE, D>, p);
+    if (e != cudaSuccess && pl.cluster) {
+        // the device could not place the cluster (size, shared memory, a partitioned GPU): same splits, merged through global memory
+        cudaGetLastError();
+        FaParams q = p;
+        q.cluster_merge = 0;
+        q.dyn_tiles = 0;
+        cfg.numAttrs = pdl ? 1 : 0;
+        e = cudaLaunchKernelEx(&cfg, fattn_mma_kernel<TYPE, D>, q);
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(fattn_mma_kernel)");
     return B200_OK;
 }
 
