@@ -47,6 +47,9 @@ enum b200_type {
     B200_TYPE_F32  = 0,
     B200_TYPE_F16  = 1,
     B200_TYPE_Q4_0 = 2,
+    B200_TYPE_Q4_1 = 3,
+    B200_TYPE_Q5_0 = 6,
+    B200_TYPE_Q5_1 = 7,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
     B200_TYPE_Q4_K = 12,

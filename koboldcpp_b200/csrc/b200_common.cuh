@@ -20,6 +20,9 @@ constexpr int QK_K = 256;  // super-block
 
 // bytes per block
 constexpr int Q4_0_BYTES = 18;
+constexpr int Q4_1_BYTES = 20;  // half d, half m, u8 qs[16]          (ggml-common.h:155-161)
+constexpr int Q5_0_BYTES = 22;  // half d, u8 qh[4], u8 qs[16]         (:164-169)
+constexpr int Q5_1_BYTES = 24;  // half d, half m, u8 qh[4], u8 qs[16] (:172-183)
 constexpr int Q8_0_BYTES = 34;
 constexpr int Q8_1_BYTES = 36;
 constexpr int Q4_K_BYTES = 144;
@@ -28,12 +31,13 @@ constexpr int Q6_K_BYTES = 210;
 
 __host__ __device__ constexpr int type_block_values(int t) {
     return (t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_I32) ? 1
-         : (t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q8_1) ? 32
+         : (t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q8_1 || t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1) ? 32
          : (t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K) ? 256 : 0;
 }
 __host__ __device__ constexpr int type_block_bytes(int t) {
     return t == B200_TYPE_F32 ? 4 : t == B200_TYPE_F16 ? 2 : t == B200_TYPE_I32 ? 4
          : t == B200_TYPE_Q4_0 ? Q4_0_BYTES : t == B200_TYPE_Q8_0 ? Q8_0_BYTES : t == B200_TYPE_Q8_1 ? Q8_1_BYTES
+         : t == B200_TYPE_Q4_1 ? Q4_1_BYTES : t == B200_TYPE_Q5_0 ? Q5_0_BYTES : t == B200_TYPE_Q5_1 ? Q5_1_BYTES
          : t == B200_TYPE_Q4_K ? Q4_K_BYTES : t == B200_TYPE_Q5_K ? Q5_K_BYTES : t == B200_TYPE_Q6_K ? Q6_K_BYTES : 0;
 }
 // bytes of 128 consecutive weights (one "slice": the unit one lane processes per step)

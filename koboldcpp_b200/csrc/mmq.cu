@@ -150,6 +150,44 @@ struct Dequant64<B200_TYPE_Q4_0, G> {
     }
 };
 
+// Q4_1 / Q5_0 / Q5_1 (dequantize_row_q4_1 / q5_0 / q5_1, ggml-quants.c:1543-1615): x d + m, or (x5 - 16) d; the fifth bit of value j
+// is bit j of qh.  Byte offsets inside a block: d 0, [m 2], [qh 4 bytes], qs 16 bytes.
+template <int TYPE>
+struct LegacyLayout {
+    static constexpr bool HAS_M = TYPE != B200_TYPE_Q5_0, HAS_H = TYPE != B200_TYPE_Q4_1;
+    static constexpr int BB = type_block_bytes(TYPE), QH = 2 + (HAS_M ? 2 : 0), QS = QH + (HAS_H ? 4 : 0);
+};
+template <int TYPE, bool G>
+struct Dequant64Legacy {
+    static __device__ __forceinline__ void run(const unsigned char *g, int c, unsigned (&o)[32]) {
+        using L = LegacyLayout<TYPE>;
+        constexpr int NWL = (2 * L::BB + 3) / 4;
+        unsigned w[NWL];
+        ld_words<G, NWL>(g + c * 2 * L::BB, w);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const int base = L::BB * b;
+            const float d = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, base) | (BYTE_OF(w, base + 1) << 8))));
+            float m = 0.f;
+            if constexpr (L::HAS_M) m = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, base + 2) | (BYTE_OF(w, base + 3) << 8))));
+            unsigned qh = 0;
+            if constexpr (L::HAS_H) qh = BYTE_OF(w, base + L::QH) | (BYTE_OF(w, base + L::QH + 1) << 8) | (BYTE_OF(w, base + L::QH + 2) << 16) | (BYTE_OF(w, base + L::QH + 3) << 24);
+            if constexpr (TYPE == B200_TYPE_Q5_0) m = d * -16.0f;
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                const unsigned q0 = BYTE_OF(w, base + L::QS + j), q1 = BYTE_OF(w, base + L::QS + 1 + j);
+                const unsigned l0 = (q0 & 15) | (((qh >> j) & 1u) << 4), l1 = (q1 & 15) | (((qh >> (j + 1)) & 1u) << 4);
+                const unsigned h0 = (q0 >> 4) | (((qh >> (16 + j)) & 1u) << 4), h1 = (q1 >> 4) | (((qh >> (17 + j)) & 1u) << 4);
+                o[16 * b + j / 2]     = pack_bf16(d * (float)l0 + m, d * (float)l1 + m);
+                o[16 * b + 8 + j / 2] = pack_bf16(d * (float)h0 + m, d * (float)h1 + m);
+            }
+        }
+    }
+};
+template <bool G> struct Dequant64<B200_TYPE_Q4_1, G> : Dequant64Legacy<B200_TYPE_Q4_1, G> {};
+template <bool G> struct Dequant64<B200_TYPE_Q5_0, G> : Dequant64Legacy<B200_TYPE_Q5_0, G> {};
+template <bool G> struct Dequant64<B200_TYPE_Q5_1, G> : Dequant64Legacy<B200_TYPE_Q5_1, G> {};
+
 template <bool G>
 struct Dequant64<B200_TYPE_Q8_0, G> {
     static __device__ __forceinline__ void run(const unsigned char *g, int c, unsigned (&o)[32]) {
@@ -393,6 +431,34 @@ struct DequantR<B200_TYPE_Q4_0, C> {
         }
     }
 };
+
+template <int TYPE, int C>
+struct DequantRLegacy {
+    static __device__ __forceinline__ void run(const unsigned (&w)[group256_words(TYPE)], unsigned (&o)[32]) {
+        using L = LegacyLayout<TYPE>;
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const int base = 2 * L::BB * C + L::BB * b;  // byte offset of the block inside the 256-value group
+            const float d = f16_at(w, base);
+            float m = 0.f;
+            if constexpr (L::HAS_M) m = f16_at(w, base + 2);
+            if constexpr (TYPE == B200_TYPE_Q5_0) m = d * -16.0f;
+            unsigned qh = 0;
+            if constexpr (L::HAS_H) qh = BYTE_OF(w, base + L::QH) | (BYTE_OF(w, base + L::QH + 1) << 8) | (BYTE_OF(w, base + L::QH + 2) << 16) | (BYTE_OF(w, base + L::QH + 3) << 24);
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                const unsigned q0 = BYTE_OF(w, base + L::QS + j), q1 = BYTE_OF(w, base + L::QS + 1 + j);
+                const unsigned l0 = (q0 & 15) | (((qh >> j) & 1u) << 4), l1 = (q1 & 15) | (((qh >> (j + 1)) & 1u) << 4);
+                const unsigned h0 = (q0 >> 4) | (((qh >> (16 + j)) & 1u) << 4), h1 = (q1 >> 4) | (((qh >> (17 + j)) & 1u) << 4);
+                o[16 * b + j / 2]     = pack_bf16(d * byte_f<0>(l0) + m, d * byte_f<0>(l1) + m);
+                o[16 * b + 8 + j / 2] = pack_bf16(d * byte_f<0>(h0) + m, d * byte_f<0>(h1) + m);
+            }
+        }
+    }
+};
+template <int C> struct DequantR<B200_TYPE_Q4_1, C> : DequantRLegacy<B200_TYPE_Q4_1, C> {};
+template <int C> struct DequantR<B200_TYPE_Q5_0, C> : DequantRLegacy<B200_TYPE_Q5_0, C> {};
+template <int C> struct DequantR<B200_TYPE_Q5_1, C> : DequantRLegacy<B200_TYPE_Q5_1, C> {};
 
 template <int C>
 struct DequantR<B200_TYPE_Q8_0, C> {
@@ -829,7 +895,8 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
                               int64_t K, int64_t M, int64_t N, void *workspace, size_t workspace_bytes, b200_stream_t stream) {
     if (!W || !X || !dst) { set_error("b200_mul_mat_q: NULL argument"); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
-    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
+    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1)) {
         set_error("b200_mul_mat_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -864,6 +931,9 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
         case B200_TYPE_Q4_K: return mmq_dispatch_bn<B200_TYPE_Q4_K>(p, st);
         case B200_TYPE_Q5_K: return mmq_dispatch_bn<B200_TYPE_Q5_K>(p, st);
         case B200_TYPE_Q6_K: return mmq_dispatch_bn<B200_TYPE_Q6_K>(p, st);
+        case B200_TYPE_Q4_1: return mmq_dispatch_bn<B200_TYPE_Q4_1>(p, st);
+        case B200_TYPE_Q5_0: return mmq_dispatch_bn<B200_TYPE_Q5_0>(p, st);
+        case B200_TYPE_Q5_1: return mmq_dispatch_bn<B200_TYPE_Q5_1>(p, st);
     }
     return B200_ERR_UNSUPPORTED;
 }
@@ -880,7 +950,8 @@ extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, s
                                  int64_t dst_stride_tok, int64_t K, int64_t M, int64_t n_used, int64_t n_b_rows, int64_t T, void *workspace,
                                  size_t workspace_bytes, b200_stream_t stream) {
     if (!as || !ids || !b || !dst) { set_error("b200_mul_mat_id_q: NULL argument"); return B200_ERR_INVALID; }
-    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
+    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1)) {
         set_error("b200_mul_mat_id_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -927,6 +998,9 @@ extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, s
         case B200_TYPE_Q4_K: return mid_dispatch_bn<B200_TYPE_Q4_K>(p, bn, n_rows, (unsigned)max_tiles, st);
         case B200_TYPE_Q5_K: return mid_dispatch_bn<B200_TYPE_Q5_K>(p, bn, n_rows, (unsigned)max_tiles, st);
         case B200_TYPE_Q6_K: return mid_dispatch_bn<B200_TYPE_Q6_K>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q4_1: return mid_dispatch_bn<B200_TYPE_Q4_1>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q5_0: return mid_dispatch_bn<B200_TYPE_Q5_0>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q5_1: return mid_dispatch_bn<B200_TYPE_Q5_1>(p, bn, n_rows, (unsigned)max_tiles, st);
     }
     return B200_ERR_UNSUPPORTED;
 }

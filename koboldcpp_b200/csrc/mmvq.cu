@@ -440,7 +440,8 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
                 const b200_gemv_fuse *fuse = nullptr) {
     if (!jobs || n_jobs < 1 || n_jobs > B200_GEMV_MAX_JOBS) { set_error("b200_mul_mat_vec_q: n_jobs=%d out of range", n_jobs); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
-    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K)) {
+    if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1)) {
         set_error("b200_mul_mat_vec_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -530,6 +531,9 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
         case B200_TYPE_Q4_K: return dispatch_cols<B200_TYPE_Q4_K>(p, (int)N, st, pdl);
         case B200_TYPE_Q5_K: return dispatch_cols<B200_TYPE_Q5_K>(p, (int)N, st, pdl);
         case B200_TYPE_Q6_K: return dispatch_cols<B200_TYPE_Q6_K>(p, (int)N, st, pdl);
+        case B200_TYPE_Q4_1: return dispatch_cols<B200_TYPE_Q4_1>(p, (int)N, st, pdl);
+        case B200_TYPE_Q5_0: return dispatch_cols<B200_TYPE_Q5_0>(p, (int)N, st, pdl);
+        case B200_TYPE_Q5_1: return dispatch_cols<B200_TYPE_Q5_1>(p, (int)N, st, pdl);
     }
     return B200_ERR_UNSUPPORTED;
 }

@@ -526,6 +526,70 @@ struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
     }
 };
 
+// ---- Q4_1 / Q5_0 / Q5_1 (ggml-common.h:155-183): 32-value blocks, 4 blocks per lane.  One block against one q8_1 block
+// (u0 = its values 0..15, u1 = 16..31), the arithmetic of vec_dot_q4_1_q8_1 / q5_0_q8_1 / q5_1_q8_1 (vecdotq.cuh:44-149):
+//   Q4_1: d d8 sum(v u) + m s8      Q5_0: d (d8 sum(v5 u) - 16 s8)      Q5_1: d d8 sum(v5 u) + m s8
+// The fifth bit of value j is bit j of qh: four bits are spread to bit 4 of four bytes with one multiply.
+template <int TYPE>
+__device__ __forceinline__ float legacy_block_dot(const unsigned char *bk, const int4 u0, const int4 u1, float d8, float s8) {
+    constexpr bool HAS_M = TYPE != B200_TYPE_Q5_0, HAS_H = TYPE != B200_TYPE_Q4_1;
+    constexpr int NW = 4 + (HAS_M ? 1 : 0) + (HAS_H ? 1 : 0) + 1;  // d (+ m) (+ qh) + 16 bytes of nibbles, as 32-bit words
+    unsigned w[NW];
+    lds_words<NW>(bk, w);  // (reads up to 2 bytes past the block: the stage carries slack)
+    const float d = h2f((unsigned short)(w[0] & 0xffff));
+    // the block starts with d (2 bytes); everything behind it is 2 bytes off the word grid unless m fills the first word
+    unsigned q[4], qh = 0;
+    float m = 0.f;
+    if constexpr (HAS_M) {
+        m = h2f((unsigned short)(w[0] >> 16));
+        if constexpr (HAS_H) qh = w[1];
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[i] = w[(HAS_H ? 2 : 1) + i];
+    } else {  // Q5_0: d, then qh and qs straddle the words
+        qh = __funnelshift_r(w[0], w[1], 16);
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[i] = __funnelshift_r(w[1 + i], w[2 + i], 16);
+    }
+    const int ua[4] = {u0.x, u0.y, u0.z, u0.w}, ub[4] = {u1.x, u1.y, u1.z, u1.w};
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        unsigned lo = q[i] & 0x0f0f0f0fu, hi = (q[i] >> 4) & 0x0f0f0f0fu;
+        if constexpr (HAS_H) {
+            lo |= ((((qh >> (4 * i)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
+            hi |= ((((qh >> (16 + 4 * i)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
+        }
+        s = dp4a((int)lo, ua[i], s);
+        s = dp4a((int)hi, ub[i], s);
+    }
+    if constexpr (TYPE == B200_TYPE_Q5_0) return d * (d8 * (float)s - 16.0f * s8);
+    else return d * d8 * (float)s + m * s8;
+}
+template <int TYPE, int NCOLS>
+struct LegacySliceDot {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int nblk, float acc[NCOLS]) {
+        constexpr int BB = type_block_bytes(TYPE);
+        const unsigned char *b = seg + lane * (4 * BB);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) {
+#pragma unroll
+                for (int n = 0; n < NCOLS; n++) {
+                    const ActView a = act_view(act_base, n_it, n);
+                    const int4 u0 = a.q[((it * 8 + k * 2 + 0) * 32) + lane];
+                    const int4 u1 = a.q[((it * 8 + k * 2 + 1) * 32) + lane];
+                    const int o = ((it * 32 + lane) << 2) + k;
+                    acc[n] += legacy_block_dot<TYPE>(b + k * BB, u0, u1, reinterpret_cast<const float *>(a.d)[o], reinterpret_cast<const float *>(a.s)[o]);
+                }
+            }
+        }
+    }
+};
+template <int NCOLS> struct SliceDot<B200_TYPE_Q4_1, NCOLS> : LegacySliceDot<B200_TYPE_Q4_1, NCOLS> {};
+template <int NCOLS> struct SliceDot<B200_TYPE_Q5_0, NCOLS> : LegacySliceDot<B200_TYPE_Q5_0, NCOLS> {};
+template <int NCOLS> struct SliceDot<B200_TYPE_Q5_1, NCOLS> : LegacySliceDot<B200_TYPE_Q5_1, NCOLS> {};
+
 // ------------------------------------------------------------------------------------------------ row dots on preloaded activations
 // One column (decode), several weight rows per step: the lane's 128 activations of step `it` are loaded into registers ONCE
 // (LaneActs) and contracted with the same 128-weight slice of every row of the step.  Same arithmetic, in the same order, as
@@ -542,7 +606,7 @@ __device__ __forceinline__ void lane_acts_load(LaneActs &A, unsigned char *act_b
 #pragma unroll
     for (int j = 0; j < 8; j++) A.u[j] = a.q[((it * 8 + j) * 32) + lane];
     A.d8 = a.d[it * 32 + lane];
-    if constexpr (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K || TYPE == B200_TYPE_Q4_0) A.s8 = a.s[it * 32 + lane];
+    if constexpr (TYPE != B200_TYPE_Q6_K && TYPE != B200_TYPE_Q8_0) A.s8 = a.s[it * 32 + lane];
     if constexpr (TYPE == B200_TYPE_Q6_K) A.g = a.g[it * 32 + lane];
 }
 
@@ -739,5 +803,22 @@ struct RowDot<B200_TYPE_Q4_0> {
         }
     }
 };
+
+
+template <int TYPE>
+struct LegacyRowDot {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int nblk, float &acc) {
+        constexpr int BB = type_block_bytes(TYPE);
+        const unsigned char *b = seg + lane * (4 * BB);
+        const float d8v[4] = {A.d8.x, A.d8.y, A.d8.z, A.d8.w}, s8v[4] = {A.s8.x, A.s8.y, A.s8.z, A.s8.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            if (k < nblk) acc += legacy_block_dot<TYPE>(b + k * BB, A.u[k * 2 + 0], A.u[k * 2 + 1], d8v[k], s8v[k]);
+        }
+    }
+};
+template <> struct RowDot<B200_TYPE_Q4_1> : LegacyRowDot<B200_TYPE_Q4_1> {};
+template <> struct RowDot<B200_TYPE_Q5_0> : LegacyRowDot<B200_TYPE_Q5_0> {};
+template <> struct RowDot<B200_TYPE_Q5_1> : LegacyRowDot<B200_TYPE_Q5_1> {};
 
 }  // namespace b200

@@ -329,6 +329,19 @@ __device__ __forceinline__ float dq_value(int type, const unsigned char *row, in
             const unsigned char *b = row + (i / 32) * Q8_0_BYTES;
             return __fmul_rn((float)(signed char)b[2 + i % 32], h2f(*reinterpret_cast<const unsigned short *>(b)));
         }
+        case B200_TYPE_Q4_1:
+        case B200_TYPE_Q5_0:
+        case B200_TYPE_Q5_1: {  // dequantize_row_q4_1 / q5_0 / q5_1 (ggml-quants.c:1543-1615)
+            const bool has_m = type != B200_TYPE_Q5_0, has_h = type != B200_TYPE_Q4_1;
+            const int qs = 2 + (has_m ? 2 : 0) + (has_h ? 4 : 0);
+            const unsigned char *b = row + (i / 32) * type_block_bytes(type);
+            const int j = (int)(i % 32);
+            int q = j < 16 ? (b[qs + j] & 0x0F) : (b[qs + j - 16] >> 4);
+            if (has_h) q |= ((b[qs - 4 + (j >> 3)] >> (j & 7)) & 1) << 4;
+            const float d = h2f(*reinterpret_cast<const unsigned short *>(b));
+            if (!has_m) return __fmul_rn((float)(q - 16), d);
+            return __fadd_rn(__fmul_rn((float)q, d), h2f(*reinterpret_cast<const unsigned short *>(b + 2)));
+        }
         case B200_TYPE_Q4_K:
         case B200_TYPE_Q5_K: {
             const int bb = type == B200_TYPE_Q4_K ? Q4_K_BYTES : Q5_K_BYTES;
@@ -731,7 +744,8 @@ extern "C" int b200_op_get_rows(const b200_tensor *src, const b200_tensor *ids, 
     REQUIRE(src && ids && dst && src->data && ids->data && dst->data, B200_ERR_INVALID, "b200_op_get_rows: NULL argument");
     REQUIRE(ids->type == B200_TYPE_I32 && dst->type == B200_TYPE_F32 && dst->nb[0] == 4, B200_ERR_UNSUPPORTED, "b200_op_get_rows: i32 ids, f32 dst");
     const int t = src->type;
-    REQUIRE(t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K,
+    REQUIRE(t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K ||
+            t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1,
             B200_ERR_UNSUPPORTED, "b200_op_get_rows: source type %d not supported", t);
     REQUIRE(dst->ne[0] == src->ne[0] && dst->ne[1] == ids->ne[0], B200_ERR_INVALID, "b200_op_get_rows: shape mismatch");
     if (nelements(dst) == 0) return B200_OK;

@@ -63,6 +63,24 @@ __global__ void __launch_bounds__(256) dequantize_kernel(const unsigned char *__
             const int q = jj < 16 ? (b[2 + jj] & 0x0F) : (b[2 + jj - 16] >> 4);
             o[l] = __fmul_rn((float)(q - 8), d);
         }
+    } else if constexpr (TYPE == B200_TYPE_Q4_1 || TYPE == B200_TYPE_Q5_0 || TYPE == B200_TYPE_Q5_1) {
+        // dequantize_row_q4_1 / q5_0 / q5_1 (ggml-quants.c:1543-1615): x*d + m (a product, then a sum); the fifth bit of value
+        // j is bit j of qh
+        constexpr bool HAS_M = TYPE != B200_TYPE_Q5_0, HAS_H = TYPE != B200_TYPE_Q4_1;
+        constexpr int BB = type_block_bytes(TYPE), QS = 2 + (HAS_M ? 2 : 0) + (HAS_H ? 4 : 0);
+        const unsigned char *b = src + (i / QK) * BB;
+        const float d = ldh(b), m = HAS_M ? ldh(b + 2) : 0.f;
+        unsigned qh = 0;
+        if constexpr (HAS_H) qh = (unsigned)b[QS - 4] | ((unsigned)b[QS - 3] << 8) | ((unsigned)b[QS - 2] << 16) | ((unsigned)b[QS - 1] << 24);
+        const int j = (int)(i % QK);
+#pragma unroll
+        for (int l = 0; l < 4; l++) {
+            const int jj = j + l;
+            int q = jj < 16 ? (b[QS + jj] & 0x0F) : (b[QS + jj - 16] >> 4);
+            if constexpr (HAS_H) q |= (int)((qh >> jj) & 1u) << 4;
+            if constexpr (TYPE == B200_TYPE_Q5_0) o[l] = __fmul_rn((float)(q - 16), d);
+            else o[l] = __fadd_rn(__fmul_rn((float)q, d), m);
+        }
     } else if constexpr (TYPE == B200_TYPE_Q8_0) {
         const unsigned char *b = src + (i / QK) * Q8_0_BYTES;
         const float d = ldh(b);
@@ -119,6 +137,9 @@ static int launch_dequant(int type, const void *src, T *dst, int64_t n, cudaStre
     switch (type) {
         case B200_TYPE_Q4_0: dequantize_kernel<B200_TYPE_Q4_0, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q8_0: dequantize_kernel<B200_TYPE_Q8_0, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_Q4_1: dequantize_kernel<B200_TYPE_Q4_1, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_Q5_0: dequantize_kernel<B200_TYPE_Q5_0, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_Q5_1: dequantize_kernel<B200_TYPE_Q5_1, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q4_K: dequantize_kernel<B200_TYPE_Q4_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q5_K: dequantize_kernel<B200_TYPE_Q5_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q6_K: dequantize_kernel<B200_TYPE_Q6_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;

@@ -10,7 +10,7 @@ from dataclasses import dataclass, field
 
 import numpy as np
 
-from .lib import BLOCK, F16, F32, Q4_0, Q4_K, Q5_K, Q6_K, Q8_0, B200Error, check, lib, row_size
+from .lib import BLOCK, F16, F32, Q4_0, Q4_1, Q4_K, Q5_0, Q5_1, Q5_K, Q6_K, Q8_0, B200Error, check, lib, row_size
 
 
 class LlamaParams(C.Structure):
@@ -189,6 +189,12 @@ def random_blocks(rng: np.random.Generator, ty: int, n_rows: int, ne0: int) -> n
         raw[:, :, 0:2] = f16(3e-3, 5.5e-3, (n_rows, nb))
     elif ty == Q8_0:
         raw[:, :, 0:2] = f16(2e-4, 3.4e-4, (n_rows, nb))
+    elif ty in (Q4_1, Q5_1):  # x d + m with x in [0, 15] / [0, 31]: m = -(mid x) d centres the values
+        d = rng.uniform(3e-3, 5.5e-3, size=(n_rows, nb)) / (1 if ty == Q4_1 else 2)
+        raw[:, :, 0:2] = d.astype(np.float16).view(np.uint8).reshape(n_rows, nb, 2)
+        raw[:, :, 2:4] = (-d * (7.5 if ty == Q4_1 else 15.5)).astype(np.float16).view(np.uint8).reshape(n_rows, nb, 2)
+    elif ty == Q5_0:
+        raw[:, :, 0:2] = f16(1.5e-3, 2.7e-3, (n_rows, nb))
     elif ty == Q4_K:
         d = rng.uniform(1.1e-4, 1.9e-4, size=(n_rows, nb))
         raw[:, :, 0:2] = d.astype(np.float16).view(np.uint8).reshape(n_rows, nb, 2)

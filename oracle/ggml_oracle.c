@@ -85,6 +85,9 @@ uint16_t orc_fp32_to_fp16(float f) {
 enum {
     Q4_0_BYTES = 18,  /* half d; u8 qs[16]                                  :144-149 */
     Q8_0_BYTES = 34,  /* half d; i8 qs[32]                                  :186-191 */
+    Q4_1_BYTES = 20,  /* half d; half m; u8 qs[16]                          :155-161 */
+    Q5_0_BYTES = 22,  /* half d; u8 qh[4]; u8 qs[16]                        :164-169 */
+    Q5_1_BYTES = 24,  /* half d; half m; u8 qh[4]; u8 qs[16]                :172-183 */
     Q8_1_BYTES = 36,  /* half d; half s; i8 qs[32]                          :194-204 */
     Q4_K_BYTES = 144, /* half d; half dmin; u8 scales[12]; u8 qs[128]       :286-298 */
     Q5_K_BYTES = 176, /* half d; half dmin; u8 scales[12]; u8 qh[32]; u8 qs[128] :303-316 */
@@ -96,6 +99,7 @@ int orc_blck_size(int type) {
     switch (type) {
         case ORC_TYPE_F32: case ORC_TYPE_F16: return 1;
         case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: case ORC_TYPE_Q8_1: return QK;
+        case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_0: case ORC_TYPE_Q5_1: return QK;
         case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: case ORC_TYPE_Q8_K: return QK_K;
     }
     return 0;
@@ -106,6 +110,9 @@ size_t orc_type_size(int type) {
         case ORC_TYPE_F32:  return 4;
         case ORC_TYPE_F16:  return 2;
         case ORC_TYPE_Q4_0: return Q4_0_BYTES;
+        case ORC_TYPE_Q4_1: return Q4_1_BYTES;
+        case ORC_TYPE_Q5_0: return Q5_0_BYTES;
+        case ORC_TYPE_Q5_1: return Q5_1_BYTES;
         case ORC_TYPE_Q8_0: return Q8_0_BYTES;
         case ORC_TYPE_Q8_1: return Q8_1_BYTES;
         case ORC_TYPE_Q4_K: return Q4_K_BYTES;
@@ -152,6 +159,25 @@ static void expand_q4_0(const uint8_t *b, int8_t *q) {
     }
 }
 static void expand_q8_0(const uint8_t *b, int8_t *q) { memcpy(q, b + 2, 32); }
+/* Q4_1: q[32] in [0,15] (values 0..15 = low nibbles, 16..31 = high nibbles), ggml-quants.c:1543-1562 */
+static void expand_q4_1(const uint8_t *b, int8_t *q) {
+    const uint8_t *qs = b + 4;
+    for (int j = 0; j < 16; j++) {
+        q[j]      = (int8_t)(qs[j] & 0x0F);
+        q[j + 16] = (int8_t)(qs[j] >> 4);
+    }
+}
+/* Q5_0 / Q5_1: the fifth bit of value j is bit j of qh (ggml-quants.c:1564-1588, 1590-1615); off = 16 (Q5_0) or 0 (Q5_1) */
+static void expand_q5(const uint8_t *qh4, const uint8_t *qs, int off, int8_t *q) {
+    uint32_t qh;
+    memcpy(&qh, qh4, 4);
+    for (int j = 0; j < 16; j++) {
+        const int xh_0 = (int)(((qh >> (j + 0)) << 4) & 0x10);
+        const int xh_1 = (int)((qh >> (j + 12)) & 0x10);
+        q[j]      = (int8_t)(((qs[j] & 0x0F) | xh_0) - off);
+        q[j + 16] = (int8_t)(((qs[j] >> 4) | xh_1) - off);
+    }
+}
 
 static void expand_q4_K(const uint8_t *b, int8_t *q, int *sc, int *mn) {
     const uint8_t *scales = b + 4, *qs = b + 16;
@@ -204,6 +230,26 @@ int orc_dequantize_row(int type, const void *src, float *dst, int64_t k) {
             for (int64_t i = 0; i < k / QK; i++, b += Q4_0_BYTES, dst += QK) {
                 const float d = rdh(b);
                 expand_q4_0(b, q);
+                for (int j = 0; j < QK; j++) dst[j] = (float)q[j] * d;
+            }
+            return 0;
+        case ORC_TYPE_Q4_1: /* :1543-1562: y = x0*d + m (a product, then a sum) */
+        case ORC_TYPE_Q5_1: /* :1590-1615 */
+            if (k % QK) return -1;
+            for (int64_t i = 0; i < k / QK; i++, b += orc_type_size(type), dst += QK) {
+                const float d = rdh(b), m = rdh(b + 2);
+                if (type == ORC_TYPE_Q4_1) expand_q4_1(b, q); else expand_q5(b + 4, b + 8, 0, q);
+                for (int j = 0; j < QK; j++) {
+                    const float prod = (float)q[j] * d;
+                    dst[j] = prod + m;
+                }
+            }
+            return 0;
+        case ORC_TYPE_Q5_0: /* :1564-1588: y = x0*d */
+            if (k % QK) return -1;
+            for (int64_t i = 0; i < k / QK; i++, b += Q5_0_BYTES, dst += QK) {
+                const float d = rdh(b);
+                expand_q5(b + 2, b + 6, 16, q);
                 for (int j = 0; j < QK; j++) dst[j] = (float)q[j] * d;
             }
             return 0;
@@ -349,7 +395,8 @@ int orc_quantize_row(int type, const float *x, void *dst, int64_t k) {
 /* ------------------------------------------------------------------ dot products (CPU semantics) */
 static int vec_dot_act_type(int wtype) {
     switch (wtype) {
-        case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: return ORC_TYPE_Q8_0; /* ggml.c:793-808, 873-889 */
+        case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: case ORC_TYPE_Q5_0: return ORC_TYPE_Q8_0; /* ggml.c:793-808, 873-889 */
+        case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_1: return ORC_TYPE_Q8_1; /* vec_dot_type of q4_1 / q5_1, ggml.c type_traits */
         case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: return ORC_TYPE_Q8_K; /* :924-959 */
     }
     return -1;
@@ -374,6 +421,31 @@ float orc_vec_dot(int wtype, int64_t n, const void *wv, const void *av) {
                 /* :5855: sumf += sumi*(d_x*d_y) */
                 sumf += (float)sumi * (rdh(w) * rdh(a));
             }
+        }
+        return sumf;
+    }
+    if (wtype == ORC_TYPE_Q5_0) { /* ggml_vec_dot_q5_0_q8_0 scalar tail, ggml-quants.c:5120-5143 */
+        float sumf = 0;
+        for (int64_t i = 0; i < n / QK; i++, w += Q5_0_BYTES, a += Q8_0_BYTES) {
+            expand_q5(w + 2, w + 6, 16, q);
+            const int8_t *y = (const int8_t *)(a + 2);
+            int sumi = 0;
+            for (int j = 0; j < QK; j++) sumi += q[j] * y[j];
+            sumf += (rdh(w) * rdh(a)) * (float)sumi;
+        }
+        return sumf;
+    }
+    if (wtype == ORC_TYPE_Q4_1 || wtype == ORC_TYPE_Q5_1) { /* ggml_vec_dot_q4_1_q8_1 :4771-4785, q5_1_q8_1 scalar tail */
+        const size_t wb = orc_type_size(wtype);
+        float sumf = 0;
+        for (int64_t i = 0; i < n / QK; i++, w += wb, a += Q8_1_BYTES) {
+            if (wtype == ORC_TYPE_Q4_1) expand_q4_1(w, q); else expand_q5(w + 4, w + 8, 0, q);
+            const int8_t *y = (const int8_t *)(a + 4);
+            int sumi = 0;
+            for (int j = 0; j < QK; j++) sumi += q[j] * y[j];
+            const float t1 = (rdh(w) * rdh(a)) * (float)sumi;
+            const float t2 = rdh(w + 2) * rdh(a + 2);
+            sumf += t1 + t2;
         }
         return sumf;
     }
@@ -438,6 +510,22 @@ double orc_vec_dot_q8_1(int wtype, int64_t n, const void *wv, const void *av) {
                 for (int j = 0; j < QK; j++) sumi += q[j] * y[j];
                 acc += dw * d8 * sumi;
             }
+        }
+        return acc;
+    }
+    if (wtype == ORC_TYPE_Q4_1 || wtype == ORC_TYPE_Q5_0 || wtype == ORC_TYPE_Q5_1) {
+        /* Q4_1 / Q5_1: d*d8*sum(v*u) + m*s8 (vecdotq.cuh:44-76, 110-149); Q5_0: d*(d8*sum(v5*u) - 16*s8) (:78-108) */
+        const size_t wb = orc_type_size(wtype);
+        for (int64_t i = 0; i < n / QK; i++, w += wb, a += Q8_1_BYTES) {
+            const int8_t *y = (const int8_t *)(a + 4);
+            const double d8 = rdh(a), s8 = rdh(a + 2), dw = rdh(w);
+            if (wtype == ORC_TYPE_Q4_1) expand_q4_1(w, q);
+            else if (wtype == ORC_TYPE_Q5_1) expand_q5(w + 4, w + 8, 0, q);
+            else expand_q5(w + 2, w + 6, 0, q);
+            int sumi = 0;
+            for (int j = 0; j < QK; j++) sumi += q[j] * y[j];
+            if (wtype == ORC_TYPE_Q5_0) acc += dw * (d8 * sumi - 16.0 * s8);
+            else acc += dw * d8 * sumi + (double)rdh(w + 2) * s8;
         }
         return acc;
     }

@@ -20,11 +20,17 @@ REF_DIR = ROOT / "oracle" / "_ref"
 
 # ggml/include/ggml.h:361-398
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K, I32 = 0, 1, 2, 8, 9, 12, 13, 14, 15, 26
-TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", Q8_K: "q8_K"}
+Q4_1, Q5_0, Q5_1 = 3, 6, 7
+TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q8_1: "q8_1", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", Q8_K: "q8_K"}
 # (values per block, bytes per block)  ggml/src/ggml-common.h:144-335
-BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q8_0: (32, 34), Q8_1: (32, 36), Q4_K: (256, 144), Q5_K: (256, 176),
+BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), Q8_1: (32, 36), Q4_K: (256, 144), Q5_K: (256, 176),
          Q6_K: (256, 210), Q8_K: (256, 292), I32: (1, 4)}
-WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K)
+WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1)
+
+
+def act_type(t: int) -> int:
+    """vec_dot_type of a weight type on the CPU backend (ggml.c type_traits)."""
+    return Q8_0 if t in (Q4_0, Q8_0, Q5_0) else Q8_1 if t in (Q4_1, Q5_1) else Q8_K
 
 
 def row_size(t: int, ne: int) -> int:
@@ -147,7 +153,7 @@ class Ref:
         return out
 
     def vec_dot(self, wt: int, w: np.ndarray, act: np.ndarray, n: int) -> float:
-        at = "q8_0" if wt in (Q4_0, Q8_0) else "q8_K"
+        at = TYPE_NAMES[act_type(wt)]
         s = C.c_float(0)
         getattr(self.lib, f"ggml_vec_dot_{TYPE_NAMES[wt]}_{at}")(n, C.byref(s), 0, w.ctypes.data, 0, act.ctypes.data, 0, 1)
         return s.value

@@ -59,7 +59,7 @@ def main():
         w = ref.quantize(t, (rng.standard_normal((M, Km)) * 0.05).astype(np.float32))
         g[f"mm_{n}_w"] = w
         g[f"mm_{n}_out"] = ref.mul_mat(t, w, xs, Km, M)
-        at = R.Q8_0 if t in (R.Q4_0, R.Q8_0) else R.Q8_K
+        at = R.act_type(t)
         a = ref.quantize_act_ref(at, xs[0])
         g[f"vd_{n}"] = np.array([ref.vec_dot(t, w[i], a, Km) for i in range(M)], dtype=np.float32)
     # --- (a9) MUL_MAT_ID

@@ -60,8 +60,10 @@ def random_blocks(t, M, K, rng):
         raw[:, :, off] = v & 0xff
         raw[:, :, off + 1] = v >> 8
 
-    if t in (R.Q4_0, R.Q8_0):
+    if t in (R.Q4_0, R.Q8_0, R.Q5_0):
         put_half(0, -0.02, 0.02)
+    elif t in (R.Q4_1, R.Q5_1):
+        put_half(0, -0.02, 0.02); put_half(2, -0.1, 0.1)
     elif t in (R.Q4_K, R.Q5_K):
         put_half(0, 0.0005, 0.002); put_half(2, 0.0005, 0.002)
     elif t == R.Q6_K:
@@ -148,7 +150,7 @@ def test_gemv_shapes(H, t, shape):
     check_gemv(H, t, K, M, N, np.random.default_rng(K + M + N + t))
 
 
-@pytest.mark.parametrize("t", (R.Q4_0, R.Q8_0), ids=["q4_0", "q8_0"])
+@pytest.mark.parametrize("t", (R.Q4_0, R.Q8_0, R.Q4_1, R.Q5_0, R.Q5_1), ids=["q4_0", "q8_0", "q4_1", "q5_0", "q5_1"])
 @pytest.mark.parametrize("K", (32, 96, 4096 + 64))
 def test_gemv_ragged_k(H, t, K):
     """Q4_0/Q8_0 rows whose length is not a multiple of the 128-weight slice; odd row byte sizes (2-byte aligned rows)."""

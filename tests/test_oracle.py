@@ -43,7 +43,7 @@ def test_vec_dot_and_mul_mat_golden(golden, t):
     K, M = x.shape[1], w.shape[0]
     out = O.mul_mat(t, w, x, K, M, nthreads=2)
     assert np.array_equal(bits(out), bits(golden[f"mm_{NAME[t]}_out"]))  # scalar reference: same summation order
-    at = R.Q8_0 if t in (R.Q4_0, R.Q8_0) else R.Q8_K
+    at = R.act_type(t)
     a = O.quantize(at, x[0])
     vd = np.array([O.vec_dot(t, w[i], a, K) for i in range(M)], dtype=np.float32)
     assert np.array_equal(bits(vd), bits(golden[f"vd_{NAME[t]}"]))
