@@ -67,7 +67,7 @@ class ModelShape:
     n_head_kv: int
     n_ff: int
     n_vocab: int
-    ftype: str = "Q4_K_M"  # Q4_0 | Q4_K_M | Q5_K_M
+    ftype: str = "Q4_K_M"  # Q4_0 | Q4_1 | Q5_0 | Q5_1 | Q4_K_M | Q5_K_M
     n_expert: int = 0
     n_expert_used: int = 0
     rope_freq_base: float = 10000.0
@@ -99,7 +99,7 @@ def use_more_bits(i: int, n: int) -> bool:
 def tensor_types(s: ModelShape) -> dict[str, int]:
     """GGUF tensor name -> ggml type, the mix llama_tensor_get_type produces (src/llama.cpp:17979-18200)."""
     t: dict[str, int] = {}
-    base = {"Q4_0": Q4_0, "Q4_K_M": Q4_K, "Q5_K_M": Q5_K}[s.ftype]
+    base = {"Q4_0": Q4_0, "Q4_1": Q4_1, "Q5_0": Q5_0, "Q5_1": Q5_1, "Q4_K_M": Q4_K, "Q5_K_M": Q5_K}[s.ftype]
     kquant_m = s.ftype in ("Q4_K_M", "Q5_K_M")
     t["token_embd.weight"] = base
     t["output_norm.weight"] = F32
