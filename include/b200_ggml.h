@@ -52,6 +52,8 @@ enum b200_type {
     B200_TYPE_Q5_1 = 7,
     B200_TYPE_Q8_0 = 8,
     B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q2_K = 10,
+    B200_TYPE_Q3_K = 11,
     B200_TYPE_Q4_K = 12,
     B200_TYPE_Q5_K = 13,
     B200_TYPE_Q6_K = 14,

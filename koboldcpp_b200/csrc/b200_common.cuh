@@ -25,6 +25,8 @@ constexpr int Q5_0_BYTES = 22;  // half d, u8 qh[4], u8 qs[16]         (:164-169
 constexpr int Q5_1_BYTES = 24;  // half d, half m, u8 qh[4], u8 qs[16] (:172-183)
 constexpr int Q8_0_BYTES = 34;
 constexpr int Q8_1_BYTES = 36;
+constexpr int Q2_K_BYTES = 84;   // u8 scales[16], u8 qs[64], half d, half dmin   (ggml-common.h:257-268)
+constexpr int Q3_K_BYTES = 110;  // u8 hmask[32], u8 qs[64], u8 scales[12], half d (:274-280)
 constexpr int Q4_K_BYTES = 144;
 constexpr int Q5_K_BYTES = 176;
 constexpr int Q6_K_BYTES = 210;
@@ -32,12 +34,13 @@ constexpr int Q6_K_BYTES = 210;
 __host__ __device__ constexpr int type_block_values(int t) {
     return (t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_I32) ? 1
          : (t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q8_1 || t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1) ? 32
-         : (t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K) ? 256 : 0;
+         : (t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K || t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K) ? 256 : 0;
 }
 __host__ __device__ constexpr int type_block_bytes(int t) {
     return t == B200_TYPE_F32 ? 4 : t == B200_TYPE_F16 ? 2 : t == B200_TYPE_I32 ? 4
          : t == B200_TYPE_Q4_0 ? Q4_0_BYTES : t == B200_TYPE_Q8_0 ? Q8_0_BYTES : t == B200_TYPE_Q8_1 ? Q8_1_BYTES
          : t == B200_TYPE_Q4_1 ? Q4_1_BYTES : t == B200_TYPE_Q5_0 ? Q5_0_BYTES : t == B200_TYPE_Q5_1 ? Q5_1_BYTES
+         : t == B200_TYPE_Q2_K ? Q2_K_BYTES : t == B200_TYPE_Q3_K ? Q3_K_BYTES
          : t == B200_TYPE_Q4_K ? Q4_K_BYTES : t == B200_TYPE_Q5_K ? Q5_K_BYTES : t == B200_TYPE_Q6_K ? Q6_K_BYTES : 0;
 }
 // bytes of 128 consecutive weights (one "slice": the unit one lane processes per step)
@@ -174,6 +177,17 @@ __device__ __forceinline__ void k4_scale_min(const unsigned sw[3], int j, int &s
         sc = (s[j + 4] & 0x0F) | ((s[j - 4] >> 6) << 4);
         mn = (s[j + 4] >> 4) | ((s[j] >> 6) << 4);
     }
+}
+
+// ---------------------------------------------------------------- 6-bit scale unpack of q3_K
+// The aux[] shuffle of dequantize_row_q3_K (ggml-quants.c:2345-2350): 12 scale bytes given as 3 words -> 16 scales, one per
+// byte of aux[0..3], each still carrying the +32 offset of the stored form.
+__device__ __forceinline__ void q3k_scales(const unsigned s0, const unsigned s1, const unsigned s2, unsigned (&aux)[4]) {
+    const unsigned kmask1 = 0x03030303u, kmask2 = 0x0f0f0f0fu;
+    aux[0] = (s0 & kmask2) | (((s2 >> 0) & kmask1) << 4);
+    aux[1] = (s1 & kmask2) | (((s2 >> 2) & kmask1) << 4);
+    aux[2] = ((s0 >> 4) & kmask2) | (((s2 >> 4) & kmask1) << 4);
+    aux[3] = ((s1 >> 4) & kmask2) | (((s2 >> 6) & kmask1) << 4);
 }
 
 // last error text (host side, per thread)

@@ -240,6 +240,61 @@ struct DequantK45 {  // Q4_K / Q5_K: half d, half dmin, u8 scales[12], (u8 qh[32
 template <bool G> struct Dequant64<B200_TYPE_Q4_K, G> : DequantK45<B200_TYPE_Q4_K, G> {};
 template <bool G> struct Dequant64<B200_TYPE_Q5_K, G> : DequantK45<B200_TYPE_Q5_K, G> {};
 
+// Q2_K / Q3_K (dequantize_row_q2_K / q3_K, ggml-quants.c:1980-2010, 2328-2373).  Chunk c (64 values) of a super-block is half
+// n = c >> 1, bit fields jb = 2 (c & 1) and jb + 1 of the half's 32 quant bytes; value vv of the chunk: field jb + vv / 32, byte
+// vv % 32, scale 8 n + 2 (jb + vv / 32) + (vv % 32) / 16.  W(i) must yield byte i of the block.
+template <int TYPE, typename ByteFn>
+__device__ __forceinline__ void dequant64_k23(ByteFn W, int c, unsigned (&o)[32]) {
+    constexpr bool Q2 = TYPE == B200_TYPE_Q2_K;
+    const int n = c >> 1, jb = 2 * (c & 1);
+    unsigned aux[4] = {0, 0, 0, 0};
+    float d, dmin = 0.f;
+    if constexpr (Q2) {
+        d = __half2float(__ushort_as_half((unsigned short)(W(80) | (W(81) << 8))));
+        dmin = __half2float(__ushort_as_half((unsigned short)(W(82) | (W(83) << 8))));
+    } else {
+        d = __half2float(__ushort_as_half((unsigned short)(W(108) | (W(109) << 8))));
+        unsigned sw[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) sw[k] = W(96 + 4 * k) | (W(97 + 4 * k) << 8) | (W(98 + 4 * k) << 16) | (W(99 + 4 * k) << 24);
+        q3k_scales(sw[0], sw[1], sw[2], aux);
+    }
+#pragma unroll
+    for (int gq = 0; gq < 4; gq++) {  // 16-value groups of the chunk
+        const int jj = jb + (gq >> 1), is = 8 * n + 2 * jj + (gq & 1);
+        float dl, ml = 0.f;
+        if constexpr (Q2) {
+            const unsigned sc = W(is);
+            dl = d * (float)(sc & 0xF);
+            ml = dmin * (float)(sc >> 4);
+        } else {
+            dl = d * (float)((int)((aux[is >> 2] >> (8 * (is & 3))) & 0xff) - 32);
+        }
+#pragma unroll
+        for (int e = 0; e < 16; e += 2) {
+            const int l = 16 * (gq & 1) + e;
+            const unsigned b0 = W((Q2 ? 16 : 32) + 32 * n + l), b1 = W((Q2 ? 16 : 32) + 32 * n + l + 1);
+            float x0 = (float)((b0 >> (2 * jj)) & 3), x1 = (float)((b1 >> (2 * jj)) & 3);
+            if constexpr (!Q2) {
+                x0 -= ((W(l) >> (4 * n + jj)) & 1) ? 0.f : 4.f;
+                x1 -= ((W(l + 1) >> (4 * n + jj)) & 1) ? 0.f : 4.f;
+            }
+            o[8 * gq + e / 2] = pack_bf16(dl * x0 - ml, dl * x1 - ml);
+        }
+    }
+}
+template <int TYPE, bool G>
+struct Dequant64K23 {
+    static __device__ __forceinline__ void run(const unsigned char *blk, int c, unsigned (&o)[32]) {
+        constexpr int NWB = (type_block_bytes(TYPE) + 3) / 4;
+        unsigned w[NWB];
+        ld_words<G, NWB>(blk, w);
+        dequant64_k23<TYPE>([&](int i) { return BYTE_OF(w, i); }, c, o);
+    }
+};
+template <bool G> struct Dequant64<B200_TYPE_Q2_K, G> : Dequant64K23<B200_TYPE_Q2_K, G> {};
+template <bool G> struct Dequant64<B200_TYPE_Q3_K, G> : Dequant64K23<B200_TYPE_Q3_K, G> {};
+
 template <bool G>
 struct Dequant64<B200_TYPE_Q6_K, G> {  // u8 ql[128], u8 qh[64], i8 scales[16], half d   (2-byte aligned blocks)
     static __device__ __forceinline__ void run(const unsigned char *blk, int c, unsigned (&o)[32]) {
@@ -503,6 +558,15 @@ struct DequantRK45 {
 };
 template <int C> struct DequantR<B200_TYPE_Q4_K, C> : DequantRK45<B200_TYPE_Q4_K, C> {};
 template <int C> struct DequantR<B200_TYPE_Q5_K, C> : DequantRK45<B200_TYPE_Q5_K, C> {};
+
+template <int TYPE, int C>
+struct DequantRK23 {
+    static __device__ __forceinline__ void run(const unsigned (&w)[group256_words(TYPE)], unsigned (&o)[32]) {
+        dequant64_k23<TYPE>([&](int i) { return BYTE_OF(w, i); }, C, o);
+    }
+};
+template <int C> struct DequantR<B200_TYPE_Q2_K, C> : DequantRK23<B200_TYPE_Q2_K, C> {};
+template <int C> struct DequantR<B200_TYPE_Q3_K, C> : DequantRK23<B200_TYPE_Q3_K, C> {};
 
 template <int C>
 struct DequantR<B200_TYPE_Q6_K, C> {
@@ -896,7 +960,7 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
     if (!W || !X || !dst) { set_error("b200_mul_mat_q: NULL argument"); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
-          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1)) {
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K)) {
         set_error("b200_mul_mat_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -934,6 +998,8 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
         case B200_TYPE_Q4_1: return mmq_dispatch_bn<B200_TYPE_Q4_1>(p, st);
         case B200_TYPE_Q5_0: return mmq_dispatch_bn<B200_TYPE_Q5_0>(p, st);
         case B200_TYPE_Q5_1: return mmq_dispatch_bn<B200_TYPE_Q5_1>(p, st);
+        case B200_TYPE_Q2_K: return mmq_dispatch_bn<B200_TYPE_Q2_K>(p, st);
+        case B200_TYPE_Q3_K: return mmq_dispatch_bn<B200_TYPE_Q3_K>(p, st);
     }
     return B200_ERR_UNSUPPORTED;
 }
@@ -951,7 +1017,7 @@ extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, s
                                  size_t workspace_bytes, b200_stream_t stream) {
     if (!as || !ids || !b || !dst) { set_error("b200_mul_mat_id_q: NULL argument"); return B200_ERR_INVALID; }
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
-          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1)) {
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K)) {
         set_error("b200_mul_mat_id_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -1001,6 +1067,8 @@ extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, s
         case B200_TYPE_Q4_1: return mid_dispatch_bn<B200_TYPE_Q4_1>(p, bn, n_rows, (unsigned)max_tiles, st);
         case B200_TYPE_Q5_0: return mid_dispatch_bn<B200_TYPE_Q5_0>(p, bn, n_rows, (unsigned)max_tiles, st);
         case B200_TYPE_Q5_1: return mid_dispatch_bn<B200_TYPE_Q5_1>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q2_K: return mid_dispatch_bn<B200_TYPE_Q2_K>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_Q3_K: return mid_dispatch_bn<B200_TYPE_Q3_K>(p, bn, n_rows, (unsigned)max_tiles, st);
     }
     return B200_ERR_UNSUPPORTED;
 }

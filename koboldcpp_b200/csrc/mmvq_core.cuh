@@ -590,6 +590,89 @@ template <int NCOLS> struct SliceDot<B200_TYPE_Q4_1, NCOLS> : LegacySliceDot<B20
 template <int NCOLS> struct SliceDot<B200_TYPE_Q5_0, NCOLS> : LegacySliceDot<B200_TYPE_Q5_0, NCOLS> {};
 template <int NCOLS> struct SliceDot<B200_TYPE_Q5_1, NCOLS> : LegacySliceDot<B200_TYPE_Q5_1, NCOLS> {};
 
+// ---- Q2_K / Q3_K (ggml-common.h:257-280): half a super-block (128 values) per lane.  Value v of the half sits in byte v % 32 of the
+// half's 32 quant bytes at bits 2 (v / 32); its scale is number v / 16 of the half's eight.  The 2-bit fields (and the q3_K high
+// bits out of hmask) are contracted IN PLACE with dp4a -- a field at bit position s only scales the sum by 2^s, removed by an exact
+// shift afterwards -- against the q8_1 activations; per 16-wide group (vec_dot_q2_K_q8_1 / q3_K_q8_1, vecdotq.cuh:230-355):
+//   Q2_K: d sc d8 sum(v u) - dmin m d8 sum(u)          Q3_K: d (sc - 32) d8 (sum(v2 u) + 4 sum(h u) - 4 sum(u))
+template <int TYPE>
+__device__ __forceinline__ float k23_half_dot(const unsigned char *b, int n, const int4 (&u)[8], const float4 d8, const int4 g) {
+    constexpr bool Q2 = TYPE == B200_TYPE_Q2_K;
+    const float d8v[4] = {d8.x, d8.y, d8.z, d8.w};
+    const int gv[4] = {g.x, g.y, g.z, g.w};
+    unsigned qw[8];
+    lds_words<8>(b + (Q2 ? 16 : 32) + 32 * n, qw);
+    if constexpr (Q2) {
+        unsigned scw[2], dm[1];
+        lds_words<2>(b + 8 * n, scw);
+        lds_words<1>(b + 80, dm);
+        const float d = h2f((unsigned short)(dm[0] & 0xffff)), dmin = h2f((unsigned short)(dm[0] >> 16));
+        float sd = 0.f, sm = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const unsigned mq = 0x03030303u << (2 * j);
+            const int ua[4] = {u[2 * j].x, u[2 * j].y, u[2 * j].z, u[2 * j].w}, ub[4] = {u[2 * j + 1].x, u[2 * j + 1].y, u[2 * j + 1].z, u[2 * j + 1].w};
+            int d0 = 0, d1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                d0 = dp4a_u(qw[i] & mq, ua[i], d0);
+                d1 = dp4a_u(qw[4 + i] & mq, ub[i], d1);
+            }
+            d0 >>= 2 * j;
+            d1 >>= 2 * j;
+            const unsigned s0 = (scw[j >> 1] >> (16 * (j & 1))) & 0xff, s1 = (scw[j >> 1] >> (16 * (j & 1) + 8)) & 0xff;
+            const int g0 = (int)(short)(gv[j] & 0xffff), g1 = gv[j] >> 16;
+            sd += d8v[j] * (float)((int)(s0 & 0xF) * d0 + (int)(s1 & 0xF) * d1);
+            sm += d8v[j] * (float)((int)(s0 >> 4) * g0 + (int)(s1 >> 4) * g1);
+        }
+        return d * sd - dmin * sm;
+    } else {
+        unsigned hm[8], tail[4], aux[4];
+        lds_words<8>(b, hm);
+        lds_words<4>(b + 96, tail);  // 12 scale bytes, then d
+        q3k_scales(tail[0], tail[1], tail[2], aux);
+        const float d = h2f((unsigned short)(tail[3] & 0xffff));
+        float sd = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const unsigned mq = 0x03030303u << (2 * j), mh = 0x01010101u << (4 * n + j);
+            const int ua[4] = {u[2 * j].x, u[2 * j].y, u[2 * j].z, u[2 * j].w}, ub[4] = {u[2 * j + 1].x, u[2 * j + 1].y, u[2 * j + 1].z, u[2 * j + 1].w};
+            int q0 = 0, q1 = 0, h0 = 0, h1 = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                q0 = dp4a_u(qw[i] & mq, ua[i], q0);
+                h0 = dp4a_u(hm[i] & mh, ua[i], h0);
+                q1 = dp4a_u(qw[4 + i] & mq, ub[i], q1);
+                h1 = dp4a_u(hm[4 + i] & mh, ub[i], h1);
+            }
+            const int g0 = (int)(short)(gv[j] & 0xffff), g1 = gv[j] >> 16;
+            const int v0 = (q0 >> (2 * j)) + 4 * (h0 >> (4 * n + j)) - 4 * g0;
+            const int v1 = (q1 >> (2 * j)) + 4 * (h1 >> (4 * n + j)) - 4 * g1;
+            const unsigned aw = n ? (j < 2 ? aux[2] : aux[3]) : (j < 2 ? aux[0] : aux[1]);
+            const int s0 = (int)((aw >> (16 * (j & 1))) & 0xff) - 32, s1 = (int)((aw >> (16 * (j & 1) + 8)) & 0xff) - 32;
+            sd += d8v[j] * (float)(s0 * v0 + s1 * v1);
+        }
+        return d * sd;
+    }
+}
+template <int TYPE, int NCOLS>
+struct K23SliceDot {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, int it, unsigned char *act_base, int n_it,
+                                               int /*nblk*/, float acc[NCOLS]) {
+        const unsigned char *b = seg + (lane >> 1) * type_block_bytes(TYPE);
+#pragma unroll
+        for (int n = 0; n < NCOLS; n++) {
+            const ActView a = act_view(act_base, n_it, n);
+            int4 u[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) u[j] = a.q[((it * 8 + j) * 32) + lane];
+            acc[n] += k23_half_dot<TYPE>(b, lane & 1, u, a.d[it * 32 + lane], a.g[it * 32 + lane]);
+        }
+    }
+};
+template <int NCOLS> struct SliceDot<B200_TYPE_Q2_K, NCOLS> : K23SliceDot<B200_TYPE_Q2_K, NCOLS> {};
+template <int NCOLS> struct SliceDot<B200_TYPE_Q3_K, NCOLS> : K23SliceDot<B200_TYPE_Q3_K, NCOLS> {};
+
 // ------------------------------------------------------------------------------------------------ row dots on preloaded activations
 // One column (decode), several weight rows per step: the lane's 128 activations of step `it` are loaded into registers ONCE
 // (LaneActs) and contracted with the same 128-weight slice of every row of the step.  Same arithmetic, in the same order, as
@@ -607,7 +690,7 @@ __device__ __forceinline__ void lane_acts_load(LaneActs &A, unsigned char *act_b
     for (int j = 0; j < 8; j++) A.u[j] = a.q[((it * 8 + j) * 32) + lane];
     A.d8 = a.d[it * 32 + lane];
     if constexpr (TYPE != B200_TYPE_Q6_K && TYPE != B200_TYPE_Q8_0) A.s8 = a.s[it * 32 + lane];
-    if constexpr (TYPE == B200_TYPE_Q6_K) A.g = a.g[it * 32 + lane];
+    if constexpr (TYPE == B200_TYPE_Q6_K || TYPE == B200_TYPE_Q2_K || TYPE == B200_TYPE_Q3_K) A.g = a.g[it * 32 + lane];
 }
 
 template <int TYPE>
@@ -820,5 +903,15 @@ struct LegacyRowDot {
 template <> struct RowDot<B200_TYPE_Q4_1> : LegacyRowDot<B200_TYPE_Q4_1> {};
 template <> struct RowDot<B200_TYPE_Q5_0> : LegacyRowDot<B200_TYPE_Q5_0> {};
 template <> struct RowDot<B200_TYPE_Q5_1> : LegacyRowDot<B200_TYPE_Q5_1> {};
+
+
+template <int TYPE>
+struct K23RowDot {
+    static __device__ __forceinline__ void run(const unsigned char *seg, int lane, const LaneActs &A, int /*nblk*/, float &acc) {
+        acc += k23_half_dot<TYPE>(seg + (lane >> 1) * type_block_bytes(TYPE), lane & 1, A.u, A.d8, A.g);
+    }
+};
+template <> struct RowDot<B200_TYPE_Q2_K> : K23RowDot<B200_TYPE_Q2_K> {};
+template <> struct RowDot<B200_TYPE_Q3_K> : K23RowDot<B200_TYPE_Q3_K> {};
 
 }  // namespace b200

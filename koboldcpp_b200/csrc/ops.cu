@@ -329,6 +329,24 @@ __device__ __forceinline__ float dq_value(int type, const unsigned char *row, in
             const unsigned char *b = row + (i / 32) * Q8_0_BYTES;
             return __fmul_rn((float)(signed char)b[2 + i % 32], h2f(*reinterpret_cast<const unsigned short *>(b)));
         }
+        case B200_TYPE_Q2_K: {  // dequantize_row_q2_K (ggml-quants.c:1980-2010)
+            const unsigned char *b = row + (i / 256) * Q2_K_BYTES;
+            const int v = (int)(i % 256), is = v / 16;
+            const int q = (b[16 + 32 * (v / 128) + v % 32] >> (2 * ((v % 128) / 32))) & 3;
+            const float dl = __fmul_rn(h2f(*reinterpret_cast<const unsigned short *>(b + 80)), (float)(b[is] & 0xF));
+            const float ml = __fmul_rn(h2f(*reinterpret_cast<const unsigned short *>(b + 82)), (float)(b[is] >> 4));
+            return __fsub_rn(__fmul_rn(dl, (float)q), ml);
+        }
+        case B200_TYPE_Q3_K: {  // dequantize_row_q3_K (:2328-2373)
+            const unsigned char *b = row + (i / 256) * Q3_K_BYTES;
+            const int v = (int)(i % 256), is = v / 16;
+            unsigned sw[3], aux[4];
+            for (int k = 0; k < 3; k++) sw[k] = (unsigned)b[96 + 4 * k] | ((unsigned)b[97 + 4 * k] << 8) | ((unsigned)b[98 + 4 * k] << 16) | ((unsigned)b[99 + 4 * k] << 24);
+            q3k_scales(sw[0], sw[1], sw[2], aux);
+            const int sc = (int)((aux[is >> 2] >> (8 * (is & 3))) & 0xff) - 32;
+            const int q = (int)((b[32 + 32 * (v / 128) + v % 32] >> (2 * ((v % 128) / 32))) & 3) - (((b[v % 32] >> (v / 32)) & 1) ? 0 : 4);
+            return __fmul_rn(__fmul_rn(h2f(*reinterpret_cast<const unsigned short *>(b + 108)), (float)sc), (float)q);
+        }
         case B200_TYPE_Q4_1:
         case B200_TYPE_Q5_0:
         case B200_TYPE_Q5_1: {  // dequantize_row_q4_1 / q5_0 / q5_1 (ggml-quants.c:1543-1615)
@@ -745,7 +763,7 @@ extern "C" int b200_op_get_rows(const b200_tensor *src, const b200_tensor *ids, 
     REQUIRE(ids->type == B200_TYPE_I32 && dst->type == B200_TYPE_F32 && dst->nb[0] == 4, B200_ERR_UNSUPPORTED, "b200_op_get_rows: i32 ids, f32 dst");
     const int t = src->type;
     REQUIRE(t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K ||
-            t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1,
+            t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 || t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K,
             B200_ERR_UNSUPPORTED, "b200_op_get_rows: source type %d not supported", t);
     REQUIRE(dst->ne[0] == src->ne[0] && dst->ne[1] == ids->ne[0], B200_ERR_INVALID, "b200_op_get_rows: shape mismatch");
     if (nelements(dst) == 0) return B200_OK;

@@ -109,6 +109,28 @@ __global__ void __launch_bounds__(256) dequantize_kernel(const unsigned char *__
             if constexpr (TYPE == B200_TYPE_Q5_K) q += ((b[16 + l0 + l] >> sb) & 1) ? 16 : 0;  // qh bit sb (ggml-quants.c:2783-2786)
             o[l] = __fsub_rn(__fmul_rn(d1, (float)q), m1);
         }
+    } else if constexpr (TYPE == B200_TYPE_Q2_K || TYPE == B200_TYPE_Q3_K) {
+        // dequantize_row_q2_K / q3_K (ggml-quants.c:1980-2010, 2328-2373): value v sits in qs[32 (v / 128) + v % 32] at bits
+        // 2 ((v % 128) / 32); its scale is number v / 16
+        constexpr bool Q2 = TYPE == B200_TYPE_Q2_K;
+        const unsigned char *b = src + (i / QK_K) * (Q2 ? Q2_K_BYTES : Q3_K_BYTES);
+        const int v = (int)(i % QK_K), is = v / 16, sh = 2 * ((v % 128) / 32);
+        const unsigned char *qs = b + (Q2 ? 16 : 32) + 32 * (v / 128) + v % 32;
+        if constexpr (Q2) {
+            const float dl = __fmul_rn(ldh(b + 80), (float)(b[is] & 0xF)), ml = __fmul_rn(ldh(b + 82), (float)(b[is] >> 4));
+#pragma unroll
+            for (int l = 0; l < 4; l++) o[l] = __fsub_rn(__fmul_rn(dl, (float)((qs[l] >> sh) & 3)), ml);
+        } else {
+            unsigned sw[3], aux[4];
+#pragma unroll
+            for (int k = 0; k < 3; k++) sw[k] = (unsigned)b[96 + 4 * k] | ((unsigned)b[97 + 4 * k] << 8) | ((unsigned)b[98 + 4 * k] << 16) | ((unsigned)b[99 + 4 * k] << 24);
+            q3k_scales(sw[0], sw[1], sw[2], aux);
+            const int sc = (int)((aux[is >> 2] >> (8 * (is & 3))) & 0xff) - 32;
+            const float dl = __fmul_rn(ldh(b + 108), (float)sc);
+            const unsigned char *hm = b + v % 32;
+#pragma unroll
+            for (int l = 0; l < 4; l++) o[l] = __fmul_rn(dl, (float)((int)((qs[l] >> sh) & 3) - (((hm[l] >> (v / 32)) & 1) ? 0 : 4)));
+        }
     } else if constexpr (TYPE == B200_TYPE_Q6_K) {
         const unsigned char *b = src + (i / QK_K) * Q6_K_BYTES;
         const int j    = (int)(i % QK_K);
@@ -140,6 +162,8 @@ static int launch_dequant(int type, const void *src, T *dst, int64_t n, cudaStre
         case B200_TYPE_Q4_1: dequantize_kernel<B200_TYPE_Q4_1, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q5_0: dequantize_kernel<B200_TYPE_Q5_0, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q5_1: dequantize_kernel<B200_TYPE_Q5_1, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_Q2_K: dequantize_kernel<B200_TYPE_Q2_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_Q3_K: dequantize_kernel<B200_TYPE_Q3_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q4_K: dequantize_kernel<B200_TYPE_Q4_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q5_K: dequantize_kernel<B200_TYPE_Q5_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q6_K: dequantize_kernel<B200_TYPE_Q6_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;

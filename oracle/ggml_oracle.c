@@ -89,6 +89,8 @@ enum {
     Q5_0_BYTES = 22,  /* half d; u8 qh[4]; u8 qs[16]                        :164-169 */
     Q5_1_BYTES = 24,  /* half d; half m; u8 qh[4]; u8 qs[16]                :172-183 */
     Q8_1_BYTES = 36,  /* half d; half s; i8 qs[32]                          :194-204 */
+    Q2_K_BYTES = 84,  /* u8 scales[16]; u8 qs[64]; half d; half dmin         :257-268 */
+    Q3_K_BYTES = 110, /* u8 hmask[32]; u8 qs[64]; u8 scales[12]; half d      :274-280 */
     Q4_K_BYTES = 144, /* half d; half dmin; u8 scales[12]; u8 qs[128]       :286-298 */
     Q5_K_BYTES = 176, /* half d; half dmin; u8 scales[12]; u8 qh[32]; u8 qs[128] :303-316 */
     Q6_K_BYTES = 210, /* u8 ql[128]; u8 qh[64]; i8 scales[16]; half d       :321-327 */
@@ -100,6 +102,7 @@ int orc_blck_size(int type) {
         case ORC_TYPE_F32: case ORC_TYPE_F16: return 1;
         case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: case ORC_TYPE_Q8_1: return QK;
         case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_0: case ORC_TYPE_Q5_1: return QK;
+        case ORC_TYPE_Q2_K: case ORC_TYPE_Q3_K:
         case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: case ORC_TYPE_Q8_K: return QK_K;
     }
     return 0;
@@ -115,6 +118,8 @@ size_t orc_type_size(int type) {
         case ORC_TYPE_Q5_1: return Q5_1_BYTES;
         case ORC_TYPE_Q8_0: return Q8_0_BYTES;
         case ORC_TYPE_Q8_1: return Q8_1_BYTES;
+        case ORC_TYPE_Q2_K: return Q2_K_BYTES;
+        case ORC_TYPE_Q3_K: return Q3_K_BYTES;
         case ORC_TYPE_Q4_K: return Q4_K_BYTES;
         case ORC_TYPE_Q5_K: return Q5_K_BYTES;
         case ORC_TYPE_Q6_K: return Q6_K_BYTES;
@@ -200,6 +205,31 @@ static void expand_q5_K(const uint8_t *b, int8_t *q, int *sc, int *mn) {
         }
     }
 }
+/* Q2_K (dequantize_row_q2_K, ggml-quants.c:1980-2010): value v of the block lives in qs[32 (v / 128) + v % 32], bits
+ * 2 ((v % 128) / 32); scale byte v / 16: low nibble = scale, high nibble = min.  q[256] in [0,3], sc[16], mn[16]. */
+static void expand_q2_K(const uint8_t *b, int8_t *q, int *sc, int *mn) {
+    const uint8_t *scales = b, *qs = b + 16;
+    for (int j = 0; j < 16; j++) { sc[j] = scales[j] & 0xF; mn[j] = scales[j] >> 4; }
+    for (int v = 0; v < QK_K; v++) q[v] = (int8_t)((qs[32 * (v / 128) + v % 32] >> (2 * ((v % 128) / 32))) & 3);
+}
+/* Q3_K (dequantize_row_q3_K, :2328-2373): low 2 bits like Q2_K, high bit = bit v / 32 of hmask[v % 32] (set: +0, clear: -4);
+ * 16 six-bit scales packed in 12 bytes (the aux[] shuffle of :2345-2350), stored value - 32.  q[256] in [-4,3], sc[16] signed. */
+static void expand_q3_K(const uint8_t *b, int8_t *q, int *sc) {
+    const uint8_t *hm = b, *qs = b + 32;
+    uint32_t aux[4];
+    memcpy(aux, b + 96, 12);
+    const uint32_t kmask1 = 0x03030303, kmask2 = 0x0f0f0f0f, tmp = aux[2];
+    aux[2] = ((aux[0] >> 4) & kmask2) | (((tmp >> 4) & kmask1) << 4);
+    aux[3] = ((aux[1] >> 4) & kmask2) | (((tmp >> 6) & kmask1) << 4);
+    aux[0] = (aux[0] & kmask2) | (((tmp >> 0) & kmask1) << 4);
+    aux[1] = (aux[1] & kmask2) | (((tmp >> 2) & kmask1) << 4);
+    const int8_t *scales = (const int8_t *)aux;
+    for (int j = 0; j < 16; j++) sc[j] = scales[j] - 32;
+    for (int v = 0; v < QK_K; v++) {
+        const int lo = (qs[32 * (v / 128) + v % 32] >> (2 * ((v % 128) / 32))) & 3;
+        q[v] = (int8_t)(lo - ((hm[v % 32] >> (v / 32)) & 1 ? 0 : 4));
+    }
+}
 static void expand_q6_K(const uint8_t *b, int8_t *q, int *sc) {
     const uint8_t *ql = b, *qh = b + 128;
     const int8_t *scales = (const int8_t *)(b + 192);
@@ -275,6 +305,32 @@ int orc_dequantize_row(int type, const void *src, float *dst, int64_t k) {
                         const float prod = dj * (float)q[32 * j + l];
                         dst[32 * j + l] = prod - mj;
                     }
+                }
+            }
+            return 0;
+        case ORC_TYPE_Q2_K: /* :1980-2010: y = (d*sc)*q - (dmin*m) */
+            if (k % QK_K) return -1;
+            for (int64_t i = 0; i < k / QK_K; i++, b += Q2_K_BYTES, dst += QK_K) {
+                int mn16[16];
+                const float d = rdh(b + 80), dmin = rdh(b + 82);
+                expand_q2_K(b, q, sc, mn16);
+                for (int j = 0; j < 16; j++) {
+                    const float dl = d * (float)sc[j], ml = dmin * (float)mn16[j];
+                    for (int l = 0; l < 16; l++) {
+                        const float prod = dl * (float)q[16 * j + l];
+                        dst[16 * j + l] = prod - ml;
+                    }
+                }
+            }
+            return 0;
+        case ORC_TYPE_Q3_K: /* :2328-2373: y = (d*(sc-32))*q */
+            if (k % QK_K) return -1;
+            for (int64_t i = 0; i < k / QK_K; i++, b += Q3_K_BYTES, dst += QK_K) {
+                const float d = rdh(b + 108);
+                expand_q3_K(b, q, sc);
+                for (int j = 0; j < 16; j++) {
+                    const float dl = d * (float)sc[j];
+                    for (int l = 0; l < 16; l++) dst[16 * j + l] = dl * (float)q[16 * j + l];
                 }
             }
             return 0;
@@ -397,6 +453,7 @@ static int vec_dot_act_type(int wtype) {
     switch (wtype) {
         case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: case ORC_TYPE_Q5_0: return ORC_TYPE_Q8_0; /* ggml.c:793-808, 873-889 */
         case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_1: return ORC_TYPE_Q8_1; /* vec_dot_type of q4_1 / q5_1, ggml.c type_traits */
+        case ORC_TYPE_Q2_K: case ORC_TYPE_Q3_K:
         case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: return ORC_TYPE_Q8_K; /* :924-959 */
     }
     return -1;
@@ -462,7 +519,26 @@ float orc_vec_dot(int wtype, int64_t n, const void *wv, const void *av) {
         memcpy(bsums, a + 4 + QK_K, 32);
         int32_t lane[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         float d;
-        if (wtype == ORC_TYPE_Q6_K) {
+        if (wtype == ORC_TYPE_Q2_K) { /* ggml_vec_dot_q2_K_q8_K scalar branch, ggml-quants.c:6892-6930: no lanes */
+            int mn16[16];
+            expand_q2_K(w, q, sc, mn16);
+            int summs = 0, isum = 0;
+            for (int j = 0; j < 16; j++) summs += bsums[j] * mn16[j];
+            for (int j = 0; j < 16; j++) {
+                int isuml = 0;
+                for (int l = 0; l < 16; l++) isuml += y[16 * j + l] * q[16 * j + l];
+                isum += sc[j] * isuml;
+            }
+            const float dall = yd * rdh(w + 80), dmn = yd * rdh(w + 82);
+            const float t1 = dall * (float)isum, t2 = dmn * (float)summs;
+            sumf += t1 - t2;
+            continue;
+        }
+        if (wtype == ORC_TYPE_Q3_K) { /* :7651-7707 */
+            expand_q3_K(w, q, sc);
+            for (int j = 0; j < QK_K; j++) lane[j & 7] += sc[j / 16] * (int32_t)(int16_t)(y[j] * q[j]);
+            d = rdh(w + 108) * yd;
+        } else if (wtype == ORC_TYPE_Q6_K) {
             expand_q6_K(w, q, sc);
             for (int j = 0; j < QK_K; j++) lane[j & 7] += sc[j / 16] * (int32_t)(int16_t)(y[j] * q[j]);
             d = rdh(w + 208) * yd;
@@ -531,6 +607,24 @@ double orc_vec_dot_q8_1(int wtype, int64_t n, const void *wv, const void *av) {
     }
     const size_t wb = orc_type_size(wtype);
     for (int64_t i = 0; i < n / QK_K; i++, w += wb, a += 8 * Q8_1_BYTES) {
+        if (wtype == ORC_TYPE_Q2_K || wtype == ORC_TYPE_Q3_K) {
+            /* per 16-wide group g (q8_1 block g / 2, half g & 1):  Q2_K: d sc d8 sum(v u) - dmin m d8 sum(u);
+             * Q3_K: d sc d8 sum(v u), v in [-4, 3]  (vecdotq.cuh:230-355 use the same per-16 integer sums) */
+            int mn16[16];
+            const double d = rdh(w + (wtype == ORC_TYPE_Q2_K ? 80 : 108)), dmin = wtype == ORC_TYPE_Q2_K ? rdh(w + 82) : 0.0;
+            if (wtype == ORC_TYPE_Q2_K) expand_q2_K(w, q, sc, mn16); else { expand_q3_K(w, q, sc); memset(mn16, 0, sizeof(mn16)); }
+            double sd = 0, sm = 0;
+            for (int g = 0; g < 16; g++) {
+                const uint8_t *blk = a + (g / 2) * Q8_1_BYTES;
+                const int8_t *y = (const int8_t *)(blk + 4) + 16 * (g & 1);
+                int sumi = 0, sumu = 0;
+                for (int l = 0; l < 16; l++) { sumi += q[16 * g + l] * y[l]; sumu += y[l]; }
+                sd += (double)rdh(blk) * sc[g] * sumi;
+                sm += (double)rdh(blk) * mn16[g] * sumu;
+            }
+            acc += d * sd - dmin * sm;
+            continue;
+        }
         if (wtype == ORC_TYPE_Q6_K) {
             expand_q6_K(w, q, sc);
             const double d = rdh(w + 208);

@@ -68,6 +68,10 @@ def random_blocks(t, M, K, rng):
         put_half(0, 0.0005, 0.002); put_half(2, 0.0005, 0.002)
     elif t == R.Q6_K:
         put_half(208, -0.001, 0.001)
+    elif t == R.Q2_K:
+        put_half(80, 0.001, 0.004); put_half(82, 0.001, 0.004)
+    elif t == R.Q3_K:
+        put_half(108, -0.002, 0.002)
     return raw.reshape(M, nb * by)
 
 
