@@ -61,7 +61,11 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
             if (!s0 || !k || !v) return false;
             if (s0->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || s0->nb[0] != 4) return false;
             if (k->type != v->type || (k->type != GGML_TYPE_F16 && k->type != GGML_TYPE_Q8_0)) return false;
-            if (s0->ne[0] != 64 && s0->ne[0] != 128) return false;
+            {   // head sizes: 64 / 128 with either cache type; 80 / 96 / 112 / 256 with an f16 cache (ggml-cuda.cu:3162-3177)
+                const int64_t D = s0->ne[0];
+                const bool d_more = (D == 80 || D == 96 || D == 112 || D == 256) && k->type == GGML_TYPE_F16;
+                if (D != 64 && D != 128 && !d_more) return false;
+            }
             if (s0->ne[3] != 1 || k->ne[3] != 1 || v->ne[3] != 1 || k->ne[2] == 0 || s0->ne[2] % k->ne[2]) return false;
             if (m && (m->type != GGML_TYPE_F16 || m->nb[0] != 2)) return false;
             const size_t al = k->type == GGML_TYPE_F16 ? 15 : (s0->ne[0] == 128 ? 7 : 3);

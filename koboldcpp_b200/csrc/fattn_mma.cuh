@@ -82,16 +82,29 @@ template <int D>
 __device__ __forceinline__ void mma_load_tile(unsigned char *dst, const unsigned char *base, size_t nb1, int row0, int n_kv, int lane) {
     using G = MmaGeo<B200_TYPE_F16, D>;
     constexpr int CPR = G::ROW_BYTES / 16;       // 16-byte chunks per row
-    constexpr int RPP = 32 / CPR;                // rows per pass of the warp
-    const int c = lane % CPR, r0 = lane / CPR;
-    const unsigned char *src = base + (size_t)(row0 + r0) * nb1 + c * 16;
-    unsigned char *d = dst + r0 * G::ROW_STRIDE + c * 16;
+    if constexpr (32 % CPR == 0 || CPR % 32 == 0) {
+        constexpr int RPP = CPR >= 32 ? 1 : 32 / CPR;  // rows per pass of the warp
+        constexpr int CPL = CPR >= 32 ? CPR / 32 : 1;  // chunks per lane and row (D = 256: 1; wider heads: more)
+        const int c = lane % CPR, r0 = CPR >= 32 ? 0 : lane / CPR;
+        const unsigned char *src = base + (size_t)(row0 + r0) * nb1 + c * 16;
+        unsigned char *d = dst + r0 * G::ROW_STRIDE + c * 16;
 #pragma unroll
-    for (int i = 0; i < FM_TP / RPP; i++) {
-        if (row0 + r0 + i * RPP < n_kv) cp_async16(d, src);
-        else *reinterpret_cast<uint4 *>(d) = make_uint4(0, 0, 0, 0);
-        src += (size_t)RPP * nb1;
-        d += RPP * G::ROW_STRIDE;
+        for (int i = 0; i < FM_TP / RPP; i++) {
+#pragma unroll
+            for (int k = 0; k < CPL; k++) {
+                if (row0 + r0 + i * RPP < n_kv) cp_async16(d + k * 512, src + k * 512);
+                else *reinterpret_cast<uint4 *>(d + k * 512) = make_uint4(0, 0, 0, 0);
+            }
+            src += (size_t)RPP * nb1;
+            d += RPP * G::ROW_STRIDE;
+        }
+    } else {  // head sizes 80 / 96 / 112: 10 / 12 / 14 chunks per row
+        for (int i = lane; i < FM_TP * CPR; i += 32) {
+            const int r = i / CPR, c = i - r * CPR;
+            unsigned char *d = dst + r * G::ROW_STRIDE + c * 16;
+            if (row0 + r < n_kv) cp_async16(d, base + (size_t)(row0 + r) * nb1 + c * 16);
+            else *reinterpret_cast<uint4 *>(d) = make_uint4(0, 0, 0, 0);
+        }
     }
 }
 

@@ -846,7 +846,9 @@ int orc_flash_attn_ext(const orc_fattn_params *p, const void *q, const void *k, 
                        const void *mask, float *dst, int nthreads) {
     if (p->type_k != ORC_TYPE_F16 && p->type_k != ORC_TYPE_Q8_0) return -1;
     if (p->type_v != ORC_TYPE_F16 && p->type_v != ORC_TYPE_Q8_0) return -1;
-    if (p->n_head % p->n_head_kv || p->D % 32) return -1;
+    if (p->n_head % p->n_head_kv) return -1;
+    /* a q8_0 row is whole blocks of 32; an f16 cache has no block constraint (head sizes 80 and 112 exist) */
+    if ((p->type_k == ORC_TYPE_Q8_0 || p->type_v == ORC_TYPE_Q8_0) && p->D % 32) return -1;
     fa_ctx c = { p, (const uint8_t *)q, (const uint8_t *)k, (const uint8_t *)v, (const uint8_t *)mask, dst, NULL };
     orc_parallel_for(p->n_head * p->N, nthreads, fa_rows, &c);
     return 0;

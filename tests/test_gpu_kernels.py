@@ -342,6 +342,43 @@ def test_flash_attn_prefill_causal(H, cfg):
         assert np.isfinite(got2).all() and np.array_equal(got2, got)
 
 
+@pytest.mark.parametrize("D", (80, 96, 112, 256))
+@pytest.mark.parametrize("shape", [
+    # (n_head, n_head_kv, n_kv, N, n_past)
+    (32, 32, 1024, 1, 1023),    # decode, one query column per head (StableLM / Phi-style head sizes; Gemma D = 256)
+    (16, 2, 2085, 1, 2084),     # GQA 8, ragged cache, several cluster splits
+    (8, 4, 330, 5, 325),        # a few columns
+    (8, 8, 384, 300, 84),       # a prompt batch through the prefill kernel, causal tiles skipped
+], ids=["decode", "gqa8", "n5", "prefill"])
+def test_flash_attn_more_head_sizes(H, D, shape):
+    """N4: head sizes 80 / 96 / 112 / 256 over an f16 cache (the reference's CUDA backend: ggml-cuda.cu:3162-3177 lists
+    64, 80, 96, 112, 128, 256).  They run on the tensor-core kernels only; a q8_0 cache with these sizes is refused."""
+    nh, nhkv, nkv, N, n_past = shape
+    rng = np.random.default_rng(D * 7 + sum(shape))
+    q = rng.standard_normal((nh, N, D)).astype(np.float32)
+    k = O.pack_kv(R.F16, rng.standard_normal((nhkv, nkv, D)))
+    v = O.pack_kv(R.F16, rng.standard_normal((nhkv, nkv, D)))
+    npad = (N + 31) // 32 * 32
+    mask = np.full((npad, nkv), -np.inf, dtype=np.float16)
+    for i in range(N):
+        mask[i, :min(nkv, n_past + i + 1)] = 0
+    got = H.flash_attn_ext(q, k, v, mask, R.F16, 1.0 / np.sqrt(D))
+    f64 = O.flash_attn_f64(q, k, v, mask, R.F16, 1.0 / np.sqrt(D))
+    assert np.isfinite(got).all()
+    assert np.abs(got - f64).max() <= TOL_FA[R.F16], float(np.abs(got - f64).max())
+    if nh * N * nkv <= 8 * 5 * 330:
+        cpu = O.flash_attn_ext(q, k, v, mask, R.F16, 1.0 / np.sqrt(D))
+        assert np.abs(got - cpu).max() <= 2 * TOL_FA[R.F16]
+
+
+def test_flash_attn_head_size_refused_for_q8_cache(H):
+    rng = np.random.default_rng(5)
+    q = rng.standard_normal((4, 1, 96)).astype(np.float32)
+    k = O.pack_kv(R.Q8_0, rng.standard_normal((4, 64, 96))); v = O.pack_kv(R.Q8_0, rng.standard_normal((4, 64, 96)))
+    with pytest.raises(Exception, match="head size"):
+        H.flash_attn_ext(q, k, v, None, R.Q8_0, 0.1)
+
+
 def test_flash_attn_no_mask_and_fully_masked_prefix(H):
     rng = np.random.default_rng(21)
     nh, nhkv, D, nkv = 4, 4, 128, 300
