@@ -220,6 +220,18 @@ typedef struct {
 B200_API size_t b200_flash_attn_workspace_bytes(const b200_fattn_args *a);
 B200_API int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, size_t workspace_bytes, b200_stream_t stream);
 
+/* b200_flash_attn_ext without a caller-owned workspace and without any allocation (no cudaMalloc / cudaFree, directly or
+ * through a library): for callers under CUDA graph capture, serving loops and harnesses that forbid allocating.
+ * No counterpart in the reference.
+ * The split partials and arrival counters live in one static device array of B200_FATTN_STATIC_WS_BYTES (8 MiB) that every
+ * GPU that loads the library holds until the process exits.  Same kernels, plan and results as b200_flash_attn_ext.
+ * Shapes whose b200_flash_attn_workspace_bytes() exceeds the array return B200_ERR_UNSUPPORTED (b200_last_error names both
+ * sizes).  ALL calls on a device share the array: calls that overlap on the GPU (different streams, or graph branches that
+ * run concurrently) race -- serialise them or use b200_flash_attn_ext with separate workspaces. */
+#define B200_FATTN_STATIC_WS_BYTES (8u << 20)
+B200_API size_t b200_flash_attn_static_workspace_max(void);
+B200_API int b200_flash_attn_ext_static(const b200_fattn_args *a, b200_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -699,6 +699,9 @@ static int fa_check(const b200_fattn_args *a) {
     return B200_OK;
 }
 
+// bytes of split arrival counters at the front of the workspace (fattn_static.cu clears exactly these before a launch)
+size_t fa_ticket_bytes(const b200_fattn_args *a) { return fa_check(a) == B200_OK ? fa_plan(a).ticket_bytes : 0; }
+
 }  // namespace b200
 
 using namespace b200;

@@ -104,6 +104,8 @@ _SIGS = {
     "b200_mul_mat_q": (C.c_int, [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200_flash_attn_workspace_bytes": (C.c_size_t, [C.POINTER(FattnArgs)]),
     "b200_flash_attn_ext": (C.c_int, [C.POINTER(FattnArgs), C.c_void_p, C.c_size_t, C.c_void_p]),
+    "b200_flash_attn_static_workspace_max": (C.c_size_t, []),
+    "b200_flash_attn_ext_static": (C.c_int, [C.POINTER(FattnArgs), C.c_void_p]),
 }
 
 # include/b200_ggml_ops.h (the subset the tests drive directly; the rest is reached through the backend)
