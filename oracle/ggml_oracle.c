@@ -95,13 +95,16 @@ enum {
     Q5_K_BYTES = 176, /* half d; half dmin; u8 scales[12]; u8 qh[32]; u8 qs[128] :303-316 */
     Q6_K_BYTES = 210, /* u8 ql[128]; u8 qh[64]; i8 scales[16]; half d       :321-327 */
     Q8_K_BYTES = 292, /* float d; i8 qs[256]; i16 bsums[16]                 :330-335 */
+    IQ4_NL_BYTES = 18,  /* half d; u8 qs[16]                                :406-410 */
+    IQ4_XS_BYTES = 136, /* half d; u16 scales_h; u8 scales_l[4]; u8 qs[128] :413-418 */
 };
 
 int orc_blck_size(int type) {
     switch (type) {
         case ORC_TYPE_F32: case ORC_TYPE_F16: return 1;
         case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: case ORC_TYPE_Q8_1: return QK;
-        case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_0: case ORC_TYPE_Q5_1: return QK;
+        case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_0: case ORC_TYPE_Q5_1: case ORC_TYPE_IQ4_NL: return QK;
+        case ORC_TYPE_IQ4_XS:
         case ORC_TYPE_Q2_K: case ORC_TYPE_Q3_K:
         case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: case ORC_TYPE_Q8_K: return QK_K;
     }
@@ -124,6 +127,8 @@ size_t orc_type_size(int type) {
         case ORC_TYPE_Q5_K: return Q5_K_BYTES;
         case ORC_TYPE_Q6_K: return Q6_K_BYTES;
         case ORC_TYPE_Q8_K: return Q8_K_BYTES;
+        case ORC_TYPE_IQ4_NL: return IQ4_NL_BYTES;
+        case ORC_TYPE_IQ4_XS: return IQ4_XS_BYTES;
     }
     return 0;
 }
@@ -164,6 +169,23 @@ static void expand_q4_0(const uint8_t *b, int8_t *q) {
     }
 }
 static void expand_q8_0(const uint8_t *b, int8_t *q) { memcpy(q, b + 2, 32); }
+/* IQ4_NL / IQ4_XS: a nibble indexes 16 non-uniform int8 levels (kvalues_iq4nl, ggml-common.h); values 0..15 of a 32-value block
+ * are the low nibbles, 16..31 the high nibbles (dequantize_row_iq4_nl, ggml-quants.c:3743-3760) */
+static const int8_t iq4_levels[16] = {-127, -104, -83, -65, -49, -35, -22, -10, 1, 13, 25, 38, 53, 69, 89, 113};
+static void expand_iq4(const uint8_t *qs, int8_t *q) {
+    for (int j = 0; j < 16; j++) {
+        q[j]      = iq4_levels[qs[j] & 0x0F];
+        q[j + 16] = iq4_levels[qs[j] >> 4];
+    }
+}
+/* IQ4_XS: q[256] levels, sc[8] = 6-bit sub-block scale - 32 (low 4 bits in scales_l, high 2 in scales_h; :3762-3785) */
+static void expand_iq4_xs(const uint8_t *b, int8_t *q, int *sc) {
+    const unsigned h = rd16(b + 2);
+    for (int ib = 0; ib < 8; ib++) {
+        sc[ib] = (int)(((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xF) | (((h >> (2 * ib)) & 3) << 4)) - 32;
+        expand_iq4(b + 8 + 16 * ib, q + 32 * ib);
+    }
+}
 /* Q4_1: q[32] in [0,15] (values 0..15 = low nibbles, 16..31 = high nibbles), ggml-quants.c:1543-1562 */
 static void expand_q4_1(const uint8_t *b, int8_t *q) {
     const uint8_t *qs = b + 4;
@@ -261,6 +283,25 @@ int orc_dequantize_row(int type, const void *src, float *dst, int64_t k) {
                 const float d = rdh(b);
                 expand_q4_0(b, q);
                 for (int j = 0; j < QK; j++) dst[j] = (float)q[j] * d;
+            }
+            return 0;
+        case ORC_TYPE_IQ4_NL: /* ggml-quants.c:3743-3760: y = d * level */
+            if (k % QK) return -1;
+            for (int64_t i = 0; i < k / QK; i++, b += IQ4_NL_BYTES, dst += QK) {
+                const float d = rdh(b);
+                expand_iq4(b + 2, q);
+                for (int j = 0; j < QK; j++) dst[j] = d * (float)q[j];
+            }
+            return 0;
+        case ORC_TYPE_IQ4_XS: /* :3762-3785: y = (d * (ls - 32)) * level */
+            if (k % QK_K) return -1;
+            for (int64_t i = 0; i < k / QK_K; i++, b += IQ4_XS_BYTES, dst += QK_K) {
+                const float d = rdh(b);
+                expand_iq4_xs(b, q, sc);
+                for (int ib = 0; ib < 8; ib++) {
+                    const float dl = d * (float)sc[ib];
+                    for (int j = 0; j < 32; j++) dst[32 * ib + j] = dl * (float)q[32 * ib + j];
+                }
             }
             return 0;
         case ORC_TYPE_Q4_1: /* :1543-1562: y = x0*d + m (a product, then a sum) */
@@ -452,6 +493,8 @@ int orc_quantize_row(int type, const float *x, void *dst, int64_t k) {
 static int vec_dot_act_type(int wtype) {
     switch (wtype) {
         case ORC_TYPE_Q4_0: case ORC_TYPE_Q8_0: case ORC_TYPE_Q5_0: return ORC_TYPE_Q8_0; /* ggml.c:793-808, 873-889 */
+        case ORC_TYPE_IQ4_NL: return ORC_TYPE_Q8_0; /* ggml.c type_traits[GGML_TYPE_IQ4_NL].vec_dot_type */
+        case ORC_TYPE_IQ4_XS: return ORC_TYPE_Q8_K;
         case ORC_TYPE_Q4_1: case ORC_TYPE_Q5_1: return ORC_TYPE_Q8_1; /* vec_dot_type of q4_1 / q5_1, ggml.c type_traits */
         case ORC_TYPE_Q2_K: case ORC_TYPE_Q3_K:
         case ORC_TYPE_Q4_K: case ORC_TYPE_Q5_K: case ORC_TYPE_Q6_K: return ORC_TYPE_Q8_K; /* :924-959 */
@@ -477,6 +520,33 @@ float orc_vec_dot(int wtype, int64_t n, const void *wv, const void *av) {
             } else {
                 /* :5855: sumf += sumi*(d_x*d_y) */
                 sumf += (float)sumi * (rdh(w) * rdh(a));
+            }
+        }
+        return sumf;
+    }
+    if (wtype == ORC_TYPE_IQ4_NL) { /* ggml_vec_dot_iq4_nl_q8_0 scalar tail, ggml-quants.c:12660-12669 */
+        float sumf = 0;
+        for (int64_t i = 0; i < n / QK; i++, w += IQ4_NL_BYTES, a += Q8_0_BYTES) {
+            expand_iq4(w + 2, q);
+            const int8_t *y = (const int8_t *)(a + 2);
+            const float d = rdh(a) * rdh(w);
+            int sumi1 = 0, sumi2 = 0;
+            for (int j = 0; j < 16; j++) { sumi1 += y[j] * q[j]; sumi2 += y[j + 16] * q[j + 16]; }
+            sumf += d * (float)(sumi1 + sumi2);
+        }
+        return sumf;
+    }
+    if (wtype == ORC_TYPE_IQ4_XS) { /* ggml_vec_dot_iq4_xs_q8_K scalar branch, ggml-quants.c:12975-13004 */
+        float sumf = 0;
+        for (int64_t i = 0; i < n / QK_K; i++, w += IQ4_XS_BYTES, a += Q8_K_BYTES) {
+            expand_iq4_xs(w, q, sc);
+            const float d4d8 = rdh(w) * rdf32(a);
+            const int8_t *y = (const int8_t *)(a + 4);
+            for (int ib = 0; ib < 8; ib++) {
+                const float dl = d4d8 * (float)sc[ib];
+                int sumi1 = 0, sumi2 = 0;
+                for (int j = 0; j < 16; j++) { sumi1 += y[32 * ib + j] * q[32 * ib + j]; sumi2 += y[32 * ib + 16 + j] * q[32 * ib + 16 + j]; }
+                sumf += dl * (float)(sumi1 + sumi2);
             }
         }
         return sumf;
@@ -586,6 +656,30 @@ double orc_vec_dot_q8_1(int wtype, int64_t n, const void *wv, const void *av) {
                 for (int j = 0; j < QK; j++) sumi += q[j] * y[j];
                 acc += dw * d8 * sumi;
             }
+        }
+        return acc;
+    }
+    if (wtype == ORC_TYPE_IQ4_NL) { /* d * d8 * sum(level * u), vecdotq.cuh:1086-1105 */
+        for (int64_t i = 0; i < n / QK; i++, w += IQ4_NL_BYTES, a += Q8_1_BYTES) {
+            const int8_t *y = (const int8_t *)(a + 4);
+            int sumi = 0;
+            expand_iq4(w + 2, q);
+            for (int j = 0; j < QK; j++) sumi += q[j] * y[j];
+            acc += (double)rdh(w) * (double)rdh(a) * sumi;
+        }
+        return acc;
+    }
+    if (wtype == ORC_TYPE_IQ4_XS) { /* d * sum_ib (ls_ib - 32) * d8_ib * sum(level * u), vecdotq.cuh:1110-1140 */
+        for (int64_t i = 0; i < n / QK_K; i++, w += IQ4_XS_BYTES, a += 8 * Q8_1_BYTES) {
+            expand_iq4_xs(w, q, sc);
+            double blk = 0;
+            for (int ib = 0; ib < 8; ib++) {
+                const int8_t *y = (const int8_t *)(a + ib * Q8_1_BYTES + 4);
+                int sumi = 0;
+                for (int j = 0; j < 32; j++) sumi += q[32 * ib + j] * y[j];
+                blk += (double)sc[ib] * (double)rdh(a + ib * Q8_1_BYTES) * sumi;
+            }
+            acc += (double)rdh(w) * blk;
         }
         return acc;
     }

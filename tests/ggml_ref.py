@@ -22,16 +22,17 @@ REF_DIR = ROOT / "oracle" / "_ref"
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K, I32 = 0, 1, 2, 8, 9, 12, 13, 14, 15, 26
 Q4_1, Q5_0, Q5_1 = 3, 6, 7
 Q2_K, Q3_K = 10, 11
-TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_K", Q3_K: "q3_K", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", Q8_K: "q8_K"}
+IQ4_NL, IQ4_XS = 20, 23
+TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_K", Q3_K: "q3_K", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", Q8_K: "q8_K", IQ4_NL: "iq4_nl", IQ4_XS: "iq4_xs"}
 # (values per block, bytes per block)  ggml/src/ggml-common.h:144-335
 BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), Q8_1: (32, 36), Q2_K: (256, 84), Q3_K: (256, 110), Q4_K: (256, 144), Q5_K: (256, 176),
-         Q6_K: (256, 210), Q8_K: (256, 292), I32: (1, 4)}
-WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K)
+         Q6_K: (256, 210), Q8_K: (256, 292), I32: (1, 4), IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
+WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K, IQ4_NL, IQ4_XS)
 
 
 def act_type(t: int) -> int:
     """vec_dot_type of a weight type on the CPU backend (ggml.c type_traits)."""
-    return Q8_0 if t in (Q4_0, Q8_0, Q5_0) else Q8_1 if t in (Q4_1, Q5_1) else Q8_K
+    return Q8_0 if t in (Q4_0, Q8_0, Q5_0, IQ4_NL) else Q8_1 if t in (Q4_1, Q5_1) else Q8_K
 
 
 def row_size(t: int, ne: int) -> int:
@@ -117,11 +118,12 @@ class Ref:
         L.ggml_tensor_overhead.restype = SZ
         L.ggml_type_size.restype = SZ; L.ggml_type_size.argtypes = [I]
         L.ggml_blck_size.restype = I64; L.ggml_blck_size.argtypes = [I]
-        for n in ("q4_0", "q8_0", "q4_K", "q5_K", "q6_K"):
+        for n in ("q4_0", "q4_1", "q5_0", "q5_1", "q8_0", "q2_K", "q3_K", "q4_K", "q5_K", "q6_K", "iq4_nl", "iq4_xs"):
             f = getattr(L, f"dequantize_row_{n}"); f.restype = None; f.argtypes = [P, P, I64]
         for n in ("q4_0", "q8_0", "q8_1", "q8_K"):
             f = getattr(L, f"quantize_row_{n}_ref"); f.restype = None; f.argtypes = [P, P, I64]
-        for n in ("q4_0_q8_0", "q8_0_q8_0", "q4_K_q8_K", "q5_K_q8_K", "q6_K_q8_K"):
+        for n in ("q4_0_q8_0", "q4_1_q8_1", "q5_0_q8_0", "q5_1_q8_1", "q8_0_q8_0", "q2_K_q8_K", "q3_K_q8_K", "q4_K_q8_K", "q5_K_q8_K",
+                  "q6_K_q8_K", "iq4_nl_q8_0", "iq4_xs_q8_K"):
             f = getattr(L, f"ggml_vec_dot_{n}"); f.restype = None; f.argtypes = [I, P, SZ, P, SZ, P, SZ, I]
         L.ggml_fp32_to_fp16_row.argtypes = [P, P, I64]
         L.ggml_fp16_to_fp32_row.argtypes = [P, P, I64]

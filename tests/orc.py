@@ -12,6 +12,7 @@ ORACLE_DIR = ROOT / "oracle"
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, Q8_K = 0, 1, 2, 8, 9, 12, 13, 14, 15
 Q4_1, Q5_0, Q5_1 = 3, 6, 7
 Q2_K, Q3_K = 10, 11
+IQ4_NL, IQ4_XS = 20, 23
 
 
 class FattnParams(C.Structure):
