@@ -36,7 +36,7 @@ def main():
     g = {}
     # --- (a1,a2) weight formats: reference-quantised gaussians + raw random blocks -> dequantised f32
     K = 1024
-    for t in R.WEIGHT_TYPES:
+    for t in R.ORACLE_WEIGHT_TYPES:
         n = R.TYPE_NAMES[t]
         x = (rng.standard_normal((4, K)) * 0.05).astype(np.float32)
         w = ref.quantize(t, x)
@@ -54,7 +54,7 @@ def main():
     Km, M, N = 1024, 24, 3
     xs = rng.standard_normal((N, Km)).astype(np.float32)
     g["mm_x"] = xs
-    for t in R.WEIGHT_TYPES:
+    for t in R.ORACLE_WEIGHT_TYPES:
         n = R.TYPE_NAMES[t]
         w = ref.quantize(t, (rng.standard_normal((M, Km)) * 0.05).astype(np.float32))
         g[f"mm_{n}_w"] = w

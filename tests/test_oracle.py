@@ -6,7 +6,7 @@ import pytest
 import ggml_ref as R
 import orc as O
 
-WT = R.WEIGHT_TYPES
+WT = R.ORACLE_WEIGHT_TYPES
 NAME = R.TYPE_NAMES
 
 
