@@ -57,6 +57,8 @@ enum b200_type {
     B200_TYPE_Q4_K = 12,
     B200_TYPE_Q5_K = 13,
     B200_TYPE_Q6_K = 14,
+    B200_TYPE_IQ4_NL = 20,
+    B200_TYPE_IQ4_XS = 23,
     B200_TYPE_I32  = 26,
 };
 

@@ -56,6 +56,8 @@ enum ggml_type {
     GGML_TYPE_Q5_K = 13,
     GGML_TYPE_Q6_K = 14,
     GGML_TYPE_Q8_K = 15,
+    GGML_TYPE_IQ4_NL = 20,
+    GGML_TYPE_IQ4_XS = 23,
     GGML_TYPE_I8   = 24,
     GGML_TYPE_I16  = 25,
     GGML_TYPE_I32  = 26,

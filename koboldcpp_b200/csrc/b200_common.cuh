@@ -30,17 +30,21 @@ constexpr int Q3_K_BYTES = 110;  // u8 hmask[32], u8 qs[64], u8 scales[12], half
 constexpr int Q4_K_BYTES = 144;
 constexpr int Q5_K_BYTES = 176;
 constexpr int Q6_K_BYTES = 210;
+constexpr int IQ4_NL_BYTES = 18;   // half d, u8 qs[16]: nibbles index 16 non-uniform int8 levels (ggml-common.h:406-410)
+constexpr int IQ4_XS_BYTES = 136;  // half d, u16 scales_h, u8 scales_l[4], u8 qs[128] (:413-418)
 
 __host__ __device__ constexpr int type_block_values(int t) {
     return (t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_I32) ? 1
-         : (t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q8_1 || t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1) ? 32
-         : (t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K || t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K) ? 256 : 0;
+         : (t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q8_1 || t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 ||
+            t == B200_TYPE_IQ4_NL) ? 32
+         : (t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K || t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K || t == B200_TYPE_IQ4_XS) ? 256 : 0;
 }
 __host__ __device__ constexpr int type_block_bytes(int t) {
     return t == B200_TYPE_F32 ? 4 : t == B200_TYPE_F16 ? 2 : t == B200_TYPE_I32 ? 4
          : t == B200_TYPE_Q4_0 ? Q4_0_BYTES : t == B200_TYPE_Q8_0 ? Q8_0_BYTES : t == B200_TYPE_Q8_1 ? Q8_1_BYTES
          : t == B200_TYPE_Q4_1 ? Q4_1_BYTES : t == B200_TYPE_Q5_0 ? Q5_0_BYTES : t == B200_TYPE_Q5_1 ? Q5_1_BYTES
          : t == B200_TYPE_Q2_K ? Q2_K_BYTES : t == B200_TYPE_Q3_K ? Q3_K_BYTES
+         : t == B200_TYPE_IQ4_NL ? IQ4_NL_BYTES : t == B200_TYPE_IQ4_XS ? IQ4_XS_BYTES
          : t == B200_TYPE_Q4_K ? Q4_K_BYTES : t == B200_TYPE_Q5_K ? Q5_K_BYTES : t == B200_TYPE_Q6_K ? Q6_K_BYTES : 0;
 }
 // bytes of 128 consecutive weights (one "slice": the unit one lane processes per step)
@@ -188,6 +192,35 @@ __device__ __forceinline__ void q3k_scales(const unsigned s0, const unsigned s1,
     aux[1] = (s1 & kmask2) | (((s2 >> 2) & kmask1) << 4);
     aux[2] = ((s0 >> 4) & kmask2) | (((s2 >> 4) & kmask1) << 4);
     aux[3] = ((s1 >> 4) & kmask2) | (((s2 >> 6) & kmask1) << 4);
+}
+
+// ---------------------------------------------------------------- IQ4_NL / IQ4_XS codebook
+// A nibble indexes 16 non-uniform int8 levels (kvalues_iq4nl, ggml-common.h): -127 -104 -83 -65 -49 -35 -22 -10 1 13 25 38 53 69 89
+// 113, held here as four little-endian words.  iq4_levels() looks up the eight nibbles of one word with the byte permute unit
+// (no memory table): PRMT selects among 8 table bytes with the low 3 bits of a selector nibble, once in the lower and once in
+// the upper half of the table; bit 3 of each nibble then picks between the two results through a byte mask (PRMT's sign
+// replication).  lo = levels of the low nibbles of bytes 0..3 (values j .. j+3 of a 32-value block), hi = those of the high
+// nibbles (values j+16 .. j+19), as int8x4 ready for dp4a.
+constexpr unsigned IQ4_T0 = 0xBFAD9881u, IQ4_T1 = 0xF6EADDCFu, IQ4_T2 = 0x26190D01u, IQ4_T3 = 0x71594535u;
+__device__ __forceinline__ unsigned prmt(unsigned a, unsigned b, unsigned sel) {
+    unsigned r;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(sel));
+    return r;
+}
+__device__ __forceinline__ void iq4_levels(unsigned q, unsigned &lo, unsigned &hi) {
+    const unsigned s = q & 0x77777777u, s2 = s >> 16;  // selector nibbles: [b0 lo, b0 hi, b1 lo, b1 hi], [b2 lo, b2 hi, b3 lo, b3 hi]
+    const unsigned la = prmt(IQ4_T0, IQ4_T1, s), lb = prmt(IQ4_T0, IQ4_T1, s2);
+    const unsigned ha = prmt(IQ4_T2, IQ4_T3, s), hb = prmt(IQ4_T2, IQ4_T3, s2);
+    const unsigned l_lo = prmt(la, lb, 0x6420u), l_hi = prmt(la, lb, 0x7531u);  // table half 0..7
+    const unsigned h_lo = prmt(ha, hb, 0x6420u), h_hi = prmt(ha, hb, 0x7531u);  // table half 8..15
+    const unsigned m_lo = prmt(q << 4, 0u, 0xBA98u), m_hi = prmt(q, 0u, 0xBA98u);  // 0xFF where bit 3 of the nibble is set
+    lo = l_lo ^ ((l_lo ^ h_lo) & m_lo);
+    hi = l_hi ^ ((l_hi ^ h_hi) & m_hi);
+}
+// one level by index (0..15), for the scalar paths
+__device__ __forceinline__ int iq4_level(unsigned n) {
+    const unsigned x = (n & 8u) ? prmt(IQ4_T2, IQ4_T3, n & 7u) : prmt(IQ4_T0, IQ4_T1, n & 7u);
+    return (int)(signed char)(x & 0xffu);
 }
 
 // last error text (host side, per thread)

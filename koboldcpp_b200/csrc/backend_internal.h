@@ -122,6 +122,8 @@ inline TypeTraits type_traits(int t) {
         case GGML_TYPE_Q5_K: return {256, 176};
         case GGML_TYPE_Q6_K: return {256, 210};
         case GGML_TYPE_Q8_K: return {256, 292};
+        case GGML_TYPE_IQ4_NL: return {32, 18};
+        case GGML_TYPE_IQ4_XS: return {256, 136};
         case GGML_TYPE_I8: return {1, 1};
         case GGML_TYPE_I16: return {1, 2};
         case GGML_TYPE_I32: return {1, 4};

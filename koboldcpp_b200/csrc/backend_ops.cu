@@ -9,7 +9,8 @@ namespace b200 {
 static bool is_hot_weight_type(int t) {
     return t == GGML_TYPE_Q4_0 || t == GGML_TYPE_Q8_0 || t == GGML_TYPE_Q4_K || t == GGML_TYPE_Q5_K || t == GGML_TYPE_Q6_K ||
            t == GGML_TYPE_Q4_1 || t == GGML_TYPE_Q5_0 || t == GGML_TYPE_Q5_1 ||  // (N4: the legacy 32-value formats ...
-           t == GGML_TYPE_Q2_K || t == GGML_TYPE_Q3_K;                            //  ... and the two small K-quants)
+           t == GGML_TYPE_Q2_K || t == GGML_TYPE_Q3_K ||                          //  ... the two small K-quants ...
+           t == GGML_TYPE_IQ4_NL || t == GGML_TYPE_IQ4_XS;                        //  ... and the non-linear 4-bit formats)
 }
 static bool rows_contiguous_f32(const ggml_tensor *t) { return t->type == GGML_TYPE_F32 && t->nb[0] == 4; }
 static bool in_split_buffer(const ggml_tensor *t) { return t->buffer && buft_is_b200_split(t->buffer->buft); }

@@ -188,6 +188,53 @@ template <bool G> struct Dequant64<B200_TYPE_Q4_1, G> : Dequant64Legacy<B200_TYP
 template <bool G> struct Dequant64<B200_TYPE_Q5_0, G> : Dequant64Legacy<B200_TYPE_Q5_0, G> {};
 template <bool G> struct Dequant64<B200_TYPE_Q5_1, G> : Dequant64Legacy<B200_TYPE_Q5_1, G> {};
 
+// IQ4_NL / IQ4_XS (dequantize_row_iq4_nl / iq4_xs, ggml-quants.c:3743-3785): dl * level[nibble], the levels looked up eight at a
+// time with the byte permute unit (iq4_levels, b200_common.cuh).  q(k) must yield byte k of the sub-block's 16 nibble bytes;
+// o16[0..7] receive values 0..15 (low nibbles), o16[8..15] values 16..31 (high nibbles).
+template <int K> __device__ __forceinline__ float s8_f(unsigned x) { return (float)(int)(signed char)((x >> (8 * K)) & 0xffu); }
+template <typename QFn>
+__device__ __forceinline__ void iq4_unpack32(QFn q, float dl, unsigned *o16) {
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        const unsigned w = q(4 * i) | (q(4 * i + 1) << 8) | (q(4 * i + 2) << 16) | (q(4 * i + 3) << 24);
+        unsigned lo, hi;
+        iq4_levels(w, lo, hi);
+        o16[2 * i]         = pack_bf16(dl * s8_f<0>(lo), dl * s8_f<1>(lo));
+        o16[2 * i + 1]     = pack_bf16(dl * s8_f<2>(lo), dl * s8_f<3>(lo));
+        o16[8 + 2 * i]     = pack_bf16(dl * s8_f<0>(hi), dl * s8_f<1>(hi));
+        o16[8 + 2 * i + 1] = pack_bf16(dl * s8_f<2>(hi), dl * s8_f<3>(hi));
+    }
+}
+// 6-bit scale of IQ4_XS sub-block ib, minus 32: nibble ib of scales_l (as one word) | bits 2ib, 2ib+1 of scales_h << 4
+__device__ __forceinline__ float iq4xs_scale(unsigned sl, unsigned sh, int ib) {
+    return (float)((int)(((sl >> (4 * ib)) & 0xFu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32);
+}
+template <bool G>
+struct Dequant64<B200_TYPE_IQ4_NL, G> {
+    static __device__ __forceinline__ void run(const unsigned char *g, int c, unsigned (&o)[32]) {
+        unsigned w[9];
+        ld_words<G, 9>(g + c * 2 * IQ4_NL_BYTES, w);
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const int base = IQ4_NL_BYTES * b;
+            const float d = __half2float(__ushort_as_half((unsigned short)(BYTE_OF(w, base) | (BYTE_OF(w, base + 1) << 8))));
+            iq4_unpack32([&](int k) { return BYTE_OF(w, base + 2 + k); }, d, o + 16 * b);
+        }
+    }
+};
+template <bool G>
+struct Dequant64<B200_TYPE_IQ4_XS, G> {
+    static __device__ __forceinline__ void run(const unsigned char *blk, int c, unsigned (&o)[32]) {
+        unsigned hdr[2], qw[8];
+        ld_words<G, 2>(blk, hdr);
+        ld_words<G, 8>(blk + 8 + 32 * c, qw);
+        const float d = f16lo(hdr[0]);
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+            iq4_unpack32([&](int k) { return BYTE_OF(qw, 16 * b + k); }, d * iq4xs_scale(hdr[1], hdr[0] >> 16, 2 * c + b), o + 16 * b);
+    }
+};
+
 template <bool G>
 struct Dequant64<B200_TYPE_Q8_0, G> {
     static __device__ __forceinline__ void run(const unsigned char *g, int c, unsigned (&o)[32]) {
@@ -514,6 +561,26 @@ struct DequantRLegacy {
 template <int C> struct DequantR<B200_TYPE_Q4_1, C> : DequantRLegacy<B200_TYPE_Q4_1, C> {};
 template <int C> struct DequantR<B200_TYPE_Q5_0, C> : DequantRLegacy<B200_TYPE_Q5_0, C> {};
 template <int C> struct DequantR<B200_TYPE_Q5_1, C> : DequantRLegacy<B200_TYPE_Q5_1, C> {};
+
+template <int C>
+struct DequantR<B200_TYPE_IQ4_NL, C> {
+    static __device__ __forceinline__ void run(const unsigned (&w)[36], unsigned (&o)[32]) {
+#pragma unroll
+        for (int b = 0; b < 2; b++) {
+            const int base = 2 * IQ4_NL_BYTES * C + IQ4_NL_BYTES * b;
+            iq4_unpack32([&](int k) { return BYTE_OF(w, base + 2 + k); }, f16_at(w, base), o + 16 * b);
+        }
+    }
+};
+template <int C>
+struct DequantR<B200_TYPE_IQ4_XS, C> {
+    static __device__ __forceinline__ void run(const unsigned (&w)[34], unsigned (&o)[32]) {
+        const float d = f16lo(w[0]);
+#pragma unroll
+        for (int b = 0; b < 2; b++)
+            iq4_unpack32([&](int k) { return BYTE_OF(w, 8 + 32 * C + 16 * b + k); }, d * iq4xs_scale(w[1], w[0] >> 16, 2 * C + b), o + 16 * b);
+    }
+};
 
 template <int C>
 struct DequantR<B200_TYPE_Q8_0, C> {
@@ -960,7 +1027,8 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
     if (!W || !X || !dst) { set_error("b200_mul_mat_q: NULL argument"); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
-          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K)) {
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K ||
+          type == B200_TYPE_IQ4_NL || type == B200_TYPE_IQ4_XS)) {
         set_error("b200_mul_mat_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -1000,6 +1068,8 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
         case B200_TYPE_Q5_1: return mmq_dispatch_bn<B200_TYPE_Q5_1>(p, st);
         case B200_TYPE_Q2_K: return mmq_dispatch_bn<B200_TYPE_Q2_K>(p, st);
         case B200_TYPE_Q3_K: return mmq_dispatch_bn<B200_TYPE_Q3_K>(p, st);
+        case B200_TYPE_IQ4_NL: return mmq_dispatch_bn<B200_TYPE_IQ4_NL>(p, st);
+        case B200_TYPE_IQ4_XS: return mmq_dispatch_bn<B200_TYPE_IQ4_XS>(p, st);
     }
     return B200_ERR_UNSUPPORTED;
 }
@@ -1017,7 +1087,8 @@ extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, s
                                  size_t workspace_bytes, b200_stream_t stream) {
     if (!as || !ids || !b || !dst) { set_error("b200_mul_mat_id_q: NULL argument"); return B200_ERR_INVALID; }
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
-          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K)) {
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K ||
+          type == B200_TYPE_IQ4_NL || type == B200_TYPE_IQ4_XS)) {
         set_error("b200_mul_mat_id_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -1069,6 +1140,8 @@ extern "C" int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, s
         case B200_TYPE_Q5_1: return mid_dispatch_bn<B200_TYPE_Q5_1>(p, bn, n_rows, (unsigned)max_tiles, st);
         case B200_TYPE_Q2_K: return mid_dispatch_bn<B200_TYPE_Q2_K>(p, bn, n_rows, (unsigned)max_tiles, st);
         case B200_TYPE_Q3_K: return mid_dispatch_bn<B200_TYPE_Q3_K>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_IQ4_NL: return mid_dispatch_bn<B200_TYPE_IQ4_NL>(p, bn, n_rows, (unsigned)max_tiles, st);
+        case B200_TYPE_IQ4_XS: return mid_dispatch_bn<B200_TYPE_IQ4_XS>(p, bn, n_rows, (unsigned)max_tiles, st);
     }
     return B200_ERR_UNSUPPORTED;
 }

@@ -441,7 +441,8 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
     if (!jobs || n_jobs < 1 || n_jobs > B200_GEMV_MAX_JOBS) { set_error("b200_mul_mat_vec_q: n_jobs=%d out of range", n_jobs); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
-          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K)) {
+          type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K ||
+          type == B200_TYPE_IQ4_NL || type == B200_TYPE_IQ4_XS)) {
         set_error("b200_mul_mat_vec_q: unsupported weight type %d", type);
         return B200_ERR_UNSUPPORTED;
     }
@@ -536,6 +537,8 @@ int mmvq_launch(int type, const b200_gemv_job *jobs, int n_jobs, size_t w_row_by
         case B200_TYPE_Q5_1: return dispatch_cols<B200_TYPE_Q5_1>(p, (int)N, st, pdl);
         case B200_TYPE_Q2_K: return dispatch_cols<B200_TYPE_Q2_K>(p, (int)N, st, pdl);
         case B200_TYPE_Q3_K: return dispatch_cols<B200_TYPE_Q3_K>(p, (int)N, st, pdl);
+        case B200_TYPE_IQ4_NL: return dispatch_cols<B200_TYPE_IQ4_NL>(p, (int)N, st, pdl);
+        case B200_TYPE_IQ4_XS: return dispatch_cols<B200_TYPE_IQ4_XS>(p, (int)N, st, pdl);
     }
     return B200_ERR_UNSUPPORTED;
 }

@@ -532,7 +532,10 @@ struct SliceDot<B200_TYPE_Q4_0, NCOLS> {
 // The fifth bit of value j is bit j of qh: four bits are spread to bit 4 of four bytes with one multiply.
 template <int TYPE>
 __device__ __forceinline__ float legacy_block_dot(const unsigned char *bk, const int4 u0, const int4 u1, float d8, float s8) {
-    constexpr bool HAS_M = TYPE != B200_TYPE_Q5_0, HAS_H = TYPE != B200_TYPE_Q4_1;
+    // IQ4_NL (ggml-common.h:406-410) has the layout of q4_0 -- d, 16 bytes of nibbles -- and no offset term: the nibbles go through
+    // the codebook (iq4_levels) and the block is d d8 sum(level u)   (vec_dot_iq4_nl_q8_1, vecdotq.cuh:1086-1105)
+    constexpr bool NL = TYPE == B200_TYPE_IQ4_NL;
+    constexpr bool HAS_M = TYPE != B200_TYPE_Q5_0 && !NL, HAS_H = TYPE != B200_TYPE_Q4_1 && !NL;
     constexpr int NW = 4 + (HAS_M ? 1 : 0) + (HAS_H ? 1 : 0) + 1;  // d (+ m) (+ qh) + 16 bytes of nibbles, as 32-bit words
     unsigned w[NW];
     lds_words<NW>(bk, w);  // (reads up to 2 bytes past the block: the stage carries slack)
@@ -545,6 +548,9 @@ __device__ __forceinline__ float legacy_block_dot(const unsigned char *bk, const
         if constexpr (HAS_H) qh = w[1];
 #pragma unroll
         for (int i = 0; i < 4; i++) q[i] = w[(HAS_H ? 2 : 1) + i];
+    } else if constexpr (NL) {  // d, then qs straddles the words
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[i] = __funnelshift_r(w[i], w[1 + i], 16);
     } else {  // Q5_0: d, then qh and qs straddle the words
         qh = __funnelshift_r(w[0], w[1], 16);
 #pragma unroll
@@ -554,7 +560,13 @@ __device__ __forceinline__ float legacy_block_dot(const unsigned char *bk, const
     int s = 0;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
-        unsigned lo = q[i] & 0x0f0f0f0fu, hi = (q[i] >> 4) & 0x0f0f0f0fu;
+        unsigned lo, hi;
+        if constexpr (NL) {
+            iq4_levels(q[i], lo, hi);
+        } else {
+            lo = q[i] & 0x0f0f0f0fu;
+            hi = (q[i] >> 4) & 0x0f0f0f0fu;
+        }
         if constexpr (HAS_H) {
             lo |= ((((qh >> (4 * i)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
             hi |= ((((qh >> (16 + 4 * i)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;
@@ -562,7 +574,8 @@ __device__ __forceinline__ float legacy_block_dot(const unsigned char *bk, const
         s = dp4a((int)lo, ua[i], s);
         s = dp4a((int)hi, ub[i], s);
     }
-    if constexpr (TYPE == B200_TYPE_Q5_0) return d * (d8 * (float)s - 16.0f * s8);
+    if constexpr (NL) return d * d8 * (float)s;
+    else if constexpr (TYPE == B200_TYPE_Q5_0) return d * (d8 * (float)s - 16.0f * s8);
     else return d * d8 * (float)s + m * s8;
 }
 template <int TYPE, int NCOLS>
@@ -589,6 +602,7 @@ struct LegacySliceDot {
 template <int NCOLS> struct SliceDot<B200_TYPE_Q4_1, NCOLS> : LegacySliceDot<B200_TYPE_Q4_1, NCOLS> {};
 template <int NCOLS> struct SliceDot<B200_TYPE_Q5_0, NCOLS> : LegacySliceDot<B200_TYPE_Q5_0, NCOLS> {};
 template <int NCOLS> struct SliceDot<B200_TYPE_Q5_1, NCOLS> : LegacySliceDot<B200_TYPE_Q5_1, NCOLS> {};
+template <int NCOLS> struct SliceDot<B200_TYPE_IQ4_NL, NCOLS> : LegacySliceDot<B200_TYPE_IQ4_NL, NCOLS> {};
 
 // ---- Q2_K / Q3_K (ggml-common.h:257-280): half a super-block (128 values) per lane.  Value v of the half sits in byte v % 32 of the
 // half's 32 quant bytes at bits 2 (v / 32); its scale is number v / 16 of the half's eight.  The 2-bit fields (and the q3_K high
@@ -599,6 +613,32 @@ template <int TYPE>
 __device__ __forceinline__ float k23_half_dot(const unsigned char *b, int n, const int4 (&u)[8], const float4 d8, const int4 g) {
     constexpr bool Q2 = TYPE == B200_TYPE_Q2_K;
     const float d8v[4] = {d8.x, d8.y, d8.z, d8.w};
+    if constexpr (TYPE == B200_TYPE_IQ4_XS) {
+        // IQ4_XS (ggml-common.h:413-418): half d, u16 scales_h, u8 scales_l[4], then 8 sub-blocks of 16 nibble bytes.  Sub-block ib has
+        // the 6-bit scale ls = nibble ib of scales_l | bits 2ib..2ib+1 of scales_h << 4; the half n holds sub-blocks 4n .. 4n+3:
+        //   d sum_j (ls_j - 32) d8_j sum(level u)      (vec_dot_iq4_xs_q8_1, vecdotq.cuh:1110-1133)
+        unsigned hw[2], qw[16];
+        lds_words<2>(b, hw);
+        lds_words<16>(b + 8 + 64 * n, qw);
+        const float d = h2f((unsigned short)(hw[0] & 0xffff));
+        const unsigned sl = hw[1] >> (16 * n), sh = hw[0] >> (16 + 8 * n);
+        float sd = 0.f;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int ua[4] = {u[2 * j].x, u[2 * j].y, u[2 * j].z, u[2 * j].w}, ub[4] = {u[2 * j + 1].x, u[2 * j + 1].y, u[2 * j + 1].z, u[2 * j + 1].w};
+            int sum = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                unsigned lo, hi;
+                iq4_levels(qw[4 * j + i], lo, hi);
+                sum = dp4a((int)lo, ua[i], sum);
+                sum = dp4a((int)hi, ub[i], sum);
+            }
+            const int ls = (int)(((sl >> (4 * j)) & 0xFu) | (((sh >> (2 * j)) & 3u) << 4)) - 32;
+            sd += d8v[j] * (float)(sum * ls);
+        }
+        return d * sd;
+    }
     const int gv[4] = {g.x, g.y, g.z, g.w};
     unsigned qw[8];
     lds_words<8>(b + (Q2 ? 16 : 32) + 32 * n, qw);
@@ -672,6 +712,7 @@ struct K23SliceDot {
 };
 template <int NCOLS> struct SliceDot<B200_TYPE_Q2_K, NCOLS> : K23SliceDot<B200_TYPE_Q2_K, NCOLS> {};
 template <int NCOLS> struct SliceDot<B200_TYPE_Q3_K, NCOLS> : K23SliceDot<B200_TYPE_Q3_K, NCOLS> {};
+template <int NCOLS> struct SliceDot<B200_TYPE_IQ4_XS, NCOLS> : K23SliceDot<B200_TYPE_IQ4_XS, NCOLS> {};
 
 // ------------------------------------------------------------------------------------------------ row dots on preloaded activations
 // One column (decode), several weight rows per step: the lane's 128 activations of step `it` are loaded into registers ONCE
@@ -903,6 +944,7 @@ struct LegacyRowDot {
 template <> struct RowDot<B200_TYPE_Q4_1> : LegacyRowDot<B200_TYPE_Q4_1> {};
 template <> struct RowDot<B200_TYPE_Q5_0> : LegacyRowDot<B200_TYPE_Q5_0> {};
 template <> struct RowDot<B200_TYPE_Q5_1> : LegacyRowDot<B200_TYPE_Q5_1> {};
+template <> struct RowDot<B200_TYPE_IQ4_NL> : LegacyRowDot<B200_TYPE_IQ4_NL> {};
 
 
 template <int TYPE>
@@ -913,5 +955,6 @@ struct K23RowDot {
 };
 template <> struct RowDot<B200_TYPE_Q2_K> : K23RowDot<B200_TYPE_Q2_K> {};
 template <> struct RowDot<B200_TYPE_Q3_K> : K23RowDot<B200_TYPE_Q3_K> {};
+template <> struct RowDot<B200_TYPE_IQ4_XS> : K23RowDot<B200_TYPE_IQ4_XS> {};
 
 }  // namespace b200

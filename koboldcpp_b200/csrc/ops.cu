@@ -347,6 +347,20 @@ __device__ __forceinline__ float dq_value(int type, const unsigned char *row, in
             const int q = (int)((b[32 + 32 * (v / 128) + v % 32] >> (2 * ((v % 128) / 32))) & 3) - (((b[v % 32] >> (v / 32)) & 1) ? 0 : 4);
             return __fmul_rn(__fmul_rn(h2f(*reinterpret_cast<const unsigned short *>(b + 108)), (float)sc), (float)q);
         }
+        case B200_TYPE_IQ4_NL: {  // dequantize_row_iq4_nl (ggml-quants.c:3743-3760)
+            const unsigned char *b = row + (i / 32) * IQ4_NL_BYTES;
+            const int j = (int)(i % 32);
+            const unsigned q = j < 16 ? (b[2 + j] & 0x0Fu) : (unsigned)(b[2 + j - 16] >> 4);
+            return __fmul_rn(h2f(*reinterpret_cast<const unsigned short *>(b)), (float)iq4_level(q));
+        }
+        case B200_TYPE_IQ4_XS: {  // dequantize_row_iq4_xs (:3762-3785)
+            const unsigned char *b = row + (i / 256) * IQ4_XS_BYTES;
+            const int v = (int)(i % 256), ib = v / 32, j = v % 32;
+            const unsigned sh = (unsigned)b[2] | ((unsigned)b[3] << 8);
+            const int ls = (int)(((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xFu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32;
+            const unsigned q = j < 16 ? (b[8 + 16 * ib + j] & 0x0Fu) : (unsigned)(b[8 + 16 * ib + j - 16] >> 4);
+            return __fmul_rn(__fmul_rn(h2f(*reinterpret_cast<const unsigned short *>(b)), (float)ls), (float)iq4_level(q));
+        }
         case B200_TYPE_Q4_1:
         case B200_TYPE_Q5_0:
         case B200_TYPE_Q5_1: {  // dequantize_row_q4_1 / q5_0 / q5_1 (ggml-quants.c:1543-1615)
@@ -763,7 +777,8 @@ extern "C" int b200_op_get_rows(const b200_tensor *src, const b200_tensor *ids, 
     REQUIRE(ids->type == B200_TYPE_I32 && dst->type == B200_TYPE_F32 && dst->nb[0] == 4, B200_ERR_UNSUPPORTED, "b200_op_get_rows: i32 ids, f32 dst");
     const int t = src->type;
     REQUIRE(t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K ||
-            t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 || t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K,
+            t == B200_TYPE_Q4_1 || t == B200_TYPE_Q5_0 || t == B200_TYPE_Q5_1 || t == B200_TYPE_Q2_K || t == B200_TYPE_Q3_K ||
+            t == B200_TYPE_IQ4_NL || t == B200_TYPE_IQ4_XS,
             B200_ERR_UNSUPPORTED, "b200_op_get_rows: source type %d not supported", t);
     REQUIRE(dst->ne[0] == src->ne[0] && dst->ne[1] == ids->ne[0], B200_ERR_INVALID, "b200_op_get_rows: shape mismatch");
     if (nelements(dst) == 0) return B200_OK;

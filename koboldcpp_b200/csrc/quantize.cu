@@ -81,6 +81,31 @@ __global__ void __launch_bounds__(256) dequantize_kernel(const unsigned char *__
             if constexpr (TYPE == B200_TYPE_Q5_0) o[l] = __fmul_rn((float)(q - 16), d);
             else o[l] = __fadd_rn(__fmul_rn((float)q, d), m);
         }
+    } else if constexpr (TYPE == B200_TYPE_IQ4_NL) {
+        // dequantize_row_iq4_nl (ggml-quants.c:3743-3760): d * level[nibble]; low nibbles are values 0..15, high nibbles 16..31
+        const unsigned char *b = src + (i / QK) * IQ4_NL_BYTES;
+        const float d = ldh(b);
+        const int j = (int)(i % QK);
+#pragma unroll
+        for (int l = 0; l < 4; l++) {
+            const int jj = j + l;
+            const unsigned q = jj < 16 ? (b[2 + jj] & 0x0Fu) : (unsigned)(b[2 + jj - 16] >> 4);
+            o[l] = __fmul_rn(d, (float)iq4_level(q));
+        }
+    } else if constexpr (TYPE == B200_TYPE_IQ4_XS) {
+        // dequantize_row_iq4_xs (ggml-quants.c:3762-3785): (d * (ls - 32)) * level[nibble], ls = 6-bit scale of the 32-value sub-block
+        const unsigned char *b = src + (i / QK_K) * IQ4_XS_BYTES;
+        const int v = (int)(i % QK_K), ib = v / 32, j = v % 32;
+        const unsigned sh = (unsigned)b[2] | ((unsigned)b[3] << 8);
+        const int ls = (int)(((b[4 + ib / 2] >> (4 * (ib % 2))) & 0xFu) | (((sh >> (2 * ib)) & 3u) << 4)) - 32;
+        const float dl = __fmul_rn(ldh(b), (float)ls);
+        const unsigned char *qs = b + 8 + 16 * ib;
+#pragma unroll
+        for (int l = 0; l < 4; l++) {
+            const int jj = j + l;
+            const unsigned q = jj < 16 ? (qs[jj] & 0x0Fu) : (unsigned)(qs[jj - 16] >> 4);
+            o[l] = __fmul_rn(dl, (float)iq4_level(q));
+        }
     } else if constexpr (TYPE == B200_TYPE_Q8_0) {
         const unsigned char *b = src + (i / QK) * Q8_0_BYTES;
         const float d = ldh(b);
@@ -164,6 +189,8 @@ static int launch_dequant(int type, const void *src, T *dst, int64_t n, cudaStre
         case B200_TYPE_Q5_1: dequantize_kernel<B200_TYPE_Q5_1, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q2_K: dequantize_kernel<B200_TYPE_Q2_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q3_K: dequantize_kernel<B200_TYPE_Q3_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_IQ4_NL: dequantize_kernel<B200_TYPE_IQ4_NL, T><<<grid, 256, 0, st>>>(s, dst, n); break;
+        case B200_TYPE_IQ4_XS: dequantize_kernel<B200_TYPE_IQ4_XS, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q4_K: dequantize_kernel<B200_TYPE_Q4_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q5_K: dequantize_kernel<B200_TYPE_Q5_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;
         case B200_TYPE_Q6_K: dequantize_kernel<B200_TYPE_Q6_K, T><<<grid, 256, 0, st>>>(s, dst, n); break;

@@ -12,8 +12,9 @@ LIB_PATH = PKG / "libkcpp_b200.so"
 F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, I32 = 0, 1, 2, 8, 9, 12, 13, 14, 26
 Q4_1, Q5_0, Q5_1 = 3, 6, 7
 Q2_K, Q3_K = 10, 11
-BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), Q8_1: (32, 36), Q2_K: (256, 84), Q3_K: (256, 110), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), I32: (1, 4)}
-TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_K", Q3_K: "q3_K", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", I32: "i32"}
+IQ4_NL, IQ4_XS = 20, 23
+BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), Q8_1: (32, 36), Q2_K: (256, 84), Q3_K: (256, 110), Q4_K: (256, 144), Q5_K: (256, 176), Q6_K: (256, 210), I32: (1, 4), IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
+TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", Q5_1: "q5_1", Q8_0: "q8_0", Q8_1: "q8_1", Q2_K: "q2_K", Q3_K: "q3_K", Q4_K: "q4_K", Q5_K: "q5_K", Q6_K: "q6_K", I32: "i32", IQ4_NL: "iq4_nl", IQ4_XS: "iq4_xs"}
 
 
 def row_size(t: int, ne: int) -> int:

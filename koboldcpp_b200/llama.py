@@ -10,7 +10,7 @@ from dataclasses import dataclass, field
 
 import numpy as np
 
-from .lib import BLOCK, F16, F32, Q2_K, Q3_K, Q4_0, Q4_1, Q4_K, Q5_0, Q5_1, Q5_K, Q6_K, Q8_0, B200Error, check, lib, row_size
+from .lib import BLOCK, F16, F32, IQ4_NL, IQ4_XS, Q2_K, Q3_K, Q4_0, Q4_1, Q4_K, Q5_0, Q5_1, Q5_K, Q6_K, Q8_0, B200Error, check, lib, row_size
 
 
 class LlamaParams(C.Structure):
@@ -99,7 +99,7 @@ def use_more_bits(i: int, n: int) -> bool:
 def tensor_types(s: ModelShape) -> dict[str, int]:
     """GGUF tensor name -> ggml type, the mix llama_tensor_get_type produces (src/llama.cpp:17979-18200)."""
     t: dict[str, int] = {}
-    base = {"Q2_K": Q2_K, "Q3_K": Q3_K, "Q4_0": Q4_0, "Q4_1": Q4_1, "Q5_0": Q5_0, "Q5_1": Q5_1, "Q4_K_M": Q4_K, "Q5_K_M": Q5_K}[s.ftype]
+    base = {"Q2_K": Q2_K, "Q3_K": Q3_K, "Q4_0": Q4_0, "Q4_1": Q4_1, "Q5_0": Q5_0, "Q5_1": Q5_1, "Q4_K_M": Q4_K, "Q5_K_M": Q5_K, "IQ4_NL": IQ4_NL, "IQ4_XS": IQ4_XS}[s.ftype]
     kquant_m = s.ftype in ("Q4_K_M", "Q5_K_M")
     t["token_embd.weight"] = base
     t["output_norm.weight"] = F32
@@ -211,6 +211,10 @@ def random_blocks(rng: np.random.Generator, ty: int, n_rows: int, ne0: int) -> n
         raw[:, :, 82:84] = (d * 1.5).astype(np.float16).view(np.uint8).reshape(n_rows, nb, 2)
     elif ty == Q3_K:  # x = d (sc - 32) q, q in [-4, 3]
         raw[:, :, 108:110] = f16(3e-4, 5e-4, (n_rows, nb))
+    elif ty == IQ4_NL:  # x = d level, levels in [-127, 113]
+        raw[:, :, 0:2] = f16(2.2e-4, 3.8e-4, (n_rows, nb))
+    elif ty == IQ4_XS:  # x = d (ls - 32) level
+        raw[:, :, 0:2] = f16(1.2e-5, 2e-5, (n_rows, nb))
     else:
         raise B200Error(f"random_blocks: unsupported type {ty}")
     return raw.reshape(n_rows, nb * by)

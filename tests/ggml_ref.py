@@ -27,8 +27,8 @@ TYPE_NAMES = {F32: "f32", F16: "f16", Q4_0: "q4_0", Q4_1: "q4_1", Q5_0: "q5_0", 
 # (values per block, bytes per block)  ggml/src/ggml-common.h:144-335
 BLOCK = {F32: (1, 4), F16: (1, 2), Q4_0: (32, 18), Q4_1: (32, 20), Q5_0: (32, 22), Q5_1: (32, 24), Q8_0: (32, 34), Q8_1: (32, 36), Q2_K: (256, 84), Q3_K: (256, 110), Q4_K: (256, 144), Q5_K: (256, 176),
          Q6_K: (256, 210), Q8_K: (256, 292), I32: (1, 4), IQ4_NL: (32, 18), IQ4_XS: (256, 136)}
-WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K)   # what the CUDA path takes
-ORACLE_WEIGHT_TYPES = WEIGHT_TYPES + (IQ4_NL, IQ4_XS)                           # what the oracle restates (golden vectors)
+WEIGHT_TYPES = (Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K, IQ4_NL, IQ4_XS)
+ORACLE_WEIGHT_TYPES = WEIGHT_TYPES  # what the oracle restates (golden vectors); kept apart in case the CUDA path lags behind
 
 
 def act_type(t: int) -> int:

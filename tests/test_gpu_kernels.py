@@ -72,6 +72,10 @@ def random_blocks(t, M, K, rng):
         put_half(80, 0.001, 0.004); put_half(82, 0.001, 0.004)
     elif t == R.Q3_K:
         put_half(108, -0.002, 0.002)
+    elif t == R.IQ4_NL:
+        put_half(0, -0.002, 0.002)
+    elif t == R.IQ4_XS:
+        put_half(0, -0.0001, 0.0001)
     return raw.reshape(M, nb * by)
 
 
@@ -154,7 +158,7 @@ def test_gemv_shapes(H, t, shape):
     check_gemv(H, t, K, M, N, np.random.default_rng(K + M + N + t))
 
 
-@pytest.mark.parametrize("t", (R.Q4_0, R.Q8_0, R.Q4_1, R.Q5_0, R.Q5_1), ids=["q4_0", "q8_0", "q4_1", "q5_0", "q5_1"])
+@pytest.mark.parametrize("t", (R.Q4_0, R.Q8_0, R.Q4_1, R.Q5_0, R.Q5_1, R.IQ4_NL), ids=["q4_0", "q8_0", "q4_1", "q5_0", "q5_1", "iq4_nl"])
 @pytest.mark.parametrize("K", (32, 96, 4096 + 64))
 def test_gemv_ragged_k(H, t, K):
     """Q4_0/Q8_0 rows whose length is not a multiple of the 128-weight slice; odd row byte sizes (2-byte aligned rows)."""

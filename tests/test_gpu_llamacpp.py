@@ -84,9 +84,9 @@ def test_7b_shaped_2_layer_q4_k_m_q8_0_kv_identical_tokens():
     print(f"7B-shaped x2 logits rel L2: worst {worst:.3e} median {med:.3e}")
 
 
-@pytest.mark.parametrize("ftype", ("Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K"))
+@pytest.mark.parametrize("ftype", ("Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K", "IQ4_NL", "IQ4_XS"))
 def test_legacy_quant_types_identical_tokens(ftype):
-    """N4: the 32-value formats Q4_1 / Q5_0 / Q5_1 and the small K-quants Q2_K / Q3_K, every matrix of the type (output.weight Q6_K) through llama_decode: prompt on the tensor-core GEMM,
+    """N4: the 32-value formats Q4_1 / Q5_0 / Q5_1 the small K-quants Q2_K / Q3_K and the non-linear IQ4_NL / IQ4_XS, every matrix of the type (output.weight Q6_K) through llama_decode: prompt on the tensor-core GEMM,
     decode on the GEMV, token embedding rows by GET_ROWS on the CPU as always."""
     model = G.build_fixture("test-dense", layer_gain=1.5, ftype=ftype)
     cpu, gpu, a, b = both(model, 40, 32)

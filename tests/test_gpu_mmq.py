@@ -8,11 +8,11 @@ import pytest
 
 import koboldcpp_b200.host as H
 import orc as O
-from koboldcpp_b200.lib import Q2_K, Q3_K, Q4_0, Q4_1, Q4_K, Q5_0, Q5_1, Q5_K, Q6_K, Q8_0
+from koboldcpp_b200.lib import IQ4_NL, IQ4_XS, Q2_K, Q3_K, Q4_0, Q4_1, Q4_K, Q5_0, Q5_1, Q5_K, Q6_K, Q8_0
 from koboldcpp_b200.llama import random_blocks
 
 pytestmark = pytest.mark.gpu
-TYPES = [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K]
+TYPES = [Q4_0, Q8_0, Q4_K, Q5_K, Q6_K, Q4_1, Q5_0, Q5_1, Q2_K, Q3_K, IQ4_NL, IQ4_XS]
 
 
 def ref64(t, w, x, K, M):

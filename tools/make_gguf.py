@@ -39,7 +39,7 @@ from koboldcpp_b200.llama import SHAPES, ModelShape, random_blocks, tensor_shape
 from koboldcpp_b200.lib import F16, F32, row_size  # noqa: E402
 
 # ggml type id -> gguf enum
-_LLAMA_FTYPE = {"Q2_K": 10, "Q3_K": 12, "Q4_0": 2, "Q4_1": 3, "Q5_0": 8, "Q5_1": 9, "Q4_K_M": 15, "Q5_K_M": 17}  # include/llama.h:150-190 (LLAMA_FTYPE_MOSTLY_*)
+_LLAMA_FTYPE = {"Q2_K": 10, "Q3_K": 12, "Q4_0": 2, "Q4_1": 3, "Q5_0": 8, "Q5_1": 9, "Q4_K_M": 15, "Q5_K_M": 17, "IQ4_NL": 25, "IQ4_XS": 30}  # include/llama.h:150-190 (LLAMA_FTYPE_MOSTLY_*)
 
 Quantizer = Callable[[int, np.ndarray], np.ndarray]  # (ggml type, f32 [rows, ne0]) -> uint8 [rows, row_bytes]
 
