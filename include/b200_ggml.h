@@ -209,7 +209,7 @@ B200_API int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const f
  * ggml/src/ggml-cuda/fattn.cu:298-345, fattn-vec-f16.cuh:8-299, fattn-common.cuh:519-708, fattn-wmma-f16.cuh:13-506
  * layouts (ggml.h:1802-1817): q f32 [D, N, n_head] (strides in bytes), k/v type_k/type_v [D, n_kv, n_head_kv]
  * views into the cache (row stride nb1, head stride nb2, bytes), mask f16 [n_kv, >=N] or NULL (row stride bytes),
- * dst f32 [D, n_head, N] contiguous.  K and V types: F16 or Q8_0.  D in {64, 128}; with an F16 cache also {80, 96, 112, 256}
+ * dst f32 [D, n_head, N] contiguous.  K and V types: F16, Q8_0 or Q4_0 (both the same).  D in {64, 128}; with an F16 cache also {80, 96, 112, 256}
  * (the head sizes of ggml-cuda.cu:3162-3177).  n_head % n_head_kv == 0. */
 typedef struct {
     const void *q, *k, *v, *mask;

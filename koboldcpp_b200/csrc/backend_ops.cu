@@ -61,7 +61,7 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
             const ggml_tensor *k = op->src[1], *v = op->src[2], *m = op->src[3];
             if (!s0 || !k || !v) return false;
             if (s0->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || s0->nb[0] != 4) return false;
-            if (k->type != v->type || (k->type != GGML_TYPE_F16 && k->type != GGML_TYPE_Q8_0)) return false;
+            if (k->type != v->type || (k->type != GGML_TYPE_F16 && k->type != GGML_TYPE_Q8_0 && k->type != GGML_TYPE_Q4_0)) return false;
             {   // head sizes: 64 / 128 with either cache type; 80 / 96 / 112 / 256 with an f16 cache (ggml-cuda.cu:3162-3177)
                 const int64_t D = s0->ne[0];
                 const bool d_more = (D == 80 || D == 96 || D == 112 || D == 256) && k->type == GGML_TYPE_F16;
@@ -97,7 +97,7 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
         case GGML_OP_CPY: case GGML_OP_DUP: case GGML_OP_CONT: {
             if (!s0) return false;
             const int a = s0->type, b = op->type;
-            if (a == GGML_TYPE_F32 && b == GGML_TYPE_Q8_0) return s0->nb[0] == 4 && s0->ne[0] % 32 == 0 && op->ne[0] % 32 == 0 && ((s0->nb[1] | s0->nb[2] | s0->nb[3]) & 15) == 0;
+            if (a == GGML_TYPE_F32 && (b == GGML_TYPE_Q8_0 || b == GGML_TYPE_Q4_0)) return s0->nb[0] == 4 && s0->ne[0] % 32 == 0 && op->ne[0] % 32 == 0 && ((s0->nb[1] | s0->nb[2] | s0->nb[3]) & 15) == 0;
             if ((a == GGML_TYPE_F32 || a == GGML_TYPE_F16) && (b == GGML_TYPE_F32 || b == GGML_TYPE_F16)) return true;
             if (a == GGML_TYPE_I32 && b == GGML_TYPE_I32) return true;
             // ggml_cast of a q8_0 K cache to f32 for the K-shift (src/llama.cpp:10165-10168; reference ggml-cuda.cu:3061)

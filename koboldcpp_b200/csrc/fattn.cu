@@ -446,6 +446,7 @@ static int fa_sm_count() {
 static bool fa_use_mma(const b200_fattn_args *a) {
     static const bool off = getenv("B200_FA_NO_MMA") != nullptr;  // developer switch: the scalar kernel
     if (a->D != 64 && a->D != 128) return true;  // head sizes 80 / 96 / 112 / 256 exist on the tensor-core kernels only
+    if (a->type_k == B200_TYPE_Q4_0) return true;  // a q4_0 cache too (tiles dequantised to f16 in shared memory)
     if (off) return false;
     // q8_0 cache: the tile is dequantised to f16 in shared memory first (~2 instructions per value); that pays as soon as several
     // query columns share it (GQA group, prompt batch): 32/8 heads @ 32k 67 -> 54 us, but one column per kv-head 28 -> 31 us
@@ -684,8 +685,8 @@ static int fa_check(const b200_fattn_args *a) {
         set_error("b200_flash_attn_ext: head size %lld not supported (64, 128; 80, 96, 112, 256 with an f16 cache)", (long long)a->D);
         return B200_ERR_UNSUPPORTED;
     }
-    if (a->type_k != a->type_v || (a->type_k != B200_TYPE_F16 && a->type_k != B200_TYPE_Q8_0)) {
-        set_error("b200_flash_attn_ext: K/V types (%d, %d) not supported (f16/f16, q8_0/q8_0)", a->type_k, a->type_v);
+    if (a->type_k != a->type_v || (a->type_k != B200_TYPE_F16 && a->type_k != B200_TYPE_Q8_0 && a->type_k != B200_TYPE_Q4_0)) {
+        set_error("b200_flash_attn_ext: K/V types (%d, %d) not supported (f16/f16, q8_0/q8_0, q4_0/q4_0)", a->type_k, a->type_v);
         return B200_ERR_UNSUPPORTED;
     }
     if (a->n_head_kv <= 0 || a->n_head % a->n_head_kv || a->N <= 0 || a->n_kv <= 0) { set_error("b200_flash_attn_ext: bad shape"); return B200_ERR_INVALID; }
@@ -775,6 +776,7 @@ extern "C" int b200_flash_attn_ext(const b200_fattn_args *a, void *workspace, si
     if (fa_use_mma(a)) {
         if (((uintptr_t)a->q | a->q_nb1 | a->q_nb2) & 7) { set_error("b200_flash_attn_ext: Q must be 8-byte aligned"); return B200_ERR_UNSUPPORTED; }
         if (a->type_k == B200_TYPE_Q8_0) return a->D == 128 ? fa_launch_mma<B200_TYPE_Q8_0, 128>(p, pl, st, pdl) : fa_launch_mma<B200_TYPE_Q8_0, 64>(p, pl, st, pdl);
+        if (a->type_k == B200_TYPE_Q4_0) return a->D == 128 ? fa_launch_mma<B200_TYPE_Q4_0, 128>(p, pl, st, pdl) : fa_launch_mma<B200_TYPE_Q4_0, 64>(p, pl, st, pdl);
         switch (a->D) {
             case 64: return fa_launch_mma<B200_TYPE_F16, 64>(p, pl, st, pdl);
             case 80: return fa_launch_mma<B200_TYPE_F16, 80>(p, pl, st, pdl);

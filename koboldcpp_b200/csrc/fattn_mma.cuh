@@ -25,13 +25,14 @@ constexpr int FM_MAX_CLUSTER = 16;  // splits merged on chip (cluster sizes abov
 
 template <int TYPE, int D>
 struct MmaGeo {
-    static constexpr bool Q8        = TYPE == B200_TYPE_Q8_0;
+    static constexpr bool Q8        = TYPE == B200_TYPE_Q8_0 || TYPE == B200_TYPE_Q4_0;  // a quantised cache (q8_0 or q4_0 blocks)
+    static constexpr int BLK        = TYPE == B200_TYPE_Q4_0 ? Q4_0_BYTES : Q8_0_BYTES;
     static constexpr int ROW_BYTES  = D * 2;           // f16 tile (what ldmatrix reads)
     static constexpr int ROW_STRIDE = ROW_BYTES + 16;  // ldmatrix: 8 rows x 16 bytes must hit 8 different bank groups
     static constexpr int TILE_BYTES = FM_TP * ROW_STRIDE;
-    // q8_0 cache: the ring holds raw rows (D/32 blocks of 34 bytes, 8- or 4-byte aligned); a warp dequantises the tile it is
+    // q8_0 / q4_0 cache: the ring holds raw rows (D/32 blocks of 34 / 18 bytes, 8- or 4-byte aligned); a warp dequantises the tile it is
     // about to use into ONE f16 tile pair of its own
-    static constexpr int RAW_ROW    = D / 32 * Q8_0_BYTES;
+    static constexpr int RAW_ROW    = D / 32 * BLK;
     static constexpr int RAW_STRIDE = (RAW_ROW + 15) / 16 * 16 + 8;
     static constexpr int RAW_TILE   = (FM_TP * RAW_STRIDE + 16 + 127) / 128 * 128;
     static constexpr int RING_TILE  = Q8 ? RAW_TILE : TILE_BYTES;                                  // one K or V tile in the ring
@@ -108,11 +109,11 @@ __device__ __forceinline__ void mma_load_tile(unsigned char *dst, const unsigned
     }
 }
 
-// q8_0: copy raw rows [row0, row0+16) of one head; rows >= n_kv are zero-filled (d = 0, q = 0: dequantises to zeros)
-template <int D>
+// q8_0 / q4_0: copy raw rows [row0, row0+16) of one head; rows >= n_kv are zero-filled (d = 0: dequantises to zeros)
+template <int TYPE, int D>
 __device__ __forceinline__ void mma_load_tile_q8(unsigned char *dst, const unsigned char *base, size_t nb1, int row0, int n_kv, int lane) {
-    using G = MmaGeo<B200_TYPE_Q8_0, D>;
-    constexpr int CH = G::RAW_ROW % 8 == 0 ? 8 : 4;  // D = 128: 136 = 17 x 8; D = 64: 68 = 17 x 4
+    using G = MmaGeo<TYPE, D>;
+    constexpr int CH = G::RAW_ROW % 8 == 0 ? 8 : 4;  // q8_0: D = 128: 136 = 17 x 8, D = 64: 68 = 17 x 4; q4_0: 72 = 9 x 8, 36 = 9 x 4
     constexpr int CPR = G::RAW_ROW / CH;
     for (int i = lane; i < FM_TP * CPR; i += 32) {
         const int r = i / CPR, c = i - r * CPR;
@@ -134,29 +135,52 @@ __device__ __forceinline__ void i8x4_to_h2x2(unsigned w, __half2 &lo, __half2 &h
     lo = __hsub2(*reinterpret_cast<const __half2 *>(&a), off);
     hi = __hsub2(*reinterpret_cast<const __half2 *>(&b), off);
 }
-// dequantise one raw q8_0 tile (16 rows x D/32 blocks) into an f16 tile: value = fp16(d * q) (one f16 rounding, 2^-11 relative)
-template <int D>
+// four nibble values 0..15 (one per byte of w) -> two half2 holding value - 8 (exact): 0x6400 | n is the half 1024 + n; minus 1032
+__device__ __forceinline__ void u4x4_to_h2x2(unsigned w, __half2 &lo, __half2 &hi) {
+    const unsigned a = __byte_perm(w, 0x64646464u, 0x4140), b = __byte_perm(w, 0x64646464u, 0x4342);
+    const __half2 off = __floats2half2_rn(1032.0f, 1032.0f);
+    lo = __hsub2(*reinterpret_cast<const __half2 *>(&a), off);
+    hi = __hsub2(*reinterpret_cast<const __half2 *>(&b), off);
+}
+// dequantise one raw q8_0 / q4_0 tile (16 rows x D/32 blocks) into an f16 tile: value = fp16(d * q) (one f16 rounding, 2^-11 relative)
+template <int TYPE, int D>
 __device__ __forceinline__ void mma_dequant_tile_q8(unsigned char *dst, const unsigned char *raw, int lane) {
-    using G = MmaGeo<B200_TYPE_Q8_0, D>;
+    using G = MmaGeo<TYPE, D>;
     constexpr int NB = D / 32;
 #pragma unroll
     for (int i = 0; i < FM_TP * NB / 32; i++) {
         const int idx = lane + 32 * i;
         const int r = idx / NB, b = idx - r * NB;
-        const unsigned char *src = raw + r * G::RAW_STRIDE + b * Q8_0_BYTES;  // 2-byte aligned: d, then 32 int8
+        const unsigned char *src = raw + r * G::RAW_STRIDE + b * G::BLK;  // 2-byte aligned: d, then the quants
         const __half dh = *reinterpret_cast<const __half *>(src);
         const __half2 d2 = __half2half2(dh);
-        unsigned w[8];
-        lds_words<8>(src + 2, w);
         uint4 out[4];
+        if constexpr (TYPE == B200_TYPE_Q4_0) {
+            // 16 bytes: low nibbles are values 0..15, high nibbles 16..31 (dequantize_row_q4_0, ggml-quants.c:1523-1541)
+            unsigned w[4];
+            lds_words<4>(src + 2, w);
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-            __half2 lo, hi;
-            i8x4_to_h2x2(w[k], lo, hi);
-            lo = __hmul2(lo, d2);
-            hi = __hmul2(hi, d2);
-            reinterpret_cast<__half2 *>(out)[2 * k] = lo;
-            reinterpret_cast<__half2 *>(out)[2 * k + 1] = hi;
+            for (int k = 0; k < 4; k++) {
+                __half2 lo, hi;
+                u4x4_to_h2x2(w[k] & 0x0f0f0f0fu, lo, hi);
+                reinterpret_cast<__half2 *>(out)[2 * k] = __hmul2(lo, d2);
+                reinterpret_cast<__half2 *>(out)[2 * k + 1] = __hmul2(hi, d2);
+                u4x4_to_h2x2((w[k] >> 4) & 0x0f0f0f0fu, lo, hi);
+                reinterpret_cast<__half2 *>(out)[8 + 2 * k] = __hmul2(lo, d2);
+                reinterpret_cast<__half2 *>(out)[8 + 2 * k + 1] = __hmul2(hi, d2);
+            }
+        } else {
+            unsigned w[8];
+            lds_words<8>(src + 2, w);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                __half2 lo, hi;
+                i8x4_to_h2x2(w[k], lo, hi);
+                lo = __hmul2(lo, d2);
+                hi = __hmul2(hi, d2);
+                reinterpret_cast<__half2 *>(out)[2 * k] = lo;
+                reinterpret_cast<__half2 *>(out)[2 * k + 1] = hi;
+            }
         }
         uint4 *o = reinterpret_cast<uint4 *>(dst + r * G::ROW_STRIDE + b * 64);
         o[0] = out[0]; o[1] = out[1]; o[2] = out[2]; o[3] = out[3];
@@ -349,8 +373,8 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         if (tt < t_hi && !sk) {
             unsigned char *kb = my_tiles + (size_t)ibuf * 2 * G::RING_TILE;
             if constexpr (Q8) {
-                mma_load_tile_q8<D>(kb, kbase, p.k_nb1, tt * FM_TP, p.n_kv, lane);
-                mma_load_tile_q8<D>(kb + G::RING_TILE, vbase, p.v_nb1, tt * FM_TP, p.n_kv, lane);
+                mma_load_tile_q8<TYPE, D>(kb, kbase, p.k_nb1, tt * FM_TP, p.n_kv, lane);
+                mma_load_tile_q8<TYPE, D>(kb + G::RING_TILE, vbase, p.v_nb1, tt * FM_TP, p.n_kv, lane);
             } else {
                 mma_load_tile<D>(kb, kbase, p.k_nb1, tt * FM_TP, p.n_kv, lane);
                 mma_load_tile<D>(kb + G::RING_TILE, vbase, p.v_nb1, tt * FM_TP, p.n_kv, lane);
@@ -419,8 +443,8 @@ __global__ void __launch_bounds__(FM_NW * 32, 2) fattn_mma_kernel(const __grid_c
         unsigned kt, vt;
         if constexpr (Q8) {
             const unsigned char *rk = my_tiles + (size_t)cbuf * 2 * G::RING_TILE;
-            mma_dequant_tile_q8<D>(my_f16, rk, lane);
-            mma_dequant_tile_q8<D>(my_f16 + G::TILE_BYTES, rk + G::RING_TILE, lane);
+            mma_dequant_tile_q8<TYPE, D>(my_f16, rk, lane);
+            mma_dequant_tile_q8<TYPE, D>(my_f16 + G::TILE_BYTES, rk + G::RING_TILE, lane);
             __syncwarp();
             kt = smem_u32(my_f16);
             vt = kt + G::TILE_BYTES;

@@ -298,6 +298,56 @@ __global__ void cpy_f32_q8_0_kernel(TD src, TD dst, int64_t nblocks, char *const
     if (part == 0) *reinterpret_cast<__half *>(out) = __float2half_rn(d);
 }
 
+// f32 -> q4_0 (KV-cache store with a q4_0 cache): 8 lanes per 32-value block; quantize_row_q4_0_ref arithmetic (ggml-quants.c:669-704):
+// d = (the value of largest magnitude, first one on ties) / -8, q = min(15, trunc(x / d + 8.5)); byte j packs values j and j + 16
+__global__ void cpy_f32_q4_0_kernel(TD src, TD dst, int64_t nblocks, char *const *ind) {
+    if (ind) dst.data = *ind;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t blk = t >> 3;
+    const int part = (int)(t & 7);
+    const bool active = blk < nblocks;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    unsigned char *out = nullptr;
+    if (active) {
+        const int64_t e = blk * 32;
+        const int64_t s0 = e % src.ne[0], s1 = (e / src.ne[0]) % src.ne[1], s2 = (e / (src.ne[0] * src.ne[1])) % src.ne[2],
+                      s3 = e / (src.ne[0] * src.ne[1] * src.ne[2]);
+        v = *(const float4 *)(src.data + (s0 + 4 * part) * 4 + s1 * src.nb[1] + s2 * src.nb[2] + s3 * src.nb[3]);
+        const int64_t bpr = dst.ne[0] / 32;
+        const int64_t d0 = blk % bpr, d1 = (blk / bpr) % dst.ne[1], d2 = (blk / (bpr * dst.ne[1])) % dst.ne[2], d3 = blk / (bpr * dst.ne[1] * dst.ne[2]);
+        out = (unsigned char *)(dst.data + d0 * Q4_0_BYTES + d1 * dst.nb[1] + d2 * dst.nb[2] + d3 * dst.nb[3]);
+    }
+    // (|x|, x, index) of the first value of largest magnitude: in the lane, then over the block's 8 lanes
+    const float xs[4] = {v.x, v.y, v.z, v.w};
+    float amax = 0.0f, vmax = 0.0f;
+    int imax = 32;
+#pragma unroll
+    for (int l = 0; l < 4; l++) {
+        if (amax < fabsf(xs[l])) { amax = fabsf(xs[l]); vmax = xs[l]; imax = 4 * part + l; }
+    }
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        const float a2 = __shfl_xor_sync(0xffffffffu, amax, o), v2 = __shfl_xor_sync(0xffffffffu, vmax, o);
+        const int i2 = __shfl_xor_sync(0xffffffffu, imax, o);
+        if (a2 > amax || (a2 == amax && i2 < imax)) { amax = a2; vmax = v2; imax = i2; }
+    }
+    const float d  = __fdiv_rn(vmax, -8.0f);
+    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+    unsigned q = 0;
+#pragma unroll
+    for (int l = 0; l < 4; l++) {
+        const int qi = min(15, __float2int_rz(__fadd_rn(__fmul_rn(xs[l], id), 8.5f)) & 0xff);
+        q |= (unsigned)qi << (8 * l);
+    }
+    const unsigned qhi = __shfl_down_sync(0xffffffffu, q, 4);  // lanes 0..3 of the block take the values 16.. of lanes 4..7
+    if (!active || part >= 4) return;
+    const unsigned w = q | (qhi << 4);
+    unsigned short *o16 = reinterpret_cast<unsigned short *>(out + 2 + 4 * part);  // 18-byte blocks: 2-byte aligned
+    o16[0] = (unsigned short)(w & 0xffff);
+    o16[1] = (unsigned short)(w >> 16);
+    if (part == 0) *reinterpret_cast<__half *>(out) = __float2half_rn(d);
+}
+
 // q8_0 -> f32 (ggml_cast of a quantised K cache before the K-shift RoPE, src/llama.cpp:10165-10168; reference cpy.cu q8_0->f32):
 // one thread per element of the linear element order; dequantize_row_q8_0 arithmetic (d * q, ggml-quants.c:1617-1632)
 __global__ void cpy_q8_0_f32_kernel(TD src, TD dst, int64_t n, char *const *ind) {
@@ -761,6 +811,11 @@ extern "C" int b200_op_cpy_indirect(const b200_tensor *src, const b200_tensor *d
                 B200_ERR_UNSUPPORTED, "b200_op_cpy: f32->q8_0 needs contiguous 16-byte aligned source rows of a multiple of 32 values");
         const int64_t nblk = n / 32;
         cpy_f32_q8_0_kernel<<<grid1d(nblk * 8, 256), 256, 0, st>>>(td(src), td(dst), nblk, ind);
+    } else if (s == B200_TYPE_F32 && d == B200_TYPE_Q4_0) {
+        REQUIRE(src->nb[0] == 4 && src->ne[0] % 32 == 0 && dst->ne[0] % 32 == 0 && dst->nb[0] == Q4_0_BYTES && (((uintptr_t)src->data | src->nb[1] | src->nb[2] | src->nb[3]) & 15) == 0,
+                B200_ERR_UNSUPPORTED, "b200_op_cpy: f32->q4_0 needs contiguous 16-byte aligned source rows of a multiple of 32 values");
+        const int64_t nblk = n / 32;
+        cpy_f32_q4_0_kernel<<<grid1d(nblk * 8, 256), 256, 0, st>>>(td(src), td(dst), nblk, ind);
     } else if (s == B200_TYPE_Q8_0 && d == B200_TYPE_F32) {
         REQUIRE(src->nb[0] == Q8_0_BYTES && src->ne[0] % 32 == 0 && dst->nb[0] == 4 && ((src->nb[1] | src->nb[2] | src->nb[3] | (uintptr_t)src->data) & 1) == 0,
                 B200_ERR_UNSUPPORTED, "b200_op_cpy: q8_0->f32 needs whole 2-byte aligned source blocks");

@@ -885,7 +885,7 @@ static void fa_rows(void *vp, int64_t r0, int64_t r1) {
         const uint8_t *mp = c->mask ? c->mask + iq1 * p->mask_nb1 : NULL;
         const int64_t hk = h / gqa;
         const float *pq = (const float *)(c->q + iq1 * p->q_nb1 + h * p->q_nb2);
-        /* Q -> K's vec_dot_type (:15788): f16 for f16 K, q8_0 for q8_0 K */
+        /* Q -> K's vec_dot_type (:15788): f16 for f16 K, q8_0 for a q8_0 or q4_0 K */
         if (p->type_k == ORC_TYPE_F16) {
             for (int64_t d = 0; d < D; d++) wr16(Qq + 2 * d, orc_fp32_to_fp16(pq[d]));
         } else {
@@ -902,7 +902,7 @@ static void fa_rows(void *vp, int64_t r0, int64_t r1) {
                 for (int64_t d = 0; d < D; d++) acc += (double)(rdh(kr + 2 * d) * rdh(Qq + 2 * d));
                 s = (float)acc;
             } else {
-                s = orc_vec_dot(ORC_TYPE_Q8_0, D, kr, Qq);
+                s = orc_vec_dot(p->type_k, D, kr, Qq); /* q8_0 . q8_0 or q4_0 . q8_0: both have vec_dot_type q8_0 */
             }
             s = s * scale;
             if (p->logit_softcap != 0.0f) s = p->logit_softcap * tanhf(s);
@@ -938,11 +938,11 @@ static void fa_rows(void *vp, int64_t r0, int64_t r1) {
 
 int orc_flash_attn_ext(const orc_fattn_params *p, const void *q, const void *k, const void *v,
                        const void *mask, float *dst, int nthreads) {
-    if (p->type_k != ORC_TYPE_F16 && p->type_k != ORC_TYPE_Q8_0) return -1;
-    if (p->type_v != ORC_TYPE_F16 && p->type_v != ORC_TYPE_Q8_0) return -1;
+    if (p->type_k != ORC_TYPE_F16 && p->type_k != ORC_TYPE_Q8_0 && p->type_k != ORC_TYPE_Q4_0) return -1;
+    if (p->type_v != ORC_TYPE_F16 && p->type_v != ORC_TYPE_Q8_0 && p->type_v != ORC_TYPE_Q4_0) return -1;
     if (p->n_head % p->n_head_kv) return -1;
     /* a q8_0 row is whole blocks of 32; an f16 cache has no block constraint (head sizes 80 and 112 exist) */
-    if ((p->type_k == ORC_TYPE_Q8_0 || p->type_v == ORC_TYPE_Q8_0) && p->D % 32) return -1;
+    if ((p->type_k != ORC_TYPE_F16 || p->type_v != ORC_TYPE_F16) && p->D % 32) return -1;
     fa_ctx c = { p, (const uint8_t *)q, (const uint8_t *)k, (const uint8_t *)v, (const uint8_t *)mask, dst, NULL };
     orc_parallel_for(p->n_head * p->N, nthreads, fa_rows, &c);
     return 0;

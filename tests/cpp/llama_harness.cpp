@@ -99,7 +99,7 @@ int main(int argc, char **argv) {
     cp.n_ubatch = a.n_ubatch;
     if (a.threads > 0) { cp.n_threads = a.threads; cp.n_threads_batch = a.threads; }
     cp.flash_attn = a.fa != 0;
-    cp.type_k = cp.type_v = a.type_kv == "q8_0" ? GGML_TYPE_Q8_0 : GGML_TYPE_F16;
+    cp.type_k = cp.type_v = a.type_kv == "q8_0" ? GGML_TYPE_Q8_0 : a.type_kv == "q4_0" ? GGML_TYPE_Q4_0 : GGML_TYPE_F16;
     cp.offload_kqv = true;
     cp.no_perf = true;
     llama_context *ctx = llama_new_context_with_model(model, cp);

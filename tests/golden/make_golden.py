@@ -74,7 +74,7 @@ def main():
         g[f"mmid_{n}_w"] = w
         g[f"mmid_{n}_out1"] = ref.mul_mat_id(t, w, ids, g["mmid_b1"], Ki, Mi, ne)
         g[f"mmid_{n}_out2"] = ref.mul_mat_id(t, w, ids, g["mmid_b2"], Ki, Mi, ne)
-    # --- (a10-a12) FLASH_ATTN_EXT, f16 and q8_0 KV, GQA, masked tail, decode (N=1) and small prefill (N=5)
+    # --- (a10-a12) FLASH_ATTN_EXT, f16, q8_0 and q4_0 KV, GQA, masked tail, decode (N=1) and small prefill (N=5)
     nh, nhkv, D, nkv = 8, 2, 128, 256
     kf = rng.standard_normal((nhkv, nkv, D)).astype(np.float32)
     vf = rng.standard_normal((nhkv, nkv, D)).astype(np.float32)
@@ -86,7 +86,7 @@ def main():
         for i in range(N):
             mask[i, 200 - (N - 1 - i) * 7:] = -np.inf
         g[f"fa_q_N{N}"], g[f"fa_mask_N{N}"] = q, mask
-        for tkv in (R.F16, R.Q8_0):
+        for tkv in (R.F16, R.Q8_0, R.Q4_0):
             k = O.pack_kv(tkv, kf) if tkv == R.F16 else ref.quantize(tkv, kf.reshape(-1, D)).reshape(nhkv, nkv, -1)
             v = O.pack_kv(tkv, vf) if tkv == R.F16 else ref.quantize(tkv, vf.reshape(-1, D)).reshape(nhkv, nkv, -1)
             g[f"fa_k_{R.TYPE_NAMES[tkv]}"], g[f"fa_v_{R.TYPE_NAMES[tkv]}"] = k, v

@@ -9,7 +9,7 @@ import pytest
 
 import koboldcpp_b200.host as H
 import orc as O
-from koboldcpp_b200.lib import F16, F32, Q4_K, Q6_K, Q8_0, GemvFuse, GemvJob, RopeParams, Tensor, check, lib, row_size
+from koboldcpp_b200.lib import F16, F32, Q4_0, Q4_K, Q6_K, Q8_0, GemvFuse, GemvJob, RopeParams, Tensor, check, lib, row_size
 from koboldcpp_b200.llama import random_blocks
 
 pytestmark = pytest.mark.gpu
@@ -197,6 +197,25 @@ def test_rope_f16_in_place_k_shift(neox):
     d32, o32 = dev(k32), H.DeviceBuffer(k32.nbytes + 256, zero=True)
     check(L.b200_op_rope(Tensor.contiguous(d32.ptr, F32, (D, HK, T)), dpos.ptr, None, Tensor.contiguous(o32.ptr, F32, (D, HK, T)), C.byref(rp), None))
     exp = o32.to_numpy(np.float32, k32.shape).astype(np.float16)
+    assert np.array_equal(got, exp)
+
+
+def test_cpy_f32_to_q4_0_is_the_reference_quantiser():
+    """KV-cache store with a q4_0 cache (ggml_cpy f32 -> q4_0, src/llama.cpp:9146-9172): bit-exact quantize_row_q4_0_ref, including
+    the tie rule (the first value of largest magnitude sets the sign of d) and an all-zero block."""
+    L = lib()
+    D, HK, T = 128, 4, 19
+    rng = np.random.default_rng(9)
+    x = rng.standard_normal((T, HK * D)).astype(np.float32)
+    x[0, :32] = 0.0                       # d = 0
+    x[1, 5] = 3.0; x[1, 20] = -3.0        # tie in magnitude: the first one wins
+    x[2, 40] = -2.5; x[2, 33] = 2.5
+    dx, out = dev(x), H.DeviceBuffer(T * HK * D // 32 * 18 + 256, zero=True)
+    src = Tensor.contiguous(dx.ptr, F32, (D, HK, T))
+    dst = Tensor.contiguous(out.ptr, Q4_0, (D, HK, T))
+    check(L.b200_op_cpy(src, dst, None))
+    got = out.to_numpy(np.uint8, (T, HK * D // 32 * 18))
+    exp = np.asarray(O.quantize_rows(Q4_0, x)).view(np.uint8).reshape(T, -1)
     assert np.array_equal(got, exp)
 
 

@@ -44,7 +44,7 @@ def both(model, n_prompt, n_gen, **opts):
         # the reference's own spread: the same run with the other attention path (flash attention toggled)
         o2 = dict(opts)
         o2["fa"] = 0 if int(opts.get("fa", 1)) else 1
-        if o2.get("type_kv") == "q8_0" and o2["fa"] == 0:
+        if o2.get("type_kv") in ("q8_0", "q4_0") and o2["fa"] == 0:
             o2.pop("type_kv")  # a quantised V cache needs flash attention (src/llama.cpp:19447-19450): compare against f16 KV instead
         LC.run(model, "cpu", n_prompt=n_prompt, n_gen=n_gen, exe=LC.harness_path(), logits_out=lc, threads=min(32, os.cpu_count() or 8), **o2)
         a2 = np.fromfile(lc, dtype=np.float32).reshape(-1, nv)
@@ -82,6 +82,14 @@ def test_7b_shaped_2_layer_q4_k_m_q8_0_kv_identical_tokens():
     cpu, gpu, a, b = both(model, 128, 128, type_kv="q8_0")
     worst, med = check_parity(cpu, gpu, a, b, min_margin_sigma=1.0)
     print(f"7B-shaped x2 logits rel L2: worst {worst:.3e} median {med:.3e}")
+
+
+def test_q4_0_kv_cache_identical_tokens():
+    """N4: a q4_0 KV cache (koboldcpp's quantkv = 2): K and V rows stored by CPY f32 -> q4_0 (bit-exact quantize_row_q4_0_ref), attention
+    over q4_0 tiles on the tensor-core kernel, prompt and decode."""
+    model = G.build_fixture("test-dense", layer_gain=1.5)
+    cpu, gpu, a, b = both(model, 40, 32, type_kv="q4_0")
+    check_parity(cpu, gpu, a, b, min_margin_sigma=0.5)
 
 
 @pytest.mark.parametrize("ftype", ("Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K", "IQ4_NL", "IQ4_XS"))

@@ -82,7 +82,7 @@ def test_mul_mat_id_rejects_bad_expert(golden):
 
 
 @pytest.mark.parametrize("N", (1, 5))
-@pytest.mark.parametrize("tkv", (R.F16, R.Q8_0), ids=["f16", "q8_0"])
+@pytest.mark.parametrize("tkv", (R.F16, R.Q8_0, R.Q4_0), ids=["f16", "q8_0", "q4_0"])
 def test_flash_attn_golden(golden, tkv, N):
     q, mask = golden[f"fa_q_N{N}"], golden[f"fa_mask_N{N}"]
     k, v = golden[f"fa_k_{NAME[tkv]}"], golden[f"fa_v_{NAME[tkv]}"]
@@ -143,7 +143,7 @@ def test_oracle_vs_reference_fresh_data(t, variant):
 
 
 @needs_ref
-@pytest.mark.parametrize("tkv", (R.F16, R.Q8_0), ids=["f16", "q8_0"])
+@pytest.mark.parametrize("tkv", (R.F16, R.Q8_0, R.Q4_0), ids=["f16", "q8_0", "q4_0"])
 def test_oracle_flash_attn_vs_reference_fresh_data(tkv):
     ref = R.load("scalar")
     rng = np.random.default_rng(7)
