@@ -25,6 +25,19 @@ static bool mul_mat_q_ok(const ggml_tensor *w, const ggml_tensor *x, const ggml_
     return w->ne[0] == x->ne[0] && dst->ne[0] == w->ne[1] && dst->ne[1] == x->ne[1];
 }
 
+// The 3-D / 4-D broadcast form (ggml.c:12486-12560; the reference loops i02 / i03 in ggml_cuda_op_mul_mat, ggml-cuda.cu:1358-1658):
+// dst[:, :, i12, i13] = w[:, :, i12 / r2, i13 / r3] . x[:, :, i12, i13].  Every (i12, i13) slice must itself satisfy mul_mat_q_ok.
+static bool mul_mat_q_bcast_ok(const ggml_tensor *w, const ggml_tensor *x, const ggml_tensor *dst) {
+    if (!is_hot_weight_type(w->type) || x->type != GGML_TYPE_F32 || dst->type != GGML_TYPE_F32 || in_split_buffer(w)) return false;
+    if (w->ne[2] < 1 || w->ne[3] < 1 || x->ne[2] % w->ne[2] || x->ne[3] % w->ne[3]) return false;
+    if (dst->ne[2] != x->ne[2] || dst->ne[3] != x->ne[3] || x->ne[2] * x->ne[3] > 4096) return false;
+    if (x->nb[0] != 4 || dst->nb[0] != 4 || ((x->nb[1] | x->nb[2] | x->nb[3]) & 15) || ((dst->nb[1] | dst->nb[2] | dst->nb[3]) & 3)) return false;
+    if (w->nb[0] != (size_t)type_traits(w->type).size || w->nb[1] < row_size(w->type, w->ne[0])) return false;
+    const size_t wal = (w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q5_K) ? 15 : 1;  // slices keep the row alignment of the 2-D case
+    if ((w->nb[1] | w->nb[2] | w->nb[3]) & wal) return false;
+    return w->ne[0] == x->ne[0] && dst->ne[0] == w->ne[1] && dst->ne[1] == x->ne[1];
+}
+
 bool op_supported(int /*device*/, const ggml_tensor *op) {
     const ggml_tensor *s0 = op->src[0], *s1 = op->src[1];
     for (int i = 0; i < GGML_MAX_SRC; i++) {
@@ -42,7 +55,7 @@ bool op_supported(int /*device*/, const ggml_tensor *op) {
             return false;
         case GGML_OP_MUL_MAT:
             if (!s0 || !s1) return false;
-            if (is_quantized(s0->type)) return mul_mat_q_ok(s0, s1, op);
+            if (is_quantized(s0->type)) return mul_mat_q_ok(s0, s1, op) || mul_mat_q_bcast_ok(s0, s1, op);
             return (s0->type == GGML_TYPE_F32 || s0->type == GGML_TYPE_F16) && s1->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 &&
                    s0->nb[0] == (size_t)type_traits(s0->type).size && s1->nb[0] == 4 && !in_split_buffer(s0);
         case GGML_OP_MUL_MAT_ID: {
@@ -223,6 +236,20 @@ static void run_mul_mat(ExecCtx &x, const ggml_tensor *n) {
     }
     const int64_t K = w->ne[0], M = w->ne[1], N = a->ne[1];
     const int64_t xs = (int64_t)(a->nb[1] / 4), ds = (int64_t)(n->nb[1] / 4);
+    if (a->ne[2] != 1 || a->ne[3] != 1 || w->ne[2] != 1 || w->ne[3] != 1) {
+        // broadcast over dims 2 and 3: one GEMM / GEMV per (i12, i13) slice, the weight slice shared by r2 x r3 of them
+        const int64_t r2 = a->ne[2] / w->ne[2], r3 = a->ne[3] / w->ne[3];
+        const size_t wsb = N > 8 ? b200_mul_mat_q_workspace_bytes(w->type, K, M, N) : 0;
+        for (int64_t i13 = 0; i13 < a->ne[3]; i13++) {
+            for (int64_t i12 = 0; i12 < a->ne[2]; i12++) {
+                const char *ws = (const char *)w->data + (i12 / r2) * w->nb[2] + (i13 / r3) * w->nb[3];
+                const float *xp = (const float *)((const char *)a->data + i12 * a->nb[2] + i13 * a->nb[3]);
+                float *dp = (float *)((char *)n->data + i12 * n->nb[2] + i13 * n->nb[3]);
+                gemm_slice(w->type, ws, w->nb[1], xp, xs, dp, ds, K, M, N, wsb <= x.scratch_bytes ? x.scratch : nullptr, x.scratch_bytes, x.stream, x.launches);
+            }
+        }
+        return;
+    }
     // N <= 8: the HBM-bound GEMV.  Larger batches: tensor-core GEMM when built, else the GEMV over column groups of 8
     // (every group re-streams the weights; correct, and only the stop-gap for prefill until b200_mul_mat_q lands)
     if (N > 8) {

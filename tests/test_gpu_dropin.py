@@ -202,3 +202,58 @@ def test_whole_graph_under_ggml_alloc_matches_cpu(T):
         L.ggml_free(ctx)
         L.ggml_free(cctx)
         L.ggml_backend_free(be)
+
+
+@pytest.mark.parametrize("wt,N", [(G.Q4_K, 1), (G.Q6_K, 3), (G.Q8_0, 20), (G.Q4_0, 5)])
+def test_broadcast_mul_mat_with_quantised_weights(wt, N):
+    """3-D / 4-D MUL_MAT with quantised weights (ggml.c:12486-12560; the reference loops i02 / i03 in ggml-cuda.cu:1358-1658):
+    weights [K, M, 2, 1], activations [K, N, 4, 3] -- every weight slice serves r2 x r3 = 2 x 3 activation slices.  Evaluated on the
+    B200 backend and on the reference CPU backend by ggml_backend_compare_graph_backend."""
+    if not G.available("portable"):
+        pytest.skip("oracle/_ref not built")
+    R, L = bind()
+    L.ggml_new_tensor_4d.restype = TP
+    B = b200lib()
+    B.ggml_backend_b200_init.restype = P
+    B.ggml_backend_b200_init.argtypes = [I]
+    be = B.ggml_backend_b200_init(0)
+    cpu = L.ggml_backend_cpu_init()
+    ctx = L.ggml_init(G.InitParams(16 << 20, None, True))
+    try:
+        rng = np.random.default_rng(3 + N)
+        K, M = 512, 96
+        w = L.ggml_new_tensor_4d(ctx, wt, K, M, 2, 1)
+        x = L.ggml_new_tensor_4d(ctx, G.F32, K, N, 4, 3)
+        out = L.ggml_mul_mat(ctx, w, x)
+        gf = L.ggml_new_graph(ctx)
+        L.ggml_build_forward_expand(gf, out)
+        buf = L.ggml_backend_alloc_ctx_tensors(ctx, be)
+        assert buf
+        wd = random_blocks(rng, wt, 2 * M, K)
+        xd = rng.standard_normal((3, 4, N, K)).astype(np.float32)
+        L.ggml_backend_tensor_set(w, wd.ctypes.data, 0, wd.nbytes)
+        L.ggml_backend_tensor_set(x, xd.ctypes.data, 0, xd.nbytes)
+        seen = []
+
+        def cb(i, t1, t2, _):
+            assert L.ggml_backend_supports_op(be, t1), "the broadcast MUL_MAT would fall back to the CPU"
+            a, b = fetch(L, t1), fetch(L, t2)
+            seen.append(float(((a - b) ** 2).sum() / max((b ** 2).sum(), 1e-30)))
+            return True
+        cbf = EVAL_CB(cb)
+        assert L.ggml_backend_compare_graph_backend(be, cpu, gf, cbf, None)
+        assert len(seen) == 1 and seen[0] < 2e-3, seen
+        # and against fp64 on the dequantised weights: slice (i12, i13) uses weight slice i12 // 2
+        got = np.empty((3, 4, N, M), dtype=np.float32)
+        L.ggml_backend_graph_compute(be, gf)
+        L.ggml_backend_tensor_get(out, got.ctypes.data, 0, got.nbytes)
+        wf = np.stack([R.dequantize(wt, r, K) for r in wd]).astype(np.float64).reshape(2, M, K)
+        for i13 in range(3):
+            for i12 in range(4):
+                exp = xd[i13, i12].astype(np.float64) @ wf[i12 // 2].T
+                assert np.linalg.norm(got[i13, i12] - exp) <= 2e-2 * np.linalg.norm(exp)
+        L.ggml_backend_buffer_free(buf)
+    finally:
+        L.ggml_free(ctx)
+        L.ggml_backend_free(cpu)
+        L.ggml_backend_free(be)
