@@ -156,11 +156,28 @@ static bool same_op_params(const ggml_tensor *a, const ggml_tensor *b) { return 
 //   * a member moved LATER (pos < at): no outside node in (pos, at] reads or writes its output, or writes one of its inputs;
 //   * a member moved EARLIER (pos > at): its inputs exist at `at` (checked by the caller), and no outside node in [at, pos)
 //     reads or writes its output bytes.
-static bool can_gather(const GraphInfo &gi, const std::vector<int> &members, int at, const std::vector<char> &done) {
+//   * `done` nodes were absorbed by an earlier step and normally ran at or before that step's position -- except the members of a
+//     deferred step (ROPE + KV store, emitted at its LAST member): exec_pos[i] != i says where node i really runs.  A member whose
+//     order against such a node changes is checked against it like against any outside node.
+static bool can_gather(const GraphInfo &gi, const std::vector<int> &members, int at, const std::vector<char> &done, const std::vector<int> &exec_pos) {
     auto is_member = [&](int i) { for (int m : members) if (m == i) return true; return false; };
     for (int m : members) {
         const ggml_tensor *t = gi.cg->nodes[m];
         const size_t len = nbytes(t);
+        for (int i = 0; i < (int)exec_pos.size(); i++) {
+            const int e = exec_pos[i];
+            if (e == i || is_member(i) || is_member(e)) continue;
+            if ((i < m) == (e < at)) continue;  // same order as in the graph
+            const ggml_tensor *o = gi.cg->nodes[i];
+            if (is_view_op(o->op)) continue;
+            if (node_touches(o, t->data, len)) return false;
+            if (o->data) {
+                for (int k = 0; k < GGML_MAX_SRC; k++) {
+                    const ggml_tensor *sk = t->src[k];
+                    if (sk && sk->data && ranges_overlap(o->data, nbytes(o), sk->data, nbytes(sk))) return false;
+                }
+            }
+        }
         const int lo = m < at ? m + 1 : at, hi = m < at ? at : m - 1;
         for (int i = lo; i <= hi; i++) {
             if (is_member(i) || (done[i] && i != at)) continue;
@@ -299,6 +316,8 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
     std::unordered_map<const ggml_tensor *, const ggml_tensor *> norm_mul_of;  // activation tensor (MUL node) -> its RMS_NORM node
     std::unordered_map<const ggml_tensor *, const ggml_tensor *> add_of;       // MUL_MAT node -> the ADD node folded into it
     std::unordered_map<int, Step> deferred;                                    // position -> step to emit there
+    std::vector<int> exec_pos((size_t)n);                                      // where node i runs: i, or the position of its deferred step
+    for (int i = 0; i < n; i++) exec_pos[(size_t)i] = i;
     std::unordered_set<const ggml_tensor *> norm_stored;                       // folded activations whose values a GEMV step already stores
 
     for (int i = 0; i < n; i++) {
@@ -350,7 +369,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
         // R5: the MoE router chain -> one launch at the position of its SOFT_MAX (the weight nodes move up past the expert matmuls)
         if (a->op == GGML_OP_SOFT_MAX) {
             int m5[5];
-            if (match_moe_router(gi, i, done, m5) && can_gather(gi, std::vector<int>(m5, m5 + 5), i, done)) {
+            if (match_moe_router(gi, i, done, m5) && can_gather(gi, std::vector<int>(m5, m5 + 5), i, done, exec_pos)) {
                 s.kind = STEP_MOE_ROUTER;
                 s.group = {cg->nodes[m5[1]], cg->nodes[m5[2]], cg->nodes[m5[3]], cg->nodes[m5[4]]};
                 for (int q = 1; q < 5; q++) done[m5[q]] = 1;
@@ -369,7 +388,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                 if (r && r != a && r->type == GGML_TYPE_F32 && same_shape(r, a) && same_shape(d, a) && is_contiguous(r) && is_contiguous(d) &&
                     (((uintptr_t)r->data | (uintptr_t)d->data) & 15) == 0 && pr < i && pd > i && !done[pd]) {
                     std::vector<int> mem = {i, pd};
-                    if (can_gather(gi, mem, i, done)) {
+                    if (can_gather(gi, mem, i, done, exec_pos)) {
                         s.kind = STEP_AR_ADD; s.n2 = d; done[pd] = 1;
                         steps.push_back(s);
                         continue;
@@ -382,12 +401,12 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             int m[4];
             if (match_rope_kv(gi, i, done, m)) {
                 std::vector<int> members(m, m + 4);
-                if (can_gather(gi, members, m[3], done)) {
+                if (can_gather(gi, members, m[3], done, exec_pos)) {
                     Step f;
                     f.kind = STEP_ROPE_KV; f.n = a; f.n2 = cg->nodes[m[1]];
                     f.group = {cg->nodes[m[2]], cg->nodes[m[3]]};
                     f.slot = slot_of[(size_t)m[2]]; f.slot2 = slot_of[(size_t)m[3]];
-                    for (int q = 0; q < 4; q++) done[m[q]] = 1;
+                    for (int q = 0; q < 4; q++) { done[m[q]] = 1; exec_pos[(size_t)m[q]] = m[3]; }
                     deferred[m[3]] = f;
                     continue;
                 }
@@ -416,7 +435,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                     if (!ok) continue;
                 } else if (b->src[0]->nb[1] != a->src[0]->nb[1]) continue;
                 std::vector<int> mem = {i, j2};
-                if (!can_gather(gi, mem, i, done)) continue;
+                if (!can_gather(gi, mem, i, done, exec_pos)) continue;
                 s.group.push_back(b);
                 done[j2] = 1;
             }
@@ -431,7 +450,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                 if (pr >= i || pd < 0 || done[pd]) continue;  // r must exist before the GEMV runs (leafs have pos -1)
                 std::vector<int> mem = {pm, pd};
                 if (pm != i) mem = {pd};  // a hoisted sibling: only the ADD moves (up to i)
-                if (!can_gather(gi, mem, i, done)) continue;
+                if (!can_gather(gi, mem, i, done, exec_pos)) continue;
                 add_of[mm] = d;
                 done[pd] = 1;
             }
@@ -452,7 +471,7 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
                     // the two matmuls are part of the fused kernel: ggml-alloc usually computes SILU in place over the gate result
                     std::vector<int> mem = {gi.pos(gt), gi.pos(up), ps, pm};
                     std::sort(mem.begin(), mem.end());
-                    if (!can_gather(gi, mem, i, done)) continue;
+                    if (!can_gather(gi, mem, i, done, exec_pos)) continue;
                     s.silu_mul = mn;
                     s.gate_idx = gi_;
                     done[ps] = 1;

@@ -144,7 +144,7 @@ struct SplitPeer {
     void *ws = nullptr; size_t ws_bytes = 0;
 };
 static SplitPeer g_peer[GGML_B200_MAX_DEVICES];
-static cudaEvent_t g_split_in = nullptr;
+static cudaEvent_t g_split_in_dev[64] = {};  // per main device: an event must be recorded on a stream of the device it was created on
 static bool g_peer_enabled[GGML_B200_MAX_DEVICES][GGML_B200_MAX_DEVICES];
 
 static void peer_prepare(int main_dev, int d, size_t xb, size_t yb, size_t wsb) {
@@ -197,7 +197,9 @@ static void run_mul_mat_split(ExecCtx &x, const ggml_tensor *n) {
     const int64_t K = w->ne[0], N = a->ne[1];
     const int64_t xs = (int64_t)(a->nb[1] / 4), ds = (int64_t)(n->nb[1] / 4);
     const size_t wrb = row_size(w->type, K);
-    if (!g_split_in) B200_CHECK_CUDA(cudaEventCreateWithFlags(&g_split_in, cudaEventDisableTiming));
+    if (x.device < 0 || x.device >= 64) backend_abort("run_mul_mat_split", "device ordinal out of range");
+    cudaEvent_t &g_split_in = g_split_in_dev[x.device];
+    if (!g_split_in) B200_CHECK_CUDA(cudaEventCreateWithFlags(&g_split_in, cudaEventDisableTiming));  // (the main device is current here)
     B200_CHECK_CUDA(cudaEventRecord(g_split_in, x.stream));  // activations are ready on the main device
     const size_t wsb_main = N > 8 ? b200_mul_mat_q_workspace_bytes(w->type, K, 1, N) : 0;
     for (int d = 0; d < sc->n_dev; d++) {

@@ -315,8 +315,8 @@ extern "C" int b200_llama_new(const b200_llama_params *p, b200_llama **out) {
     LL_REQUIRE(p->n_embd > 0 && p->n_layer > 0 && p->n_head > 0 && p->n_head_kv > 0 && p->n_head % p->n_head_kv == 0 && p->n_vocab > 0 && p->n_ctx > 0,
                B200_ERR_INVALID, "b200_llama_new: bad hyper-parameters");
     LL_REQUIRE(p->n_ctx % KV_PAD == 0, B200_ERR_INVALID, "b200_llama_new: n_ctx must be a multiple of %d (flash-attention KV padding)", KV_PAD);
-    LL_REQUIRE((p->type_k == B200_TYPE_F16 || p->type_k == B200_TYPE_Q8_0) && p->type_v == p->type_k, B200_ERR_UNSUPPORTED,
-               "b200_llama_new: KV cache types must be f16/f16 or q8_0/q8_0");
+    LL_REQUIRE((p->type_k == B200_TYPE_F16 || p->type_k == B200_TYPE_Q8_0 || p->type_k == B200_TYPE_Q4_0) && p->type_v == p->type_k, B200_ERR_UNSUPPORTED,
+               "b200_llama_new: KV cache types must be f16/f16, q8_0/q8_0 or q4_0/q4_0");
     LL_REQUIRE(ggml_backend_b200_get_device_count() > 0, B200_ERR_CUDA, "b200_llama_new: no CUDA device (there is no CPU fallback)");
     if (p->tp_world > 1) {
         LL_REQUIRE(p->tp_rank >= 0 && p->tp_rank < p->tp_world && b200_comm_world() == p->tp_world && b200_comm_rank() == p->tp_rank, B200_ERR_INVALID,
@@ -757,13 +757,22 @@ int enqueue_decode(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32
 
 }  // namespace
 
+// Tensor parallel: an all-reduce whose peer never arrived gives up after its timeout and flags the window (comm.cu); the sums of
+// that step are stale, so the step must not be reported as done.  One 4-byte read per synchronised step, tensor-parallel runs only.
+static int peer_check(b200_llama *m) {
+    if (m->hp.tp_world <= 1) return B200_OK;
+    const int st = b200_comm_peer_status();
+    LL_REQUIRE(st == 0, B200_ERR_CUDA, "b200_llama: a tensor-parallel peer did not arrive in time (peer status %d): the step's results are invalid", st);
+    return B200_OK;
+}
+
 extern "C" int b200_llama_decode_async(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32_t n_past, float *logits, int32_t logits_all) {
     return enqueue_decode(m, tokens, n_tokens, n_past, logits, logits_all);
 }
 extern "C" int b200_llama_synchronize(b200_llama *m) {
     LL_REQUIRE(m && m->be, B200_ERR_INVALID, "b200_llama_synchronize: NULL model");
     m->be->iface.synchronize(m->be);
-    return B200_OK;
+    return peer_check(m);
 }
 extern "C" int b200_llama_decode(b200_llama *m, const int32_t *tokens, int32_t n_tokens, int32_t n_past, float *logits, int32_t logits_all) {
     const int rc = enqueue_decode(m, tokens, n_tokens, n_past, logits, logits_all);
@@ -771,7 +780,7 @@ extern "C" int b200_llama_decode(b200_llama *m, const int32_t *tokens, int32_t n
     const auto ts0 = std::chrono::steady_clock::now();
     m->be->iface.synchronize(m->be);
     m->t_sync += std::chrono::duration<double>(std::chrono::steady_clock::now() - ts0).count();
-    return B200_OK;
+    return peer_check(m);
 }
 extern "C" int b200_llama_replay(b200_llama *m) {
     LL_REQUIRE(m && m->finalized && m->graph.n_nodes > 0, B200_ERR_INVALID, "b200_llama_replay: nothing decoded yet");

@@ -299,6 +299,8 @@ class LlamaModel:
         x = rng.standard_normal((n_cells, width), dtype=np.float32)
         if self.type_kv == F16:
             rows = x.astype(np.float16).view(np.uint8).reshape(n_cells, -1)
+        elif self.type_kv != Q8_0:
+            raise B200Error("fill_kv: f16 and q8_0 caches only")
         else:
             xb = x.reshape(n_cells, width // 32, 32)
             amax = np.abs(xb).max(axis=2)

@@ -29,12 +29,12 @@ class RefModel:
         self.type_kv = type_kv
 
     def _store(self, x: np.ndarray) -> np.ndarray:
-        """What a cache row holds after the CPY node: f16 rounding, or q8_0 round trip (quantize_row_q8_0_ref)."""
+        """What a cache row holds after the CPY node: f16 rounding, or the q8_0 / q4_0 round trip (quantize_row_q8_0_ref / q4_0_ref)."""
         if self.type_kv == F16:
             return x.astype(np.float32).astype(np.float16).astype(np.float64)
         rows = x.astype(np.float32)
-        packed = O.quantize_rows(Q8_0, rows)
-        return O.dequantize(Q8_0, packed.reshape(-1), rows.size).reshape(rows.shape).astype(np.float64)
+        packed = O.quantize_rows(self.type_kv, rows)  # q8_0 or q4_0 blocks
+        return O.dequantize(self.type_kv, packed.reshape(-1), rows.size).reshape(rows.shape).astype(np.float64)
 
     def _rms(self, x: np.ndarray, w: np.ndarray) -> np.ndarray:
         return x / np.sqrt((x * x).mean(axis=-1, keepdims=True) + self.s.rms_eps) * w

@@ -7,7 +7,7 @@ from __future__ import annotations
 import numpy as np
 import pytest
 
-from koboldcpp_b200.lib import F16, F32, Q8_0
+from koboldcpp_b200.lib import F16, F32, Q4_0, Q8_0
 from koboldcpp_b200.llama import SHAPES, LlamaModel, _l, random_blocks, tensor_shape, tensor_types
 
 pytestmark = pytest.mark.gpu
@@ -38,7 +38,7 @@ def rel_rms(a, b):
     return float(np.sqrt(((a - b) ** 2).mean()) / (np.sqrt((b ** 2).mean()) + 1e-30))
 
 
-@pytest.mark.parametrize("cfg,type_kv", [("test-dense", F16), ("test-dense", Q8_0), ("test-moe", F16)])
+@pytest.mark.parametrize("cfg,type_kv", [("test-dense", F16), ("test-dense", Q8_0), ("test-dense", Q4_0), ("test-moe", F16)])
 def test_decode_matches_fp64_reference(cfg, type_kv):
     from llama_ref import RefModel
     shape = SHAPES[cfg]
