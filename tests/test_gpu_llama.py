@@ -45,18 +45,23 @@ def test_decode_matches_fp64_reference(cfg, type_kv):
     tensors = make_tensors(shape, 11)
     ref = RefModel(shape, tensors, 512, type_kv)
     m = build(shape, tensors, 512, type_kv)
+    # q4_0 cache: both sides store bit-identical blocks for identical inputs, but the inputs differ in the last f32 bits (q8_1 vs
+    # fp64 matmuls), and a value that sits on a rounding boundary of the 4-bit quantiser then lands on the neighbouring level -- one
+    # level is 1/8 of the block's largest value.  The bar is wider there; greedy-token parity with a q4_0 cache is checked against the
+    # reference itself in test_gpu_llamacpp.py.
+    tol = 1e-1 if type_kv == Q4_0 else 4e-2
     try:
         prompt = [(i * 7919 + 3) % shape.n_vocab for i in range(5)]
         got = m.decode(prompt, 0, logits_all=True).copy()
         exp = ref.decode(prompt, 0)
         assert np.isfinite(got).all()
-        assert rel_rms(got, exp) < 4e-2, rel_rms(got, exp)
+        assert rel_rms(got, exp) < tol, rel_rms(got, exp)
         n_past = len(prompt)
         tok = int(np.argmax(exp[-1]))
         for _ in range(6):
             got = m.decode([tok], n_past).copy()
             exp = ref.decode([tok], n_past)
-            assert rel_rms(got[0], exp[0]) < 4e-2, rel_rms(got[0], exp[0])
+            assert rel_rms(got[0], exp[0]) < tol, rel_rms(got[0], exp[0])
             n_past += 1
             tok = int(np.argmax(exp[0]))
         # the cache rows written by the CPY nodes: f16 rounding of nearly equal values
