@@ -1,6 +1,7 @@
 // backend_device.cu -- reg / device / backend (stream) objects of the B200 ggml backend.
 // Contracts: /root/reference/ggml/src/ggml-backend-impl.h:86-216; the reference implementation being replaced is
 // ggml-cuda.cu:2355-2453 (backend), :2886-3256 (device), :3260-3340 (reg).
+#include <chrono>
 #include "backend_internal.h"
 
 namespace b200 {
@@ -118,7 +119,20 @@ static void dev_get_props(ggml_backend_dev_t d, ggml_backend_dev_props *p) {
 static ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) { return ggml_backend_b200_init(((DeviceCtx *)d->context)->device); }
 static ggml_backend_buffer_type_t dev_get_buft(ggml_backend_dev_t d) { return ggml_backend_b200_buffer_type(((DeviceCtx *)d->context)->device); }
 static ggml_backend_buffer_type_t dev_get_host_buft(ggml_backend_dev_t) { return ggml_backend_b200_host_buffer_type(); }
-static bool dev_supports_op(ggml_backend_dev_t d, const ggml_tensor *op) { return op_supported(((DeviceCtx *)d->context)->device, op); }
+// (B200_HOST_TIMING: the scheduler asks this for every node of every graph -- ggml-backend.cpp:1615-1975 -- so its cost is part of
+// what the caller pays per token)
+static const bool g_sup_timing = getenv("B200_HOST_TIMING") != nullptr;
+static double g_sup_s = 0;
+static long g_sup_calls = 0;
+static void sup_report() { fprintf(stderr, "B200 host timing: supports_op %ld calls, %.1f ns per call, %.3f ms in total\n", g_sup_calls, 1e9 * g_sup_s / (double)(g_sup_calls ? g_sup_calls : 1), 1e3 * g_sup_s); }
+static bool dev_supports_op(ggml_backend_dev_t d, const ggml_tensor *op) {
+    if (!g_sup_timing) return op_supported(((DeviceCtx *)d->context)->device, op);
+    if (g_sup_calls++ == 0) atexit(sup_report);
+    const auto t0 = std::chrono::steady_clock::now();
+    const bool r = op_supported(((DeviceCtx *)d->context)->device, op);
+    g_sup_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return r;
+}
 static bool dev_supports_buft(ggml_backend_dev_t d, ggml_backend_buffer_type_t buft) {
     if (buft_is_b200_split(buft)) return true;
     if (buft_is_b200_device(buft)) return ((BuftCtx *)buft->context)->device == ((DeviceCtx *)d->context)->device;
