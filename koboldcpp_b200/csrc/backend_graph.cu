@@ -367,6 +367,20 @@ static void plan_steps(GraphExec *g, const ggml_cgraph *cg) {
             continue;
         }
         if (j < n && silu_mul_pair(a, cg->nodes[j])) { s.kind = STEP_SILU_MUL; s.n2 = cg->nodes[j]; done[j] = 1; steps.push_back(s); continue; }
+        // prompt graphs order the parallel FFN as gate, SILU, up, MUL (llm_build_ffn through the depth-first graph build): the SILU
+        // waits for its MUL two or three nodes further on and the pair runs there as one launch
+        if (a->op == GGML_OP_UNARY && a->op_params[0] == GGML_UNARY_OP_SILU && gi.sole_user(a)) {
+            const ggml_tensor *mu = gi.sole_user(a);
+            const int pm = gi.pos(mu);
+            if (pm > i && pm <= i + 6 && !done[pm] && deferred.find(pm) == deferred.end() && silu_mul_pair(a, mu) &&
+                can_gather(gi, std::vector<int>{i, pm}, pm, done, exec_pos)) {
+                s.kind = STEP_SILU_MUL; s.n2 = mu;
+                done[i] = 1; done[pm] = 1;
+                exec_pos[(size_t)i] = pm;
+                deferred[pm] = s;
+                continue;
+            }
+        }
 
         // R5: the MoE router chain -> one launch at the position of its SOFT_MAX (the weight nodes move up past the expert matmuls)
         if (a->op == GGML_OP_SOFT_MAX) {
