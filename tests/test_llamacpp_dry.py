@@ -29,11 +29,20 @@ def moe():
     return G.build_fixture("test-moe", layer_gain=1.5)
 
 
-@pytest.mark.parametrize("opts", [dict(), dict(type_kv="q8_0"), dict(fa=0), dict(n_prompt=200, n_batch=64, n_ubatch=64)])
+@pytest.mark.parametrize("opts", [dict(), dict(type_kv="q8_0"), dict(type_kv="q4_0"), dict(fa=0), dict(n_prompt=200, n_batch=64, n_ubatch=64)])
 def test_dense_graph_stays_on_the_backend(dense, opts):
     o = LC.run(dense, "b200", n_prompt=opts.pop("n_prompt", 40), n_gen=4, sched_debug=True, dry_devices=1, **opts)
     assert o["sched"]["cpu_nodes"] == ONLY_EMBD, o["sched"]
     assert o["sched"]["nodes_per_backend"].get("B200_", 0) > 100
+
+
+@pytest.mark.parametrize("ftype", ["Q4_1", "Q5_0", "Q5_1", "Q2_K", "Q3_K", "IQ4_NL", "IQ4_XS"])
+def test_other_weight_types_stay_on_the_backend(ftype):
+    """N4: every matmul of a model quantised to one of the further formats is accepted by supports_op and planned on the backend."""
+    model = G.build_fixture("test-dense", layer_gain=1.5, ftype=ftype)
+    for n_prompt in (1, 40):
+        o = LC.run(model, "b200", n_prompt=n_prompt, n_gen=2, sched_debug=True, dry_devices=1)
+        assert o["sched"]["cpu_nodes"] == ONLY_EMBD, o["sched"]
 
 
 @pytest.mark.parametrize("type_kv", ["f16", "q8_0"])
