@@ -197,7 +197,9 @@ B200_API int b200_mul_mat_id_q(int type, const void *as, size_t w_row_bytes, siz
 /* ---- (a7) prefill GEMM on tcgen05: dst[n][m] = sum_k W[m][k] * X[n][k], any N ------------------------
  * replaces: ggml_cuda_op_mul_mat_q + mul_mat_q<type,...> + stream-k fixup + quantize_mmq_q8_1 and the cuBLAS
  * dequantise-then-GEMM fallback, ggml/src/ggml-cuda/mmq.cuh:2495-2905, mmq.cu:3-151, ggml-cuda.cu:1186-1284
- * workspace: b200_mul_mat_q_workspace_bytes() bytes of device memory (may be NULL when that returns 0). */
+ * workspace: b200_mul_mat_q_workspace_bytes() bytes of device memory (may be NULL when that returns 0).
+ * The call first converts X to bf16 at the front of the workspace.  X == NULL: the workspace still holds the converted activations
+ * of the previous call with the same K and N (sibling matmuls over one activation: Q / K / V, gate / up) and they are used as is. */
 B200_API size_t b200_mul_mat_q_workspace_bytes(int type, int64_t K, int64_t M, int64_t N);
 B200_API int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const float *X, int64_t x_stride,
                             float *dst, int64_t dst_stride, int64_t K, int64_t M, int64_t N,

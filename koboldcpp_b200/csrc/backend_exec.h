@@ -13,6 +13,10 @@ struct ExecCtx {
     void  *fa_ws;          // split-K workspace of FLASH_ATTN_EXT; its ticket counters are zero between launches
     size_t fa_ws_bytes;
     int64_t launches;      // kernels launched through this context
+    // the activations whose bf16 copy sits at the front of `scratch` (left there by the last prefill GEMM); valid only while the
+    // steps in between were prefill GEMMs too: the next sibling matmul over the same activation skips the conversion
+    const void *xb_src = nullptr;
+    int64_t xb_k = 0, xb_n = 0, xb_stride = 0;
 };
 
 // Run one graph node.  dst_slot != NULL (CPY only): the destination base pointer is read on the device from *dst_slot.

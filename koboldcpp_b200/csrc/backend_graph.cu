@@ -596,6 +596,7 @@ static KeyHash graph_key(const ggml_cgraph *cg) {
 
 // ------------------------------------------------------------------------------------------------ execution
 static void run_step(GraphExec *g, ExecCtx &x, const Step &s) {
+    if (!(s.kind == STEP_NODE && s.n->op == GGML_OP_MUL_MAT)) x.xb_src = nullptr;  // anything else may write the activations or the scratch
     switch (s.kind) {
         case STEP_NODE:
             run_node(x, s.n, s.slot >= 0 ? (void *const *)(g->slots_dev + s.slot) : nullptr);

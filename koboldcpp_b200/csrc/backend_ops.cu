@@ -229,6 +229,8 @@ static void run_mul_mat_split(ExecCtx &x, const ggml_tensor *n) {
 
 static void run_mul_mat(ExecCtx &x, const ggml_tensor *n) {
     const ggml_tensor *w = n->src[0], *a = n->src[1];
+    const void *xb_prev = x.xb_src;  // only the plain prefill GEMM below keeps the bf16 activations in the scratch meaningful
+    x.xb_src = nullptr;
     if (in_split_buffer(w)) { run_mul_mat_split(x, n); return; }
     if (!is_quantized(w->type)) {
         b200_tensor tw = as_b200(w), ta = as_b200(a), td = as_b200(n);
@@ -257,8 +259,15 @@ static void run_mul_mat(ExecCtx &x, const ggml_tensor *n) {
     if (N > 8) {
         const size_t ws = b200_mul_mat_q_workspace_bytes(w->type, K, M, N);
         if (ws <= x.scratch_bytes) {
-            const int rc = b200_mul_mat_q(w->type, w->data, w->nb[1], (const float *)a->data, xs, (float *)n->data, ds, K, M, N, x.scratch, x.scratch_bytes, x.stream);
-            if (rc == B200_OK) { x.launches++; return; }
+            // Q / K / V and gate / up read one activation: the first of the group converts it to bf16, the others find it in the scratch
+            const bool have_xb = xb_prev && xb_prev == a->data && x.xb_k == K && x.xb_n == N && x.xb_stride == xs;
+            const int rc = b200_mul_mat_q(w->type, w->data, w->nb[1], have_xb ? nullptr : (const float *)a->data, xs, (float *)n->data, ds, K, M, N, x.scratch,
+                                          x.scratch_bytes, x.stream);
+            if (rc == B200_OK) {
+                x.launches++;
+                x.xb_src = a->data; x.xb_k = K; x.xb_n = N; x.xb_stride = xs;
+                return;
+            }
             if (rc != B200_ERR_UNSUPPORTED) backend_abort("b200_mul_mat_q", b200_last_error());
         }
     }

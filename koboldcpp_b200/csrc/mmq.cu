@@ -1024,7 +1024,7 @@ extern "C" size_t b200_mul_mat_q_workspace_bytes(int type, int64_t K, int64_t M,
 
 extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const float *X, int64_t x_stride, float *dst, int64_t dst_stride,
                               int64_t K, int64_t M, int64_t N, void *workspace, size_t workspace_bytes, b200_stream_t stream) {
-    if (!W || !X || !dst) { set_error("b200_mul_mat_q: NULL argument"); return B200_ERR_INVALID; }
+    if (!W || !dst) { set_error("b200_mul_mat_q: NULL argument"); return B200_ERR_INVALID; }
     const int bv = type_block_values(type);
     if (!(type == B200_TYPE_Q4_0 || type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_K || type == B200_TYPE_Q5_K || type == B200_TYPE_Q6_K ||
           type == B200_TYPE_Q4_1 || type == B200_TYPE_Q5_0 || type == B200_TYPE_Q5_1 || type == B200_TYPE_Q2_K || type == B200_TYPE_Q3_K ||
@@ -1041,7 +1041,7 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
         set_error("b200_mul_mat_q: q4_K/q5_K rows must be 16-byte aligned");
         return B200_ERR_UNSUPPORTED;
     }
-    if (((uintptr_t)X & 15) || (x_stride & 3)) { set_error("b200_mul_mat_q: X must be 16-byte aligned with a row stride multiple of 4"); return B200_ERR_UNSUPPORTED; }
+    if (X && (((uintptr_t)X & 15) || (x_stride & 3))) { set_error("b200_mul_mat_q: X must be 16-byte aligned with a row stride multiple of 4"); return B200_ERR_UNSUPPORTED; }
     const size_t need = b200_mul_mat_q_workspace_bytes(type, K, M, N);
     if (!workspace || workspace_bytes < need || ((uintptr_t)workspace & 15)) {
         set_error("b200_mul_mat_q: workspace of %zu bytes (16-byte aligned) required, %zu given", need, workspace_bytes);
@@ -1051,9 +1051,11 @@ extern "C" int b200_mul_mat_q(int type, const void *W, size_t w_row_bytes, const
     const int64_t n_pad = mmq_n_pad(N);
     if (n_pad > 65535) { set_error("b200_mul_mat_q: N too large"); return B200_ERR_UNSUPPORTED; }
     __nv_bfloat16 *xb = (__nv_bfloat16 *)workspace;
-    dim3 g1((unsigned)((K / 4 + 255) / 256), (unsigned)n_pad);
-    mmq_x_to_bf16_kernel<<<g1, 256, 0, st>>>(X, x_stride, K, N, n_pad, xb);
-    B200_CUDA_TRY(cudaGetLastError());
+    if (X) {  // (X == NULL: the workspace holds the bf16 activations of the previous call with this K and N)
+        dim3 g1((unsigned)((K / 4 + 255) / 256), (unsigned)n_pad);
+        mmq_x_to_bf16_kernel<<<g1, 256, 0, st>>>(X, x_stride, K, N, n_pad, xb);
+        B200_CUDA_TRY(cudaGetLastError());
+    }
     MmqParams p;
     p.W = (const unsigned char *)W; p.w_row_bytes = w_row_bytes; p.Xb = xb; p.dst = dst; p.dst_stride = dst_stride; p.K = K; p.M = M; p.N = N;
     p.tile_tab = nullptr; p.row_dst = nullptr; p.expert_bytes = 0;
