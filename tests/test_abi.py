@@ -61,6 +61,32 @@ def test_no_gpu_means_loud_failure_not_fallback():
         H.mul_mat_vec_q(12, np.zeros((1, 144), np.uint8), np.zeros((1, 256), np.float32), 256, 1)
 
 
+def test_static_scratch_entry_point_without_a_gpu():
+    """b200_flash_attn_ext_static (no reference counterpart): the stated limit is what the header says, an over-sized shape is
+    refused before anything touches a device, and without a GPU a fitting shape fails loudly (no fallback)."""
+    import ctypes as C
+    import re
+    from pathlib import Path
+
+    import pytest
+
+    import koboldcpp_b200.lib as L
+    lib = L.lib()
+    hdr = (Path(__file__).resolve().parent.parent / "include" / "b200_ggml.h").read_text()
+    m = re.search(r"#define\s+B200_FATTN_STATIC_WS_BYTES\s+\((\d+)u\s*<<\s*(\d+)\)", hdr)
+    assert m and lib.b200_flash_attn_static_workspace_max() == int(m.group(1)) << int(m.group(2)) == 8 << 20
+
+    def args(nh, nhkv, D, nkv, N):
+        return L.FattnArgs(256, 256, 256, None, 256, D, N, nh, nhkv, nkv, L.F16, L.F16, 4 * D, 4 * D * N, 2 * D, 2 * D * nkv, 2 * D, 2 * D * nkv, 0, 0.1, 0.0, 0.0)
+    big = args(64, 64, 128, 32768, 24)
+    assert lib.b200_flash_attn_workspace_bytes(C.byref(big)) > 8 << 20
+    assert lib.b200_flash_attn_ext_static(C.byref(big), None) != 0
+    assert b"static array holds" in lib.b200_last_error()
+    if lib.b200_device_count() > 0:
+        pytest.skip("a GPU is present")
+    assert lib.b200_flash_attn_ext_static(C.byref(args(32, 8, 128, 4096, 1)), None) != 0
+
+
 def test_product_does_not_import_the_oracle():
     """The product path (package + csrc) must never reference oracle/ -- only tests, smoke() and bench's CPU legs may."""
     for p in list((ROOT / "koboldcpp_b200").rglob("*.py")) + list((ROOT / "koboldcpp_b200" / "csrc").glob("*")):
